@@ -1,0 +1,126 @@
+"""K-means assignment / accumulation op.
+
+CUDA tensors run the hand-written sm_100a kernels in ``csrc/kmeans.cu``
+(tcgen05 TF32 distance GEMM + TMEM arg-min epilogue + L2 vector reductions).
+CPU tensors run a plain PyTorch restatement of the reference's hot loop
+(``ml/java/.../kmeans/regroupallgather/CenCalcTask.java:67-100``) so that the
+multi-process semantics can be tested without a GPU.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from .. import _native
+
+
+@dataclass
+class KMeansStepResult:
+    sums: torch.Tensor      # [k, d] fp32: Σ of the points assigned to each centroid
+    counts: torch.Tensor    # [k] fp32
+    assign: Optional[torch.Tensor]  # [n] int32 or None
+    obj: Optional[torch.Tensor]     # [1] float64: Σ min squared distance, or None
+
+
+def workspace_bytes(n: int, k: int, d: int, simt: bool = False) -> int:
+    lib = _native.lib()
+    if simt or not lib.hb_kmeans_tc_supported(d, k):
+        return int(lib.hb_kmeans_simt_workspace_bytes(n, k, d))
+    return int(lib.hb_kmeans_workspace_bytes(k, d))
+
+
+def _cpu_step(X, C, sums, counts, assign, obj, zero):
+    # exact (x-c)^2 in the tensor's own precision, lowest index wins ties
+    d2 = torch.cdist(X.double(), C.double()).pow(2) if X.shape[0] * C.shape[0] <= (1 << 24) else None
+    if d2 is None:
+        best = torch.empty(X.shape[0], dtype=torch.int64)
+        bestd = torch.empty(X.shape[0], dtype=torch.float64)
+        for s in range(0, X.shape[0], 65536):
+            blk = torch.cdist(X[s:s + 65536].double(), C.double()).pow(2)
+            bestd[s:s + 65536], best[s:s + 65536] = blk.min(dim=1)
+    else:
+        bestd, best = d2.min(dim=1)
+    if zero:
+        sums.zero_()
+        counts.zero_()
+        if obj is not None:
+            obj.zero_()
+    sums.index_add_(0, best, X.to(sums.dtype))
+    counts.index_add_(0, best, torch.ones_like(best, dtype=counts.dtype))
+    if assign is not None:
+        assign.copy_(best.to(assign.dtype))
+    if obj is not None:
+        obj += bestd.sum()
+
+
+def kmeans_step(
+    X: torch.Tensor,
+    C: torch.Tensor,
+    sums: Optional[torch.Tensor] = None,
+    counts: Optional[torch.Tensor] = None,
+    assign: Optional[torch.Tensor] = None,
+    obj: Optional[torch.Tensor] = None,
+    workspace: Optional[torch.Tensor] = None,
+    *,
+    want_assign: bool = False,
+    want_obj: bool = False,
+    accumulate: bool = False,
+    force_simt: bool = False,
+) -> KMeansStepResult:
+    """One pass of Lloyd's assignment over ``X[n,d]`` against ``C[k,d]``."""
+    assert X.dim() == 2 and C.dim() == 2 and X.shape[1] == C.shape[1]
+    n, d = X.shape
+    k = C.shape[0]
+    dev = X.device
+    if sums is None:
+        sums = torch.empty(k, d, dtype=torch.float32, device=dev)
+        counts = torch.empty(k, dtype=torch.float32, device=dev)
+        if accumulate:
+            sums.zero_(); counts.zero_()
+    if want_assign and assign is None:
+        assign = torch.empty(n, dtype=torch.int32, device=dev)
+    if want_obj and obj is None:
+        obj = torch.zeros(1, dtype=torch.float64, device=dev)
+
+    if dev.type != "cuda":
+        _cpu_step(X, C, sums, counts, assign, obj, zero=not accumulate)
+        return KMeansStepResult(sums, counts, assign, obj)
+
+    lib = _native.lib()
+    assert X.dtype == torch.float32 and C.dtype == torch.float32, "CUDA K-means path is fp32/TF32"
+    X = X.contiguous()
+    C = C.contiguous()
+    simt = force_simt or not lib.hb_kmeans_tc_supported(d, k)
+    need = workspace_bytes(n, k, d, simt)
+    if workspace is None or workspace.numel() * workspace.element_size() < need:
+        workspace = torch.empty((need + 255) // 256 * 256, dtype=torch.uint8, device=dev)
+    flags = (1 if simt else 0) | (2 if accumulate else 0)
+    rc = lib.hb_kmeans_step(
+        _native.ptr(X), n, d, _native.ptr(C), k, _native.ptr(sums), _native.ptr(counts),
+        _native.ptr(assign), _native.ptr(obj), _native.ptr(workspace),
+        workspace.numel() * workspace.element_size(), flags, _native.stream_ptr(),
+    )
+    _native.check(rc, "hb_kmeans_step")
+    _native.count_launch(3 if simt else 2)
+    return KMeansStepResult(sums, counts, assign, obj)
+
+
+def kmeans_finalize(sums: torch.Tensor, counts: torch.Tensor, C_out: torch.Tensor, keep_empty: bool = False) -> torch.Tensor:
+    """``C_out[j] = sums[j] / counts[j]``; empty clusters → zero vector (or untouched)."""
+    k, d = sums.shape
+    if sums.device.type != "cuda":
+        nz = counts > 0
+        if keep_empty:
+            C_out[nz] = (sums[nz] / counts[nz, None]).to(C_out.dtype)
+        else:
+            C_out.zero_()
+            C_out[nz] = (sums[nz] / counts[nz, None]).to(C_out.dtype)
+        return C_out
+    lib = _native.lib()
+    rc = lib.hb_kmeans_finalize(_native.ptr(sums), _native.ptr(counts), k, d, _native.ptr(C_out),
+                                1 if keep_empty else 0, _native.stream_ptr())
+    _native.check(rc, "hb_kmeans_finalize")
+    _native.count_launch(1)
+    return C_out

@@ -1,0 +1,77 @@
+"""GPU numerics of the K-means kernels against a plain PyTorch fp32/fp64 reference."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(X, C):
+    d2 = torch.cdist(X.double(), C.double()).pow(2)
+    bestd, best = d2.min(dim=1)
+    k, d = C.shape
+    sums = torch.zeros(k, d, dtype=torch.float64, device=X.device).index_add_(0, best, X.double())
+    counts = torch.zeros(k, dtype=torch.float64, device=X.device).index_add_(0, best, torch.ones_like(bestd))
+    return best, bestd, sums, counts, d2
+
+
+def _check(n, d, k, force_simt, seed=0, scale=1.0):
+    from harp_b200.ops.kmeans import kmeans_step
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    X = torch.rand(n, d, device="cuda", generator=g) * scale
+    C = torch.rand(k, d, device="cuda", generator=g) * scale
+    res = kmeans_step(X, C, want_assign=True, want_obj=True, force_simt=force_simt)
+    torch.cuda.synchronize()
+    best, bestd, sums, counts, d2 = _ref(X, C)
+    a = res.assign.long()
+    assert int(a.min()) >= 0 and int(a.max()) < k
+    # the chosen centroid must be (near-)optimal: TF32 may flip near-ties only
+    chosen = d2.gather(1, a[:, None]).squeeze(1)
+    tol = (1e-5 if force_simt else 4e-3) * d * scale * scale
+    assert float((chosen - bestd).max()) <= tol, float((chosen - bestd).max())
+    mismatch = float((a != best).double().mean())
+    assert mismatch <= (1e-4 if force_simt else 0.05), mismatch
+    # sums / counts must be exactly consistent with the kernel's own assignment
+    sums_a = torch.zeros(k, d, dtype=torch.float64, device="cuda").index_add_(0, a, X.double())
+    counts_a = torch.zeros(k, dtype=torch.float64, device="cuda").index_add_(0, a, torch.ones(n, dtype=torch.float64, device="cuda"))
+    assert torch.equal(res.counts.double(), counts_a)
+    assert float(res.counts.sum()) == n
+    torch.testing.assert_close(res.sums.double(), sums_a, rtol=1e-4, atol=1e-3 * scale)
+    obj_a = float(chosen.sum())
+    assert abs(float(res.obj) - obj_a) <= 1e-3 * abs(obj_a) + 1e-6
+
+
+@pytest.mark.parametrize("n,d,k", [(1000, 100, 10), (4096, 128, 512), (5000, 64, 300), (777, 32, 7), (20000, 128, 1000), (300, 4, 3)])
+def test_kmeans_tc_matches_reference(native_built, n, d, k):
+    _check(n, d, k, force_simt=False)
+
+
+@pytest.mark.parametrize("n,d,k", [(1000, 100, 10), (513, 37, 19), (2000, 130, 40)])
+def test_kmeans_simt_matches_reference(native_built, n, d, k):
+    _check(n, d, k, force_simt=True)
+
+
+def test_kmeans_tc_vs_simt_agree(native_built):
+    from harp_b200.ops.kmeans import kmeans_step
+    g = torch.Generator(device="cuda").manual_seed(3)
+    X = torch.randn(30000, 128, device="cuda", generator=g)
+    C = X[torch.randperm(30000, device="cuda", generator=g)[:2000]].clone()
+    r1 = kmeans_step(X, C, want_assign=True)
+    r2 = kmeans_step(X, C, want_assign=True, force_simt=True)
+    torch.cuda.synchronize()
+    agree = float((r1.assign == r2.assign).double().mean())
+    assert agree > 0.98, agree
+    assert float(r1.counts.sum()) == 30000
+
+
+def test_kmeans_finalize(native_built):
+    from harp_b200.ops.kmeans import kmeans_finalize
+    sums = torch.rand(50, 16, device="cuda")
+    counts = torch.randint(0, 4, (50,), device="cuda").float()
+    C = torch.full((50, 16), 7.0, device="cuda")
+    kmeans_finalize(sums, counts, C)
+    ref = torch.where(counts[:, None] > 0, sums / counts[:, None].clamp(min=1), torch.zeros_like(sums))
+    torch.testing.assert_close(C, ref)
+    C2 = torch.full((50, 16), 7.0, device="cuda")
+    kmeans_finalize(sums, counts, C2, keep_empty=True)
+    ref2 = torch.where(counts[:, None] > 0, sums / counts[:, None].clamp(min=1), torch.full_like(sums, 7.0))
+    torch.testing.assert_close(C2, ref2)
