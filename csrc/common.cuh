@@ -358,6 +358,25 @@ __device__ __forceinline__ void red_release_gpu_add(uint32_t* p, uint32_t v) {
 }
 __device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 
+// 16-byte load that always goes to memory (peer data must not be served from a stale L1 line).
+__device__ __forceinline__ int4 ld_volatile_v4(const void* p) {
+  int4 r;
+  asm volatile("ld.volatile.global.v4.s32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ float4 ld_volatile_f4(const void* p) {
+  const int4 r = ld_volatile_v4(p);
+  return make_float4(__int_as_float(r.x), __int_as_float(r.y), __int_as_float(r.z), __int_as_float(r.w));
+}
+__device__ __forceinline__ float ld_volatile_f32(const void* p) {
+  float r;
+  asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");
+  return r;
+}
+
 // Vector fp32 reduction into global memory (one 16-byte L2 atomic).
 __device__ __forceinline__ void red_add_v4(float* p, float4 v) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),

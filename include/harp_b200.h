@@ -55,6 +55,55 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
 int hb_kmeans_finalize(const float* sums, const float* counts, int k, int d, float* C,
                        int keep_empty, void* stream);
 
+/* ---- NVLink peer-memory collectives (csrc/coll.cu) ------------------------
+ * Replace the TCP collectives of HC/collective/*.java.  Every rank passes the
+ * same table `peer_ptrs[world]` of peer-mapped slab base addresses (index =
+ * rank; entry `rank` is the local slab), the same byte offsets into the slab,
+ * and the same `ticket`.  Tickets must grow by at least 2 per call on a given
+ * flags area (each call consumes `ticket` and `ticket + 1`).  The flags area
+ * (hb_coll_flags_bytes() bytes at `flags_offset` inside every slab) must be
+ * zeroed once before first use.  All ranks must issue the calls in the same
+ * order; a peer that never arrives trips a ~10 s in-kernel watchdog. */
+#define HB_MAX_RANKS 16
+#define HB_COLL_MAX_CTAS 256
+enum { HB_F32 = 0, HB_F64 = 1, HB_I32 = 2, HB_I64 = 3 };
+enum { HB_OP_SUM = 0, HB_OP_MINUS = 1, HB_OP_PROD = 2, HB_OP_MAX = 3, HB_OP_MIN = 4 };
+
+size_t hb_coll_flags_bytes(void);
+/* mode 0: allreduce in place (HC/collective/AllreduceCollective.java:150-292)
+ * mode 1: reduce-scatter — rank r ends with the reduced r-th slice in place
+ *         (dense regroup, HC/collective/RegroupCollective.java:154-226)
+ * mode 2: reduce to `root` (HC/collective/ReduceCollective.java:150-336) */
+int hb_coll_reduce(const void* const* peer_ptrs, int rank, int world, size_t offset_bytes,
+                   size_t count, int dtype, int op, int mode, int root, size_t flags_offset,
+                   uint32_t ticket, void* stream);
+/* mode 0: allgather — shard `rank` of size `bytes` at offset+rank*bytes is pushed to all peers
+ *         (HC/collective/AllgatherCollective.java:147-213)
+ * mode 1: broadcast of [offset, +bytes) from `root` (HC/collective/BcastCollective.java:338-386)
+ * mode 2: rotate — pull [src_offset, +bytes) of rank `root` into local [offset, +bytes)
+ *         (HC/collective/LocalGlobalSyncCollective.java:710-772) */
+int hb_coll_move(const void* const* peer_ptrs, int rank, int world, size_t offset_bytes,
+                 size_t src_offset_bytes, size_t bytes, int mode, int root, size_t flags_offset,
+                 uint32_t ticket, void* stream);
+/* (HC/collective/Communication.java:61-183) */
+int hb_coll_barrier(const void* const* peer_ptrs, int rank, int world, size_t flags_offset,
+                    uint32_t ticket, void* stream);
+/* Fused regroup -> divide -> allgather of K-means partial sums
+ * (MJ/kmeans/regroupallgather/KMeansCollectiveMapper.java:168-185): reads every
+ * peer's [sums(k*d) | counts(k)] at acc_offset, writes new centroids at c_offset
+ * of every peer. */
+int hb_kmeans_regroup_allgather(const void* const* peer_ptrs, int rank, int world,
+                                size_t acc_offset_bytes, size_t c_offset_bytes, int k, int d,
+                                int keep_empty, size_t flags_offset, uint32_t ticket, void* stream);
+
+/* CUDA-IPC plumbing used when torch symmetric memory is unavailable.
+ * hb_slab_alloc is the only function of this library that allocates device memory. */
+int hb_ipc_export(const void* dev_ptr, void* handle64);
+int hb_ipc_open(const void* handle64, void** out_ptr);
+int hb_ipc_close(void* ptr);
+int hb_slab_alloc(size_t bytes, void** out_ptr);
+int hb_slab_free(void* ptr);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,99 @@
+"""torchrun worker: checks the NVLink peer-memory collectives against NCCL (run by test_symm_gpu.py)."""
+import os
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import torch
+import torch.distributed as dist
+
+
+def main():
+    backend = sys.argv[1] if len(sys.argv) > 1 else "auto"
+    rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"]); lr = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    dev = torch.device("cuda", lr)
+    dist.init_process_group("nccl", device_id=dev)
+    from harp_b200.parallel.symm import SymmetricWorkspace
+    from harp_b200.models.kmeans import KMeansEngine
+
+    ws = SymmetricWorkspace(dev, 64 << 20, backend=backend)
+    if rank == 0:
+        print(f"backend={ws.backend} multicast_ptr={ws.multicast_ptr:#x} world={world}", flush=True)
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+
+    # allreduce, several sizes / dtypes / ops, repeated to exercise ticket reuse
+    for n in (1, 7, 1000, 1 << 20, 1290000 + 3):
+        for dt in (torch.float32, torch.float64, torch.int32, torch.int64):
+            ws.reset()
+            t = ws.alloc(n, dt)
+            for op, red in (("sum", dist.ReduceOp.SUM), ("max", dist.ReduceOp.MAX), ("min", dist.ReduceOp.MIN)):
+                for rep in range(2):
+                    src = (torch.rand(n, device=dev, generator=g) * 100).to(dt)
+                    ref = src.clone(); dist.all_reduce(ref, op=red)
+                    t.copy_(src)
+                    ws.allreduce_(t, op)
+                    torch.cuda.synchronize()
+                    if dt.is_floating_point:
+                        torch.testing.assert_close(t, ref, rtol=1e-5, atol=1e-4)
+                    else:
+                        assert torch.equal(t, ref), (n, dt, op)
+    # reduce-scatter / reduce / allgather / broadcast / rotate / barrier
+    ws.reset()
+    n = 4096 * world + 0
+    t = ws.alloc(n, torch.float32)
+    src = torch.rand(n, device=dev, generator=g); ref = src.clone(); dist.all_reduce(ref)
+    t.copy_(src); mine = ws.reduce_scatter_(t); torch.cuda.synchronize()
+    per = n // world
+    torch.testing.assert_close(mine, ref[rank * per:(rank + 1) * per], rtol=1e-5, atol=1e-5)
+    t.copy_(src); ws.reduce_(t, root=world - 1); torch.cuda.synchronize()
+    if rank == world - 1:
+        torch.testing.assert_close(t, ref, rtol=1e-5, atol=1e-5)
+    shard = torch.full((per,), float(rank + 1), device=dev)
+    t.zero_(); t[rank * per:(rank + 1) * per] = shard; ws.allgather_(t); torch.cuda.synchronize()
+    exp = torch.arange(1, world + 1, device=dev, dtype=torch.float32).repeat_interleave(per)
+    assert torch.equal(t, exp)
+    t.fill_(float(rank)); ws.broadcast_(t, root=1 % world); torch.cuda.synchronize()
+    assert torch.equal(t, torch.full_like(t, float(1 % world)))
+    a = ws.alloc(1000, torch.float32); b = ws.alloc(1000, torch.float32)
+    a.fill_(float(rank)); ws.rotate_(b, a, (rank - 1) % world); torch.cuda.synchronize()
+    assert torch.equal(b, torch.full_like(b, float((rank - 1) % world)))
+    for _ in range(50):
+        ws.barrier()
+    torch.cuda.synchronize()
+
+    # fused K-means p2p path == NCCL path
+    ws.reset()
+    X = torch.rand(20000, 64, device=dev, generator=g)
+    C0 = torch.rand(300, 64, device=dev, generator=torch.Generator(device=dev).manual_seed(5))
+    e1 = KMeansEngine(X, 300, comm="p2p", symm=ws); e1.set_centroids(C0)
+    e2 = KMeansEngine(X, 300, comm="nccl"); e2.set_centroids(C0)
+    for it in range(4):
+        o1 = e1.step().clone(); o2 = e2.step().clone(); torch.cuda.synchronize()
+        torch.testing.assert_close(o1, o2, rtol=1e-6, atol=1e-6)
+        torch.testing.assert_close(e1.C, e2.C, rtol=1e-4, atol=1e-5)
+
+    # timing of the 5 MB allreduce vs NCCL
+    ws.reset()
+    n = 10000 * 129
+    t = ws.alloc(n, torch.float32); u = torch.rand(n, device=dev)
+    for fn, name in ((lambda: ws.allreduce_sum_(t), "p2p"), (lambda: dist.all_reduce(u), "nccl")):
+        for _ in range(5):
+            fn()
+        torch.cuda.synchronize(); dist.barrier()
+        e0 = torch.cuda.Event(enable_timing=True); e1_ = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20):
+            fn()
+        e1_.record(); torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1_) / 20], device=dev); dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            print(f"allreduce 5.16MB {name}: {ms.item()*1e3:.1f} us", flush=True)
+    dist.barrier()
+    if rank == 0:
+        print("SYMM_OK", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

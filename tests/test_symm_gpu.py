@@ -1,0 +1,25 @@
+"""Multi-GPU check of the NVLink peer-memory collectives (needs >= 2 GPUs on the box)."""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+ROOT = Path(__file__).resolve().parent.parent
+
+
+@pytest.mark.parametrize("backend", ["auto"])
+def test_symm_collectives_multi_gpu(native_built, backend):
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = 2 if n < 4 else (4 if n < 8 else 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", "29533",
+           str(ROOT / "tests" / "mp_symm_worker.py"), backend]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    sys.stdout.write(res.stdout[-4000:]); sys.stderr.write(res.stderr[-4000:])
+    assert res.returncode == 0 and "SYMM_OK" in res.stdout
