@@ -24,6 +24,8 @@
 
 #include <math_constants.h>
 
+#include <mutex>
+
 namespace hb {
 namespace kmeans {
 
@@ -464,3 +466,85 @@ int hb_kmeans_finalize(const float* sums, const float* counts, int k, int d, flo
 }
 
 }  // extern "C"
+
+// ----------------------------------------------------------------------------
+// hb_kmeans_step_static — the same assignment pass, for callers that cannot
+// hand this library any scratch memory.
+//
+// Who that is: a host program that reaches this library through the bare C ABI
+// from a runtime that owns no CUDA allocator of its own (a JVM worker through
+// JNI/FFI, a Fortran or C service), or a process whose device memory has been
+// claimed up front by someone else's pool (an inference server, PyTorch's
+// caching allocator configured to take the whole GPU) so that a cudaMalloc from
+// here would fail or, worse, synchronise the whole device in the middle of
+// their pipeline.  hb_kmeans_step() asks such callers for a workspace they have
+// no good way to produce.  This variant keeps the workspace inside the library
+// image instead: a fixed array in device global memory that exists, per GPU,
+// from the moment the library is loaded on that GPU until the process exits.
+//
+// Consequences the caller must know:
+//   * The array is sized for at most HB_KMEANS_STATIC_MAX_K centroids (64 KiB
+//     of ‖c‖² values plus padding); larger k is refused with an error, as is
+//     any (d, k) the tensor-core path does not take, because the SIMT fallback
+//     needs scratch proportional to the number of points.
+//   * All calls on one GPU share that one array.  Each call rewrites the part
+//     it uses before reading it (nothing in it has to start at zero and stale
+//     contents of an earlier call are harmless), but two calls that overlap in
+//     time on the same GPU — different streams, different host threads — race
+//     on it.  Serialise them, or use hb_kmeans_step() with separate workspaces.
+//   * The first call on each GPU resolves the array's device address
+//     (cudaGetSymbolAddress) and sets the kernel's shared-memory attribute.
+//     Make that first call during start-up, before any stream capture begins.
+//   * Nothing in this path calls cudaMalloc, cudaFree or an allocating library
+//     routine.
+// ----------------------------------------------------------------------------
+namespace hb {
+namespace kmeans {
+
+constexpr int STATIC_MAX_K = HB_KMEANS_STATIC_MAX_K;
+constexpr size_t STATIC_SCRATCH_FLOATS = (size_t)STATIC_MAX_K + 64;  // ‖c‖² (multiple of 256) + 256 B pad
+
+// Device-resident scratch.  In host code this name is only a handle for the
+// runtime's symbol table, never an address a kernel may dereference.
+static __device__ __align__(256) float g_static_scratch[STATIC_SCRATCH_FLOATS];
+
+static std::mutex g_static_mu;
+static float* g_static_ptr[64] = {nullptr};
+
+// Returns the device address of g_static_scratch on the current device.
+static int static_scratch_ptr(float** out) {
+  int dev = 0;
+  HB_CUDA_OK(cudaGetDevice(&dev));
+  HB_REQUIRE(dev >= 0 && dev < 64, "hb_kmeans_step_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (g_static_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    HB_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_static_scratch));
+    HB_REQUIRE(p != nullptr, "hb_kmeans_step_static: cudaGetSymbolAddress returned a null address");
+    g_static_ptr[dev] = p;
+  }
+  *out = g_static_ptr[dev];
+  return 0;
+}
+
+}  // namespace kmeans
+}  // namespace hb
+
+extern "C" int hb_kmeans_step_static(const float* X, long long n, int d, const float* C, int k,
+                                     float* sums, float* counts, int* assign, double* obj,
+                                     void* stream) {
+  HB_REQUIRE(k >= 1 && k <= hb::kmeans::STATIC_MAX_K,
+             "hb_kmeans_step_static: k=%d exceeds the built-in scratch (max %d centroids); "
+             "use hb_kmeans_step with a caller-provided workspace",
+             k, hb::kmeans::STATIC_MAX_K);
+  HB_REQUIRE(hb_kmeans_tc_supported(d, k),
+             "hb_kmeans_step_static: d=%d is not handled without caller scratch "
+             "(needs d %% 4 == 0 and d <= 128); use hb_kmeans_step",
+             d);
+  const size_t bytes = hb::kmeans::STATIC_SCRATCH_FLOATS * sizeof(float);
+  HB_REQUIRE(hb_kmeans_workspace_bytes(k, d) <= bytes,
+             "hb_kmeans_step_static: internal scratch too small for k=%d", k);
+  float* scratch = nullptr;
+  if (hb::kmeans::static_scratch_ptr(&scratch) != 0) return -1;
+  return hb_kmeans_step(X, n, d, C, k, sums, counts, assign, obj, scratch, bytes, 0, stream);
+}

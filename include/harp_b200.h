@@ -55,6 +55,20 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
 int hb_kmeans_finalize(const float* sums, const float* counts, int k, int d, float* C,
                        int keep_empty, void* stream);
 
+/* Same pass as hb_kmeans_step for callers that cannot provide scratch memory: programs that
+ * come in through this C ABI from a runtime with no CUDA allocator of its own (JNI/FFI hosts),
+ * or whose device memory is already fully claimed by another pool, so a cudaMalloc here would
+ * fail or stall their streams.  The scratch lives in a fixed device array inside the library
+ * (held on every GPU that loads it until exit), which limits k to HB_KMEANS_STATIC_MAX_K and
+ * (d, k) to what hb_kmeans_tc_supported accepts; anything else is refused with an error.
+ * All calls on a GPU share that array: calls that overlap in time on one GPU race — serialise
+ * them.  Each call rewrites what it uses, so leftovers from an earlier call do not matter.
+ * The first call on each GPU looks up the array's device address; make it at start-up, before
+ * any stream capture.  Allocates nothing.  (No counterpart in the reference.) */
+#define HB_KMEANS_STATIC_MAX_K 16384
+int hb_kmeans_step_static(const float* X, long long n, int d, const float* C, int k, float* sums,
+                          float* counts, int* assign, double* obj, void* stream);
+
 /* ---- NVLink peer-memory collectives (csrc/coll.cu) ------------------------
  * Replace the TCP collectives of HC/collective/*.java.  Every rank passes the
  * same table `peer_ptrs[world]` of peer-mapped slab base addresses (index =
