@@ -84,13 +84,14 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-// Arrive on the same-offset barrier of CTA `cta` of this cluster.
+// Arrive on the same-offset barrier of CTA `cta` of this cluster (default .release.cta semantics:
+// no GPU-scope MEMBAR; tcgen05 traffic is ordered by tcgen05.fence::before_thread_sync).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) {
   asm volatile(
       "{\n"
       ".reg .b32 ra;\n"
       "mapa.shared::cluster.u32 ra, %0, %1;\n"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n"
       "}\n" ::"r"(bar),
       "r"(cta)
       : "memory");
@@ -108,13 +109,15 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+constexpr long long kMbarTimeoutCycles = 8000000000LL;  // ~4 s at 2 GHz
 // Bounded wait: a protocol bug traps (→ launch error on the host) instead of
 // hanging the GPU.  try_wait itself sleeps in hardware, so the counter only
 // advances on time-outs of the hardware wait window.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t spins = 0;
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 24)) {
+    if (clock64() - t0 > kMbarTimeoutCycles) {
       printf("harp_b200: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n",
              blockIdx.x, threadIdx.x, bar, parity);
       __trap();
@@ -123,7 +126,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 }
 // Same, but acquire at cluster scope (barrier arrived on by a peer CTA).
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-  uint32_t spins = 0;
+  const long long t0 = clock64();
   for (;;) {
     uint32_t ok;
     asm volatile(
@@ -136,7 +139,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
         : "r"(bar), "r"(parity)
         : "memory");
     if (ok) break;
-    if (++spins > (1u << 24)) {
+    if (clock64() - t0 > kMbarTimeoutCycles) {
       printf("harp_b200: cluster mbarrier wait timed out (block %d thread %d)\n", blockIdx.x,
              threadIdx.x);
       __trap();
@@ -319,6 +322,19 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&v)[32])
 }
 __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// Wait for outstanding tcgen05.ld and tie the result registers to the wait, so the compiler
+// cannot schedule a consumer of v[] above it (the registers are not valid until the wait).
+__device__ __forceinline__ void tmem_ld_wait_regs(uint32_t (&v)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]),
+                 "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]),
+                 "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]),
+                 "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]),
+                 "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]),
+                 "+r"(v[31])
+               :
+               : "memory");
 }
 
 // ----------------------------------------------------------------------------

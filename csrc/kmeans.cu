@@ -25,6 +25,7 @@
 #include <math_constants.h>
 
 #include <mutex>
+#include <stdlib.h>
 
 namespace hb {
 namespace kmeans {
@@ -94,6 +95,100 @@ __global__ void prep_kernel(const float* __restrict__ C, int k, int d, int kpad,
     for (size_t i = tid; i < (size_t)k; i += nth) counts[i] = 0.f;
     if (tid == 0 && obj != nullptr) *obj = 0.0;
   }
+}
+
+// Running arg-min over 32 accumulator columns held in registers.  d = ‖c‖² - 2·x·c.
+__device__ __forceinline__ void argmin_chunk(const uint32_t (&v)[32], const float4* __restrict__ cn4,
+                                             int cbase, float& best, int& bi) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    const float4 cnv = cn4[j >> 2];
+    const float d0 = fmaf(-2.f, __uint_as_float(v[j + 0]), cnv.x);
+    const float d1 = fmaf(-2.f, __uint_as_float(v[j + 1]), cnv.y);
+    const float d2 = fmaf(-2.f, __uint_as_float(v[j + 2]), cnv.z);
+    const float d3 = fmaf(-2.f, __uint_as_float(v[j + 3]), cnv.w);
+    const float m = fminf(fminf(d0, d1), fminf(d2, d3));
+    if (m < best) {
+      best = m;
+      // lowest index wins ties inside the group
+      bi = cbase + j + (d0 == m ? 0 : (d1 == m ? 1 : (d2 == m ? 2 : 3)));
+    }
+  }
+}
+
+// Branch-free arg-min over 32 accumulator columns: the column's index inside the chunk is
+// packed into the low mantissa byte of d = ‖c‖² - 2·x·c (a 2^-15 relative perturbation,
+// far below the TF32 product error), so one FMNMX tree yields both the minimum and where it
+// was.  No data-dependent branch, no serial compare chain.
+template <bool kNoLds = false>
+__device__ __forceinline__ float packed_min32(const uint32_t (&v)[32], const float4* __restrict__ cn4) {
+  float key[32];
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    const float4 cnv = kNoLds ? make_float4(1.f, 2.f, 3.f, 4.f) : cn4[j >> 2];
+    const float d0 = fmaf(-2.f, __uint_as_float(v[j + 0]), cnv.x);
+    const float d1 = fmaf(-2.f, __uint_as_float(v[j + 1]), cnv.y);
+    const float d2 = fmaf(-2.f, __uint_as_float(v[j + 2]), cnv.z);
+    const float d3 = fmaf(-2.f, __uint_as_float(v[j + 3]), cnv.w);
+    // one PRMT each: low mantissa byte <- column index (AND+OR with two immediates costs two LOP3)
+    key[j + 0] = __uint_as_float(__byte_perm(__float_as_uint(d0), (uint32_t)(j + 0), 0x3214));
+    key[j + 1] = __uint_as_float(__byte_perm(__float_as_uint(d1), (uint32_t)(j + 1), 0x3214));
+    key[j + 2] = __uint_as_float(__byte_perm(__float_as_uint(d2), (uint32_t)(j + 2), 0x3214));
+    key[j + 3] = __uint_as_float(__byte_perm(__float_as_uint(d3), (uint32_t)(j + 3), 0x3214));
+  }
+#pragma unroll
+  for (int w = 16; w > 0; w >>= 1) {
+#pragma unroll
+    for (int j = 0; j < w; ++j) key[j] = fminf(key[j], key[j + w]);
+  }
+  return key[0];
+}
+
+// Folds the 32 points owned by this warp (row0 + lane, arg-min index `bi` per lane) into
+// sums / counts with 16-byte L2 reductions; returns this lane's share of Σ ‖x - c‖² (exact fp32).
+__device__ __forceinline__ float fold_points(const float* __restrict__ X, const float* __restrict__ C,
+                                             long long n, int d, long long row0, int bi, int lane,
+                                             float* __restrict__ sums, float* __restrict__ counts,
+                                             int* __restrict__ assign, bool want_obj,
+                                             int i_begin = 0, int i_end = 32) {
+  const int nl4 = d >> 2;
+  if (assign != nullptr && i_begin == 0 && row0 + lane < n) assign[row0 + lane] = bi;
+  float sq = 0.f;
+  const bool act = lane < nl4;
+  // 8 rows per batch: all loads are issued before the first reduction needs its data, so the
+  // batch costs one memory round trip instead of eight.
+#pragma unroll 1
+  for (int i0 = i_begin; i0 < i_end; i0 += 8) {
+    float4 xv[8], cv[8];
+    int idx[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      idx[u] = __shfl_sync(0xffffffffu, bi, i0 + u);
+      const long long row = row0 + i0 + u;
+      xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      cv[u] = xv[u];
+      if (act && row < n) {
+        xv[u] = __ldcs(reinterpret_cast<const float4*>(X + (size_t)row * d) + lane);
+        if (want_obj) cv[u] = __ldg(reinterpret_cast<const float4*>(C + (size_t)idx[u] * d) + lane);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const long long row = row0 + i0 + u;
+      if (row < n) {
+        if (act) {
+          red_add_v4(sums + (size_t)idx[u] * d + lane * 4, xv[u]);
+          if (want_obj) {
+            const float e0 = xv[u].x - cv[u].x, e1 = xv[u].y - cv[u].y, e2 = xv[u].z - cv[u].z,
+                        e3 = xv[u].w - cv[u].w;
+            sq = fmaf(e0, e0, sq); sq = fmaf(e1, e1, sq); sq = fmaf(e2, e2, sq); sq = fmaf(e3, e3, sq);
+          }
+        }
+        if (lane == 0) atomicAdd(counts + idx[u], 1.0f);
+      }
+    }
+  }
+  return sq;
 }
 
 // ----------------------------------------------------------------------------
@@ -212,7 +307,6 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
   } else {
     // ===================== Epilogue warps (4 x 32 rows) =====================
     const int q = warp & 3;                              // TMEM lane quadrant of this warp
-    const int nl4 = d >> 2;                              // float4s per row
     uint32_t ga = 0;
     double obj_local = 0.0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -225,24 +319,19 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
         tc_fence_after();
         const float4* cn4 = reinterpret_cast<const float4*>(base_ptr + SmemLayout::cn + a * CN_BYTES);
         const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + a * BN;
+        // Software-pipelined: the TMEM load of chunk c+1 is in flight while chunk c is reduced.
+        // Per group of 4 columns: 4 FFMA + 3 FMNMX + 1 compare; the index search only runs when
+        // the group actually improves on the running minimum (~ln(k) times per point).
+        uint32_t va[32], vb[32];
+        tmem_ld_32x32(taddr, va);
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-          uint32_t v[32];
-          tmem_ld_32x32(taddr + c * 32, v);
-          tmem_ld_wait();
-          const int cbase = ct * BN + c * 32;
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 cnv = cn4[c * 8 + (j >> 2)];
-            const float d0 = fmaf(-2.f, __uint_as_float(v[j + 0]), cnv.x);
-            const float d1 = fmaf(-2.f, __uint_as_float(v[j + 1]), cnv.y);
-            const float d2 = fmaf(-2.f, __uint_as_float(v[j + 2]), cnv.z);
-            const float d3 = fmaf(-2.f, __uint_as_float(v[j + 3]), cnv.w);
-            if (d0 < best) { best = d0; bi = cbase + j + 0; }
-            if (d1 < best) { best = d1; bi = cbase + j + 1; }
-            if (d2 < best) { best = d2; bi = cbase + j + 2; }
-            if (d3 < best) { best = d3; bi = cbase + j + 3; }
-          }
+        for (int c = 0; c < BN / 32; c += 2) {
+          tmem_ld_wait_regs(va);
+          tmem_ld_32x32(taddr + (c + 1) * 32, vb);
+          argmin_chunk(va, cn4 + c * 8, ct * BN + c * 32, best, bi);
+          tmem_ld_wait_regs(vb);
+          if (c + 2 < BN / 32) tmem_ld_32x32(taddr + (c + 2) * 32, va);
+          argmin_chunk(vb, cn4 + (c + 1) * 8, ct * BN + (c + 1) * 32, best, bi);
         }
         tc_fence_before();
         __syncwarp();
@@ -250,25 +339,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
       }
       // ---- fold the 32 points of this warp into sums / counts (L2 reductions) ----
       const long long row0 = tile * BM + q * 32;
-      if (assign != nullptr && row0 + lane < n) assign[row0 + lane] = bi;
-      float sq = 0.f;
-#pragma unroll 4
-      for (int i = 0; i < 32; ++i) {
-        const long long row = row0 + i;
-        const int idx = __shfl_sync(0xffffffffu, bi, i);
-        if (row < n) {
-          if (lane < nl4) {
-            const float4 xv = ld_nc_v4(X + (size_t)row * d + lane * 4);
-            red_add_v4(sums + (size_t)idx * d + lane * 4, xv);
-            if (obj != nullptr) {
-              const float4 cv = *reinterpret_cast<const float4*>(C + (size_t)idx * d + lane * 4);
-              const float e0 = xv.x - cv.x, e1 = xv.y - cv.y, e2 = xv.z - cv.z, e3 = xv.w - cv.w;
-              sq = fmaf(e0, e0, sq); sq = fmaf(e1, e1, sq); sq = fmaf(e2, e2, sq); sq = fmaf(e3, e3, sq);
-            }
-          }
-          if (lane == 0) atomicAdd(counts + idx, 1.0f);
-        }
-      }
+      const float sq = fold_points(X, C, n, d, row0, bi, lane, sums, counts, assign, obj != nullptr);
       obj_local += (double)sq;
     }
     if (obj != nullptr) {
@@ -281,6 +352,274 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc_1sm(tmem_base, TMEM_COLS);
+}
+
+
+// ----------------------------------------------------------------------------
+// v2: CTA-pair kernel (tcgen05 cta_group::2).  Two CTAs on one TPC share every
+// centroid tile: each loads only its 128-row half of the 256-centroid tile and
+// the tensor cores of both SMs read both halves, so L2->SMEM traffic per point
+// is halved (the v1 kernel is bound by exactly that traffic: ncu shows 7.7 TB/s
+// of L2 reads with the tensor pipe 46 % busy).  UMMA shape M=256 (128 points per
+// CTA) x N=256 x K=8.  The point tile is double-buffered so the next tile's TMA
+// overlaps the current tile's 40 centroid tiles.
+// ----------------------------------------------------------------------------
+namespace pair {
+constexpr int NTHREADS2 = 320;                   // warps 0..7 epilogue, warp 8 TMA, warp 9 MMA
+constexpr int NSTAGE2 = 5;
+constexpr int NCN = 8;                           // ‖c‖² ring slots (decoupled from the 2 accumulators)
+constexpr int BH = BN / 2;                        // centroid rows each CTA loads
+constexpr int B_HALF_BYTES = BH * BK * 4;         // 16 KB
+constexpr int X_TILE_BYTES = MAX_KCH * X_CHUNK_BYTES;  // 64 KB
+struct Smem {
+  static constexpr int x = 0;                                   // 2 x 64 KB
+  static constexpr int b = x + 2 * X_TILE_BYTES;                // NSTAGE2 x 16 KB
+  static constexpr int cn = b + NSTAGE2 * B_HALF_BYTES;         // NCN x 1 KB
+  static constexpr int bars = cn + NCN * CN_BYTES;
+  static constexpr int tmem_slot = bars + 48 * 8;
+  static constexpr int merge = tmem_slot + 16;                  // 128 x 4 B hand-over between warp halves
+  static constexpr int total = merge + 128 * 4;
+};
+static_assert(Smem::total <= 232448, "pair kernel exceeds the 227 KB shared-memory limit");
+enum : int {
+  X_FULL = 0,                   // 2, used in the leader CTA
+  X_EMPTY = 2,                  // 2, both CTAs (multicast commit)
+  B_FULL = 4,                   // NSTAGE2, leader
+  B_EMPTY = B_FULL + NSTAGE2,   // NSTAGE2, both
+  T_FULL = B_EMPTY + NSTAGE2,   // 2, both
+  T_EMPTY = T_FULL + 2,         // 2, leader (8 arrivals: 4 epilogue warps x 2 CTAs)
+  CN_FULL = T_EMPTY + 2,        // NCN, local
+  CN_EMPTY = CN_FULL + NCN,     // NCN, local (8 arrivals)
+  NBARS = CN_EMPTY + NCN
+};
+static_assert(NBARS <= 48, "barrier area too small");
+}  // namespace pair
+
+template <int DBG>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(pair::NTHREADS2, 1)
+assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_c,
+                      const float* __restrict__ X, const float* __restrict__ C,
+                      const float* __restrict__ cn_pad, long long n, int d, int k, int kpad,
+                      float* __restrict__ sums, float* __restrict__ counts, int* __restrict__ assign,
+                      double* __restrict__ obj) {
+  using namespace pair;
+  constexpr int dbg = DBG;
+  // Role layout: the SMSP arbiter favours higher warp ids, so the two latency-critical
+  // single-thread roles get the highest ids; epilogue warps 0..7 (two per TMEM quadrant).
+  constexpr int TMA_WARP = 8, MMA_WARP = 9;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = smem_u32(smem_raw);
+  if ((base & 1023u) != 0) { if (threadIdx.x == 0) printf("harp_b200: smem base not 1024-aligned\n"); __trap(); }
+  const uint32_t bars = base + Smem::bars;
+  auto bar = [&](int i) -> uint32_t { return bars + 8u * i; };
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem_raw + Smem::tmem_slot);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();           // 0 = leader
+  const bool leader = (cta == 0);
+  const int kch = (d + BK - 1) / BK;
+  const int nct = kpad / BN;
+  const long long npairs = (n + 2 * BM - 1) / (2 * BM);   // pair-tiles of 256 points
+  const long long cluster_id = blockIdx.x >> 1;
+  const long long nclusters = gridDim.x >> 1;
+  const uint32_t x_bytes = (uint32_t)kch * X_CHUNK_BYTES;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar(X_FULL + i), 1);
+      mbar_init(bar(X_EMPTY + i), 1);
+      mbar_init(bar(T_FULL + i), 1);
+      mbar_init(bar(T_EMPTY + i), 16);   // 8 epilogue warps x 2 CTAs
+    }
+    for (int i = 0; i < NCN; ++i) {
+      mbar_init(bar(CN_FULL + i), 1);
+      mbar_init(bar(CN_EMPTY + i), 8);
+    }
+    for (int s = 0; s < NSTAGE2; ++s) {
+      mbar_init(bar(B_FULL + s), 1);
+      mbar_init(bar(B_EMPTY + s), 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == MMA_WARP) {
+    tmem_alloc_2sm(smem_u32(const_cast<uint32_t*>(tmem_slot)), TMEM_COLS);
+    tmem_relinquish_2sm();
+  }
+  if (warp == TMA_WARP && lane == 0) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_c);
+  }
+  tc_fence_before();
+  cluster_sync_all();            // barriers of both CTAs initialised before anyone signals them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == TMA_WARP) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      const uint64_t pol_keep = policy_evict_last();
+      const uint64_t pol_stream = policy_evict_first();
+      uint32_t it = 0, ga = 0, gp = 0;
+      for (long long tp = cluster_id; tp < npairs; tp += nclusters, ++gp) {
+        const uint32_t xb = gp & 1, xph = (gp >> 1) & 1;
+        mbar_wait(bar(X_EMPTY + xb), xph ^ 1);
+        if (leader) mbar_expect_tx(bar(X_FULL + xb), 2 * x_bytes);
+        const int32_t row0 = (int32_t)(tp * 2 * BM + cta * BM);
+        for (int kc = 0; kc < kch; ++kc)
+          tma_load_2d_2sm(base + Smem::x + xb * X_TILE_BYTES + kc * X_CHUNK_BYTES, &tmap_x,
+                          bar(X_FULL + xb) & kPeerBitMask, kc * BK, row0, pol_stream);
+        for (int ct = 0; ct < nct; ++ct, ++ga) {
+          // ‖c‖² tile -> its own 8-deep ring: with only as many slots as accumulators this
+          // prefetch would be gated on the epilogue of tile ct-2 and epilogue + TMA latency
+          // would sit on the tensor core's critical path.
+          {
+            const uint32_t cs = ga % NCN, cph = (ga / NCN) & 1;
+            mbar_wait(bar(CN_EMPTY + cs), cph ^ 1);
+            mbar_expect_tx(bar(CN_FULL + cs), CN_BYTES);
+            bulk_load_1d(base + Smem::cn + cs * CN_BYTES, cn_pad + (size_t)ct * BN, CN_BYTES,
+                         bar(CN_FULL + cs));
+          }
+          for (int kc = 0; kc < kch; ++kc, ++it) {
+            const uint32_t s = it % NSTAGE2, ph = (it / NSTAGE2) & 1;
+            mbar_wait(bar(B_EMPTY + s), ph ^ 1);
+            if (leader) mbar_expect_tx(bar(B_FULL + s), 2 * B_HALF_BYTES);
+            tma_load_2d_2sm(base + Smem::b + s * B_HALF_BYTES, &tmap_c, bar(B_FULL + s) & kPeerBitMask,
+                            kc * BK, ct * BN + (int)cta * BH, pol_keep);
+          }
+        }
+      }
+    }
+  } else if (warp == MMA_WARP) {
+    // ===================== MMA issuer (leader CTA, one thread) =====================
+    if (leader && lane == 0) {
+      const uint32_t idesc = umma_idesc_tf32(2 * BM, BN);
+      uint32_t it = 0, ga = 0, gp = 0;
+      for (long long tp = cluster_id; tp < npairs; tp += nclusters, ++gp) {
+        const uint32_t xb = gp & 1, xph = (gp >> 1) & 1;
+        mbar_wait(bar(X_FULL + xb), xph);
+        for (int ct = 0; ct < nct; ++ct, ++ga) {
+          const uint32_t a = ga & 1, aph = (ga >> 1) & 1;
+          mbar_wait_cluster(bar(T_EMPTY + a), aph ^ 1);
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + a * BN;
+          for (int kc = 0; kc < kch; ++kc, ++it) {
+            const uint32_t s = it % NSTAGE2, ph = (it / NSTAGE2) & 1;
+            mbar_wait(bar(B_FULL + s), ph);
+            tc_fence_after();
+            const uint32_t a_addr = base + Smem::x + xb * X_TILE_BYTES + kc * X_CHUNK_BYTES;
+            const uint32_t b_addr = base + Smem::b + s * B_HALF_BYTES;
+            int ksteps = (d - kc * BK + UK - 1) / UK;
+            if (ksteps > BK / UK) ksteps = BK / UK;
+            for (int j = 0; j < ksteps; ++j) {
+              const uint64_t da = umma_desc_kmajor_sw128(a_addr + j * UK * 4);
+              const uint64_t db = umma_desc_kmajor_sw128(b_addr + j * UK * 4);
+              umma_tf32_2sm(tmem_d, da, db, idesc, (kc | j) != 0 ? 1u : 0u);
+            }
+            umma_commit_2sm_mc(bar(B_EMPTY + s), 0x3);     // frees the stage in both CTAs
+          }
+          umma_commit_2sm_mc(bar(T_FULL + a), 0x3);          // accumulators ready in both CTAs
+        }
+        umma_commit_2sm_mc(bar(X_EMPTY + xb), 0x3);
+      }
+    }
+  } else {
+    // ===================== Epilogue warps (both CTAs) =====================
+    // 8 warps: two per TMEM lane quadrant; warp (q, h) reduces columns [h*128, h*128+128) of
+    // every accumulator for the quadrant's 32 point rows.
+    const int q = warp & 3;
+    const int h = warp >> 2;
+    constexpr int CH = BN / 32 / 2;          // 4 chunks of 32 columns per warp per tile
+    float* merge = reinterpret_cast<float*>(smem_raw + Smem::merge);
+    uint32_t ga = 0;
+    double obj_local = 0.0;
+    long long prof_wait = 0, prof_work = 0, prof_n = 0;
+    for (long long tp = cluster_id; tp < npairs; tp += nclusters) {
+      float best = CUDART_INF_F;
+      int bi = 0;
+      for (int ct = 0; ct < nct; ++ct, ++ga) {
+        const uint32_t a = ga & 1, aph = (ga >> 1) & 1;
+        const int tbase = ct * BN + h * (BN / 2);
+        const uint32_t cs = ga % NCN, cph = (ga / NCN) & 1;
+        const float4* cng = reinterpret_cast<const float4*>(smem_raw + Smem::cn + cs * CN_BYTES) + h * (BN / 8);
+        long long tw0 = 0;
+        if (dbg & 16) tw0 = clock64();
+        mbar_wait(bar(CN_FULL + cs), cph);
+        mbar_wait(bar(T_FULL + a), aph);
+        if (dbg & 16) { const long long now = clock64(); prof_wait += now - tw0; tw0 = now; }
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + a * BN + h * (BN / 2);
+        if (!(dbg & 1)) {
+          uint32_t va[32], vb[32];
+          tmem_ld_32x32(taddr, va);
+#pragma unroll
+          for (int c = 0; c < CH; c += 2) {
+            tmem_ld_wait_regs(va);
+            tmem_ld_32x32(taddr + (c + 1) * 32, vb);
+            if (dbg & 2) { best = fminf(best, __uint_as_float(va[0]) + __uint_as_float(va[31])); } else
+            {
+              const float m = packed_min32<(DBG & 8) != 0>(va, cng + c * 8);
+              const bool lt = m < best;
+              best = lt ? m : best;
+              bi = lt ? tbase + c * 32 : bi;
+            }
+            tmem_ld_wait_regs(vb);
+            if (c + 2 < CH) tmem_ld_32x32(taddr + (c + 2) * 32, va);
+            if (dbg & 2) { best = fminf(best, __uint_as_float(vb[0]) + __uint_as_float(vb[31])); } else
+            {
+              const float m = packed_min32<(DBG & 8) != 0>(vb, cng + (c + 1) * 8);
+              const bool lt = m < best;
+              best = lt ? m : best;
+              bi = lt ? tbase + (c + 1) * 32 : bi;
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(bar(CN_EMPTY + cs));                 // local ‖c‖² slot
+          mbar_arrive_cluster(bar(T_EMPTY + a), 0);        // accumulator slot, tracked by the leader
+        }
+        if (dbg & 16) { prof_work += clock64() - tw0; ++prof_n; }
+      }
+      // unpack the in-chunk column, then merge the two column halves of each row through smem
+      bi += (int)(__float_as_uint(best) & 255u);
+      // (512 B of smem: best goes over first, then the index, then the verdict comes back)
+      const int slot = q * 32 + lane;
+      if (h == 1) merge[slot] = best;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      float obest = 0.f;
+      if (h == 0) obest = merge[slot];
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (h == 1) merge[slot] = __int_as_float(bi);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (h == 0) {
+        if (obest < best) { best = obest; bi = __float_as_int(merge[slot]); }
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (h == 0) merge[slot] = __int_as_float(bi);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (h == 1) bi = __float_as_int(merge[slot]);
+      asm volatile("bar.sync 1, 256;" ::: "memory");       // merge[] is rewritten by the next tile
+      const long long row0 = tp * 2 * BM + (long long)cta * BM + q * 32;
+      if (!(dbg & 4))
+        obj_local += fold_points(X, C, n, d, row0, bi, lane, sums, counts, assign, obj != nullptr,
+                                 h * 16, h * 16 + 16);
+      else if (best == 12345.f && assign) assign[0] = bi;
+    }
+    if (obj != nullptr) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) obj_local += __shfl_xor_sync(0xffffffffu, obj_local, o);
+      if (lane == 0) atomicAdd(obj, obj_local);
+    }
+    if ((dbg & 16) && lane == 0 && blockIdx.x < 2 && prof_n > 0)
+      printf("prof cta %d warp %d: tiles %lld wait/tile %lld work/tile %lld cycles\n", blockIdx.x, warp,
+             prof_n, prof_wait / prof_n, prof_work / prof_n);
+  }
+
+  tc_fence_before();
+  cluster_sync_all();            // nobody leaves while the peer may still touch its smem / TMEM / barriers
+  if (warp == MMA_WARP) tmem_dealloc_2sm(tmem_base, TMEM_COLS);
 }
 
 // ----------------------------------------------------------------------------
@@ -407,20 +746,50 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
     if (make_tmap_2d_f32(&tc, C, (uint64_t)k, (uint64_t)d, (uint64_t)d * 4, BN, BK,
                          CU_TENSOR_MAP_SWIZZLE_128B) != 0)
       return -3;
-    static bool attr_set[64] = {false};
     int dev = 0;
     HB_CUDA_OK(cudaGetDevice(&dev));
-    if (dev < 64 && !attr_set[dev]) {
-      HB_CUDA_OK(cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      SMEM_BYTES));
-      attr_set[dev] = true;
-    }
     const long long ntiles = (n + BM - 1) / BM;
-    int grid = sm_count();
-    if ((long long)grid > ntiles) grid = (int)ntiles;
-    assign_tc_kernel<<<grid, NTHREADS, SMEM_BYTES, stream>>>(tx, tc, X, C, cn, n, d, k, kpad, sums,
-                                                             counts, assign, obj);
-    HB_CUDA_OK(cudaGetLastError());
+    const bool use_pair = (flags & HB_KMEANS_SINGLE_CTA) == 0 && ntiles >= 2;
+    if (use_pair) {
+      // CTA-pair kernel: each CTA loads a 128-row half of every centroid tile
+      CUtensorMap tch;
+      if (make_tmap_2d_f32(&tch, C, (uint64_t)k, (uint64_t)d, (uint64_t)d * 4, BN / 2, BK,
+                           CU_TENSOR_MAP_SWIZZLE_128B) != 0)
+        return -3;
+      const int dbg = (flags >> 8) & 0xff;
+      auto kern = assign_tc_pair_kernel<0>;
+      if (dbg == 1) kern = assign_tc_pair_kernel<1>;
+      else if (dbg == 2) kern = assign_tc_pair_kernel<2>;
+      else if (dbg == 4) kern = assign_tc_pair_kernel<4>;
+      else if (dbg == 7) kern = assign_tc_pair_kernel<7>;
+      else if (dbg == 6) kern = assign_tc_pair_kernel<6>;
+      else if (dbg == 12) kern = assign_tc_pair_kernel<12>;
+      else if (dbg == 16) kern = assign_tc_pair_kernel<16>;
+      else if (dbg == 23) kern = assign_tc_pair_kernel<23>;
+      HB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::Smem::total));
+      const long long npairs = (n + 2 * BM - 1) / (2 * BM);
+      long long nclusters = sm_count() / 2;
+      if (const char* e = getenv("HB_KMEANS_MAX_CLUSTERS")) {   // perf-triage knob
+        const long long cap = atoll(e);
+        if (cap > 0 && cap < nclusters) nclusters = cap;
+      }
+      if (nclusters > npairs) nclusters = npairs;
+      kern<<<(unsigned)(2 * nclusters), pair::NTHREADS2, pair::Smem::total, stream>>>(
+          tx, tch, X, C, cn, n, d, k, kpad, sums, counts, assign, obj);
+      HB_CUDA_OK(cudaGetLastError());
+    } else {
+      static bool attr_set[64] = {false};
+      if (dev < 64 && !attr_set[dev]) {
+        HB_CUDA_OK(cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        SMEM_BYTES));
+        attr_set[dev] = true;
+      }
+      int grid = sm_count();
+      if ((long long)grid > ntiles) grid = (int)ntiles;
+      assign_tc_kernel<<<grid, NTHREADS, SMEM_BYTES, stream>>>(tx, tc, X, C, cn, n, d, k, kpad, sums,
+                                                               counts, assign, obj);
+      HB_CUDA_OK(cudaGetLastError());
+    }
   } else {
     // SIMT path needs an assignment + distance buffer; it lives behind ‖c‖² in the workspace
     // only if the caller sized it with hb_kmeans_simt_workspace_bytes.

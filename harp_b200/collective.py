@@ -1,0 +1,468 @@
+"""Table collectives with Harp semantics on top of torch.distributed (gloo on CPU, NCCL on GPU)
+and the NVLink peer-memory kernels.
+
+Reference: ``core/harp-collective/src/main/java/edu/iu/harp/collective/*`` —
+every op is "union of partition ids, combine on collision" (``partition/PartitionUtil.java:92-130``):
+
+=================  =====================================================================
+``barrier``        ``Communication.java:61-183``
+``broadcast``      root's partitions added to every table (``BcastCollective.java:338-386``)
+``reduce``         all partitions combined at root, non-root tables released (``ReduceCollective.java:150-336``)
+``allreduce``      every worker ends with the combination of everything (``AllreduceCollective.java:150-292``)
+``allgather``      every worker ends with the union of everything (``AllgatherCollective.java:147-213``)
+``regroup``        partition p moves to ``partitioner(p)``; collisions combine (``RegroupCollective.java:154-226``)
+``aggregate``      regroup → PartitionFunction → allgather (``RegroupCollective.java:252-297``)
+``rotate``         whole table moves to next / ``rotateMap[self]`` (``LocalGlobalSyncCollective.java:710-772``)
+``push`` / ``pull`` local↔global tables, ownership discovered at call time (``:456-698``)
+``join``           dynamic partitions travel to where the static ones live (``GraphCollective.java:313-517``)
+``group_by_key``   regroup-aggregate of a KV table (``GroupByKeyCollective.java:110-118``)
+=================  =====================================================================
+
+Two data paths:
+
+* **dense path** — all ranks hold the same partition ids with equal-shaped tensor payloads and an
+  element-wise combiner: one flat buffer, one ``all_reduce`` / ``all_gather`` / NVLink kernel
+  (``SymmetricWorkspace``) — no per-partition traffic at all.
+* **generic path** — arbitrary ids, unequal sizes, ``Writable`` payloads, custom combiners: an
+  all-to-all-v where tensor payloads stay on the device and only metadata is pickled.
+
+Results of float reductions are bit-identical on all ranks (contributions are folded in rank order).
+"""
+from __future__ import annotations
+
+import pickle
+from typing import Any, Callable, Dict, Iterable, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+from .partition import (ArrayCombiner, Operation, Partition, PartitionCombiner, PartitionFunction,
+                        Partitioner, PartitionStatus, Table, add_partitions_to_table)
+from .resource import Array, decode_payload, encode_payload
+
+_REDUCE_OPS = {Operation.SUM: dist.ReduceOp.SUM, Operation.MAX: dist.ReduceOp.MAX,
+               Operation.MIN: dist.ReduceOp.MIN, Operation.MULTIPLY: dist.ReduceOp.PRODUCT}
+_SYMM_OPS = {Operation.SUM: "sum", Operation.MAX: "max", Operation.MIN: "min", Operation.MULTIPLY: "prod"}
+
+
+class Comm:
+    """Rank/world + the two primitive data movers every table collective is built from."""
+
+    def __init__(self, group=None, device: Optional[torch.device] = None, symm=None):
+        self.group = group
+        if dist.is_available() and dist.is_initialized():
+            self.rank = dist.get_rank(group)
+            self.world = dist.get_world_size(group)
+            backend = dist.get_backend(group)
+        else:
+            self.rank, self.world, backend = 0, 1, "none"
+        self.backend = backend
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device()) if "nccl" in backend else torch.device("cpu")
+        self.device = torch.device(device)
+        self.symm = symm
+        self.stats = {"bytes_sent": 0, "ops": 0}
+
+    # ------------------------------------------------------------------ primitives
+    def is_the_only_worker(self) -> bool:
+        return self.world == 1
+
+    def barrier(self) -> bool:
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        return True
+
+    def all_gather_object(self, obj: Any) -> List[Any]:
+        if self.world == 1:
+            return [obj]
+        out: List[Any] = [None] * self.world
+        dist.all_gather_object(out, obj, group=self.group)
+        return out
+
+    def exchange(self, send: Dict[int, List[Tuple[int, Any]]]) -> List[Tuple[int, int, Any]]:
+        """All-to-all-v of ``(partition id, payload)`` lists.
+
+        Returns ``[(src, pid, payload)]`` ordered by source rank then by send order.  Tensor payloads
+        travel as raw bytes on the communicator's device; everything else is pickled with the metadata.
+        """
+        me, N = self.rank, self.world
+        meta: Dict[int, List[tuple]] = {}
+        chunks: Dict[int, List[torch.Tensor]] = {}
+        sizes = [0] * N
+        for dest, items in send.items():
+            if dest == me or not items:
+                continue
+            m: List[tuple] = []
+            ch: List[torch.Tensor] = []
+            for pid, payload in items:
+                t = payload.get() if isinstance(payload, Array) else payload
+                if isinstance(t, torch.Tensor):
+                    flat = t.detach().contiguous().view(-1).view(torch.uint8)
+                    nb = flat.numel()
+                    pad = (-nb) % 16
+                    m.append(("t", pid, str(t.dtype), tuple(t.shape), nb,
+                              type(payload).__name__ if isinstance(payload, Array) else None))
+                    ch.append(flat.to(self.device))
+                    if pad:
+                        ch.append(torch.zeros(pad, dtype=torch.uint8, device=self.device))
+                    sizes[dest] += nb + pad
+                else:
+                    m.append(("o", pid, encode_payload(payload)))
+            meta[dest] = m
+            chunks[dest] = ch
+        all_meta = self.all_gather_object(meta)
+        in_splits = sizes
+        out_splits = [0] * N
+        for src in range(N):
+            if src == me:
+                continue
+            for e in all_meta[src].get(me, []):
+                if e[0] == "t":
+                    out_splits[src] += e[4] + ((-e[4]) % 16)
+        total_in, total_out = sum(in_splits), sum(out_splits)
+        # all ranks must agree on whether a data phase happens
+        any_data = any(e[0] == "t" for m in all_meta for lst in m.values() for e in lst)
+        outbuf = torch.empty(total_out, dtype=torch.uint8, device=self.device)
+        if any_data:
+            parts = [c for d in range(N) for c in chunks.get(d, [])]
+            inbuf = torch.cat(parts) if parts else torch.empty(0, dtype=torch.uint8, device=self.device)
+            dist.all_to_all_single(outbuf, inbuf, out_splits, in_splits, group=self.group)
+        self.stats["bytes_sent"] += total_in
+        self.stats["ops"] += 1
+        received: List[Tuple[int, int, Any]] = []
+        off = 0
+        for src in range(N):
+            if src == me:
+                continue
+            for e in all_meta[src].get(me, []):
+                if e[0] == "t":
+                    _, pid, dt, shape, nb, arr_cls = e
+                    dtype = getattr(torch, dt.replace("torch.", ""))
+                    t = outbuf[off:off + nb].view(dtype).view(shape)
+                    off += nb + ((-nb) % 16)
+                    if arr_cls is not None:
+                        from . import resource as _r
+                        t = getattr(_r, arr_cls).wrap(t.view(-1))
+                    received.append((src, pid, t))
+                else:
+                    received.append((src, e[1], decode_payload(e[2], None)))
+        return received
+
+    # ------------------------------------------------------------------ dense-path detection
+    def uniform_signature(self, table: Table) -> Optional[Tuple]:
+        """Local layout signature, or None when this table cannot take the dense path."""
+        comb = table.get_combiner()
+        if not isinstance(comb, ArrayCombiner):
+            return None
+        sig = []
+        dtype = None
+        for pid in sorted(table.get_partition_ids()):
+            t = table.get_partition(pid).get()
+            t = t.get() if isinstance(t, Array) else t
+            if not isinstance(t, torch.Tensor):
+                return None
+            if dtype is None:
+                dtype = t.dtype
+            elif t.dtype != dtype:
+                return None
+            sig.append((pid, tuple(t.shape)))
+        return (str(dtype), comb.op.value, tuple(sig))
+
+    def all_same(self, sig: Any) -> bool:
+        sigs = self.all_gather_object(sig)
+        return all(s is not None and s == sigs[0] for s in sigs)
+
+
+def _tensor_of(payload) -> Optional[torch.Tensor]:
+    if isinstance(payload, Array):
+        return payload.get()
+    return payload if isinstance(payload, torch.Tensor) else None
+
+
+def _flat_views(table: Table) -> List[torch.Tensor]:
+    return [_tensor_of(table.get_partition(pid).get()) for pid in sorted(table.get_partition_ids())]
+
+
+def _dense_buffer(comm: Comm, table: Table) -> Tuple[torch.Tensor, bool]:
+    """One flat tensor holding all partitions in ascending id order. Returns (buffer, is_view)."""
+    if table.is_dense() and table.slab.is_contiguous() and sorted(table.get_partition_ids()) == table.get_partition_ids():
+        return table.slab.view(-1), True
+    views = _flat_views(table)
+    return torch.cat([v.reshape(-1) for v in views]), False
+
+
+def _scatter_back(table: Table, buf: torch.Tensor) -> None:
+    off = 0
+    for v in _flat_views(table):
+        n = v.numel()
+        v.copy_(buf[off:off + n].view_as(v))
+        off += n
+
+
+def _fold_in_rank_order(comm: Comm, table: Table, received: List[Tuple[int, int, Any]],
+                        own_rank: Optional[int] = None) -> bool:
+    """Adds received partitions so that float results do not depend on which rank does the folding:
+    for tensor payloads under an ArrayCombiner, contributions are combined in ascending source rank."""
+    own_rank = comm.rank if own_rank is None else own_rank
+    comb = table.get_combiner()
+    ok = True
+    if isinstance(comb, ArrayCombiner):
+        by_pid: Dict[int, List[Tuple[int, Any]]] = {}
+        for src, pid, payload in received:
+            by_pid.setdefault(pid, []).append((src, payload))
+        for pid, lst in by_pid.items():
+            cur = table.get_partition(pid)
+            contribs = list(lst)
+            if cur is not None:
+                contribs.append((own_rank, cur.get()))
+            contribs.sort(key=lambda x: x[0])
+            first = _tensor_of(contribs[0][1])
+            if first is None or len(contribs) == 1 and cur is None:
+                table.insert_partition(Partition(pid, contribs[0][1]))
+                continue
+            acc = first.clone()
+            for _, pl in contribs[1:]:
+                if comb.combine(acc, _tensor_of(pl).to(acc.device)) is PartitionStatus.COMBINE_FAILED:
+                    ok = False
+            if cur is not None:
+                _tensor_of(cur.get()).copy_(acc.to(_tensor_of(cur.get()).device))
+            else:
+                table.insert_partition(Partition(pid, acc))
+        return ok
+    for src, pid, payload in received:
+        st = table.add_partition(Partition(pid, payload))
+        if st in (PartitionStatus.ADD_FAILED, PartitionStatus.COMBINE_FAILED):
+            ok = False
+    return ok
+
+
+# =====================================================================================
+# collectives
+# =====================================================================================
+def barrier(comm: Comm, context_name: str = "", operation_name: str = "") -> bool:
+    return comm.barrier()
+
+
+def broadcast(comm: Comm, table: Table, root: int, use_mst_bcast: bool = False) -> bool:
+    if comm.is_the_only_worker():
+        return True
+    send: Dict[int, List[Tuple[int, Any]]] = {}
+    if comm.rank == root:
+        items = [(p.id(), p.get()) for p in table.get_partitions()]
+        send = {d: items for d in range(comm.world) if d != root}
+    received = comm.exchange(send)
+    return _fold_in_rank_order(comm, table, received)
+
+
+def reduce(comm: Comm, table: Table, root: int) -> bool:
+    if comm.is_the_only_worker():
+        return True
+    send = {}
+    if comm.rank != root:
+        send = {root: [(p.id(), p.get()) for p in table.get_partitions()]}
+    received = comm.exchange(send)
+    if comm.rank != root:
+        table.release()          # ReduceCollective.java:234-238
+        return True
+    return _fold_in_rank_order(comm, table, received)
+
+
+def allreduce(comm: Comm, table: Table, assume_uniform: Optional[bool] = None) -> bool:
+    if comm.is_the_only_worker():
+        return True
+    sig = comm.uniform_signature(table)
+    comb = table.get_combiner()
+    uniform = assume_uniform if assume_uniform is not None else comm.all_same(sig)
+    if uniform and sig is not None and isinstance(comb, ArrayCombiner) and comb.op in _REDUCE_OPS \
+            and table.get_num_partitions() > 0:
+        buf, is_view = _dense_buffer(comm, table)
+        if comm.symm is not None and is_view and comm.symm.contains(buf) and buf.dtype in (
+                torch.float32, torch.float64, torch.int32, torch.int64):
+            comm.symm.allreduce_(buf, _SYMM_OPS[comb.op])       # in-kernel NVLink allreduce
+            return True
+        work = buf if buf.device == comm.device else buf.to(comm.device)
+        dist.all_reduce(work, op=_REDUCE_OPS[comb.op], group=comm.group)
+        if not is_view or work is not buf:
+            _scatter_back(table, work.to(buf.device) if work.device != buf.device else work)
+        return True
+    # generic: everyone receives everything, folds in rank order
+    items = [(p.id(), p.get()) for p in table.get_partitions()]
+    send = {d: items for d in range(comm.world) if d != comm.rank}
+    received = comm.exchange(send)
+    return _fold_in_rank_order(comm, table, received)
+
+
+def allgather(comm: Comm, table: Table) -> bool:
+    if comm.is_the_only_worker():
+        return True
+    items = [(p.id(), p.get()) for p in table.get_partitions()]
+    send = {d: items for d in range(comm.world) if d != comm.rank}
+    received = comm.exchange(send)
+    return _fold_in_rank_order(comm, table, received)
+
+
+def regroup(comm: Comm, table: Table, partitioner: Optional[Partitioner] = None) -> bool:
+    if comm.is_the_only_worker():
+        return True
+    partitioner = partitioner or Partitioner(comm.world)
+    send: Dict[int, List[Tuple[int, Any]]] = {}
+    for p in table.get_partitions():
+        dest = partitioner.get_worker_id(p.id())
+        if dest != comm.rank:
+            send.setdefault(dest, []).append((p.id(), p.get()))
+    for items in send.values():          # RegroupCollective.java:200-216 — sent partitions leave the table
+        for pid, _ in items:
+            table.remove_partition(pid)
+    received = comm.exchange(send)
+    return _fold_in_rank_order(comm, table, received)
+
+
+def apply_partition_function(table: Table, fn) -> None:
+    """``RegroupCollective.applyPartitionFunction`` (``RegroupCollective.java:236-250``)."""
+    for p in table.get_partitions():
+        if isinstance(fn, PartitionFunction):
+            fn.apply(p)
+        else:
+            fn(p)
+
+
+def aggregate(comm: Comm, table: Table, partitioner: Optional[Partitioner], fn) -> bool:
+    ok = regroup(comm, table, partitioner)
+    if fn is not None:
+        apply_partition_function(table, fn)
+    return allgather(comm, table) and ok
+
+
+def rotate(comm: Comm, table: Table, rotate_map: Optional[Dict[int, int]] = None) -> bool:
+    if comm.is_the_only_worker():
+        return True
+    dest = (comm.rank + 1) % comm.world if rotate_map is None else int(rotate_map[comm.rank])
+    parts = table.get_partitions()
+    send = {dest: [(p.id(), p.get()) for p in parts]} if dest != comm.rank else {}
+    received = comm.exchange(send)
+    if dest != comm.rank:
+        for p in parts:                     # LocalGlobalSyncCollective.java:763-771
+            table.remove_partition(p.id())
+    ok = True
+    for src, pid, payload in received:
+        if table.add_partition(Partition(pid, payload)) in (PartitionStatus.ADD_FAILED, PartitionStatus.COMBINE_FAILED):
+            ok = False
+    return ok
+
+
+def _ownership(comm: Comm, global_table: Table, partitioner: Optional[Partitioner], wanted: Iterable[int]) -> Dict[int, int]:
+    """pid → owner: ids already present in some worker's global table stay there (lowest rank wins),
+    unknown ids go to the partitioner (``PartitionUtil.java:143-160``)."""
+    owned = comm.all_gather_object(sorted(global_table.get_partition_ids()))
+    owner: Dict[int, int] = {}
+    for r, ids in enumerate(owned):
+        for pid in ids:
+            owner.setdefault(pid, r)
+    partitioner = partitioner or Partitioner(comm.world)
+    for pid in wanted:
+        if pid not in owner:
+            owner[pid] = partitioner.get_worker_id(pid)
+    return owner
+
+
+def push(comm: Comm, local_table: Table, global_table: Table, partitioner: Optional[Partitioner] = None) -> bool:
+    """local → global; ``local_table`` is left untouched (``LocalGlobalSyncCollective.java:456-549``)."""
+    all_wanted = comm.all_gather_object(sorted(local_table.get_partition_ids()))
+    wanted = sorted({pid for ids in all_wanted for pid in ids})
+    owner = _ownership(comm, global_table, partitioner, wanted)
+    send: Dict[int, List[Tuple[int, Any]]] = {}
+    received: List[Tuple[int, int, Any]] = []
+    for p in local_table.get_partitions():
+        dest = owner[p.id()]
+        payload = p.get()
+        if dest == comm.rank:
+            t = _tensor_of(payload)
+            received.append((comm.rank, p.id(), t.clone() if t is not None else pickle.loads(pickle.dumps(payload))))
+        else:
+            send.setdefault(dest, []).append((p.id(), payload))
+    if not comm.is_the_only_worker():
+        received.extend(comm.exchange(send))
+    received.sort(key=lambda x: x[0])
+    ok = True
+    comb = global_table.get_combiner()
+    for src, pid, payload in received:
+        if global_table.add_partition(Partition(pid, payload)) in (PartitionStatus.ADD_FAILED, PartitionStatus.COMBINE_FAILED):
+            ok = False
+    return ok
+
+
+def pull(comm: Comm, local_table: Table, global_table: Table, use_bcast: bool = False) -> bool:
+    """global → local; received partitions are *combined* into ``local_table`` — callers zero it first
+    (``LocalGlobalSyncCollective.java:564-698``)."""
+    wanted_all = comm.all_gather_object(sorted(local_table.get_partition_ids()))
+    owned = comm.all_gather_object(sorted(global_table.get_partition_ids()))
+    owner: Dict[int, int] = {}
+    for r, ids in enumerate(owned):
+        for pid in ids:
+            owner.setdefault(pid, r)
+    send: Dict[int, List[Tuple[int, Any]]] = {}
+    local_hits: List[Tuple[int, int, Any]] = []
+    for r, ids in enumerate(wanted_all):
+        for pid in ids:
+            if owner.get(pid) != comm.rank:
+                continue
+            payload = global_table.get_partition(pid).get()
+            if r == comm.rank:
+                t = _tensor_of(payload)
+                local_hits.append((comm.rank, pid, t.clone() if t is not None else pickle.loads(pickle.dumps(payload))))
+            else:
+                send.setdefault(r, []).append((pid, payload))
+    received = local_hits
+    if not comm.is_the_only_worker():
+        received = received + comm.exchange(send)
+    ok = True
+    for src, pid, payload in received:
+        if local_table.add_partition(Partition(pid, payload)) in (PartitionStatus.ADD_FAILED, PartitionStatus.COMBINE_FAILED):
+            ok = False
+    return ok
+
+
+def join(comm: Comm, dynamic_table: Table, static_table: Table) -> bool:
+    """Graph join (``GraphCollective.java:313-447``): every dynamic partition is delivered to all
+    workers that hold a static partition with the same id; partitions nobody holds are dropped."""
+    static_sets = comm.all_gather_object(sorted(static_table.get_partition_ids()))
+    where: Dict[int, List[int]] = {}
+    for r, ids in enumerate(static_sets):
+        for pid in ids:
+            where.setdefault(pid, []).append(r)
+    send: Dict[int, List[Tuple[int, Any]]] = {}
+    keep: List[Partition] = []
+    for p in dynamic_table.get_partitions():
+        for dest in where.get(p.id(), []):
+            if dest == comm.rank:
+                keep.append(p)
+            else:
+                send.setdefault(dest, []).append((p.id(), p.get()))
+    received = comm.exchange(send) if not comm.is_the_only_worker() else []
+    for p in dynamic_table.get_partitions():
+        dynamic_table.remove_partition(p.id())
+    for p in keep:
+        dynamic_table.add_partition(p)
+    ok = True
+    for src, pid, payload in received:
+        if dynamic_table.add_partition(Partition(pid, payload)) in (PartitionStatus.ADD_FAILED, PartitionStatus.COMBINE_FAILED):
+            ok = False
+    return ok
+
+
+def group_by_key(comm: Comm, table: Table, partitioner: Optional[Partitioner] = None, fn=None) -> bool:
+    """``GroupByKeyCollective.java:110-118`` — regroup a KV table so that each key lives on one worker."""
+    ok = regroup(comm, table, partitioner)
+    if fn is not None:
+        apply_partition_function(table, fn)
+    return ok
+
+
+# small-object helpers (Communication.java:196-287)
+def gather_objects(comm: Comm, obj: Any, root: int) -> Optional[List[Any]]:
+    out = comm.all_gather_object(obj)
+    return out if comm.rank == root else None
+
+
+def allgather_objects(comm: Comm, obj: Any) -> List[Any]:
+    return comm.all_gather_object(obj)

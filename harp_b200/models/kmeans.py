@@ -15,6 +15,7 @@ Reference semantics kept: an empty cluster collapses to the zero vector
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -36,6 +37,7 @@ class KMeansEngine:
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if self.world > 1 else 0
         self.symm = symm
+        self.variant = os.environ.get("HB_KMEANS_VARIANT", "auto")
         if comm == "auto":
             comm = "p2p" if (symm is not None and self.world > 1) else "nccl"
         self.comm = comm
@@ -72,7 +74,7 @@ class KMeansEngine:
     def step(self, want_obj: bool = True) -> Optional[torch.Tensor]:
         """One Lloyd iteration; returns the (device) Σ min-distance² of the *input* centroids."""
         kops.kmeans_step(self.X, self.C, self.sums, self.counts, None,
-                         self.obj if want_obj else None, self.workspace)
+                         self.obj if want_obj else None, self.workspace, variant=self.variant)
         if self.world > 1 and self.comm == "p2p" and self.d % 4 != 0:
             self.symm.allreduce_sum_(self.acc)
             if want_obj:

@@ -8,6 +8,7 @@ multi-process semantics can be tested without a GPU.
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import Optional
 
@@ -68,6 +69,7 @@ def kmeans_step(
     want_obj: bool = False,
     accumulate: bool = False,
     force_simt: bool = False,
+    variant: str = "auto",
 ) -> KMeansStepResult:
     """One pass of Lloyd's assignment over ``X[n,d]`` against ``C[k,d]``."""
     assert X.dim() == 2 and C.dim() == 2 and X.shape[1] == C.shape[1]
@@ -96,7 +98,9 @@ def kmeans_step(
     need = workspace_bytes(n, k, d, simt)
     if workspace is None or workspace.numel() * workspace.element_size() < need:
         workspace = torch.empty((need + 255) // 256 * 256, dtype=torch.uint8, device=dev)
-    flags = (1 if simt else 0) | (2 if accumulate else 0)
+    # variant: "auto"/"pair" = CTA-pair tcgen05 kernel, "single" = 1-CTA tcgen05 kernel
+    flags = (1 if simt else 0) | (2 if accumulate else 0) | (4 if variant == "single" else 0)
+    flags |= (int(os.environ.get("HB_KMEANS_DBG", "0")) & 0xff) << 8   # perf-triage switches (pair kernel)
     rc = lib.hb_kmeans_step(
         _native.ptr(X), n, d, _native.ptr(C), k, _native.ptr(sums), _native.ptr(counts),
         _native.ptr(assign), _native.ptr(obj), _native.ptr(workspace),

@@ -33,6 +33,7 @@ int hb_l2_flush(void* buf, size_t bytes, void* stream);
  *      contrib/.../kmeans/allreduce/KmeansMapper.java:173-215) ------------- */
 #define HB_KMEANS_FORCE_SIMT 1 /* use the exact-fp32 SIMT kernel */
 #define HB_KMEANS_NO_ZERO 2    /* accumulate into sums/counts/obj instead of zeroing them */
+#define HB_KMEANS_SINGLE_CTA 4 /* use the 1-CTA tcgen05 kernel instead of the CTA-pair (cta_group::2) one */
 
 /* Scratch the tensor-core path needs: ‖c‖² padded to a multiple of 256. */
 size_t hb_kmeans_workspace_bytes(int k, int d);

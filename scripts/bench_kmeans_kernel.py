@@ -16,6 +16,7 @@ def main():
     d = int(sys.argv[2]) if len(sys.argv) > 2 else 128
     k = int(sys.argv[3]) if len(sys.argv) > 3 else 10_000
     iters = int(sys.argv[4]) if len(sys.argv) > 4 else 5
+    variant = sys.argv[5] if len(sys.argv) > 5 else "auto"
     torch.manual_seed(0)
     X = torch.rand(n, d, device="cuda")
     C = X[torch.randperm(n, device="cuda")[:k]].clone()
@@ -24,19 +25,19 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     lib = _native.lib()
     for _ in range(3):
-        kmeans_step(X, C, sums, counts, workspace=ws)
+        kmeans_step(X, C, sums, counts, workspace=ws, variant=variant)
     torch.cuda.synchronize()
     times = []
     for _ in range(iters):
         lib.hb_l2_flush(_native.ptr(flush), flush.numel(), _native.stream_ptr())
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
         e0.record()
-        kmeans_step(X, C, sums, counts, workspace=ws)
+        kmeans_step(X, C, sums, counts, workspace=ws, variant=variant)
         e1.record(); torch.cuda.synchronize()
         times.append(e0.elapsed_time(e1))
     ms = sorted(times)[len(times) // 2]
     flops = 2.0 * n * k * d
-    out = {"n": n, "d": d, "k": k, "ms_median": ms, "ms_all": times, "tflops_tf32": flops / ms / 1e9,
+    out = {"variant": variant, "n": n, "d": d, "k": k, "ms_median": ms, "ms_all": times, "tflops_tf32": flops / ms / 1e9,
            "points_per_s": n / ms * 1e3, "counts_sum": float(counts.sum())}
     # torch baseline: fp32 matmul (TF32 allowed) + argmin + index_add
     torch.backends.cuda.matmul.allow_tf32 = True

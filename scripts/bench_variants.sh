@@ -1,0 +1,10 @@
+#!/bin/bash
+mkdir -p gpurun_out
+for v in single pair; do
+  HB_KMEANS_VARIANT=$v timeout 200 python bench.py --steps 10 --warmup 3 --no-e2e > gpurun_out/bench_$v.json 2>/dev/null
+  python - "$v" <<'PY'
+import json, sys
+d = json.loads(open(f'gpurun_out/bench_{sys.argv[1]}.json').read().strip().splitlines()[-1])
+print(sys.argv[1], d["ms_per_step"], d["tflops_tf32_aggregate"], d["clocks"])
+PY
+done

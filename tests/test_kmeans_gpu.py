@@ -14,12 +14,12 @@ def _ref(X, C):
     return best, bestd, sums, counts, d2
 
 
-def _check(n, d, k, force_simt, seed=0, scale=1.0):
+def _check(n, d, k, force_simt, seed=0, scale=1.0, variant="auto"):
     from harp_b200.ops.kmeans import kmeans_step
     g = torch.Generator(device="cuda").manual_seed(seed)
     X = torch.rand(n, d, device="cuda", generator=g) * scale
     C = torch.rand(k, d, device="cuda", generator=g) * scale
-    res = kmeans_step(X, C, want_assign=True, want_obj=True, force_simt=force_simt)
+    res = kmeans_step(X, C, want_assign=True, want_obj=True, force_simt=force_simt, variant=variant)
     torch.cuda.synchronize()
     best, bestd, sums, counts, d2 = _ref(X, C)
     a = res.assign.long()
@@ -43,6 +43,11 @@ def _check(n, d, k, force_simt, seed=0, scale=1.0):
 @pytest.mark.parametrize("n,d,k", [(1000, 100, 10), (4096, 128, 512), (5000, 64, 300), (777, 32, 7), (20000, 128, 1000), (300, 4, 3)])
 def test_kmeans_tc_matches_reference(native_built, n, d, k):
     _check(n, d, k, force_simt=False)
+
+
+@pytest.mark.parametrize("n,d,k", [(1000, 100, 10), (4096, 128, 512), (777, 32, 7), (50000, 128, 3000)])
+def test_kmeans_tc_single_cta_matches_reference(native_built, n, d, k):
+    _check(n, d, k, force_simt=False, variant="single")
 
 
 @pytest.mark.parametrize("n,d,k", [(1000, 100, 10), (513, 37, 19), (2000, 130, 40)])
