@@ -77,8 +77,9 @@ def kmeans_step(
     k = C.shape[0]
     dev = X.device
     if sums is None:
-        sums = torch.empty(k, d, dtype=torch.float32, device=dev)
-        counts = torch.empty(k, dtype=torch.float32, device=dev)
+        acc_dt = torch.float32 if dev.type == "cuda" else X.dtype     # CPU path keeps the input precision
+        sums = torch.empty(k, d, dtype=acc_dt, device=dev)
+        counts = torch.empty(k, dtype=acc_dt, device=dev)
         if accumulate:
             sums.zero_(); counts.zero_()
     if want_assign and assign is None:

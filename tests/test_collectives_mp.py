@@ -1,0 +1,66 @@
+"""Multi-process (gloo, CPU) tests: collective semantics and the K-means apps end to end."""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+_PORT = [29700]
+
+
+def _torchrun(nproc, args, timeout=600):
+    _PORT[0] += 1
+    env = dict(os.environ, HARP_FORCE_CPU="1", OMP_NUM_THREADS="2")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_PORT[0])] + args
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env, cwd=str(ROOT))
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    return res.stdout
+
+
+@pytest.mark.parametrize("nproc", [2, 4])
+def test_collectives_verify(nproc):
+    out = _torchrun(nproc, [str(ROOT / "tests" / "mp_collectives_worker.py")])
+    assert f"COLLECTIVES_OK {nproc}" in out
+
+
+def test_kmeans_regroup_allgather_matches_oracle(tmp_path):
+    """README config (1000 pts, 10 centroids, dim 100, 2 workers, 10 iters) vs the float64 oracle."""
+    from harp_b200.io import formats as F
+    from oracle import kmeans as oracle
+    work = tmp_path / "work"
+    _torchrun(2, ["-m", "harp_b200.launch.kmeans", "1000", "10", "100", "5", "2", "2", "10", str(work), str(tmp_path / "local")])
+    got = F.read_centroids_text(str(work / "centroids" / "out" / "output"), 100)
+    files = sorted((work / "data").iterdir())
+    assert len(files) == 10
+    pts = np.concatenate([F.read_kmeans_points_bin(str(f), 100) for f in files])
+    init = F.read_centroids_text(str(work / "centroids" / "init_centroids"), 100)
+    want, hist = oracle.run(pts, init, 10)
+    assert got.shape == (10, 100)
+    np.testing.assert_allclose(got, want, rtol=1e-9, atol=1e-9)
+    assert all(a >= b - 1e-6 for a, b in zip(hist, hist[1:]))          # Lloyd is monotone
+
+
+@pytest.mark.parametrize("op", ["allreduce", "regroup-allgather", "broadcast-reduce", "push-pull"])
+def test_contrib_kmeans_quality_gate(tmp_path, op):
+    """contrib/test_scripts/km.sh: 1000 x 10, 10 centroids, 2 mappers, 100 iterations -> 7.0 < MSE < 7.8."""
+    from harp_b200.io import formats as F
+    work = tmp_path / op
+    _torchrun(2, ["-m", "harp_b200.launch.kmeans_contrib", "1000", "10", "10", "2", "100", str(work),
+                  str(tmp_path / "local"), op])
+    name, mse = F.read_evaluation(str(work / "evaluation"))
+    assert name == "MSE" and 7.0 < mse < 7.8, mse
+    assert (work / "out" / "part-m-00000").exists()
+
+
+def test_kmeans_rotation_matches_regroup_allgather(tmp_path):
+    from harp_b200.io import formats as F
+    a, b = tmp_path / "a", tmp_path / "b"
+    _torchrun(2, ["-m", "harp_b200.launch.kmeans", "600", "8", "12", "2", "2", "1", "5", str(a), str(tmp_path / "l")])
+    _torchrun(2, ["-m", "harp_b200.launch.kmeans_rotation", "600", "8", "12", "2", "2", "1", "5", str(b), str(tmp_path / "l")])
+    ca = F.read_centroids_text(str(a / "centroids" / "out" / "output"), 12)
+    cb = F.read_centroids_text(str(b / "centroids" / "out" / "output"), 12)
+    np.testing.assert_allclose(ca, cb, rtol=1e-9, atol=1e-9)
