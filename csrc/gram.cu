@@ -1,0 +1,396 @@
+// Gram / cross-product kernels for the DAAL-style algorithms (covariance, PCA-correlation,
+// linear & ridge regression by normal equations, low-order moments).
+//
+// Replaces the local step of Intel DAAL's distributed algorithms — covariance
+// DistributedStep1Local (ml/daal/.../daal_cov/densedistri/COVDaalCollectiveMapper.java:143-152),
+// pca (daal_pca/cordensedistr/PCADaalCollectiveMapper.java:121-127), linear_regression normEq
+// (daal_linreg/normaleq/LinRegDaalCollectiveMapper.java:162-167), low_order_moments
+// (daal_mom/densedistri/MOMDaalCollectiveMapper.java) — which run MKL SYRK/GEMM on Xeon.
+//
+// G = XᵀX for row-major X[n, d] (fp32, d % 32 == 0) on the tensor cores:
+//   * operands are MN-major: the TMA box {32 features, KC rows, 8 feature-slabs} of a 3-D view
+//     of X lands in shared memory exactly in the canonical MN-major tf32 layout
+//     (SWIZZLE_128B_BASE32B: [slab][row][32 floats]; LBO = KC*128 B between slabs, SBO = 512 B
+//     between 4-row groups; TMA side: SWIZZLE_128B_ATOM_32B),
+//     so X is never transposed or copied;
+//   * each CTA owns a 256x256 macro-tile of G (both 128x256 TMEM accumulators = all 512
+//     columns) for one slab of rows, K-steps of 8 rows, kind::tf32, fp32 accumulate;
+//   * only macro-tiles on or above the diagonal are computed (diagonal ones load one operand);
+//   * split-K partial tiles are folded into G with 16-byte L2 reductions; a mirror pass fills
+//     the lower triangle.
+// Column moments (sum, sum of squares, min, max) come from a separate streaming kernel.
+#include "common.cuh"
+#include "../include/harp_b200.h"
+
+#include <math_constants.h>
+
+namespace hb {
+namespace gram {
+
+constexpr int MT = 256;              // macro-tile edge (features)
+constexpr int KC = 16;               // rows per pipeline stage
+constexpr int UK = 8;                // rows per tcgen05.mma (tf32)
+constexpr int NSTAGE = 6;
+constexpr int SLAB = 32;             // features per 128-byte slab
+constexpr int OPER_BYTES = MT * KC * 4;          // 16 KB: one operand, one stage
+constexpr int STAGE_BYTES = 2 * OPER_BYTES;      // A + B
+constexpr int LBO_BYTES = KC * SLAB * 4;         // 2048: next 32-feature slab
+constexpr int SBO_BYTES = 4 * SLAB * 4;          // 512: next group of 4 rows (the 32B-base swizzle atom)
+constexpr int KSTEP_BYTES = UK * SLAB * 4;       // 1024: 8 rows = one tcgen05.mma K step
+constexpr int NTHREADS = 192;
+constexpr int TMEM_COLS = 512;
+
+struct Smem {
+  static constexpr int stages = 0;
+  static constexpr int bars = NSTAGE * STAGE_BYTES;   // 196608
+  static constexpr int tmem_slot = bars + 32 * 8;
+  static constexpr int total = tmem_slot + 16;
+};
+enum : int { B_FULL = 0, B_EMPTY = NSTAGE, T_FULL = 2 * NSTAGE, T_EMPTY = 2 * NSTAGE + 1 };
+
+// MN-major operand descriptor.  For 32-bit (tf32) MN-major operands the only legal shared-memory
+// layout is SWIZZLE_128B_BASE32B (layout type 1): 128-byte rows of 32 features, atoms of 4 rows,
+// 32-byte chunks XOR-swizzled by (row % 4) — what TMA produces with SWIZZLE_128B_ATOM_32B.
+__device__ __forceinline__ uint64_t desc_mnmajor_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(LBO_BYTES >> 4) << 16;
+  d |= static_cast<uint64_t>(SBO_BYTES >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(1) << 61;   // SWIZZLE_128B_BASE32B
+  return d;
+}
+
+__device__ __forceinline__ void tma_load_3d(uint32_t dst_smem, const CUtensorMap* m, uint32_t bar,
+                                            int32_t c0, int32_t c1, int32_t c2, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(dst_smem),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(policy)
+      : "memory");
+}
+
+// unit -> (macro-tile row ti, col tj >= ti, row slab s)
+__device__ __forceinline__ void decode_unit(long long u, int ntri, int nmt, int& ti, int& tj, long long& s) {
+  s = u / ntri;
+  int t = (int)(u % ntri);
+  ti = 0;
+  int rowlen = nmt;
+  while (t >= rowlen) { t -= rowlen; ++ti; --rowlen; }
+  tj = ti + t;
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int nmt, int ntri,
+               long long rows_per_slab, long long nslabs, float* __restrict__ G) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = smem_u32(smem_raw);
+  if ((base & 1023u) != 0) { if (threadIdx.x == 0) printf("harp_b200: smem base not 1024-aligned\n"); __trap(); }
+  const uint32_t bars = base + Smem::bars;
+  auto bar = [&](int i) -> uint32_t { return bars + 8u * i; };
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem_raw + Smem::tmem_slot);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long nunits = (long long)ntri * nslabs;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NSTAGE; ++s) { mbar_init(bar(B_FULL + s), 1); mbar_init(bar(B_EMPTY + s), 1); }
+    mbar_init(bar(T_FULL), 1);
+    mbar_init(bar(T_EMPTY), 4);
+    fence_barrier_init();
+  }
+  if (warp == 1) { tmem_alloc_1sm(smem_u32(const_cast<uint32_t*>(tmem_slot)), TMEM_COLS); tmem_relinquish_1sm(); }
+  if (warp == 0 && lane == 0) tma_prefetch_desc(&tmap);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      const uint64_t pol = policy_evict_last();     // a row slab is re-read by every macro-tile of its wave
+      uint32_t it = 0;
+      for (long long u = blockIdx.x; u < nunits; u += gridDim.x) {
+        int ti, tj; long long s;
+        decode_unit(u, ntri, nmt, ti, tj, s);
+        const long long r0 = s * rows_per_slab;
+        long long r1 = r0 + rows_per_slab; if (r1 > n) r1 = n;
+        const bool diag = (ti == tj);
+        for (long long r = r0; r < r1; r += KC, ++it) {
+          const uint32_t st = it % NSTAGE, ph = (it / NSTAGE) & 1;
+          mbar_wait(bar(B_EMPTY + st), ph ^ 1);
+          mbar_expect_tx(bar(B_FULL + st), diag ? OPER_BYTES : STAGE_BYTES);
+          const uint32_t dst = base + Smem::stages + st * STAGE_BYTES;
+          tma_load_3d(dst, &tmap, bar(B_FULL + st), 0, (int32_t)r, ti * (MT / SLAB), pol);
+          if (!diag) tma_load_3d(dst + OPER_BYTES, &tmap, bar(B_FULL + st), 0, (int32_t)r, tj * (MT / SLAB), pol);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_tf32(128, MT, 1, 1);   // both operands MN-major
+      uint32_t it = 0, gu = 0;
+      for (long long u = blockIdx.x; u < nunits; u += gridDim.x, ++gu) {
+        int ti, tj; long long s;
+        decode_unit(u, ntri, nmt, ti, tj, s);
+        const long long r0 = s * rows_per_slab;
+        long long r1 = r0 + rows_per_slab; if (r1 > n) r1 = n;
+        const bool diag = (ti == tj);
+        mbar_wait(bar(T_EMPTY), (gu & 1) ^ 1);
+        tc_fence_after();
+        uint32_t first = 1;
+        for (long long r = r0; r < r1; r += KC, ++it) {
+          const uint32_t st = it % NSTAGE, ph = (it / NSTAGE) & 1;
+          mbar_wait(bar(B_FULL + st), ph);
+          tc_fence_after();
+#ifdef HB_GRAM_DEBUG
+          if (it == 0 && blockIdx.x == 0) {
+            const float* sp = reinterpret_cast<const float*>(smem_raw + Smem::stages);
+            printf("dbg smem[0..3]=%f %f %f %f  [32]=%f [512]=%f [4096+0]=%f\n", sp[0], sp[1], sp[2], sp[3], sp[32], sp[512], sp[4096]);
+          }
+#endif
+          const uint32_t a_addr = base + Smem::stages + st * STAGE_BYTES;
+          const uint32_t b_addr = diag ? a_addr : a_addr + OPER_BYTES;
+          long long rem = r1 - r;                       // rows past n are zero-filled by TMA
+          int ksteps = (int)((rem + UK - 1) / UK); if (ksteps > KC / UK) ksteps = KC / UK;
+          for (int j = 0; j < ksteps; ++j) {
+            const uint64_t db = desc_mnmajor_sw128(b_addr + j * KSTEP_BYTES);
+#pragma unroll
+            for (int mh = 0; mh < 2; ++mh) {            // the two 128-feature halves of the A side
+              const uint64_t da = desc_mnmajor_sw128(a_addr + mh * 4 * LBO_BYTES + j * KSTEP_BYTES);
+              umma_tf32_1sm(tmem_base + mh * MT, da, db, idesc, first ? 0u : 1u);
+            }
+            first = 0;
+          }
+          umma_commit_1sm(bar(B_EMPTY + st));
+        }
+        umma_commit_1sm(bar(T_FULL));
+      }
+    }
+  } else {
+    // ===================== Epilogue: TMEM -> G (split-K reduction in L2) =====================
+    const int q = warp & 3;
+    uint32_t gu = 0;
+    for (long long u = blockIdx.x; u < nunits; u += gridDim.x, ++gu) {
+      int ti, tj; long long s;
+      decode_unit(u, ntri, nmt, ti, tj, s);
+      mbar_wait(bar(T_FULL), gu & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int mh = 0; mh < 2; ++mh) {
+        const int grow = ti * MT + mh * 128 + q * 32 + lane;           // row of G owned by this thread
+        const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + mh * MT;
+#pragma unroll 1
+        for (int c = 0; c < MT / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32(taddr + c * 32, v);
+          tmem_ld_wait_regs(v);
+#ifdef HB_GRAM_DEBUG
+          if (blockIdx.x == 0 && mh == 0 && c == 0 && q == 0 && lane < 2)
+            printf("dbg tmem lane %d: %f %f %f %f\n", lane, __uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]), __uint_as_float(v[3]));
+#endif
+          const int gcol = tj * MT + c * 32;
+          if (grow < d && gcol < d) {
+            float* dst = G + (size_t)grow * d + gcol;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              red_add_v4(dst + j, make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                              __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])));
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(T_EMPTY));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc_1sm(tmem_base, TMEM_COLS);
+}
+
+// Only macro-tiles with tj >= ti were computed: copy the upper triangle onto the lower one.
+__global__ void mirror_kernel(float* __restrict__ G, int d) {
+  const size_t total = (size_t)d * d;
+  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total;
+       idx += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(idx / d), c = (int)(idx % d);
+    if (r > c) G[idx] = G[(size_t)c * d + r];      // strict lower triangle <- upper (exactly symmetric output)
+  }
+}
+
+// SIMT fallback (any d): one block per 32x32 tile of G, rows strided across the grid's z.
+__global__ void gram_simt_kernel(const float* __restrict__ X, long long n, int d, float* __restrict__ G,
+                                 long long rows_per_block) {
+  __shared__ float As[32][33], Bs[32][33];
+  const int ti = blockIdx.y, tj = blockIdx.x;
+  if (tj < ti) return;
+  const long long r0 = blockIdx.z * rows_per_block;
+  long long r1 = r0 + rows_per_block; if (r1 > n) r1 = n;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8 threads
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (long long r = r0; r < r1; r += 32) {
+    for (int k = ty; k < 32; k += 8) {
+      const long long row = r + k;
+      const int ca = ti * 32 + tx, cb = tj * 32 + tx;
+      As[k][tx] = (row < r1 && ca < d) ? X[(size_t)row * d + ca] : 0.f;
+      Bs[k][tx] = (row < r1 && cb < d) ? X[(size_t)row * d + cb] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int k = 0; k < 32; ++k) {
+      const float b = Bs[k][tx];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[i] = fmaf(As[k][ty + 8 * i], b, acc[i]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gr = ti * 32 + ty + 8 * i, gc = tj * 32 + tx;
+    if (gr < d && gc < d) atomicAdd(G + (size_t)gr * d + gc, acc[i]);
+  }
+}
+__global__ void mirror32_kernel(float* __restrict__ G, int d) {
+  const size_t total = (size_t)d * d;
+  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total;
+       idx += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(idx / d), c = (int)(idx % d);
+    if (r / 32 > c / 32) G[idx] = G[(size_t)c * d + r];
+  }
+}
+
+// Column moments: sum, sum of squares, min, max over rows (DAAL low_order_moments partials).
+// out = [4][d] doubles for sum / sumsq, floats reinterpret for min/max kept in separate arrays.
+__global__ void moments_kernel(const float* __restrict__ X, long long n, int d, double* __restrict__ sum,
+                               double* __restrict__ sumsq, float* __restrict__ mn, float* __restrict__ mx) {
+  // block = 256 threads: 32 column-lanes x 8 row-lanes; grid.x tiles columns, grid.y strides rows
+  const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + cl;
+  double s = 0.0, ss = 0.0;
+  float lo = CUDART_INF_F, hi = -CUDART_INF_F;
+  if (col < d) {
+    for (long long r = blockIdx.y * 8LL + rl; r < n; r += (long long)gridDim.y * 8) {
+      const float v = X[(size_t)r * d + col];
+      s += v; ss += (double)v * v;
+      lo = fminf(lo, v); hi = fmaxf(hi, v);
+    }
+  }
+  __shared__ double sh_s[8][32], sh_ss[8][32];
+  __shared__ float sh_lo[8][32], sh_hi[8][32];
+  sh_s[rl][cl] = s; sh_ss[rl][cl] = ss; sh_lo[rl][cl] = lo; sh_hi[rl][cl] = hi;
+  __syncthreads();
+  if (rl == 0 && col < d) {
+    for (int i = 1; i < 8; ++i) {
+      s += sh_s[i][cl]; ss += sh_ss[i][cl];
+      lo = fminf(lo, sh_lo[i][cl]); hi = fmaxf(hi, sh_hi[i][cl]);
+    }
+    atomicAdd(sum + col, s);
+    atomicAdd(sumsq + col, ss);
+    // float atomic min/max through the ordered-int trick
+    int* imn = reinterpret_cast<int*>(mn + col);
+    int* imx = reinterpret_cast<int*>(mx + col);
+    if (lo >= 0.f) atomicMin(imn, __float_as_int(lo)); else atomicMax(reinterpret_cast<unsigned int*>(imn), __float_as_uint(lo));
+    if (hi >= 0.f) atomicMax(imx, __float_as_int(hi)); else atomicMin(reinterpret_cast<unsigned int*>(imx), __float_as_uint(hi));
+  }
+}
+__global__ void moments_init_kernel(int d, double* sum, double* sumsq, float* mn, float* mx) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < d) { sum[i] = 0.0; sumsq[i] = 0.0; mn[i] = CUDART_INF_F; mx[i] = -CUDART_INF_F; }
+}
+
+}  // namespace gram
+}  // namespace hb
+
+using namespace hb;
+using namespace hb::gram;
+
+extern "C" {
+
+int hb_gram_tc_supported(int d) { return (d >= 32 && d % 32 == 0 && d <= 16384) ? 1 : 0; }
+
+// G[d,d] (+)= XᵀX.  flags: HB_GRAM_NO_ZERO accumulates, HB_GRAM_FORCE_SIMT uses the fp32 SIMT kernel.
+int hb_gram(const float* X, long long n, int d, float* G, int flags, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  HB_REQUIRE(n >= 0 && d >= 1, "hb_gram: bad shape n=%lld d=%d", n, d);
+  if ((flags & HB_GRAM_NO_ZERO) == 0) HB_CUDA_OK(cudaMemsetAsync(G, 0, (size_t)d * d * sizeof(float), stream));
+  if (n == 0) return 0;
+  const bool tc = (flags & HB_GRAM_FORCE_SIMT) == 0 && hb_gram_tc_supported(d) &&
+                  (reinterpret_cast<uintptr_t>(X) & 15) == 0 && (reinterpret_cast<uintptr_t>(G) & 15) == 0 &&
+                  n < (1LL << 31);
+  if (tc) {
+    // 3-D view of X: dim0 = 32 floats inside a slab, dim1 = rows, dim2 = slab index
+    typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                      CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                      CUtensorMapFloatOOBfill);
+    static EncodeTiledFn fn = nullptr;
+    if (fn == nullptr) {
+      void* p = nullptr;
+      cudaDriverEntryPointQueryResult q;
+      HB_CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+      HB_REQUIRE(q == cudaDriverEntryPointSuccess && p != nullptr, "cuTensorMapEncodeTiled unavailable");
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    CUtensorMap tm;
+    cuuint64_t gdim[3] = {(cuuint64_t)SLAB, (cuuint64_t)n, (cuuint64_t)(d / SLAB)};
+    cuuint64_t gstr[2] = {(cuuint64_t)d * 4, (cuuint64_t)SLAB * 4};
+    cuuint32_t box[3] = {SLAB, KC, MT / SLAB};
+    cuuint32_t est[3] = {1, 1, 1};
+    CUresult r = fn(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(X), gdim, gstr, box, est,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    HB_REQUIRE(r == CUDA_SUCCESS, "hb_gram: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    const int nmt = (d + MT - 1) / MT;
+    const int ntri = nmt * (nmt + 1) / 2;
+    const int sms = sm_count();
+    // row slabs: enough units to balance the grid, each a multiple of KC rows
+    long long nslabs = (5LL * sms + ntri - 1) / ntri;
+    long long rows_per_slab = ((n + nslabs - 1) / nslabs + KC - 1) / KC * KC;
+    if (rows_per_slab < 4 * KC) rows_per_slab = 4 * KC;
+    nslabs = (n + rows_per_slab - 1) / rows_per_slab;
+    const long long nunits = nslabs * ntri;
+    int grid = sms; if ((long long)grid > nunits) grid = (int)nunits;
+    HB_CUDA_OK(cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::total));
+    gram_tc_kernel<<<grid, NTHREADS, Smem::total, stream>>>(tm, n, d, nmt, ntri, rows_per_slab, nslabs, G);
+    HB_CUDA_OK(cudaGetLastError());
+    mirror_kernel<<<sms * 2, 256, 0, stream>>>(G, d);
+    HB_CUDA_OK(cudaGetLastError());
+  } else {
+    const int nt = (d + 31) / 32;
+    long long zb = (sm_count() * 4 + (long long)nt * nt - 1) / ((long long)nt * nt);
+    if (zb < 1) zb = 1;
+    if (zb > 65535) zb = 65535;
+    long long rows_per_block = ((n + zb - 1) / zb + 31) / 32 * 32;
+    zb = (n + rows_per_block - 1) / rows_per_block;
+    dim3 grid(nt, nt, (unsigned)zb);
+    gram_simt_kernel<<<grid, 256, 0, stream>>>(X, n, d, G, rows_per_block);
+    HB_CUDA_OK(cudaGetLastError());
+    mirror32_kernel<<<sm_count() * 2, 256, 0, stream>>>(G, d);
+    HB_CUDA_OK(cudaGetLastError());
+  }
+  return 0;
+}
+
+// Column sum / sum of squares (double) and min / max (float) over the rows of X[n,d].
+int hb_moments(const float* X, long long n, int d, double* sum, double* sumsq, float* mn, float* mx,
+               int flags, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  HB_REQUIRE(n >= 0 && d >= 1, "hb_moments: bad shape");
+  if ((flags & HB_GRAM_NO_ZERO) == 0) {
+    moments_init_kernel<<<(d + 255) / 256, 256, 0, stream>>>(d, sum, sumsq, mn, mx);
+    HB_CUDA_OK(cudaGetLastError());
+  }
+  if (n == 0) return 0;
+  const int gx = (d + 31) / 32;
+  long long gy = (sm_count() * 8 + gx - 1) / gx;
+  if (gy > (n + 7) / 8) gy = (n + 7) / 8;
+  if (gy < 1) gy = 1;
+  if (gy > 65535) gy = 65535;
+  moments_kernel<<<dim3(gx, (unsigned)gy), 256, 0, stream>>>(X, n, d, sum, sumsq, mn, mx);
+  HB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -70,6 +70,20 @@ int hb_kmeans_finalize(const float* sums, const float* counts, int k, int d, flo
 int hb_kmeans_step_static(const float* X, long long n, int d, const float* C, int k, float* sums,
                           float* counts, int* assign, double* obj, void* stream);
 
+/* ---- Gram / moments (csrc/gram.cu) — local step of the DAAL-style distributed algorithms
+ * (ml/daal/.../daal_cov/densedistri/COVDaalCollectiveMapper.java:143-152,
+ *  daal_pca/cordensedistr/PCADaalCollectiveMapper.java:121-127,
+ *  daal_linreg/normaleq/LinRegDaalCollectiveMapper.java:162-167, daal_mom/...) ------------- */
+#define HB_GRAM_FORCE_SIMT 1
+#define HB_GRAM_NO_ZERO 2
+/* 1 when d is handled by the tcgen05 path (d % 32 == 0). */
+int hb_gram_tc_supported(int d);
+/* G[d,d] (+)= X^T X for row-major fp32 X[n,d]; TF32 products, fp32 accumulate; full symmetric output. */
+int hb_gram(const float* X, long long n, int d, float* G, int flags, void* stream);
+/* Per-column sum / sum of squares (double) and min / max (float) of X[n,d]. */
+int hb_moments(const float* X, long long n, int d, double* sum, double* sumsq, float* mn, float* mx,
+               int flags, void* stream);
+
 /* ---- NVLink peer-memory collectives (csrc/coll.cu) ------------------------
  * Replace the TCP collectives of HC/collective/*.java.  Every rank passes the
  * same table `peer_ptrs[world]` of peer-mapped slab base addresses (index =

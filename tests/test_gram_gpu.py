@@ -1,0 +1,41 @@
+"""GPU numerics of the Gram / moments kernels vs a float64 PyTorch reference."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("n,d", [(1000, 256), (5000, 512), (777, 32), (4096, 1024), (20000, 96), (100, 320)])
+def test_gram_tc(native_built, n, d):
+    from harp_b200.ops.gram import gram
+    X = torch.randn(n, d, device="cuda")
+    G = gram(X)
+    torch.cuda.synchronize()
+    ref = (X.double().t() @ X.double())
+    err = (G.double() - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    assert err <= 2e-3 * scale, (err, scale)                  # TF32 products
+    assert torch.equal(G, G.t())                               # lower triangle is a copy of the upper one
+    G2 = gram(X, out=G.clone(), accumulate=True)
+    torch.cuda.synchronize()
+    assert (G2.double() - 2 * ref).abs().max().item() <= 4e-3 * scale
+
+
+@pytest.mark.parametrize("n,d", [(1000, 100), (513, 37), (3000, 256)])
+def test_gram_simt(native_built, n, d):
+    from harp_b200.ops.gram import gram
+    X = torch.randn(n, d, device="cuda")
+    G = gram(X, force_simt=True)
+    torch.cuda.synchronize()
+    ref = (X.double().t() @ X.double())
+    torch.testing.assert_close(G.double(), ref, rtol=1e-4, atol=1e-3)
+
+
+def test_moments(native_built):
+    from harp_b200.ops.gram import moments
+    X = torch.randn(10001, 77, device="cuda") * 3 - 1
+    m = moments(X)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(m.sum, X.double().sum(0), rtol=1e-9, atol=1e-6)
+    torch.testing.assert_close(m.sumsq, (X.double() ** 2).sum(0), rtol=1e-9, atol=1e-6)
+    assert torch.equal(m.min, X.min(0).values) and torch.equal(m.max, X.max(0).values)
