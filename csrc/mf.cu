@@ -1,0 +1,295 @@
+// Matrix-factorisation kernels: SGD block pass, RMSE, CCD++ rank-one update.
+//
+// Replaces SGDMPTask.doRun (ml/java/src/main/java/edu/iu/sgd/SGDMPTask.java:46-77), the
+// row/column-exclusive dynamic block scheduler with its timer (ml/java/.../dymoro/Scheduler.java:
+// 95-237), RMSETask (ml/java/.../sgd/RMSETask.java:67-103), the native mf_sgd.Distri kernel of the
+// experimental Harp-DAAL build (experimental/.../daal_sgd/SGDDaalCollectiveMapper.java:274-352) and
+// CCDMPTask.doRowCCD/doColCCD (ml/java/.../ccd/CCDMPTask.java:67-125).
+//
+// SGD design.  The ratings of one "panel" (this worker's rows x the visiting H slice) are bucketed
+// into a B x B grid of blocks and, inside a block, sorted by column.  ONE persistent cooperative
+// kernel runs B CTAs; CTA i owns row-block i for the whole pass and walks the column-blocks in
+// Latin-square order c = (i + t) mod B.  A column-block is handed from CTA to CTA through an
+// acquire/release ticket in global memory, so no two CTAs ever touch the same rows or the same
+// columns at the same time (the invariant the reference's Scheduler maintains with its
+// rowCount/colCount bookkeeping) and there is no grid-wide barrier: CTAs drift apart by as much
+// as the load imbalance wants.  Inside a CTA a warp takes one column run at a time: h stays in
+// registers for the whole run (sequential SGD down the column, exactly the reference's inner
+// loop order), each rating costs one 128-bit-per-lane read and write of its w row and a 5-step
+// shuffle reduction.  Two warps of a CTA may meet on a row (different columns); that rare
+// intra-block collision is resolved last-writer-wins.  A %globaltimer deadline gives the
+// reference's timer-bounded partial pass; the number of ratings actually trained is returned.
+#include "common.cuh"
+#include "../include/harp_b200.h"
+
+#include <cooperative_groups.h>
+
+namespace hb {
+namespace mf {
+
+constexpr int SGD_THREADS = 512;
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ float4 ldcg4(const float* p) {
+  float4 r;
+  asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stcg4(float* p, float4 v) {
+  asm volatile("st.global.cg.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+struct SgdArgs {
+  float* W;                  // [rows_local, rank]
+  float* H;                  // [cols_slice, rank]
+  const int* blk_seg_ptr;    // [B*B + 1]  segments (column runs) of block (i, c) = i * B + c
+  const int* seg_col;        // [nseg]     column of the run (slice-local index)
+  const int* seg_ptr;        // [nseg + 1] ratings of the run
+  const int* r_row;          // [nnz]      row (worker-local index)
+  const float* r_val;        // [nnz]
+  unsigned int* col_ticket;  // [B]        hand-over tickets (monotone across launches)
+  unsigned long long* trained;   // [1]    ratings updated (atomicAdd)
+  unsigned long long deadline_ns;  // time budget in ns measured from kernel entry; 0 = no deadline
+  unsigned int ticket_base;
+  int B;
+  int rank;
+  float eps, lambda;
+};
+
+template <int RV>   // float4s per lane: rank <= 128 * RV
+__global__ void __launch_bounds__(SGD_THREADS, 1) sgd_pass_kernel(SgdArgs a) {
+  __shared__ int s_next;      // next segment of the current block
+  __shared__ int s_stop;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int i = blockIdx.x, B = a.B;
+  const int nl4 = a.rank >> 2;
+  unsigned long long local_trained = 0;
+  bool expired = false;
+  const unsigned long long t_end = a.deadline_ns ? globaltimer_ns() + a.deadline_ns : 0ULL;
+  for (int t = 0; t < B; ++t) {
+    const int c = (i + t) % B;
+    // ---- acquire column-block c ----
+    if (threadIdx.x == 0) {
+      const unsigned int want = a.ticket_base + (unsigned)t;
+      while (ld_acquire_gpu(a.col_ticket + c) != want) { __nanosleep(64); }
+      const int s0 = a.blk_seg_ptr[(size_t)i * B + c];
+      s_next = s0;
+      s_stop = (t_end != 0 && globaltimer_ns() > t_end) ? 1 : 0;
+    }
+    __syncthreads();
+    expired = (s_stop != 0);
+    const int s_end = a.blk_seg_ptr[(size_t)i * B + c + 1];
+    if (!expired) {
+      for (;;) {
+        int seg = 0;
+        if (lane == 0) seg = atomicAdd(&s_next, 1);
+        seg = __shfl_sync(0xffffffffu, seg, 0);
+        if (seg >= s_end) break;
+        // bit 31 of seg_col marks a sub-run of a long column run that was split so that several warps
+        // can work on a popular column at once; such sub-runs merge their h deltas additively
+        const int col_raw = a.seg_col[seg];
+        const bool shared_col = col_raw < 0;
+        const int col = col_raw & 0x7FFFFFFF;
+        const int k0 = a.seg_ptr[seg], k1 = a.seg_ptr[seg + 1];
+        float4 h[RV], h0[RV];
+#pragma unroll
+        for (int u = 0; u < RV; ++u) {
+          h[u] = (lane + 32 * u < nl4) ? ldcg4(a.H + (size_t)col * a.rank + (lane + 32 * u) * 4)
+                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+          h0[u] = h[u];
+        }
+        // software pipeline: w of rating k+1 is in flight while rating k is updated
+        int row_n = (k0 < k1) ? a.r_row[k0] : 0;
+        float4 w_n[RV];
+#pragma unroll
+        for (int u = 0; u < RV; ++u)
+          w_n[u] = (k0 < k1 && lane + 32 * u < nl4) ? ldcg4(a.W + (size_t)row_n * a.rank + (lane + 32 * u) * 4)
+                                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k = k0; k < k1; ++k) {
+          const int row = row_n;
+          float4 w[RV];
+#pragma unroll
+          for (int u = 0; u < RV; ++u) w[u] = w_n[u];
+          const float v = a.r_val[k];
+          if (k + 1 < k1) {
+            row_n = a.r_row[k + 1];
+#pragma unroll
+            for (int u = 0; u < RV; ++u)
+              if (lane + 32 * u < nl4) w_n[u] = ldcg4(a.W + (size_t)row_n * a.rank + (lane + 32 * u) * 4);
+          }
+          float dot = 0.f;
+#pragma unroll
+          for (int u = 0; u < RV; ++u)
+            dot += w[u].x * h[u].x + w[u].y * h[u].y + w[u].z * h[u].z + w[u].w * h[u].w;
+          const float e = warp_sum(dot) - v;
+          const float ee = a.eps * e, el = a.eps * a.lambda;
+#pragma unroll
+          for (int u = 0; u < RV; ++u) {
+            // w -= eps (e h + lambda w);  h -= eps (e w_old + lambda h)     (SGDMPTask.java:60-72)
+            float4 wn, hn;
+            wn.x = w[u].x - (ee * h[u].x + el * w[u].x); hn.x = h[u].x - (ee * w[u].x + el * h[u].x);
+            wn.y = w[u].y - (ee * h[u].y + el * w[u].y); hn.y = h[u].y - (ee * w[u].y + el * h[u].y);
+            wn.z = w[u].z - (ee * h[u].z + el * w[u].z); hn.z = h[u].z - (ee * w[u].z + el * h[u].z);
+            wn.w = w[u].w - (ee * h[u].w + el * w[u].w); hn.w = h[u].w - (ee * w[u].w + el * h[u].w);
+            h[u] = hn;
+            if (lane + 32 * u < nl4) stcg4(a.W + (size_t)row * a.rank + (lane + 32 * u) * 4, wn);
+          }
+          // a run may revisit a row only through another run (different column), never within itself,
+          // except for duplicate (row, col) ratings: make the prefetched copy coherent then
+          if (k + 1 < k1 && row_n == row) {
+#pragma unroll
+            for (int u = 0; u < RV; ++u)
+              if (lane + 32 * u < nl4) w_n[u] = ldcg4(a.W + (size_t)row_n * a.rank + (lane + 32 * u) * 4);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < RV; ++u) {
+          if (lane + 32 * u < nl4) {
+            float* hp = a.H + (size_t)col * a.rank + (lane + 32 * u) * 4;
+            if (shared_col)
+              red_add_v4(hp, make_float4(h[u].x - h0[u].x, h[u].y - h0[u].y, h[u].z - h0[u].z, h[u].w - h0[u].w));
+            else
+              stcg4(hp, h[u]);
+          }
+        }
+        if (lane == 0) local_trained += (unsigned long long)(k1 - k0);
+      }
+    }
+    // ---- release column-block c to the next CTA in the ring ----
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(a.col_ticket + c), "r"(a.ticket_base + (unsigned)t + 1u) : "memory");
+    }
+  }
+  if (lane == 0 && local_trained) atomicAdd(a.trained, local_trained);
+}
+
+// Σ (v - w·h)^2 over a rating list; one warp per rating.
+__global__ void rmse_kernel(const float* __restrict__ W, const float* __restrict__ H, const int* __restrict__ rows,
+                            const int* __restrict__ cols, const float* __restrict__ vals, long long n, int rank,
+                            double* __restrict__ sq_err) {
+  const int lane = threadIdx.x & 31;
+  const long long wid = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  double acc = 0.0;
+  for (long long k = wid; k < n; k += nw) {
+    const float* w = W + (size_t)rows[k] * rank;
+    const float* h = H + (size_t)cols[k] * rank;
+    float dot = 0.f;
+    for (int j = lane; j < rank; j += 32) dot = fmaf(w[j], h[j], dot);
+    dot = warp_sum(dot);
+    const float e = vals[k] - dot;
+    acc += (double)e * e;
+  }
+  if (lane == 0 && acc != 0.0) atomicAdd(sq_err, acc);
+}
+
+// CCD++ rank-one subproblem for one side: given residuals r_ij = v_ij - Σ_f w_if h_jf (kept per
+// rating), feature f:  for each row i:  w_if <- Σ_j (r_ij + w_if h_jf) h_jf / (λ + Σ_j h_jf²), then
+// r_ij updated in place.  CSR over the side being updated; one warp per row.
+// (CCDMPTask.doRowCCD / doColCCD, ml/java/.../ccd/CCDMPTask.java:67-125)
+__global__ void ccd_update_kernel(const int* __restrict__ ptr, const int* __restrict__ idx,
+                                  float* __restrict__ resid, const int* __restrict__ resid_perm,
+                                  float* __restrict__ Wf, const float* __restrict__ Hf, int nrows, float lambda) {
+  const int lane = threadIdx.x & 31;
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nw = (gridDim.x * blockDim.x) >> 5;
+  for (int i = wid; i < nrows; i += nw) {
+    const int k0 = ptr[i], k1 = ptr[i + 1];
+    if (k0 == k1) continue;
+    const float wi = Wf[i];
+    float up = 0.f, down = 0.f;
+    for (int k = k0 + lane; k < k1; k += 32) {
+      const float hj = Hf[idx[k]];
+      const int rk = resid_perm ? resid_perm[k] : k;
+      up = fmaf(resid[rk] + wi * hj, hj, up);
+      down = fmaf(hj, hj, down);
+    }
+    up = warp_sum(up); down = warp_sum(down);
+    const float wnew = up / (lambda + down);
+    const float delta = wi - wnew;
+    for (int k = k0 + lane; k < k1; k += 32) {
+      const int rk = resid_perm ? resid_perm[k] : k;
+      resid[rk] += delta * Hf[idx[k]];
+    }
+    if (lane == 0) Wf[i] = wnew;
+  }
+}
+
+}  // namespace mf
+}  // namespace hb
+
+using namespace hb;
+using namespace hb::mf;
+
+extern "C" {
+
+// Largest B (CTAs = blocks per side) a single cooperative launch can keep resident.
+int hb_sgd_max_blocks(int rank) {
+  int dev = 0, per_sm = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  const void* fn = rank <= 128 ? (const void*)sgd_pass_kernel<1> : rank <= 256 ? (const void*)sgd_pass_kernel<2>
+                                                                                 : (const void*)sgd_pass_kernel<4>;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, SGD_THREADS, 0) != cudaSuccess) return 0;
+  return per_sm * sm_count();
+}
+
+int hb_sgd_pass(float* W, float* H, const int* blk_seg_ptr, const int* seg_col, const int* seg_ptr,
+                const int* r_row, const float* r_val, int B, int rank, float eps, float lambda,
+                unsigned int* col_ticket, unsigned int ticket_base, unsigned long long deadline_ns,
+                unsigned long long* trained, void* stream) {
+  HB_REQUIRE(B >= 1 && rank >= 4 && rank % 4 == 0 && rank <= 512, "hb_sgd_pass: need rank %% 4 == 0 and rank <= 512 (got %d)", rank);
+  HB_REQUIRE(B <= hb_sgd_max_blocks(rank), "hb_sgd_pass: B=%d blocks cannot be co-resident (max %d)", B, hb_sgd_max_blocks(rank));
+  SgdArgs a;
+  a.W = W; a.H = H; a.blk_seg_ptr = blk_seg_ptr; a.seg_col = seg_col; a.seg_ptr = seg_ptr; a.r_row = r_row;
+  a.r_val = r_val; a.col_ticket = col_ticket; a.trained = trained; a.deadline_ns = deadline_ns;
+  a.ticket_base = ticket_base; a.B = B; a.rank = rank; a.eps = eps; a.lambda = lambda;
+  void* args[] = {&a};
+  const void* fn = rank <= 128 ? (const void*)sgd_pass_kernel<1> : rank <= 256 ? (const void*)sgd_pass_kernel<2>
+                                                                                 : (const void*)sgd_pass_kernel<4>;
+  // cooperative launch: all B CTAs are guaranteed resident, which the ticket ring relies on
+  HB_CUDA_OK(cudaLaunchCooperativeKernel(fn, dim3(B), dim3(SGD_THREADS), args, 0, (cudaStream_t)stream));
+  return 0;
+}
+
+// Device wall clock (ns) usable as a deadline base for hb_sgd_pass.
+__global__ void read_timer_kernel(unsigned long long* out) { *out = globaltimer_ns(); }
+int hb_device_time_ns(unsigned long long* out_dev, void* stream) {
+  read_timer_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(out_dev);
+  HB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int hb_mf_sq_err(const float* W, const float* H, const int* rows, const int* cols, const float* vals,
+                 long long n, int rank, double* sq_err, void* stream) {
+  if (n == 0) return 0;
+  long long blocks = (n * 32 + 255) / 256;
+  const long long cap = (long long)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  rmse_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(W, H, rows, cols, vals, n, rank, sq_err);
+  HB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int hb_ccd_update(const int* ptr, const int* idx, float* resid, const int* resid_perm, float* Wf,
+                  const float* Hf, int nrows, float lambda, void* stream) {
+  if (nrows == 0) return 0;
+  long long blocks = ((long long)nrows * 32 + 255) / 256;
+  const long long cap = (long long)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  ccd_update_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(ptr, idx, resid, resid_perm, Wf, Hf, nrows, lambda);
+  HB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

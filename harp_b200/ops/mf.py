@@ -1,0 +1,188 @@
+"""Matrix-factorisation ops: SGD panel pass, squared error, CCD++ rank-one update.
+
+CUDA tensors run ``csrc/mf.cu``; CPU tensors run restatements of the Java loops
+(``SGDMPTask.doRun``, ``RMSETask``, ``CCDMPTask``) so that apps and tests work without a GPU.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from .. import _native
+
+
+def _declare(lib) -> None:
+    if getattr(lib, "_hb_mf_declared", False):
+        return
+    P, I, LL, F, U, ULL = (ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_uint32,
+                           ctypes.c_ulonglong)
+    lib.hb_sgd_max_blocks.argtypes = [I]
+    lib.hb_sgd_pass.argtypes = [P, P, P, P, P, P, P, I, I, F, F, P, U, ULL, P, P]
+    lib.hb_device_time_ns.argtypes = [P, P]
+    lib.hb_mf_sq_err.argtypes = [P, P, P, P, P, LL, I, P, P]
+    lib.hb_ccd_update.argtypes = [P, P, P, P, P, P, I, F, P]
+    lib._hb_mf_declared = True
+
+
+@dataclass
+class SgdPanel:
+    """Ratings of (this worker's rows) x (one H slice), bucketed B x B, column-sorted inside blocks."""
+    B: int
+    blk_seg_ptr: torch.Tensor   # int32 [B*B+1]
+    seg_col: torch.Tensor       # int32 [nseg]
+    seg_ptr: torch.Tensor       # int32 [nseg+1]
+    r_row: torch.Tensor         # int32 [nnz]
+    r_val: torch.Tensor         # float32 [nnz]
+    col_ticket: torch.Tensor    # uint32-as-int32 [B]
+    ticket_base: int = 0
+
+    @property
+    def nnz(self) -> int:
+        return int(self.r_row.numel())
+
+
+def max_blocks(rank: int) -> int:
+    lib = _native.lib()
+    _declare(lib)
+    return int(lib.hb_sgd_max_blocks(rank))
+
+
+def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: int, max_run: int = 32) -> SgdPanel:
+    """Buckets a COO rating list (worker-local row ids, slice-local column ids).  Row block = row % B,
+    column block = col % B; inside a block ratings are ordered by column (then by original order).
+    Column runs longer than ``max_run`` are cut into sub-runs (flagged in bit 31 of ``seg_col``) so that a
+    popular column does not serialise a whole block on one warp."""
+    dev = rows.device
+    rows = rows.to(torch.int64)
+    cols = cols.to(torch.int64)
+    n = rows.numel()
+    if n == 0:
+        z = torch.zeros(B * B + 1, dtype=torch.int32, device=dev)
+        e = torch.zeros(0, dtype=torch.int32, device=dev)
+        return SgdPanel(B, z, e, torch.zeros(1, dtype=torch.int32, device=dev), e,
+                        torch.zeros(0, dtype=torch.float32, device=dev), torch.zeros(B, dtype=torch.int32, device=dev))
+    blk = (rows % B) * B + (cols % B)
+    ncols = int(cols.max().item()) + 1
+    key = blk * ncols + cols
+    order = torch.argsort(key, stable=True)
+    key_s = key[order]
+    uniq, counts = torch.unique_consecutive(key_s, return_counts=True)
+    if max_run and int(counts.max().item()) > max_run:
+        pieces = (counts + max_run - 1) // max_run                       # sub-runs per run
+        rep = torch.repeat_interleave(torch.arange(uniq.numel(), device=dev), pieces)
+        first = torch.zeros(uniq.numel(), dtype=torch.int64, device=dev)
+        first[1:] = torch.cumsum(pieces, 0)[:-1]
+        j = torch.arange(rep.numel(), device=dev) - first[rep]           # index of the piece inside its run
+        base, extra = counts[rep] // pieces[rep], counts[rep] % pieces[rep]
+        sub_counts = base + (j < extra).to(torch.int64)                  # near-equal pieces
+        split_flag = (pieces[rep] > 1)
+        uniq, counts = uniq[rep], sub_counts
+    else:
+        split_flag = torch.zeros(uniq.numel(), dtype=torch.bool, device=dev)
+    seg_ptr = torch.zeros(uniq.numel() + 1, dtype=torch.int64, device=dev)
+    seg_ptr[1:] = torch.cumsum(counts, 0)
+    seg_blk = uniq // ncols
+    seg_col = (uniq % ncols).to(torch.int32)
+    seg_col = torch.where(split_flag, seg_col | torch.tensor(-2147483648, dtype=torch.int32, device=dev), seg_col)
+    blk_seg_ptr = torch.searchsorted(seg_blk, torch.arange(B * B + 1, device=dev, dtype=torch.int64)).to(torch.int32)
+    return SgdPanel(B, blk_seg_ptr.contiguous(), seg_col.contiguous(), seg_ptr.to(torch.int32).contiguous(),
+                    rows[order].to(torch.int32).contiguous(), vals[order].to(torch.float32).contiguous(),
+                    torch.zeros(B, dtype=torch.int32, device=dev))
+
+
+def _cpu_sgd_pass(panel: SgdPanel, W, H, eps, lam) -> int:
+    # sequential restatement in the kernel's own order: Latin-square steps, blocks, column runs
+    B = panel.B
+    bsp, sc, sp = panel.blk_seg_ptr.tolist(), (panel.seg_col & 0x7FFFFFFF).tolist(), panel.seg_ptr.tolist()
+    rr, rv = panel.r_row.tolist(), panel.r_val.tolist()
+    n = 0
+    for t in range(B):
+        for i in range(B):
+            c = (i + t) % B
+            for s in range(bsp[i * B + c], bsp[i * B + c + 1]):
+                h = H[sc[s]]
+                for k in range(sp[s], sp[s + 1]):
+                    w = W[rr[k]]
+                    e = float(w @ h) - rv[k]
+                    w_new = w - eps * (e * h + lam * w)
+                    h.sub_(eps * (e * w + lam * h))
+                    W[rr[k]] = w_new
+                    n += 1
+    return n
+
+
+def sgd_pass(panel: SgdPanel, W: torch.Tensor, H: torch.Tensor, eps: float, lam: float,
+             deadline_ms: Optional[float] = None, trained: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """One pass over the panel; returns a 1-element int64 tensor with the number of ratings trained."""
+    if W.device.type != "cuda":
+        n = _cpu_sgd_pass(panel, W, H, eps, lam)
+        out = trained if trained is not None else torch.zeros(1, dtype=torch.int64)
+        out += n
+        return out
+    lib = _native.lib()
+    _declare(lib)
+    assert W.dtype == torch.float32 and H.dtype == torch.float32 and W.is_contiguous() and H.is_contiguous()
+    rank = W.shape[1]
+    if trained is None:
+        trained = torch.zeros(1, dtype=torch.int64, device=W.device)
+    deadline = int(deadline_ms * 1e6) if deadline_ms is not None else 0     # budget from kernel entry
+    rc = lib.hb_sgd_pass(_native.ptr(W), _native.ptr(H), _native.ptr(panel.blk_seg_ptr), _native.ptr(panel.seg_col),
+                         _native.ptr(panel.seg_ptr), _native.ptr(panel.r_row), _native.ptr(panel.r_val), panel.B, rank,
+                         float(eps), float(lam), _native.ptr(panel.col_ticket), panel.ticket_base & 0xFFFFFFFF,
+                         deadline, _native.ptr(trained), _native.stream_ptr())
+    _native.check(rc, "hb_sgd_pass")
+    panel.ticket_base = (panel.ticket_base + panel.B) & 0x7FFFFFFF
+    _native.count_launch()
+    return trained
+
+
+def sq_err(W: torch.Tensor, H: torch.Tensor, rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor,
+           out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``Σ (v - w·h)²`` (float64, accumulated into ``out``)."""
+    if out is None:
+        out = torch.zeros(1, dtype=torch.float64, device=W.device)
+    if rows.numel() == 0:
+        return out
+    if W.device.type != "cuda":
+        pred = (W[rows.long()] * H[cols.long()]).sum(1)
+        out += ((vals - pred).double() ** 2).sum()
+        return out
+    lib = _native.lib()
+    _declare(lib)
+    r32 = rows.to(torch.int32).contiguous()      # keep the converted tensors alive across the launch
+    c32 = cols.to(torch.int32).contiguous()
+    v32 = vals.float().contiguous()
+    rc = lib.hb_mf_sq_err(_native.ptr(W), _native.ptr(H), _native.ptr(r32), _native.ptr(c32), _native.ptr(v32),
+                          rows.numel(), W.shape[1], _native.ptr(out), _native.stream_ptr())
+    _native.check(rc, "hb_mf_sq_err")
+    _native.count_launch()
+    return out
+
+
+def ccd_update(ptr: torch.Tensor, idx: torch.Tensor, resid: torch.Tensor, perm: Optional[torch.Tensor],
+               Wf: torch.Tensor, Hf: torch.Tensor, lam: float) -> None:
+    """CCD++ rank-one update of ``Wf`` (one feature) given ``Hf``; ``resid`` (per rating, addressed through
+    ``perm`` when the CSR order differs from the residual order) is updated in place."""
+    nrows = Wf.numel()
+    if Wf.device.type != "cuda":
+        for i in range(nrows):
+            k0, k1 = int(ptr[i]), int(ptr[i + 1])
+            if k0 == k1:
+                continue
+            j = idx[k0:k1].long()
+            rk = perm[k0:k1].long() if perm is not None else torch.arange(k0, k1)
+            hj = Hf[j]
+            wi = Wf[i]
+            wnew = ((resid[rk] + wi * hj) * hj).sum() / (lam + (hj * hj).sum())
+            resid[rk] += (wi - wnew) * hj
+            Wf[i] = wnew
+        return
+    lib = _native.lib()
+    _declare(lib)
+    rc = lib.hb_ccd_update(_native.ptr(ptr), _native.ptr(idx), _native.ptr(resid), _native.ptr(perm), _native.ptr(Wf),
+                           _native.ptr(Hf), nrows, float(lam), _native.stream_ptr())
+    _native.check(rc, "hb_ccd_update")
+    _native.count_launch()

@@ -84,6 +84,29 @@ int hb_gram(const float* X, long long n, int d, float* G, int flags, void* strea
 int hb_moments(const float* X, long long n, int d, double* sum, double* sumsq, float* mn, float* mx,
                int flags, void* stream);
 
+/* ---- Matrix factorisation (csrc/mf.cu) — SGDMPTask.doRun (MJ/sgd/SGDMPTask.java:46-77), the
+ * dymoro block Scheduler (MJ/dymoro/Scheduler.java:95-237), RMSETask (MJ/sgd/RMSETask.java:67-103),
+ * CCDMPTask (MJ/ccd/CCDMPTask.java:67-125) -------------------------------------------------- */
+/* How many blocks per side one cooperative launch can keep resident for this rank. */
+int hb_sgd_max_blocks(int rank);
+/* One SGD pass over a panel bucketed into B x B blocks (block (i,c) = runs
+ * blk_seg_ptr[i*B+c] .. blk_seg_ptr[i*B+c+1]); run s covers ratings seg_ptr[s]..seg_ptr[s+1] of
+ * column seg_col[s].  col_ticket[B] must hold `ticket_base` on entry and holds ticket_base + B on
+ * exit.  deadline_ns (time budget from kernel entry, 0 = none) bounds the pass as the reference's
+ * Timer does; *trained += ratings updated. */
+int hb_sgd_pass(float* W, float* H, const int* blk_seg_ptr, const int* seg_col, const int* seg_ptr,
+                const int* r_row, const float* r_val, int B, int rank, float eps, float lambda,
+                unsigned int* col_ticket, unsigned int ticket_base, unsigned long long deadline_ns,
+                unsigned long long* trained, void* stream);
+/* Writes the device wall clock (ns) to *out_dev. */
+int hb_device_time_ns(unsigned long long* out_dev, void* stream);
+/* *sq_err += sum (v - w.h)^2 over a rating list. */
+int hb_mf_sq_err(const float* W, const float* H, const int* rows, const int* cols, const float* vals,
+                 long long n, int rank, double* sq_err, void* stream);
+/* CCD++ rank-one update of one feature column Wf[nrows] against Hf, residuals updated in place. */
+int hb_ccd_update(const int* ptr, const int* idx, float* resid, const int* resid_perm, float* Wf,
+                  const float* Hf, int nrows, float lambda, void* stream);
+
 /* ---- NVLink peer-memory collectives (csrc/coll.cu) ------------------------
  * Replace the TCP collectives of HC/collective/*.java.  Every rank passes the
  * same table `peer_ptrs[world]` of peer-mapped slab base addresses (index =
