@@ -1,0 +1,174 @@
+"""LDA-CGS engine with model rotation (``ml/java/src/main/java/edu/iu/lda/LDAMPCollectiveMapper.java:183-378``).
+
+Documents (and their dense doc-topic rows) stay on their worker; the word-topic table is sharded by
+word (home worker ``w % N``, slice ``(w // N) % 2``, slice-local row ``w // 2N``) and its two slices
+travel the ring, double-buffered in symmetric memory and pulled over NVLink on a side stream while
+the other slice is being sampled.  Global topic sums are refreshed once per iteration
+(``:442-475``); log-likelihood follows ``CalcLikelihoodTask`` (``:699-752``).
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import lda as L
+
+
+class LDAEngine:
+    def __init__(self, docs: torch.Tensor, words: torch.Tensor, num_docs_local: int, vocab: int, K: int,
+                 alpha: float, beta: float, *, symm=None, blocks: Optional[int] = None, seed: int = 0, group=None):
+        self.dev = docs.device
+        self.K, self.V = int(K), int(vocab)
+        self.alpha, self.beta = float(alpha), float(beta)
+        self.group = group
+        self.N = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.me = dist.get_rank(group) if dist.is_initialized() else 0
+        self.symm = symm if self.N > 1 else None
+        N = self.N
+        self.cap = max(1, (self.V + 2 * N - 1) // (2 * N))
+        if self.dev.type == "cuda":
+            sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
+            self.B = int(blocks) if blocks else min(L.max_blocks(self.K), sms)
+        else:
+            self.B = int(blocks) if blocks else 2
+        self.seed = int(seed)
+        self.iteration = 0
+        g = torch.Generator(device=self.dev).manual_seed(seed + 31 * self.me)
+        self.ntok = int(docs.numel())
+        z = torch.randint(0, self.K, (self.ntok,), device=self.dev, generator=g)
+        words = words.to(torch.int64)
+        shard, slc, local = words % N, (words // N) % 2, words // (2 * N)
+        self.panels: List[List[L.TokenPanel]] = []
+        for s in range(N):
+            per = []
+            for k in range(2):
+                m = (shard == s) & (slc == k)
+                per.append(L.build_token_panel(docs[m], local[m], z[m], self.B))
+            self.panels.append(per)
+        cdt = torch.int32
+        self.n_dk = torch.zeros(num_docs_local, self.K, dtype=cdt, device=self.dev)
+        for s in range(N):
+            for k in range(2):
+                p = self.panels[s][k]
+                L.count_into(p.tok_doc, p.tok_z, self.K, self.n_dk)
+        self.Wbuf: List[List[torch.Tensor]] = []
+        for k in range(2):
+            pair = []
+            for _ in range(2 if N > 1 else 1):
+                if self.symm is not None:
+                    t = self.symm.alloc(self.cap * self.K, cdt).view(self.cap, self.K)
+                else:
+                    t = torch.empty(self.cap, self.K, dtype=cdt, device=self.dev)
+                t.zero_()
+                pair.append(t)
+            self.Wbuf.append(pair)
+        self.cur, self.rot = [0, 0], [0, 0]
+        if self.dev.type == "cuda":
+            self.comm_stream = torch.cuda.Stream(device=self.dev)
+            self.ev_compute = [torch.cuda.Event(), torch.cuda.Event()]
+            self.ev_comm = [torch.cuda.Event(), torch.cuda.Event()]
+            for e in self.ev_comm:
+                e.record()
+        # word-topic table: one full rotation in which every worker adds its tokens to the visiting shard
+        for _ in range(N):
+            for k in range(2):
+                self._wait_slice(k)
+                p = self.panels[self._visiting(k)][k]
+                L.count_into(p.tok_word, p.tok_z, self.K, self.Wbuf[k][self.cur[k]])
+                self._rotate(k)
+        self.topic_sums = torch.zeros(self.K, dtype=torch.int64, device=self.dev)
+        self.commons = torch.zeros(self.K, dtype=torch.float32, device=self.dev)
+        self.trained = torch.zeros(1, dtype=torch.int64, device=self.dev)
+        self._refresh_topic_sums()
+
+    def _visiting(self, k: int) -> int:
+        return (self.me - self.rot[k]) % self.N
+
+    def _wait_slice(self, k: int) -> None:
+        if self.N > 1 and self.symm is not None and self.dev.type == "cuda":
+            torch.cuda.current_stream().wait_event(self.ev_comm[k])
+
+    def _rotate(self, k: int) -> None:
+        if self.N == 1:
+            return
+        src, dst = self.Wbuf[k][self.cur[k]], self.Wbuf[k][1 - self.cur[k]]
+        pred = (self.me - 1) % self.N
+        if self.symm is not None and self.dev.type == "cuda":
+            self.ev_compute[k].record()
+            with torch.cuda.stream(self.comm_stream):
+                self.comm_stream.wait_event(self.ev_compute[k])
+                self.symm.rotate_(dst, src, pred)
+                self.ev_comm[k].record()
+        else:
+            ops = [dist.P2POp(dist.isend, src.contiguous(), (self.me + 1) % self.N, group=self.group),
+                   dist.P2POp(dist.irecv, dst, pred, group=self.group)]
+            for r in dist.batch_isend_irecv(ops):
+                r.wait()
+        self.cur[k] ^= 1
+        self.rot[k] += 1
+
+    def _refresh_topic_sums(self) -> None:
+        self.topic_sums.zero_()
+        for k in range(2):
+            self._wait_slice(k)
+            L.topic_sums(self.Wbuf[k][self.cur[k]], self.topic_sums)
+        if self.N > 1:
+            dist.all_reduce(self.topic_sums, group=self.group)
+        self.commons.copy_((1.0 / (self.topic_sums.double() + self.beta * self.V)).float())
+
+    def iterate(self, deadline_ms: Optional[float] = None) -> torch.Tensor:
+        """One iteration = N rotations x 2 slices, then the global topic-sum refresh."""
+        self.trained.zero_()
+        self.iteration += 1
+        for j in range(self.N):
+            for k in range(2):
+                self._wait_slice(k)
+                p = self.panels[self._visiting(k)][k]
+                L.lda_pass(p, self.n_dk, self.Wbuf[k][self.cur[k]], self.commons, self.alpha, self.beta,
+                           self.seed * 1000003 + self.iteration * 7919 + j * 2 + k + 104729 * self.me, deadline_ms, self.trained)
+                self._rotate(k)
+        self._refresh_topic_sums()
+        return self.trained
+
+    def log_likelihood(self) -> float:
+        """Word-side model log-likelihood (MALLET ``modelLogLikelihood`` form used by the reference):
+        ``Σ_k Σ_w lgamma(β + n_wk) − Σ_k lgamma(Vβ + n_k) + K lgamma(Vβ) − K V lgamma(β)`` plus the
+        document side ``Σ_d [Σ_k lgamma(α + n_dk) − lgamma(Kα + n_d)] + D lgamma(Kα) − D K lgamma(α)``."""
+        b, a, K, V = self.beta, self.alpha, self.K, self.V
+        acc = torch.zeros(1, dtype=torch.float64, device=self.dev)
+        for k in range(2):
+            self._wait_slice(k)
+            tab = self.Wbuf[k][self.cur[k]].double()
+            # only rows that are real words of this shard/slice
+            s = self._visiting(k)
+            gid = torch.arange(self.cap, device=self.dev) * (2 * self.N) + k * self.N + s
+            tab = tab[gid < V]
+            acc += torch.lgamma(tab + b).sum() - tab.shape[0] * K * math.lgamma(b)
+        nd = self.n_dk.double()
+        doc = (torch.lgamma(nd + a).sum() - torch.lgamma(nd.sum(1) + K * a).sum()
+               + nd.shape[0] * (math.lgamma(K * a) - K * math.lgamma(a)))
+        acc += doc
+        if self.N > 1:
+            dist.all_reduce(acc, group=self.group)
+        acc += -(torch.lgamma(self.topic_sums.double() + V * b)).sum() + K * math.lgamma(V * b)
+        return float(acc.item())
+
+    def synchronize(self) -> None:
+        if self.dev.type == "cuda":
+            for k in range(2):
+                self._wait_slice(k)
+            torch.cuda.synchronize(self.dev)
+
+    def home_word_rows(self):
+        """``(global word ids, count rows)`` of the word-topic rows currently resident."""
+        ids, rows = [], []
+        for k in range(2):
+            self._wait_slice(k)
+            s = self._visiting(k)
+            gid = torch.arange(self.cap, device=self.dev) * (2 * self.N) + k * self.N + s
+            keep = gid < self.V
+            ids.append(gid[keep]); rows.append(self.Wbuf[k][self.cur[k]][keep])
+        return torch.cat(ids), torch.cat(rows)

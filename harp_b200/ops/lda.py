@@ -1,0 +1,135 @@
+"""LDA collapsed-Gibbs ops (``csrc/lda.cu``) with a CPU restatement of the same sampler
+(``ml/java/src/main/java/edu/iu/lda/LDAMPTask.java:85-331`` — same conditional distribution, dense
+instead of SparseLDA's bucket decomposition)."""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from .. import _native
+from . import mf
+
+
+def _declare(lib) -> None:
+    if getattr(lib, "_hb_lda_declared", False):
+        return
+    P, I, LL, F, U, ULL = (ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_uint32,
+                           ctypes.c_ulonglong)
+    lib.hb_lda_max_blocks.argtypes = [I]
+    lib.hb_lda_pass.argtypes = [P, P, P, P, P, P, P, P, I, I, F, F, ULL, P, U, ULL, P, P]
+    lib.hb_lda_topic_sums.argtypes = [P, LL, I, P, P]
+    lib.hb_lda_count.argtypes = [P, P, LL, I, P, P]
+    lib._hb_lda_declared = True
+
+
+@dataclass
+class TokenPanel:
+    """Tokens of (this worker's documents) x (one word slice): B x B blocks, word-sorted inside a block."""
+    B: int
+    blk_seg_ptr: torch.Tensor
+    seg_word: torch.Tensor
+    seg_ptr: torch.Tensor
+    tok_doc: torch.Tensor     # int32 [ntok]
+    tok_z: torch.Tensor       # int32 [ntok] (updated in place by the sampler)
+    tok_word: torch.Tensor    # int32 [ntok] slice-local word id (for table initialisation / checks)
+    col_ticket: torch.Tensor
+    ticket_base: int = 0
+
+    @property
+    def ntok(self) -> int:
+        return int(self.tok_doc.numel())
+
+
+def max_blocks(K: int) -> int:
+    lib = _native.lib()
+    _declare(lib)
+    return int(lib.hb_lda_max_blocks(K))
+
+
+def build_token_panel(docs: torch.Tensor, words: torch.Tensor, z: torch.Tensor, B: int, max_run: int = 64) -> TokenPanel:
+    sp = mf.build_panel(docs, words, z.to(torch.float32), B, max_run=max_run)
+    # recover each token's word from the run structure
+    seg_len = (sp.seg_ptr[1:] - sp.seg_ptr[:-1]).long()
+    tok_word = torch.repeat_interleave((sp.seg_col & 0x7FFFFFFF).to(torch.int32), seg_len)
+    return TokenPanel(B, sp.blk_seg_ptr, sp.seg_col, sp.seg_ptr, sp.r_row, sp.r_val.to(torch.int32).contiguous(),
+                      tok_word.contiguous(), sp.col_ticket)
+
+
+def count_into(idx0: torch.Tensor, z: torch.Tensor, K: int, counts: torch.Tensor) -> None:
+    """``counts[idx0[t], z[t]] += 1``."""
+    if idx0.numel() == 0:
+        return
+    if counts.device.type != "cuda":
+        counts.view(-1).index_add_(0, idx0.long() * K + z.long(), torch.ones(idx0.numel(), dtype=counts.dtype))
+        return
+    lib = _native.lib()
+    _declare(lib)
+    i32, z32 = idx0.to(torch.int32).contiguous(), z.to(torch.int32).contiguous()
+    _native.check(lib.hb_lda_count(_native.ptr(i32), _native.ptr(z32), idx0.numel(), K, _native.ptr(counts),
+                                   _native.stream_ptr()), "hb_lda_count")
+    _native.count_launch()
+
+
+def topic_sums(n_wk: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """``out[k] += Σ_w n_wk[w, k]`` (int64)."""
+    if n_wk.device.type != "cuda":
+        out += n_wk.long().sum(0)
+        return out
+    lib = _native.lib()
+    _declare(lib)
+    _native.check(lib.hb_lda_topic_sums(_native.ptr(n_wk), n_wk.shape[0], n_wk.shape[1], _native.ptr(out),
+                                        _native.stream_ptr()), "hb_lda_topic_sums")
+    _native.count_launch()
+    return out
+
+
+def _cpu_pass(panel: TokenPanel, n_dk, n_wk, commons, alpha, beta, seed) -> int:
+    g = torch.Generator().manual_seed(int(seed) & 0x7FFFFFFF)
+    B = panel.B
+    bsp, sw, sp = panel.blk_seg_ptr.tolist(), (panel.seg_word & 0x7FFFFFFF).tolist(), panel.seg_ptr.tolist()
+    td = panel.tok_doc.tolist()
+    n = 0
+    cm = commons.double()
+    for t in range(B):
+        for i in range(B):
+            c = (i + t) % B
+            for s in range(bsp[i * B + c], bsp[i * B + c + 1]):
+                w = sw[s]
+                for tk in range(sp[s], sp[s + 1]):
+                    d, zo = td[tk], int(panel.tok_z[tk])
+                    n_dk[d, zo] -= 1; n_wk[w, zo] -= 1
+                    p = (n_dk[d].double() + alpha) * (n_wk[w].double() + beta) * cm
+                    zn = int(torch.multinomial(p / p.sum(), 1, generator=g))
+                    n_dk[d, zn] += 1; n_wk[w, zn] += 1
+                    panel.tok_z[tk] = zn
+                    n += 1
+    return n
+
+
+def lda_pass(panel: TokenPanel, n_dk: torch.Tensor, n_wk: torch.Tensor, commons: torch.Tensor, alpha: float,
+             beta: float, seed: int, deadline_ms: Optional[float] = None,
+             trained: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if n_dk.device.type != "cuda":
+        n = _cpu_pass(panel, n_dk, n_wk, commons, alpha, beta, seed)
+        out = trained if trained is not None else torch.zeros(1, dtype=torch.int64)
+        out += n
+        return out
+    lib = _native.lib()
+    _declare(lib)
+    assert n_dk.dtype == torch.int32 and n_wk.dtype == torch.int32 and commons.dtype == torch.float32
+    K = n_dk.shape[1]
+    if trained is None:
+        trained = torch.zeros(1, dtype=torch.int64, device=n_dk.device)
+    deadline = int(deadline_ms * 1e6) if deadline_ms is not None else 0
+    rc = lib.hb_lda_pass(_native.ptr(n_dk), _native.ptr(n_wk), _native.ptr(commons), _native.ptr(panel.blk_seg_ptr),
+                         _native.ptr(panel.seg_word), _native.ptr(panel.seg_ptr), _native.ptr(panel.tok_doc),
+                         _native.ptr(panel.tok_z), panel.B, K, float(alpha), float(beta), int(seed) & 0xFFFFFFFFFFFFFFFF,
+                         _native.ptr(panel.col_ticket), panel.ticket_base & 0xFFFFFFFF, deadline, _native.ptr(trained),
+                         _native.stream_ptr())
+    _native.check(rc, "hb_lda_pass")
+    panel.ticket_base = (panel.ticket_base + panel.B) & 0x7FFFFFFF
+    _native.count_launch()
+    return trained

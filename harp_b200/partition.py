@@ -221,6 +221,27 @@ class RandomPartitioner(Partitioner):
 
     getWorkerID = get_worker_id
 
+    def worker_ids(self, partition_ids: torch.Tensor) -> torch.Tensor:
+        """Vectorised splitmix64 (two's-complement int64 arithmetic wraps like the scalar version)."""
+        def lsr(v, n):      # logical shift right on int64
+            return (v >> n) & ((1 << (64 - n)) - 1)
+        def mul(v, c):      # wrapping multiply by an unsigned 64-bit constant
+            c = c - (1 << 64) if c >= (1 << 63) else c
+            return v * c
+        seed_mix = (self.seed * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+        seed_mix = seed_mix - (1 << 64) if seed_mix >= (1 << 63) else seed_mix
+        x = partition_ids.to(torch.int64) + seed_mix
+        x = x ^ lsr(x, 30)
+        x = mul(x, 0xBF58476D1CE4E5B9)
+        x = x ^ lsr(x, 27)
+        x = mul(x, 0x94D049BB133111EB)
+        x = x ^ lsr(x, 31)
+        # unsigned modulo of a value stored as signed int64
+        n = self.num_workers
+        lo = (x & 0x7FFFFFFFFFFFFFFF) % n
+        hi = torch.where(x < 0, torch.full_like(x, (1 << 63) % n), torch.zeros_like(x))
+        return (lo + hi) % n
+
 
 class PartitionFunction:
     """Post-regroup per-partition callback (``partition/PartitionFunction.java:25-27``)."""

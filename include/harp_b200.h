@@ -107,6 +107,21 @@ int hb_mf_sq_err(const float* W, const float* H, const int* rows, const int* col
 int hb_ccd_update(const int* ptr, const int* idx, float* resid, const int* resid_perm, float* Wf,
                   const float* Hf, int nrows, float lambda, void* stream);
 
+/* ---- LDA collapsed Gibbs sampling (csrc/lda.cu) — LDAMPTask.doRun/sample
+ * (MJ/lda/LDAMPTask.java:85-331), topic sums (MJ/lda/LDAMPCollectiveMapper.java:442-475) ------- */
+int hb_lda_max_blocks(int K);
+/* One sampling pass over a token panel bucketed B x B like the SGD panels (documents = rows, words =
+ * columns).  n_dk[docs,K], n_wk[words_slice,K] are dense int32 count tables updated in place with
+ * atomics, tok_z holds the assignments, commons[k] = 1/(n_k + V beta) is frozen for the pass. */
+int hb_lda_pass(int* n_dk, int* n_wk, const float* commons, const int* blk_seg_ptr, const int* seg_word,
+                const int* seg_ptr, const int* tok_doc, int* tok_z, int B, int K, float alpha, float beta,
+                unsigned long long seed, unsigned int* col_ticket, unsigned int ticket_base,
+                unsigned long long deadline_ns, unsigned long long* trained, void* stream);
+/* sums[k] += sum over words of n_wk[w][k] (int64). */
+int hb_lda_topic_sums(const int* n_wk, long long words, int K, long long* sums, void* stream);
+/* counts[idx0[t] * K + z[t]] += 1 for every token. */
+int hb_lda_count(const int* idx0, const int* z, long long n, int K, int* counts, void* stream);
+
 /* ---- NVLink peer-memory collectives (csrc/coll.cu) ------------------------
  * Replace the TCP collectives of HC/collective/*.java.  Every rank passes the
  * same table `peer_ptrs[world]` of peer-mapped slab base addresses (index =
