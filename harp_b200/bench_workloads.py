@@ -1,0 +1,134 @@
+"""Secondary bench.py workloads (BASELINE configs 3, 4, 5): ``--workload sgd | lda | gram``.
+
+Same contract as the K-means default: W untimed warm-up steps, K timed steps between barriers +
+synchronises, CUDA-event time, max over ranks, ONE JSON line from rank 0.  Strong scaling: the
+named global problem is split over the N GPUs.
+"""
+from __future__ import annotations
+
+import json
+import math
+import time
+
+import torch
+import torch.distributed as dist
+
+from . import _native
+
+
+def _finish(args, rank, world, dev, ms_local, out):
+    t = torch.tensor([ms_local], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / args.steps
+    out.update({"n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "impl": "harp_b200",
+                "data": "synthetic", "vs_baseline": None, "gpu_launches": _native.launches()})
+    return ms, out
+
+
+def run_workload(args, rank, world, dev):
+    symm = None
+    if world > 1:
+        from .parallel.symm import SymmetricWorkspace
+        try:
+            symm = SymmetricWorkspace(dev, bytes_=1 << 30)
+        except Exception:  # noqa: BLE001
+            symm = None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    if args.workload == "sgd":
+        from .models.mfsgd import MFSGDEngine
+        rows, cols, nnz, rk = 480_000, 17_700, 100_000_000, 128
+        n_local = nnz // world
+        g = torch.Generator(device=dev).manual_seed(11 + rank)
+        rows_local = (rows + world - 1) // world
+        r = (torch.rand(n_local, device=dev, generator=g) ** 2 * rows_local).long() % rows_local
+        c = (torch.rand(n_local, device=dev, generator=g) ** 2 * cols).long() % cols
+        v = torch.rand(n_local, device=dev, generator=g) * 4 + 1
+        eng = MFSGDEngine(r, c, v, rows_local, cols, rk, 0.001, 0.01, symm=symm, seed=3)
+        del r, c, v
+        for _ in range(args.warmup):
+            eng.epoch()
+        eng.synchronize(); barrier()
+        _native.reset_launches()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier(); e0.record()
+        for _ in range(args.steps):
+            eng.epoch()
+        eng.synchronize(); e1.record(); barrier()
+        ms, out = _finish(args, rank, world, dev, e0.elapsed_time(e1), {})
+        if rank == 0:
+            out.update({"metric": "mfsgd_updates_per_s", "value": nnz / (ms / 1e3), "unit": "updates/s",
+                        "higher_is_better": True, "scaling": "strong", "dtype": "fp32",
+                        "config": {"model": "MF-SGD model rotation (BASELINE config 3)", "rows": rows, "cols": cols,
+                                   "ratings": nnz, "rank": rk, "parallelism": f"rows dp{world} + H rotation",
+                                   "l2": "W (245 MB) + ratings (1.2 GB) exceed L2"}})
+            print(json.dumps(out))
+    elif args.workload == "lda":
+        from .models.lda import LDAEngine
+        D, V, K, L = 1_000_000, 100_000, 1000, 100
+        d_local = D // world
+        g = torch.Generator(device=dev).manual_seed(5 + rank)
+        docs = torch.arange(d_local, device=dev).repeat_interleave(L)
+        words = (torch.rand(d_local * L, device=dev, generator=g) ** 3 * V).long() % V
+        eng = LDAEngine(docs, words, d_local, V, K, 0.01, 0.01, symm=symm, seed=1)
+        for _ in range(args.warmup):
+            eng.iterate()
+        eng.synchronize(); barrier()
+        _native.reset_launches()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier(); e0.record()
+        for _ in range(args.steps):
+            eng.iterate()
+        eng.synchronize(); e1.record(); barrier()
+        ms, out = _finish(args, rank, world, dev, e0.elapsed_time(e1), {})
+        if rank == 0:
+            out.update({"metric": "lda_cgs_tokens_per_s", "value": D * L / (ms / 1e3), "unit": "tokens/s",
+                        "higher_is_better": True, "scaling": "strong", "dtype": "int32 counts / fp32 probabilities",
+                        "config": {"model": "LDA-CGS model rotation (BASELINE config 4)", "docs": D, "vocab": V,
+                                   "topics": K, "tokens": D * L, "parallelism": f"docs dp{world} + word-topic rotation",
+                                   "l2": "doc-topic table (4 GB) exceeds L2"}})
+            print(json.dumps(out))
+    else:  # gram
+        from .ops.gram import gram, moments
+        n, d = 50_000_000 // world, 1024
+        n = min(n, 6_250_000)
+        X = torch.randn(n, d, device=dev)
+        G = symm.alloc(d * d, torch.float32).view(d, d) if symm is not None else torch.empty(d, d, device=dev)
+        s = symm.alloc(d, torch.float64) if symm is not None else None
+
+        def step():
+            gram(X, out=G)
+            m = moments(X)
+            if world > 1:
+                if symm is not None:
+                    symm.allreduce_sum_(G)
+                    s.copy_(m.sum); symm.allreduce_sum_(s)
+                else:
+                    dist.all_reduce(G); dist.all_reduce(m.sum)
+        for _ in range(args.warmup):
+            step()
+        barrier()
+        _native.reset_launches()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier(); e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record(); barrier()
+        ms, out = _finish(args, rank, world, dev, e0.elapsed_time(e1), {})
+        if rank == 0:
+            out.update({"metric": "gram_s_per_pass", "value": ms / 1e3, "unit": "s/pass", "higher_is_better": False,
+                        "scaling": "weak", "dtype": "tf32",
+                        "config": {"model": "covariance/PCA/linreg partial results + allreduce (BASELINE config 5)",
+                                   "rows_per_gpu": n, "dim": d, "parallelism": f"dp{world}",
+                                   "l2": "X (25.6 GB per GPU) exceeds L2"},
+                        "tflops_tf32_aggregate": 2.0 * n * world * d * d / (ms / 1e3) / 1e12})
+            print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0

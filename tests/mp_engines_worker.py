@@ -1,0 +1,64 @@
+"""torchrun worker (GPU, NCCL): the rotation engines with the NVLink symmetric workspace."""
+import math
+import os
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import torch
+import torch.distributed as dist
+
+
+def main():
+    rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"]); lr = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr); dev = torch.device("cuda", lr)
+    dist.init_process_group("nccl", device_id=dev)
+    from harp_b200.parallel.symm import SymmetricWorkspace
+    from harp_b200.models.mfsgd import MFSGDEngine
+    from harp_b200.models.lda import LDAEngine
+    ws = SymmetricWorkspace(dev, 512 << 20)
+    # ---- MF-SGD ----
+    g = torch.Generator(device=dev).manual_seed(1 + rank)
+    nr, nc, nnz, rk = 20000, 3000, 600000, 64
+    Wt = torch.randn(nr, 8, device=dev, generator=g) / math.sqrt(8)
+    Ht = torch.randn(nc, 8, device=dev, generator=torch.Generator(device=dev).manual_seed(77)) / math.sqrt(8)
+    r = torch.randint(0, nr, (nnz,), device=dev, generator=g); c = torch.randint(0, nc, (nnz,), device=dev, generator=g)
+    v = (Wt[r] * Ht[c]).sum(1) * 2 + 3
+    eng = MFSGDEngine(r, c, v, nr, nc, rk, 0.01, 0.02, symm=ws, seed=5)
+    e0 = eng.rmse(r, c, v)
+    for it in range(12):
+        n = eng.epoch()
+        assert int(n.item()) == nnz, (int(n.item()), nnz)
+    eng.synchronize()
+    e1 = eng.rmse(r, c, v)
+    assert e1 < 0.5 * e0, (e0, e1)
+    assert eng.rot[0] % world == 0 and eng.rot[1] % world == 0
+    ids = torch.cat([x[0] for x in eng.home_H().values()])
+    assert bool((ids % world == rank).all())                       # shards are home again
+    # ---- LDA ----
+    D, V, K, L = 3000, 2000, 64, 50
+    docs = torch.arange(D, device=dev).repeat_interleave(L)
+    words = (torch.rand(D * L, device=dev, generator=g) ** 2 * V).long() % V
+    lda = LDAEngine(docs, words, D, V, K, 0.1, 0.01, symm=ws, seed=2)
+    assert int(lda.topic_sums.sum()) == D * L * world
+    ll0 = lda.log_likelihood()
+    for it in range(8):
+        n = lda.iterate()
+        assert int(n.item()) == D * L
+    lda.synchronize()
+    ll1 = lda.log_likelihood()
+    assert ll1 > ll0, (ll0, ll1)
+    assert int(lda.topic_sums.sum()) == D * L * world and int(lda.n_dk.sum()) == D * L
+    tot = torch.zeros(1, dtype=torch.int64, device=dev)
+    for k in range(2):
+        tot += lda.Wbuf[k][lda.cur[k]].sum()
+    dist.all_reduce(tot)
+    assert int(tot.item()) == D * L * world
+    dist.barrier()
+    if rank == 0:
+        print(f"ENGINES_OK world={world} sgd_rmse {e0:.4f}->{e1:.4f} lda_ll {ll0:.4e}->{ll1:.4e}", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

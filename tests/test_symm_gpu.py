@@ -23,3 +23,15 @@ def test_symm_collectives_multi_gpu(native_built, backend):
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     sys.stdout.write(res.stdout[-4000:]); sys.stderr.write(res.stderr[-4000:])
     assert res.returncode == 0 and "SYMM_OK" in res.stdout
+
+
+def test_rotation_engines_multi_gpu(native_built):
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = 2 if n < 4 else 4
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", "29534", str(ROOT / "tests" / "mp_engines_worker.py")]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=400)
+    sys.stdout.write(res.stdout[-3000:]); sys.stderr.write(res.stderr[-3000:])
+    assert res.returncode == 0 and "ENGINES_OK" in res.stdout
