@@ -64,3 +64,46 @@ def test_kmeans_rotation_matches_regroup_allgather(tmp_path):
     ca = F.read_centroids_text(str(a / "centroids" / "out" / "output"), 12)
     cb = F.read_centroids_text(str(b / "centroids" / "out" / "output"), 12)
     np.testing.assert_allclose(ca, cb, rtol=1e-9, atol=1e-9)
+
+
+def test_secondary_apps_end_to_end(tmp_path):
+    """PageRank, iterative SVM, MLR, LDA-CVB (static + push/pull), NN, random forest, subgraph counting
+    (allgather + SAHAD rotation), WDA-MDS and the SGX-cost-model K-means on generated inputs, 2 workers."""
+    out = _torchrun(2, [str(ROOT / "tests" / "mp_apps_worker.py"), str(tmp_path)], timeout=900)
+    assert "APPS_OK 2" in out
+
+
+def test_mf_sgd_and_ccd_launchers(tmp_path):
+    from harp_b200.io import datagen, formats as F
+    r, c, v = datagen.synth_ratings(300, 120, 9000, rank=4, seed=1, noise=0.05)
+    (tmp_path / "train").mkdir(); (tmp_path / "test").mkdir()
+    idx = np.arange(9000)
+    for k, part in enumerate(np.array_split(idx[:8000], 4)):
+        F.write_coo(str(tmp_path / "train" / f"part_{k}"), r[part], c[part], v[part])
+    F.write_coo(str(tmp_path / "test" / "part_0"), r[8000:], c[8000:], v[8000:])
+    out = _torchrun(2, ["-m", "harp_b200.launch.sgd", str(tmp_path / "train"), "8", "0.05", "0.02", "25", "100", "2", "1", "2",
+                        "2000", str(tmp_path / "work"), str(tmp_path / "test")])
+    rmse = float(open(tmp_path / "work" / "model" / "evaluation").read())
+    assert rmse < 0.5 * float(np.std(v)), rmse
+    ids, W = F.read_mf_model(str(tmp_path / "work" / "model" / "W-0"))
+    assert W.shape[1] == 8 and len(ids) > 50 and (tmp_path / "work" / "model" / "H-1").exists()
+    out = _torchrun(2, ["-m", "harp_b200.launch.ccd", str(tmp_path / "train"), "8", "0.05", "6", "2", "1", "2000",
+                        str(tmp_path / "workc"), str(tmp_path / "test")])
+    rmse_c = float(open(tmp_path / "workc" / "model" / "evaluation").read())
+    assert rmse_c < 0.7 * float(np.std(v)), rmse_c
+
+
+def test_lda_launcher(tmp_path):
+    from harp_b200.io import datagen
+    datagen.generate_corpus_files(60, 50, 3, 25, 4, str(tmp_path / "docs"), seed=2)
+    out = _torchrun(2, ["-m", "harp_b200.launch.lda", str(tmp_path / "docs"), "3", "0.1", "0.01", "8", "100", "100", "2", "1", "2",
+                        "2000", str(tmp_path / "work"), "true", "--print_interval=4"])
+    ll = float(open(tmp_path / "work" / "model" / "evaluation").read())
+    assert ll < 0 and (tmp_path / "work" / "model" / "tmp_word_model" / "8" / "0").exists()
+
+
+def test_daal_launcher_matches_numpy(tmp_path):
+    from harp_b200.io import datagen
+    datagen.generate_dense_csv(400, 8, 4, str(tmp_path / "cov"), seed=0)
+    out = _torchrun(2, ["-m", "harp_b200.launch.daal", "cov", "2", "2", "2000", "1", str(tmp_path / "cov"), str(tmp_path / "work"), "8"])
+    assert "Harp-DAAL cov finished" in out and "cov.covariance:" in out
