@@ -31,7 +31,8 @@ class LDAEngine:
         self.cap = max(1, (self.V + 2 * N - 1) // (2 * N))
         if self.dev.type == "cuda":
             sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
-            self.B = int(blocks) if blocks else min(L.max_blocks(self.K), sms)
+            from ..ops.mf import auto_blocks
+            self.B = int(blocks) if blocks else auto_blocks(docs.numel() / (2.0 * N), min(L.max_blocks(self.K), sms), per_block=32)
         else:
             self.B = int(blocks) if blocks else 2
         self.seed = int(seed)

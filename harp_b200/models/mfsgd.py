@@ -40,7 +40,7 @@ class MFSGDEngine:
         if self.dev.type == "cuda":
             mx = mf.max_blocks(self.rank_k)
             sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
-            self.B = int(blocks) if blocks else min(mx, 2 * sms)
+            self.B = int(blocks) if blocks else mf.auto_blocks(rows.numel() / (2.0 * N), min(mx, 2 * sms))
         else:
             self.B = int(blocks) if blocks else 4
         g = torch.Generator(device=self.dev).manual_seed(seed + 7919 * self.me)

@@ -50,7 +50,15 @@ def max_blocks(rank: int) -> int:
     return int(lib.hb_sgd_max_blocks(rank))
 
 
-def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: int, max_run: int = 32) -> SgdPanel:
+def auto_blocks(nnz_per_panel: float, limit: int, per_block: int = 64) -> int:
+    """Blocks per side for a panel: a pass costs ~B hand-overs plus nnz/(B * warps) updates, so small panels
+    want fewer, fatter blocks; capped by what one cooperative launch keeps resident."""
+    import math
+    return int(max(8, min(limit, math.isqrt(max(1, int(nnz_per_panel / per_block))))))
+
+
+def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: int, max_run: int = 32,
+                hot_spread: bool = True) -> SgdPanel:
     """Buckets a COO rating list (worker-local row ids, slice-local column ids).  Row block = row % B,
     column block = col % B; inside a block ratings are ordered by column (then by original order).
     Column runs longer than ``max_run`` are cut into sub-runs (flagged in bit 31 of ``seg_col``) so that a
@@ -64,8 +72,24 @@ def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: i
         e = torch.zeros(0, dtype=torch.int32, device=dev)
         return SgdPanel(B, z, e, torch.zeros(1, dtype=torch.int32, device=dev), e,
                         torch.zeros(0, dtype=torch.float32, device=dev), torch.zeros(B, dtype=torch.int32, device=dev))
-    blk = (rows % B) * B + (cols % B)
     ncols = int(cols.max().item()) + 1
+    # Hot columns (a blockbuster item, a stop word): if all their ratings sat in ONE column-block, that
+    # heavy block would be handed round the ring through all B CTAs one after the other.  Their ratings
+    # are dealt round-robin over all column-blocks instead; every run of such a column is flagged shared
+    # (bit 31), i.e. its updates are merged with atomics, since several CTAs now work on it at once.
+    cnt = torch.bincount(cols, minlength=ncols)
+    hot_thr = max(4 * max_run if max_run else 256, n // (4 * B) if hot_spread else n + 1)
+    hot_col = cnt > hot_thr if hot_spread else torch.zeros(ncols, dtype=torch.bool, device=dev)
+    cb = cols % B
+    if bool(hot_col.any()):
+        order_c = torch.argsort(cols, stable=True)
+        first = torch.zeros(ncols + 1, dtype=torch.int64, device=dev)
+        first[1:] = torch.cumsum(cnt, 0)
+        rank_in_col = torch.empty(n, dtype=torch.int64, device=dev)
+        rank_in_col[order_c] = torch.arange(n, device=dev) - first[cols[order_c]]
+        is_hot = hot_col[cols]
+        cb = torch.where(is_hot, (cols + rank_in_col) % B, cb)
+    blk = (rows % B) * B + cb
     key = blk * ncols + cols
     order = torch.argsort(key, stable=True)
     key_s = key[order]
@@ -82,6 +106,7 @@ def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: i
         uniq, counts = uniq[rep], sub_counts
     else:
         split_flag = torch.zeros(uniq.numel(), dtype=torch.bool, device=dev)
+    split_flag = split_flag | hot_col[uniq % ncols]
     seg_ptr = torch.zeros(uniq.numel() + 1, dtype=torch.int64, device=dev)
     seg_ptr[1:] = torch.cumsum(counts, 0)
     seg_blk = uniq // ncols
