@@ -68,8 +68,13 @@ enum : int {
 // ----------------------------------------------------------------------------
 // prep: ‖c‖² (padded with +inf to a multiple of BN), zero the accumulators
 // ----------------------------------------------------------------------------
+// tf32 keeps 10 explicit mantissa bits: clearing the low 13 makes the value exactly representable, so the
+// tensor core's own truncation of it is the identity
+__device__ __forceinline__ float tf32_trunc(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+
 __global__ void prep_kernel(const float* __restrict__ C, int k, int d, int kpad,
-                            float* __restrict__ cn, float* __restrict__ sums,
+                            float* __restrict__ cn, float* __restrict__ cn_ext, float* __restrict__ ones_ext,
+                            float* __restrict__ sums,
                             float* __restrict__ counts, double* __restrict__ obj, int zero_acc) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -86,6 +91,25 @@ __global__ void prep_kernel(const float* __restrict__ C, int k, int d, int kpad,
       for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     }
     if (lane == 0) cn[j] = s;
+    if (cn_ext != nullptr && lane < 8) {
+      // row j of the extra GEMM operand: -‖c‖²/2 as an exact sum of three tf32 numbers (hi, mid, lo);
+      // with the matching A row [1,1,1,0,...] one more K=8 MMA step turns the accumulator into
+      // x·c - ‖c‖²/2, whose arg-MAX is the nearest centroid.  Padding rows get a huge negative bias.
+      float v = 0.f;
+      if (j >= k) { v = (lane == 0) ? -3.0e38f : 0.f; v = tf32_trunc(v); }
+      else {
+        const float t0 = -0.5f * s;
+        const float hi = tf32_trunc(t0);
+        const float mid = tf32_trunc(t0 - hi);
+        const float lo = tf32_trunc(t0 - hi - mid);
+        v = lane == 0 ? hi : (lane == 1 ? mid : (lane == 2 ? lo : 0.f));
+      }
+      cn_ext[(size_t)j * 8 + lane] = v;
+    }
+  }
+  if (ones_ext != nullptr) {
+    const int tid0 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid0 < 128 * 8) ones_ext[tid0] = ((tid0 & 7) < 3) ? 1.0f : 0.0f;
   }
   if (zero_acc) {
     const size_t tid = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -368,14 +392,18 @@ namespace pair {
 constexpr int NTHREADS2 = 320;                   // warps 0..7 epilogue, warp 8 TMA, warp 9 MMA
 constexpr int NSTAGE2 = 5;
 constexpr int NCN = 8;                           // ‖c‖² ring slots (decoupled from the 2 accumulators)
+constexpr int NEXT = 3;                          // ring slots of the 4 KB GEMM-extension operand (EXT kernels)
+constexpr int EXT_BYTES = 128 * 8 * 4;           // 128 rows x 8 floats (one tf32 K step), SWIZZLE_32B
 constexpr int BH = BN / 2;                        // centroid rows each CTA loads
 constexpr int B_HALF_BYTES = BH * BK * 4;         // 16 KB
 constexpr int X_TILE_BYTES = MAX_KCH * X_CHUNK_BYTES;  // 64 KB
 struct Smem {
   static constexpr int x = 0;                                   // 2 x 64 KB
   static constexpr int b = x + 2 * X_TILE_BYTES;                // NSTAGE2 x 16 KB
-  static constexpr int cn = b + NSTAGE2 * B_HALF_BYTES;         // NCN x 1 KB
-  static constexpr int bars = cn + NCN * CN_BYTES;
+  static constexpr int cn = b + NSTAGE2 * B_HALF_BYTES;         // NCN x 1 KB  |  EXT: A_ext + NEXT x B_ext
+  static constexpr int aext = cn;
+  static constexpr int bext = cn + EXT_BYTES;
+  static constexpr int bars = cn + 16384;
   static constexpr int tmem_slot = bars + 48 * 8;
   static constexpr int merge = tmem_slot + 16;                  // 128 x 4 B hand-over between warp halves
   static constexpr int total = merge + 128 * 4;
@@ -388,16 +416,43 @@ enum : int {
   B_EMPTY = B_FULL + NSTAGE2,   // NSTAGE2, both
   T_FULL = B_EMPTY + NSTAGE2,   // 2, both
   T_EMPTY = T_FULL + 2,         // 2, leader (8 arrivals: 4 epilogue warps x 2 CTAs)
-  CN_FULL = T_EMPTY + 2,        // NCN, local
-  CN_EMPTY = CN_FULL + NCN,     // NCN, local (8 arrivals)
-  NBARS = CN_EMPTY + NCN
+  CN_FULL = T_EMPTY + 2,        // NCN, local            | EXT: BX_FULL (leader) in the first NEXT slots
+  CN_EMPTY = CN_FULL + NCN,     // NCN, local (8 arrivals)| EXT: BX_EMPTY (both)
+  AEXT_FULL = CN_EMPTY + NCN,   // EXT: the constant A_ext tiles of both CTAs have landed (leader)
+  NBARS = AEXT_FULL + 1
 };
+static_assert(NCN * CN_BYTES <= 16384 && EXT_BYTES * (1 + NEXT) <= 16384, "cn / ext region is 16 KB");
 static_assert(NBARS <= 48, "barrier area too small");
 }  // namespace pair
 
-template <int DBG>
+// K-major operand in the SWIZZLE_32B layout (32-byte rows = one tf32 K step, 8-row groups 256 B apart).
+__device__ __forceinline__ uint64_t umma_desc_kmajor_sw32(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>(256 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(6) << 61;             // SWIZZLE_32B
+  return d;
+}
+
+// Arg-max counterpart of packed_min32 for the EXT kernels (accumulator already holds x·c - ‖c‖²/2).
+__device__ __forceinline__ float packed_max32(const uint32_t (&v)[32]) {
+  float key[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) key[j] = __uint_as_float(__byte_perm(v[j], (uint32_t)j, 0x3214));
+#pragma unroll
+  for (int w = 16; w > 0; w >>= 1) {
+#pragma unroll
+    for (int j = 0; j < w; ++j) key[j] = fmaxf(key[j], key[j + w]);
+  }
+  return key[0];
+}
+
+template <int DBG, int EXT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(pair::NTHREADS2, 1)
 assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_c,
+                      const __grid_constant__ CUtensorMap tmap_ones, const __grid_constant__ CUtensorMap tmap_cext,
                       const float* __restrict__ X, const float* __restrict__ C,
                       const float* __restrict__ cn_pad, long long n, int d, int k, int kpad,
                       float* __restrict__ sums, float* __restrict__ counts, int* __restrict__ assign,
@@ -434,8 +489,9 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
     }
     for (int i = 0; i < NCN; ++i) {
       mbar_init(bar(CN_FULL + i), 1);
-      mbar_init(bar(CN_EMPTY + i), 8);
+      mbar_init(bar(CN_EMPTY + i), EXT ? 1 : 8);
     }
+    mbar_init(bar(AEXT_FULL), 1);
     for (int s = 0; s < NSTAGE2; ++s) {
       mbar_init(bar(B_FULL + s), 1);
       mbar_init(bar(B_EMPTY + s), 1);
@@ -461,6 +517,10 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
       const uint64_t pol_keep = policy_evict_last();
       const uint64_t pol_stream = policy_evict_first();
       uint32_t it = 0, ga = 0, gp = 0;
+      if (EXT) {      // the constant [1,1,1,0..] operand rows, once per CTA
+        if (leader) mbar_expect_tx(bar(AEXT_FULL), 2 * EXT_BYTES);
+        tma_load_2d_2sm(base + Smem::aext, &tmap_ones, bar(AEXT_FULL) & kPeerBitMask, 0, 0, pol_keep);
+      }
       for (long long tp = cluster_id; tp < npairs; tp += nclusters, ++gp) {
         const uint32_t xb = gp & 1, xph = (gp >> 1) & 1;
         mbar_wait(bar(X_EMPTY + xb), xph ^ 1);
@@ -473,12 +533,19 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           // ‖c‖² tile -> its own 8-deep ring: with only as many slots as accumulators this
           // prefetch would be gated on the epilogue of tile ct-2 and epilogue + TMA latency
           // would sit on the tensor core's critical path.
-          {
+          if (!EXT) {
             const uint32_t cs = ga % NCN, cph = (ga / NCN) & 1;
             mbar_wait(bar(CN_EMPTY + cs), cph ^ 1);
             mbar_expect_tx(bar(CN_FULL + cs), CN_BYTES);
             bulk_load_1d(base + Smem::cn + cs * CN_BYTES, cn_pad + (size_t)ct * BN, CN_BYTES,
                          bar(CN_FULL + cs));
+          } else {
+            // EXT: this CTA's 128 rows of the [-‖c‖²/2 hi|mid|lo] operand for centroid tile ct
+            const uint32_t es = ga % NEXT, eph = (ga / NEXT) & 1;
+            mbar_wait(bar(CN_EMPTY + es), eph ^ 1);
+            if (leader) mbar_expect_tx(bar(CN_FULL + es), 2 * EXT_BYTES);
+            tma_load_2d_2sm(base + Smem::bext + es * EXT_BYTES, &tmap_cext, bar(CN_FULL + es) & kPeerBitMask,
+                            0, ct * BN + (int)cta * BH, pol_keep);
           }
           for (int kc = 0; kc < kch; ++kc, ++it) {
             const uint32_t s = it % NSTAGE2, ph = (it / NSTAGE2) & 1;
@@ -491,10 +558,17 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
       }
     }
   } else if (warp == MMA_WARP) {
-    // ===================== MMA issuer (leader CTA, one thread) =====================
-    if (leader && lane == 0) {
+    // ===================== MMA issuer (leader CTA) =====================
+    // The whole warp walks the loop converged and one elected lane issues: descriptors stay
+    // warp-uniform, so the compiler keeps them in uniform registers instead of emitting an
+    // ELECT / R2UR.BROADCAST loop per tcgen05 instruction.  The issue latency of a tile sits
+    // on the epilogue -> issuer -> tensor pipe -> epilogue chain, so every instruction counts.
+    if (leader) {
       const uint32_t idesc = umma_idesc_tf32(2 * BM, BN);
+      const uint64_t dhi = umma_desc_kmajor_sw128(0);          // address-free part of the descriptor
       uint32_t it = 0, ga = 0, gp = 0;
+      long long prof_issue = 0, prof_n = 0;
+      if (EXT) mbar_wait(bar(AEXT_FULL), 0);
       for (long long tp = cluster_id; tp < npairs; tp += nclusters, ++gp) {
         const uint32_t xb = gp & 1, xph = (gp >> 1) & 1;
         mbar_wait(bar(X_FULL + xb), xph);
@@ -502,26 +576,48 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
           const uint32_t a = ga & 1, aph = (ga >> 1) & 1;
           mbar_wait_cluster(bar(T_EMPTY + a), aph ^ 1);
           tc_fence_after();
+          long long t0 = 0;
+          if (dbg & 16) t0 = clock64();
           const uint32_t tmem_d = tmem_base + a * BN;
           for (int kc = 0; kc < kch; ++kc, ++it) {
             const uint32_t s = it % NSTAGE2, ph = (it / NSTAGE2) & 1;
             mbar_wait(bar(B_FULL + s), ph);
             tc_fence_after();
-            const uint32_t a_addr = base + Smem::x + xb * X_TILE_BYTES + kc * X_CHUNK_BYTES;
-            const uint32_t b_addr = base + Smem::b + s * B_HALF_BYTES;
+            const uint64_t da0 = dhi | (((base + Smem::x + xb * X_TILE_BYTES + kc * X_CHUNK_BYTES) & 0x3FFFFu) >> 4);
+            const uint64_t db0 = dhi | (((base + Smem::b + s * B_HALF_BYTES) & 0x3FFFFu) >> 4);
             int ksteps = (d - kc * BK + UK - 1) / UK;
             if (ksteps > BK / UK) ksteps = BK / UK;
-            for (int j = 0; j < ksteps; ++j) {
-              const uint64_t da = umma_desc_kmajor_sw128(a_addr + j * UK * 4);
-              const uint64_t db = umma_desc_kmajor_sw128(b_addr + j * UK * 4);
-              umma_tf32_2sm(tmem_d, da, db, idesc, (kc | j) != 0 ? 1u : 0u);
+            if (elect_one()) {
+#pragma unroll
+              for (int j = 0; j < BK / UK; ++j)
+                if (j < ksteps)
+                  umma_tf32_2sm(tmem_d, da0 + (uint64_t)(j * UK * 4 / 16), db0 + (uint64_t)(j * UK * 4 / 16), idesc,
+                                (kc | j) != 0 ? 1u : 0u);
+              umma_commit_2sm_mc(bar(B_EMPTY + s), 0x3);     // frees the stage in both CTAs
             }
-            umma_commit_2sm_mc(bar(B_EMPTY + s), 0x3);     // frees the stage in both CTAs
+            __syncwarp();
           }
-          umma_commit_2sm_mc(bar(T_FULL + a), 0x3);          // accumulators ready in both CTAs
+          if (EXT) {   // one more K=8 step: accumulator += [1,1,1,0..] · [-‖c‖²/2 hi,mid,lo,0..]ᵀ
+            const uint32_t es = ga % NEXT, eph = (ga / NEXT) & 1;
+            mbar_wait(bar(CN_FULL + es), eph);
+            tc_fence_after();
+            if (elect_one()) {
+              umma_tf32_2sm(tmem_d, umma_desc_kmajor_sw32(base + Smem::aext),
+                            umma_desc_kmajor_sw32(base + Smem::bext + es * EXT_BYTES), idesc, 1u);
+              umma_commit_2sm_mc(bar(CN_EMPTY + es), 0x3);
+              umma_commit_2sm_mc(bar(T_FULL + a), 0x3);        // accumulators ready in both CTAs
+            }
+          } else if (elect_one()) {
+            umma_commit_2sm_mc(bar(T_FULL + a), 0x3);
+          }
+          __syncwarp();
+          if (dbg & 16) { prof_issue += clock64() - t0; ++prof_n; }
         }
-        umma_commit_2sm_mc(bar(X_EMPTY + xb), 0x3);
+        if (elect_one()) umma_commit_2sm_mc(bar(X_EMPTY + xb), 0x3);
+        __syncwarp();
       }
+      if ((dbg & 16) && lane == 0 && blockIdx.x < 2 && prof_n > 0)
+        printf("prof cta %d issuer: tiles %lld issue/tile %lld cycles\n", blockIdx.x, prof_n, prof_issue / prof_n);
     }
   } else {
     // ===================== Epilogue warps (both CTAs) =====================
@@ -535,7 +631,9 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
     double obj_local = 0.0;
     long long prof_wait = 0, prof_work = 0, prof_n = 0;
     for (long long tp = cluster_id; tp < npairs; tp += nclusters) {
+      // !EXT: best = min of ‖c‖² - 2 x·c;  EXT: best = -(max of x·c - ‖c‖²/2), kept negated so the merge below is shared
       float best = CUDART_INF_F;
+      float bestx = -CUDART_INF_F;
       int bi = 0;
       for (int ct = 0; ct < nct; ++ct, ++ga) {
         const uint32_t a = ga & 1, aph = (ga >> 1) & 1;
@@ -544,12 +642,35 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
         const float4* cng = reinterpret_cast<const float4*>(smem_raw + Smem::cn + cs * CN_BYTES) + h * (BN / 8);
         long long tw0 = 0;
         if (dbg & 16) tw0 = clock64();
-        mbar_wait(bar(CN_FULL + cs), cph);
+        if (!EXT) mbar_wait(bar(CN_FULL + cs), cph);
         mbar_wait(bar(T_FULL + a), aph);
         if (dbg & 16) { const long long now = clock64(); prof_wait += now - tw0; tw0 = now; }
         tc_fence_after();
         const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + a * BN + h * (BN / 2);
-        if (!(dbg & 1)) {
+        const bool skip_math = ((dbg & 32) && !leader) || ((dbg & 64) && leader);
+        if (EXT == 2 && !(dbg & 1) && !skip_math) {
+          // one TMEM load per warp per tile: all 128 columns of this warp's half at once
+          uint32_t v[128];
+          tmem_ld_32x128(taddr, v);
+          tmem_ld_wait_regs128(v);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(bar(T_EMPTY + a), 0);     // accumulator free as soon as it is in registers
+          float key[128];
+#pragma unroll
+          for (int j = 0; j < 128; ++j) key[j] = __uint_as_float(__byte_perm(v[j], (uint32_t)j, 0x3214));
+#pragma unroll
+          for (int w = 64; w > 0; w >>= 1) {
+#pragma unroll
+            for (int j = 0; j < w; ++j) key[j] = fmaxf(key[j], key[j + w]);
+          }
+          const bool gt = key[0] > bestx;
+          bestx = gt ? key[0] : bestx;
+          bi = gt ? tbase : bi;
+          if (dbg & 16) { prof_work += clock64() - tw0; ++prof_n; }
+          continue;
+        }
+        if (!(dbg & 1) && !skip_math) {
           uint32_t va[32], vb[32];
           tmem_ld_32x32(taddr, va);
 #pragma unroll
@@ -557,7 +678,12 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
             tmem_ld_wait_regs(va);
             tmem_ld_32x32(taddr + (c + 1) * 32, vb);
             if (dbg & 2) { best = fminf(best, __uint_as_float(va[0]) + __uint_as_float(va[31])); } else
-            {
+            if (EXT) {
+              const float m = packed_max32(va);
+              const bool gt = m > bestx;
+              bestx = gt ? m : bestx;
+              bi = gt ? tbase + c * 32 : bi;
+            } else {
               const float m = packed_min32<(DBG & 8) != 0>(va, cng + c * 8);
               const bool lt = m < best;
               best = lt ? m : best;
@@ -565,8 +691,19 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
             }
             tmem_ld_wait_regs(vb);
             if (c + 2 < CH) tmem_ld_32x32(taddr + (c + 2) * 32, va);
+            else {
+              // last chunk is in registers: hand the accumulator back before doing its math
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive_cluster(bar(T_EMPTY + a), 0);
+            }
             if (dbg & 2) { best = fminf(best, __uint_as_float(vb[0]) + __uint_as_float(vb[31])); } else
-            {
+            if (EXT) {
+              const float m = packed_max32(vb);
+              const bool gt = m > bestx;
+              bestx = gt ? m : bestx;
+              bi = gt ? tbase + (c + 1) * 32 : bi;
+            } else {
               const float m = packed_min32<(DBG & 8) != 0>(vb, cng + (c + 1) * 8);
               const bool lt = m < best;
               best = lt ? m : best;
@@ -574,16 +711,20 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
             }
           }
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) {
-          mbar_arrive(bar(CN_EMPTY + cs));                 // local ‖c‖² slot
-          mbar_arrive_cluster(bar(T_EMPTY + a), 0);        // accumulator slot, tracked by the leader
+        if ((dbg & 1) || skip_math) {                     // (debug paths skip the loop that hands it back)
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(bar(T_EMPTY + a), 0);
+        }
+        if (!EXT) {
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar(CN_EMPTY + cs));   // local ‖c‖² slot
         }
         if (dbg & 16) { prof_work += clock64() - tw0; ++prof_n; }
       }
       // unpack the in-chunk column, then merge the two column halves of each row through smem
-      bi += (int)(__float_as_uint(best) & 255u);
+      if (EXT) { bi += (int)(__float_as_uint(bestx) & 255u); best = -bestx; }
+      else bi += (int)(__float_as_uint(best) & 255u);
       // (512 B of smem: best goes over first, then the index, then the verdict comes back)
       const int slot = q * 32 + lane;
       if (h == 1) merge[slot] = best;
@@ -700,10 +841,21 @@ using namespace hb::kmeans;
 
 extern "C" {
 
+// Scratch layout: [ ‖c‖² : kpad floats | pad to 256 B ][ -‖c‖²/2 as 3 tf32 terms : kpad x 8 floats ][ ones : 128 x 8 ].
+// The first part alone (hb_kmeans_min_workspace_bytes) is enough for the single-CTA kernel; a caller that
+// provides only that much gets that kernel.
+static size_t ws_base_bytes(int k) {
+  const size_t kpad = ((size_t)k + BN - 1) / BN * BN;
+  return kpad * sizeof(float) + 256;
+}
+size_t hb_kmeans_min_workspace_bytes(int k, int d) {
+  (void)d;
+  return ws_base_bytes(k);
+}
 size_t hb_kmeans_workspace_bytes(int k, int d) {
   const size_t kpad = ((size_t)k + BN - 1) / BN * BN;
   (void)d;
-  return kpad * sizeof(float) + 256;
+  return ws_base_bytes(k) + kpad * 8 * sizeof(float) + 128 * 8 * sizeof(float);
 }
 
 int hb_kmeans_tc_supported(int d, int k) { return (d % 4 == 0 && d >= 4 && d <= BK * MAX_KCH && k >= 1) ? 1 : 0; }
@@ -714,12 +866,14 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
   cudaStream_t stream = (cudaStream_t)stream_;
   HB_REQUIRE(n >= 0 && d >= 1 && k >= 1, "hb_kmeans_step: bad shape n=%lld d=%d k=%d", n, d, k);
   const int kpad = (k + BN - 1) / BN * BN;
-  HB_REQUIRE(workspace != nullptr && workspace_bytes >= hb_kmeans_workspace_bytes(k, d),
-             "hb_kmeans_step: workspace too small (%zu < %zu)", workspace_bytes,
-             hb_kmeans_workspace_bytes(k, d));
+  HB_REQUIRE(workspace != nullptr && workspace_bytes >= ws_base_bytes(k),
+             "hb_kmeans_step: workspace too small (%zu < %zu)", workspace_bytes, ws_base_bytes(k));
+  const bool have_ext = workspace_bytes >= hb_kmeans_workspace_bytes(k, d);
   HB_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0,
              "hb_kmeans_step: workspace must be 256-byte aligned");
   float* cn = reinterpret_cast<float*>(workspace);
+  float* cn_ext = have_ext ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + ws_base_bytes(k)) : nullptr;
+  float* ones_ext = have_ext ? cn_ext + (size_t)kpad * 8 : nullptr;
   const bool force_simt = (flags & HB_KMEANS_FORCE_SIMT) != 0;
   const bool zero_acc = (flags & HB_KMEANS_NO_ZERO) == 0;
   const bool use_tc = !force_simt && hb_kmeans_tc_supported(d, k) &&
@@ -733,7 +887,7 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
     const int cap = sm_count() * 8;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    prep_kernel<<<blocks, threads, 0, stream>>>(C, k, d, kpad, cn, sums, counts, obj, zero_acc ? 1 : 0);
+    prep_kernel<<<blocks, threads, 0, stream>>>(C, k, d, kpad, cn, cn_ext, ones_ext, sums, counts, obj, zero_acc ? 1 : 0);
     HB_CUDA_OK(cudaGetLastError());
   }
   if (n == 0) return 0;
@@ -757,15 +911,22 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
                            CU_TENSOR_MAP_SWIZZLE_128B) != 0)
         return -3;
       const int dbg = (flags >> 8) & 0xff;
-      auto kern = assign_tc_pair_kernel<0>;
-      if (dbg == 1) kern = assign_tc_pair_kernel<1>;
-      else if (dbg == 2) kern = assign_tc_pair_kernel<2>;
-      else if (dbg == 4) kern = assign_tc_pair_kernel<4>;
-      else if (dbg == 7) kern = assign_tc_pair_kernel<7>;
-      else if (dbg == 6) kern = assign_tc_pair_kernel<6>;
-      else if (dbg == 12) kern = assign_tc_pair_kernel<12>;
-      else if (dbg == 16) kern = assign_tc_pair_kernel<16>;
-      else if (dbg == 23) kern = assign_tc_pair_kernel<23>;
+      // EXT (default when the workspace holds the extension operands): ‖c‖² folded into the GEMM
+      const bool ext = have_ext && (flags & HB_KMEANS_NO_EXT) == 0;
+      const bool ext128 = ext && (flags & HB_KMEANS_EXT_X128) != 0;
+      CUtensorMap tones = tch, tcext = tch;
+      if (ext) {
+        if (make_tmap_2d_f32(&tones, ones_ext, 128, 8, 32, 128, 8, CU_TENSOR_MAP_SWIZZLE_32B) != 0) return -3;
+        if (make_tmap_2d_f32(&tcext, cn_ext, (uint64_t)kpad, 8, 32, BN / 2, 8, CU_TENSOR_MAP_SWIZZLE_32B) != 0) return -3;
+      }
+      auto kern = ext128 ? assign_tc_pair_kernel<0, 2> : (ext ? assign_tc_pair_kernel<0, 1> : assign_tc_pair_kernel<0, 0>);
+      if (dbg == 1) kern = assign_tc_pair_kernel<1, 0>;
+      else if (dbg == 2) kern = assign_tc_pair_kernel<2, 0>;
+      else if (dbg == 4) kern = ext ? assign_tc_pair_kernel<4, 1> : assign_tc_pair_kernel<4, 0>;
+      else if (dbg == 7) kern = assign_tc_pair_kernel<7, 0>;
+      else if (dbg == 36) kern = assign_tc_pair_kernel<36, 1>;
+      else if (dbg == 68) kern = assign_tc_pair_kernel<68, 1>;
+      else if (dbg == 16) kern = ext128 ? assign_tc_pair_kernel<16, 2> : (ext ? assign_tc_pair_kernel<16, 1> : assign_tc_pair_kernel<16, 0>);
       HB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::Smem::total));
       const long long npairs = (n + 2 * BM - 1) / (2 * BM);
       long long nclusters = sm_count() / 2;
@@ -775,7 +936,7 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
       }
       if (nclusters > npairs) nclusters = npairs;
       kern<<<(unsigned)(2 * nclusters), pair::NTHREADS2, pair::Smem::total, stream>>>(
-          tx, tch, X, C, cn, n, d, k, kpad, sums, counts, assign, obj);
+          tx, tch, tones, tcext, X, C, cn, n, d, k, kpad, sums, counts, assign, obj);
       HB_CUDA_OK(cudaGetLastError());
     } else {
       static bool attr_set[64] = {false};
@@ -911,9 +1072,10 @@ extern "C" int hb_kmeans_step_static(const float* X, long long n, int d, const f
              "(needs d %% 4 == 0 and d <= 128); use hb_kmeans_step",
              d);
   const size_t bytes = hb::kmeans::STATIC_SCRATCH_FLOATS * sizeof(float);
-  HB_REQUIRE(hb_kmeans_workspace_bytes(k, d) <= bytes,
+  HB_REQUIRE(hb_kmeans_min_workspace_bytes(k, d) <= bytes,
              "hb_kmeans_step_static: internal scratch too small for k=%d", k);
   float* scratch = nullptr;
   if (hb::kmeans::static_scratch_ptr(&scratch) != 0) return -1;
-  return hb_kmeans_step(X, n, d, C, k, sums, counts, assign, obj, scratch, bytes, 0, stream);
+  // 64 KiB of scratch holds ‖c‖² only, which is what the single-CTA tcgen05 kernel needs
+  return hb_kmeans_step(X, n, d, C, k, sums, counts, assign, obj, scratch, bytes, HB_KMEANS_SINGLE_CTA, stream);
 }

@@ -38,6 +38,8 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
     lib.hb_l2_flush.argtypes = [P, c_size_t, P]
     lib.hb_kmeans_workspace_bytes.restype = c_size_t
     lib.hb_kmeans_workspace_bytes.argtypes = [c_int, c_int]
+    lib.hb_kmeans_min_workspace_bytes.restype = c_size_t
+    lib.hb_kmeans_min_workspace_bytes.argtypes = [c_int, c_int]
     lib.hb_kmeans_simt_workspace_bytes.restype = c_size_t
     lib.hb_kmeans_simt_workspace_bytes.argtypes = [c_longlong, c_int, c_int]
     lib.hb_kmeans_tc_supported.argtypes = [c_int, c_int]

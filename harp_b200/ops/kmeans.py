@@ -99,8 +99,9 @@ def kmeans_step(
     need = workspace_bytes(n, k, d, simt)
     if workspace is None or workspace.numel() * workspace.element_size() < need:
         workspace = torch.empty((need + 255) // 256 * 256, dtype=torch.uint8, device=dev)
-    # variant: "auto"/"pair" = CTA-pair tcgen05 kernel, "single" = 1-CTA tcgen05 kernel
-    flags = (1 if simt else 0) | (2 if accumulate else 0) | (4 if variant == "single" else 0)
+    # variant: "auto"/"pair" = CTA-pair tcgen05 kernel (‖c‖² folded into the GEMM), "pair_noext" = CTA-pair with
+    # ‖c‖² added in the epilogue, "single" = 1-CTA tcgen05 kernel
+    flags = (1 if simt else 0) | (2 if accumulate else 0) | (4 if variant == "single" else 0) | (8 if variant == "pair_noext" else 0) | (16 if variant == "pair_x128" else 0)
     flags |= (int(os.environ.get("HB_KMEANS_DBG", "0")) & 0xff) << 8   # perf-triage switches (pair kernel)
     rc = lib.hb_kmeans_step(
         _native.ptr(X), n, d, _native.ptr(C), k, _native.ptr(sums), _native.ptr(counts),

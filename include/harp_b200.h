@@ -34,9 +34,14 @@ int hb_l2_flush(void* buf, size_t bytes, void* stream);
 #define HB_KMEANS_FORCE_SIMT 1 /* use the exact-fp32 SIMT kernel */
 #define HB_KMEANS_NO_ZERO 2    /* accumulate into sums/counts/obj instead of zeroing them */
 #define HB_KMEANS_SINGLE_CTA 4 /* use the 1-CTA tcgen05 kernel instead of the CTA-pair (cta_group::2) one */
+#define HB_KMEANS_NO_EXT 8     /* CTA-pair kernel: add ‖c‖² in the epilogue instead of folding it into the GEMM */
+#define HB_KMEANS_EXT_X128 16  /* CTA-pair kernel with folded ‖c‖²: one 128-column TMEM load per warp per tile (slower; kept for study) */
 
-/* Scratch the tensor-core path needs: ‖c‖² padded to a multiple of 256. */
+/* Scratch of the default (CTA-pair) tensor-core path: ‖c‖² padded to a multiple of 256, plus the
+ * -‖c‖²/2 GEMM-extension operand (3 tf32 terms per centroid) and a constant tile. */
 size_t hb_kmeans_workspace_bytes(int k, int d);
+/* Smallest workspace hb_kmeans_step accepts (‖c‖² only); with it the single-CTA kernel is used. */
+size_t hb_kmeans_min_workspace_bytes(int k, int d);
 /* Scratch for the SIMT path (adds per-point assignment + distance). */
 size_t hb_kmeans_simt_workspace_bytes(long long n, int k, int d);
 /* 1 when (d, k) is handled by the tcgen05 path (d % 4 == 0, d <= 128). */

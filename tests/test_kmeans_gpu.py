@@ -50,6 +50,16 @@ def test_kmeans_tc_single_cta_matches_reference(native_built, n, d, k):
     _check(n, d, k, force_simt=False, variant="single")
 
 
+@pytest.mark.parametrize("n,d,k", [(1000, 100, 10), (4096, 128, 512), (50000, 128, 3000)])
+def test_kmeans_tc_pair_noext_matches_reference(native_built, n, d, k):
+    _check(n, d, k, force_simt=False, variant="pair_noext")
+
+
+def test_kmeans_large_offset_data(native_built):
+    """Points far from the origin: ‖c‖² is large, so the hi/mid/lo split of the folded bias matters."""
+    _check(20000, 64, 200, force_simt=False, scale=100.0)
+
+
 @pytest.mark.parametrize("n,d,k", [(1000, 100, 10), (513, 37, 19), (2000, 130, 40)])
 def test_kmeans_simt_matches_reference(native_built, n, d, k):
     _check(n, d, k, force_simt=True)

@@ -42,10 +42,12 @@ def _run_both(lib, nat, n, d, k, seed):
             rc = lib.hb_kmeans_step_static(nat.ptr(X), n, d, nat.ptr(C), k, nat.ptr(sums), nat.ptr(counts),
                                            nat.ptr(assign), nat.ptr(obj), stream)
         else:
+            # same kernel as the built-in-scratch entry runs (flag 4 = single-CTA tcgen05 kernel), so the
+            # two outputs are comparable element by element
             nbytes = int(lib.hb_kmeans_workspace_bytes(k, d))
             ws = torch.empty((nbytes + 255) // 256 * 256, dtype=torch.uint8, device="cuda")
             rc = lib.hb_kmeans_step(nat.ptr(X), n, d, nat.ptr(C), k, nat.ptr(sums), nat.ptr(counts),
-                                    nat.ptr(assign), nat.ptr(obj), nat.ptr(ws), ws.numel(), 0, stream)
+                                    nat.ptr(assign), nat.ptr(obj), nat.ptr(ws), ws.numel(), 4, stream)
         assert rc == 0, lib.hb_last_error().decode()
         torch.cuda.synchronize()
         outs.append((sums, counts, assign, obj))
