@@ -127,9 +127,10 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (converged warp, one elected lane issues) =====================
+    {
       const uint32_t idesc = umma_idesc_tf32(128, MT, 1, 1);   // both operands MN-major
+      const uint64_t dhi = desc_mnmajor_sw128(0);
       uint32_t it = 0, gu = 0;
       for (long long u = blockIdx.x; u < nunits; u += gridDim.x, ++gu) {
         int ti, tj; long long s;
@@ -144,28 +145,29 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int
           const uint32_t st = it % NSTAGE, ph = (it / NSTAGE) & 1;
           mbar_wait(bar(B_FULL + st), ph);
           tc_fence_after();
-#ifdef HB_GRAM_DEBUG
-          if (it == 0 && blockIdx.x == 0) {
-            const float* sp = reinterpret_cast<const float*>(smem_raw + Smem::stages);
-            printf("dbg smem[0..3]=%f %f %f %f  [32]=%f [512]=%f [4096+0]=%f\n", sp[0], sp[1], sp[2], sp[3], sp[32], sp[512], sp[4096]);
-          }
-#endif
           const uint32_t a_addr = base + Smem::stages + st * STAGE_BYTES;
           const uint32_t b_addr = diag ? a_addr : a_addr + OPER_BYTES;
+          const uint64_t da0 = dhi | ((a_addr & 0x3FFFFu) >> 4);
+          const uint64_t db0 = dhi | ((b_addr & 0x3FFFFu) >> 4);
           long long rem = r1 - r;                       // rows past n are zero-filled by TMA
           int ksteps = (int)((rem + UK - 1) / UK); if (ksteps > KC / UK) ksteps = KC / UK;
-          for (int j = 0; j < ksteps; ++j) {
-            const uint64_t db = desc_mnmajor_sw128(b_addr + j * KSTEP_BYTES);
+          const bool last = (r + KC >= r1);
+          if (elect_one()) {
 #pragma unroll
-            for (int mh = 0; mh < 2; ++mh) {            // the two 128-feature halves of the A side
-              const uint64_t da = desc_mnmajor_sw128(a_addr + mh * 4 * LBO_BYTES + j * KSTEP_BYTES);
-              umma_tf32_1sm(tmem_base + mh * MT, da, db, idesc, first ? 0u : 1u);
+            for (int j = 0; j < KC / UK; ++j) {
+              if (j < ksteps) {
+#pragma unroll
+                for (int mh = 0; mh < 2; ++mh)            // the two 128-feature halves of the A side
+                  umma_tf32_1sm(tmem_base + mh * MT, da0 + (uint64_t)((mh * 4 * LBO_BYTES + j * KSTEP_BYTES) >> 4),
+                                db0 + (uint64_t)((j * KSTEP_BYTES) >> 4), idesc, (first && j == 0) ? 0u : 1u);
+              }
             }
-            first = 0;
+            umma_commit_1sm(bar(B_EMPTY + st));
+            if (last) umma_commit_1sm(bar(T_FULL));
           }
-          umma_commit_1sm(bar(B_EMPTY + st));
+          __syncwarp();
+          first = 0;
         }
-        umma_commit_1sm(bar(T_FULL));
       }
     }
   } else {

@@ -297,9 +297,10 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (converged warp, one elected lane issues) =====================
+    {
       const uint32_t idesc = umma_idesc_tf32(BM, BN);
+      const uint64_t dhi = umma_desc_kmajor_sw128(0);
       uint32_t it = 0, ga = 0, gp = 0;
       for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++gp) {
         mbar_wait(bar(BAR_X_FULL), gp & 1);
@@ -312,20 +313,24 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
             const uint32_t s = it % NSTAGE, ph = (it / NSTAGE) & 1;
             mbar_wait(bar(BAR_B_FULL + s), ph);
             tc_fence_after();
-            const uint32_t a_addr = base + SmemLayout::x + kc * X_CHUNK_BYTES;
-            const uint32_t b_addr = base + SmemLayout::b + s * B_STAGE_BYTES;
+            const uint64_t da0 = dhi | (((base + SmemLayout::x + kc * X_CHUNK_BYTES) & 0x3FFFFu) >> 4);
+            const uint64_t db0 = dhi | (((base + SmemLayout::b + s * B_STAGE_BYTES) & 0x3FFFFu) >> 4);
             int ksteps = (d - kc * BK + UK - 1) / UK;
             if (ksteps > BK / UK) ksteps = BK / UK;
-            for (int j = 0; j < ksteps; ++j) {
-              const uint64_t da = umma_desc_kmajor_sw128(a_addr + j * UK * 4);
-              const uint64_t db = umma_desc_kmajor_sw128(b_addr + j * UK * 4);
-              umma_tf32_1sm(tmem_d, da, db, idesc, (kc | j) != 0 ? 1u : 0u);
+            if (elect_one()) {
+#pragma unroll
+              for (int j = 0; j < BK / UK; ++j)
+                if (j < ksteps)
+                  umma_tf32_1sm(tmem_d, da0 + (uint64_t)(j * UK * 4 / 16), db0 + (uint64_t)(j * UK * 4 / 16), idesc,
+                                (kc | j) != 0 ? 1u : 0u);
+              umma_commit_1sm(bar(BAR_B_EMPTY + s));      // frees the smem stage when the MMAs retire
+              if (kc == kch - 1) umma_commit_1sm(bar(BAR_T_FULL + a));   // accumulator ready for the epilogue
             }
-            umma_commit_1sm(bar(BAR_B_EMPTY + s));      // frees the smem stage when the MMAs retire
+            __syncwarp();
           }
-          umma_commit_1sm(bar(BAR_T_FULL + a));          // accumulator ready for the epilogue
         }
-        umma_commit_1sm(bar(BAR_X_EMPTY));               // point tile no longer read by the tensor core
+        if (elect_one()) umma_commit_1sm(bar(BAR_X_EMPTY));   // point tile no longer read by the tensor core
+        __syncwarp();
       }
     }
   } else {
