@@ -40,7 +40,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="harp_b200", choices=["harp_b200", "reference"])
     ap.add_argument("--workload", default="kmeans", choices=["kmeans", "sgd", "lda", "gram"])
-    ap.add_argument("--comm", default="auto", choices=["auto", "nccl", "p2p"])
+    ap.add_argument("--comm", default="auto", choices=["auto", "nccl", "p2p", "fused"])
     ap.add_argument("--points-per-gpu", type=int, default=POINTS_PER_GPU)
     ap.add_argument("--dim", type=int, default=DIM)
     ap.add_argument("--k", type=int, default=K)
@@ -159,16 +159,18 @@ def main():
 
     symm = None
     comm = args.comm
-    if world > 1 and comm in ("auto", "p2p"):
+    if world > 1 and comm in ("auto", "p2p", "fused"):
         try:
             symm = SymmetricWorkspace(dev, bytes_=64 << 20)
         except Exception as e:  # noqa: BLE001
-            if comm == "p2p":
+            if comm in ("p2p", "fused"):
                 raise
             if rank == 0:
                 print(f"[bench] symmetric workspace unavailable ({e!r}); using NCCL", file=sys.stderr)
             symm = None
-    eng = KMeansEngine(X, k, comm=("p2p" if symm is not None else "nccl"), symm=symm)
+    if comm == "auto":
+        comm = "fused" if (world == 1 or symm is not None) else "nccl"
+    eng = KMeansEngine(X, k, comm=comm, symm=symm)
     eng.set_centroids(C0)
 
     def barrier():

@@ -427,6 +427,14 @@ __device__ __forceinline__ void red_add_v4(float* p, float4 v) {
                "f"(v.z), "f"(v.w)
                : "memory");
 }
+// Scalar fire-and-forget reductions (atomicAdd() may compile to the value-returning ATOMG form when later
+// code in the kernel reads the same memory, which puts an L2 round trip on the issuing warp's scoreboard).
+__device__ __forceinline__ void red_add_f32(float* p, float v) {
+  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_f64(double* p, double v) {
+  asm volatile("red.global.add.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
 // Streaming 128-bit load that does not allocate in L1.
 __device__ __forceinline__ float4 ld_nc_v4(const float* p) {
   float4 r;

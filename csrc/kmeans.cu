@@ -83,14 +83,22 @@ __global__ void prep_kernel(const float* __restrict__ C, int k, int d, int kpad,
     float s = CUDART_INF_F;
     if (j < k) {
       s = 0.f;
-      for (int t = lane; t < d; t += 32) {
-        float v = C[(size_t)j * d + t];
-        s = fmaf(v, v, s);
+      if ((d & 3) == 0) {     // same element order as the fused kernel's tail: both produce identical bits
+        const float4* row4 = reinterpret_cast<const float4*>(C + (size_t)j * d);
+        for (int c4 = lane; c4 < (d >> 2); c4 += 32) {
+          const float4 v = row4[c4];
+          s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
+        }
+      } else {
+        for (int t = lane; t < d; t += 32) {
+          float v = C[(size_t)j * d + t];
+          s = fmaf(v, v, s);
+        }
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     }
-    if (lane == 0) cn[j] = s;
+    if (lane == 0 && cn != nullptr) cn[j] = s;
     if (cn_ext != nullptr && lane < 8) {
       // row j of the extra GEMM operand: -‖c‖²/2 as an exact sum of three tf32 numbers (hi, mid, lo);
       // with the matching A row [1,1,1,0,...] one more K=8 MMA step turns the accumulator into
@@ -208,7 +216,7 @@ __device__ __forceinline__ float fold_points(const float* __restrict__ X, const 
             sq = fmaf(e0, e0, sq); sq = fmaf(e1, e1, sq); sq = fmaf(e2, e2, sq); sq = fmaf(e3, e3, sq);
           }
         }
-        if (lane == 0) atomicAdd(counts + idx[u], 1.0f);
+        if (lane == 0) red_add_f32(counts + idx[u], 1.0f);
       }
     }
   }
@@ -374,7 +382,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
     if (obj != nullptr) {
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) obj_local += __shfl_xor_sync(0xffffffffu, obj_local, o);
-      if (lane == 0) atomicAdd(obj, obj_local);
+      if (lane == 0) red_add_f64(obj, obj_local);
     }
   }
 
@@ -454,14 +462,209 @@ __device__ __forceinline__ float packed_max32(const uint32_t (&v)[32]) {
   return key[0];
 }
 
-template <int DBG, int EXT>
+// ----------------------------------------------------------------------------
+// Fused iteration (FUSED = 1): the same launch that computes distances / arg-min /
+// partial sums also performs Harp's regroup -> centroid update -> allgather
+// (ml/java/.../kmeans/regroupallgather/KMeansCollectiveMapper.java:168-185) over
+// NVLink peer memory, and prepares the GEMM-extension operand of the next iteration.
+//
+// Every rank keeps one "fused state" block at the same offset of its symmetric slab:
+//   ctl | ones_ext | ext[2] | C[2] | acc[2]          ([2] = ping-pong by iteration parity)
+// Iteration e reads C[e&1]/ext[e&1], folds into acc[e&1]; its tail writes C[~e&1]/ext[~e&1] of EVERY
+// rank and zeroes the local acc[~e&1] for the next iteration.  Tail, executed by all CTAs (one per SM,
+// co-resident):
+//   1. local:  every CTA adds 1 to ctl.done1 and spins until all CTAs of this GPU have folded;
+//   2. global: CTA 0 publishes flag1[rank] = e+1 on every peer; every CTA waits for all peers' flag1;
+//   3. warp-per-row over this rank's 1/N of the centroids: sum the peers' partial sums and counts in
+//      rank order (bit-deterministic), divide, push the row and its [-|c|^2/2 hi|mid|lo] operand row
+//      into every peer; CTA 0 also adds up the peers' objective terms;
+//   4. the last CTA through ctl.done2 publishes flag2[rank] = e+1 on every peer; CTA 0 waits for all
+//      peers' flag2 before exiting, so kernel completion on a rank means its new centroids are whole
+//      and nobody still reads its acc[e&1].
+// ----------------------------------------------------------------------------
+struct FusedCtl {
+  uint32_t done1, done2, pad0[2];
+  uint32_t flag1[HB_MAX_RANKS];
+  uint32_t flag2[HB_MAX_RANKS];
+  double obj[2];          // this rank's objective term per parity
+  double obj_total;       // sum over ranks, written by the tail
+  double pad1;
+};
+static_assert(sizeof(FusedCtl) <= 256, "FusedCtl must fit its 256-byte slot");
+
+struct FusedArgs {
+  uint8_t* peer[HB_MAX_RANKS];   // fused-state base of every rank (peer[rank] is local memory)
+  int rank, world;
+  uint32_t epoch;
+  int keep_empty;
+  unsigned long long off_ext[2], off_c[2], off_acc[2];
+};
+
+__device__ __forceinline__ void spin_until(const uint32_t* p, uint32_t target, bool sys, const char* what) {
+  const long long t0 = clock64();
+  while ((int32_t)((sys ? ld_acquire_sys(p) : ld_acquire_gpu(p)) - target) < 0) {
+    if (clock64() - t0 > 20000000000LL) {
+      printf("harp_b200: fused K-means tail timed out waiting for %s (cta %d thread %d)\n", what, blockIdx.x, threadIdx.x);
+      __trap();
+    }
+  }
+}
+
+__device__ __noinline__ void fused_tail(const FusedArgs& fa, int k, int d, uint32_t* smem_flag) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nwarps_cta = blockDim.x >> 5;
+  const uint32_t cur = fa.epoch & 1u, nxt = cur ^ 1u, target = fa.epoch + 1u;
+  uint8_t* me = fa.peer[fa.rank];
+  FusedCtl* ctl = reinterpret_cast<FusedCtl*>(me);
+  // 1. all CTAs of this GPU have issued their reductions into acc[cur]
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    atomicAdd(&ctl->done1, 1u);
+    spin_until(&ctl->done1, gridDim.x, false, "local CTAs");
+  }
+  __syncthreads();
+  // 2. every rank's partial sums are complete
+  if (tid < fa.world) {
+    if (blockIdx.x == 0) {
+      fence_sys();
+      st_release_sys(&reinterpret_cast<FusedCtl*>(fa.peer[tid])->flag1[fa.rank], target);
+    }
+    spin_until(&ctl->flag1[tid], target, true, "peer partial sums");
+  }
+  __syncthreads();
+  // 3. regroup (reduce this rank's rows over all peers) -> divide -> allgather (push to all peers)
+  const int world = fa.world;
+  const int rows_per = (k + world - 1) / world;
+  const int r0 = min(k, fa.rank * rows_per), r1 = min(k, r0 + rows_per);
+  const int gw = blockIdx.x * nwarps_cta + warp, nw = gridDim.x * nwarps_cta;
+  const size_t acc_cur = fa.off_acc[cur];
+  // 4 rows per warp at a time and up to 4 peers' loads in flight per row, so a batch costs about two NVLink
+  // round trips instead of rows x peers; sums are still added in rank order
+  const int d4 = d >> 2;
+  constexpr int RB = 4, PB = 4;
+  for (int rowb = r0 + gw * RB; rowb < r1; rowb += nw * RB) {
+    float cnt[RB];
+#pragma unroll
+    for (int u = 0; u < RB; ++u) cnt[u] = 0.f;
+    for (int p0 = 0; p0 < world; p0 += PB) {
+      float cv[PB][RB];
+#pragma unroll
+      for (int pp = 0; pp < PB; ++pp)
+#pragma unroll
+        for (int u = 0; u < RB; ++u) {
+          cv[pp][u] = 0.f;
+          if (p0 + pp < world && rowb + u < r1)
+            cv[pp][u] = ld_volatile_f32(fa.peer[p0 + pp] + acc_cur + ((size_t)k * d + rowb + u) * sizeof(float));
+        }
+#pragma unroll
+      for (int pp = 0; pp < PB; ++pp)
+#pragma unroll
+        for (int u = 0; u < RB; ++u) cnt[u] += cv[pp][u];
+    }
+    float sq[RB];
+#pragma unroll
+    for (int u = 0; u < RB; ++u) sq[u] = 0.f;
+    for (int c4 = lane; c4 < d4; c4 += 32) {
+      float4 sacc[RB];
+#pragma unroll
+      for (int u = 0; u < RB; ++u) sacc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int p0 = 0; p0 < world; p0 += PB) {
+        float4 xv[PB][RB];
+#pragma unroll
+        for (int pp = 0; pp < PB; ++pp)
+#pragma unroll
+          for (int u = 0; u < RB; ++u) {
+            xv[pp][u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (p0 + pp < world && rowb + u < r1)
+              xv[pp][u] = ld_volatile_f4(fa.peer[p0 + pp] + acc_cur + ((size_t)(rowb + u) * d + c4 * 4) * sizeof(float));
+          }
+#pragma unroll
+        for (int pp = 0; pp < PB; ++pp)
+#pragma unroll
+          for (int u = 0; u < RB; ++u) {
+            sacc[u].x += xv[pp][u].x; sacc[u].y += xv[pp][u].y; sacc[u].z += xv[pp][u].z; sacc[u].w += xv[pp][u].w;
+          }
+      }
+#pragma unroll
+      for (int u = 0; u < RB; ++u) {
+        if (rowb + u >= r1) continue;
+        const size_t eoff = ((size_t)(rowb + u) * d + c4 * 4) * sizeof(float);
+        float4 c;
+        if (cnt[u] > 0.f) c = make_float4(sacc[u].x / cnt[u], sacc[u].y / cnt[u], sacc[u].z / cnt[u], sacc[u].w / cnt[u]);
+        else if (fa.keep_empty) c = *reinterpret_cast<const float4*>(me + fa.off_c[cur] + eoff);
+        else c = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int p = 0; p < world; ++p)
+          *reinterpret_cast<float4*>(fa.peer[(fa.rank + p) % world] + fa.off_c[nxt] + eoff) = c;
+        sq[u] = fmaf(c.x, c.x, sq[u]); sq[u] = fmaf(c.y, c.y, sq[u]); sq[u] = fmaf(c.z, c.z, sq[u]); sq[u] = fmaf(c.w, c.w, sq[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < RB; ++u) {
+      float sv = sq[u];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) sv += __shfl_xor_sync(0xffffffffu, sv, o);
+      if (lane < 8 && rowb + u < r1) {
+        const float t0 = -0.5f * sv;
+        const float hi = tf32_trunc(t0);
+        const float mid = tf32_trunc(t0 - hi);
+        const float lo = tf32_trunc(t0 - hi - mid);
+        const float v = lane == 0 ? hi : (lane == 1 ? mid : (lane == 2 ? lo : 0.f));
+        for (int p = 0; p < world; ++p)
+          *reinterpret_cast<float*>(fa.peer[(fa.rank + p) % world] + fa.off_ext[nxt] + ((size_t)(rowb + u) * 8 + lane) * sizeof(float)) = v;
+      }
+    }
+  }
+  if (blockIdx.x == 0 && tid == 0) {
+    double tot = 0.0;
+    for (int p = 0; p < world; ++p) {
+      const volatile double* po = &reinterpret_cast<const FusedCtl*>(fa.peer[p])->obj[cur];
+      tot += *po;
+    }
+    ctl->obj_total = tot;
+  }
+  // accumulators of the NEXT iteration: no peer reads acc[nxt] any more (each acknowledged the end of its
+  // previous tail before our previous launch completed); zeroed here rather than at the start of the next
+  // launch so the lines are still in L2 when the next launch's reductions arrive
+  {
+    float4* z = reinterpret_cast<float4*>(me + fa.off_acc[nxt]);
+    const size_t total4 = ((size_t)k * d + k + 3) / 4;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + tid; i < total4; i += (size_t)gridDim.x * blockDim.x)
+      z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (blockIdx.x == 0 && tid == 0) ctl->obj[nxt] = 0.0;
+  }
+  // 4. publish "my pushes are done, I no longer read your acc[cur]"
+  fence_sys();
+  __syncthreads();
+  if (tid == 0) {
+    const uint32_t old = atomicAdd(&ctl->done2, 1u);
+    const bool last = (old == gridDim.x - 1);
+    if (last) {            // every CTA is past its done1 spin: recycle both counters for the next launch
+      ctl->done2 = 0u;
+      ctl->done1 = 0u;
+      fence_sys();
+    }
+    *smem_flag = last ? 1u : 0u;
+  }
+  __syncthreads();
+  const bool last = (*smem_flag != 0u);
+  if (tid < world) {
+    if (last) {
+      fence_sys();
+      st_release_sys(&reinterpret_cast<FusedCtl*>(fa.peer[tid])->flag2[fa.rank], target);
+    }
+    if (blockIdx.x == 0) spin_until(&ctl->flag2[tid], target, true, "peer centroid pushes");
+  }
+}
+
+template <int DBG, int EXT, int FUSED = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(pair::NTHREADS2, 1)
 assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_c,
                       const __grid_constant__ CUtensorMap tmap_ones, const __grid_constant__ CUtensorMap tmap_cext,
                       const float* __restrict__ X, const float* __restrict__ C,
                       const float* __restrict__ cn_pad, long long n, int d, int k, int kpad,
                       float* __restrict__ sums, float* __restrict__ counts, int* __restrict__ assign,
-                      double* __restrict__ obj) {
+                      double* __restrict__ obj, const FusedArgs fa) {
   using namespace pair;
   constexpr int dbg = DBG;
   // Role layout: the SMSP arbiter favours higher warp ids, so the two latency-critical
@@ -756,7 +959,7 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
     if (obj != nullptr) {
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) obj_local += __shfl_xor_sync(0xffffffffu, obj_local, o);
-      if (lane == 0) atomicAdd(obj, obj_local);
+      if (lane == 0) red_add_f64(obj, obj_local);
     }
     if ((dbg & 16) && lane == 0 && blockIdx.x < 2 && prof_n > 0)
       printf("prof cta %d warp %d: tiles %lld wait/tile %lld work/tile %lld cycles\n", blockIdx.x, warp,
@@ -766,6 +969,7 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
   tc_fence_before();
   cluster_sync_all();            // nobody leaves while the peer may still touch its smem / TMEM / barriers
   if (warp == MMA_WARP) tmem_dealloc_2sm(tmem_base, TMEM_COLS);
+  if (FUSED) fused_tail(fa, k, d, reinterpret_cast<uint32_t*>(smem_raw + Smem::merge));
 }
 
 // ----------------------------------------------------------------------------
@@ -940,8 +1144,10 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
         if (cap > 0 && cap < nclusters) nclusters = cap;
       }
       if (nclusters > npairs) nclusters = npairs;
+      FusedArgs nofuse;
+      memset(&nofuse, 0, sizeof(nofuse));
       kern<<<(unsigned)(2 * nclusters), pair::NTHREADS2, pair::Smem::total, stream>>>(
-          tx, tch, tones, tcext, X, C, cn, n, d, k, kpad, sums, counts, assign, obj);
+          tx, tch, tones, tcext, X, C, cn, n, d, k, kpad, sums, counts, assign, obj, nofuse);
       HB_CUDA_OK(cudaGetLastError());
     } else {
       static bool attr_set[64] = {false};
@@ -980,6 +1186,119 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
     if (assign != nullptr)
       HB_CUDA_OK(cudaMemcpyAsync(assign, asg, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
   }
+  return 0;
+}
+
+// ---- fused iteration: distance GEMM + arg-min + partial sums + regroup/update/allgather in one launch ----
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+struct FusedLayout { size_t ones, ext[2], c[2], acc[2], total; };
+static FusedLayout fused_layout(int k, int d) {
+  const size_t kpad = ((size_t)k + BN - 1) / BN * BN;
+  FusedLayout L;
+  size_t o = 256;                                   // FusedCtl
+  L.ones = o; o += 128 * 8 * sizeof(float);
+  for (int i = 0; i < 2; ++i) { L.ext[i] = o; o = align_up(o + kpad * 8 * sizeof(float), 256); }
+  for (int i = 0; i < 2; ++i) { L.c[i] = o; o = align_up(o + (size_t)k * d * sizeof(float), 256); }
+  for (int i = 0; i < 2; ++i) { L.acc[i] = o; o = align_up(o + ((size_t)k * d + k + 3) / 4 * 16, 256); }
+  L.total = o;
+  return L;
+}
+size_t hb_kmeans_fused_state_bytes(int k, int d) { return fused_layout(k, d).total; }
+
+int hb_kmeans_fused_offsets(int k, int d, unsigned long long* out8) {
+  HB_REQUIRE(out8 != nullptr, "hb_kmeans_fused_offsets: null output");
+  const FusedLayout L = fused_layout(k, d);
+  out8[0] = L.c[0]; out8[1] = L.c[1]; out8[2] = L.acc[0]; out8[3] = L.acc[1];
+  out8[4] = offsetof(FusedCtl, obj); out8[5] = offsetof(FusedCtl, obj_total); out8[6] = L.ext[0]; out8[7] = L.ext[1];
+  return 0;
+}
+
+// (Re)computes the GEMM-extension operand of centroid buffer `parity` from its current contents.
+int hb_kmeans_fused_prep(void* state, int k, int d, int parity, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  HB_REQUIRE(state != nullptr && (parity == 0 || parity == 1), "hb_kmeans_fused_prep: bad arguments");
+  const FusedLayout L = fused_layout(k, d);
+  const int kpad = (k + BN - 1) / BN * BN;
+  uint8_t* st = reinterpret_cast<uint8_t*>(state);
+  const int threads = 256;
+  int blocks = (kpad * 32 + threads - 1) / threads;
+  const int cap = sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  prep_kernel<<<blocks, threads, 0, stream>>>(reinterpret_cast<const float*>(st + L.c[parity]), k, d, kpad, nullptr,
+                                              reinterpret_cast<float*>(st + L.ext[parity]),
+                                              reinterpret_cast<float*>(st + L.ones), nullptr, nullptr, nullptr, 0);
+  HB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// Zeroes the state, loads the initial centroids into buffer 0 and prepares both operand buffers.  Every rank
+// must have returned from this (and synchronised with its peers) before any rank launches the first step.
+int hb_kmeans_fused_init(void* state, int k, int d, const float* C0, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  HB_REQUIRE(state != nullptr && k >= 1 && d >= 4 && d % 4 == 0 && hb_kmeans_tc_supported(d, k),
+             "hb_kmeans_fused_init: shape (k=%d, d=%d) not supported by the fused kernel", k, d);
+  HB_REQUIRE((reinterpret_cast<uintptr_t>(state) & 255) == 0, "hb_kmeans_fused_init: state must be 256-byte aligned");
+  const FusedLayout L = fused_layout(k, d);
+  HB_CUDA_OK(cudaMemsetAsync(state, 0, L.total, stream));
+  if (C0 != nullptr)
+    HB_CUDA_OK(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(state) + L.c[0], C0, (size_t)k * d * sizeof(float),
+                               cudaMemcpyDeviceToDevice, stream));
+  if (hb_kmeans_fused_prep(state, k, d, 1, stream_) != 0) return -1;   // padding rows of buffer 1
+  return hb_kmeans_fused_prep(state, k, d, 0, stream_);
+}
+
+int hb_kmeans_fused_step(const float* X, long long n, int d, int k, void* const* peer_state, int rank, int world,
+                         unsigned epoch, int keep_empty, int* assign, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  HB_REQUIRE(world >= 1 && world <= HB_MAX_RANKS && rank >= 0 && rank < world, "hb_kmeans_fused_step: bad rank %d / world %d", rank, world);
+  HB_REQUIRE(n >= 0 && k >= 1 && hb_kmeans_tc_supported(d, k), "hb_kmeans_fused_step: shape (n=%lld, k=%d, d=%d) not supported", n, k, d);
+  HB_REQUIRE(n == 0 || (X != nullptr && (reinterpret_cast<uintptr_t>(X) & 15) == 0), "hb_kmeans_fused_step: X must be 16-byte aligned");
+  const FusedLayout L = fused_layout(k, d);
+  const int kpad = (k + BN - 1) / BN * BN;
+  const uint32_t cur = epoch & 1u;
+  FusedArgs fa;
+  memset(&fa, 0, sizeof(fa));
+  for (int i = 0; i < world; ++i) {
+    HB_REQUIRE(peer_state[i] != nullptr, "hb_kmeans_fused_step: null state pointer for rank %d", i);
+    fa.peer[i] = reinterpret_cast<uint8_t*>(peer_state[i]);
+  }
+  fa.rank = rank; fa.world = world; fa.epoch = epoch; fa.keep_empty = keep_empty;
+  for (int i = 0; i < 2; ++i) { fa.off_ext[i] = L.ext[i]; fa.off_c[i] = L.c[i]; fa.off_acc[i] = L.acc[i]; }
+  uint8_t* me = fa.peer[rank];
+  const float* C = reinterpret_cast<const float*>(me + L.c[cur]);
+  float* sums = reinterpret_cast<float*>(me + L.acc[cur]);
+  float* counts = sums + (size_t)k * d;
+  double* obj = &reinterpret_cast<FusedCtl*>(me)->obj[cur];
+  CUtensorMap tx, tch, tones, tcext;
+  // a rank without points still takes part in the collective tail; its X map is never dereferenced
+  const float* Xm = n > 0 ? X : C;
+  const uint64_t nm = n > 0 ? (uint64_t)n : (uint64_t)k;
+  if (make_tmap_2d_f32(&tx, Xm, nm, (uint64_t)d, (uint64_t)d * 4, BM, BK, CU_TENSOR_MAP_SWIZZLE_128B) != 0) return -3;
+  if (make_tmap_2d_f32(&tch, C, (uint64_t)k, (uint64_t)d, (uint64_t)d * 4, BN / 2, BK, CU_TENSOR_MAP_SWIZZLE_128B) != 0) return -3;
+  if (make_tmap_2d_f32(&tones, me + L.ones, 128, 8, 32, 128, 8, CU_TENSOR_MAP_SWIZZLE_32B) != 0) return -3;
+  if (make_tmap_2d_f32(&tcext, me + L.ext[cur], (uint64_t)kpad, 8, 32, BN / 2, 8, CU_TENSOR_MAP_SWIZZLE_32B) != 0) return -3;
+  auto kern = assign_tc_pair_kernel<0, 1, 1>;
+  if (const char* e = getenv("HB_FUSED_DBG")) { if (atoi(e) == 16) kern = assign_tc_pair_kernel<16, 1, 1>; else if (atoi(e) == 4) kern = assign_tc_pair_kernel<4, 1, 1>; }   // triage knob
+  HB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::Smem::total));
+  const long long npairs = (n + 2 * BM - 1) / (2 * BM);
+  long long nclusters = sm_count() / 2;
+  if (nclusters > npairs) nclusters = npairs;
+  if (nclusters < 1) nclusters = 1;
+  // The tail spins on counters fed by the other CTAs of this launch, so all of them must be resident at once:
+  // one CTA per SM, never more CTAs than SMs, and a cooperative launch so the driver refuses otherwise.
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)(2 * nclusters));
+  cfg.blockDim = dim3(pair::NTHREADS2);
+  cfg.dynamicSmemBytes = pair::Smem::total;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = getenv("HB_FUSED_NO_COOP") ? 0 : 1;      // triage knob
+  HB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tx, tch, tones, tcext, Xm, C, (const float*)nullptr, n, d, k, kpad, sums, counts,
+                                assign, obj, fa));
   return 0;
 }
 

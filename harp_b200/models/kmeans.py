@@ -8,7 +8,11 @@ cross-worker step is selectable:
 ``comm="p2p"``      the in-kernel NVLink peer-memory reduce-scatter + all-gather
                     (``csrc/coll.cu``; Harp's regroup→allgather shape,
                     ``ml/java/.../kmeans/regroupallgather/KMeansCollectiveMapper.java:168-185``)
-``comm="auto"``     p2p when a symmetric workspace is available, else nccl
+``comm="fused"``    ONE launch per iteration: the tcgen05 distance/arg-min/accumulate kernel also does the
+                    regroup → update → allgather over NVLink and prepares the next iteration's operands
+                    (``ops.kmeans.FusedKMeans``); works on one GPU too (3 launches become 1)
+``comm="auto"``     fused on CUDA when the shape is supported (and, for >1 rank, a symmetric workspace is
+                    given), else p2p / nccl
 
 Reference semantics kept: an empty cluster collapses to the zero vector
 (``KMeansCollectiveMapper.java:170-183``) unless ``keep_empty=True``.
@@ -28,7 +32,7 @@ class KMeansEngine:
     def __init__(self, X: torch.Tensor, k: int, *, comm: str = "auto", group=None,
                  keep_empty: bool = False, symm=None):
         assert X.dim() == 2
-        self.X = X
+        self.X = X.contiguous() if X.device.type == "cuda" else X
         self.n, self.d = X.shape
         self.k = int(k)
         self.dev = X.device
@@ -38,26 +42,52 @@ class KMeansEngine:
         self.rank = dist.get_rank(group) if self.world > 1 else 0
         self.symm = symm
         self.variant = os.environ.get("HB_KMEANS_VARIANT", "auto")
-        if comm == "auto":
-            comm = "p2p" if (symm is not None and self.world > 1) else "nccl"
-        self.comm = comm
         k, d = self.k, self.d
+        if comm == "auto":
+            fused_ok = (self.dev.type == "cuda" and X.dtype == torch.float32 and d % 4 == 0 and d <= 256
+                        and self.variant in ("auto", "pair") and (self.world == 1 or symm is not None))
+            comm = "fused" if fused_ok else ("p2p" if (symm is not None and self.world > 1) else "nccl")
+        self.comm = comm
+        self.fused = None
+        if self.comm == "fused":
+            nbytes = kops.FusedKMeans.state_bytes(k, d)
+            if self.world > 1:
+                assert symm is not None, "comm='fused' on several ranks needs a SymmetricWorkspace"
+                st = symm.alloc(nbytes, torch.uint8)
+                off = symm.offset_of(st)
+                peers = [p + off for p in symm.peer_ptrs]
+            else:
+                st = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
+                peers = [st.data_ptr()]
+            self.fused = kops.FusedKMeans(st, peers, self.rank, k, d, keep_empty)
+            self.fused.init(None)
+            if self.world > 1:
+                torch.cuda.synchronize(self.dev)
+                dist.barrier(group=group)          # nobody signals a peer whose flags are not zeroed yet
+            self.obj = self.fused.obj_total
+            self.workspace = None
+            self.total_points = float(self.n)
+            if self.world > 1:
+                t = torch.tensor([float(self.n)], dtype=torch.float64, device=self.dev)
+                dist.all_reduce(t, group=group)
+                self.total_points = float(t.item())
+            return
         # one slab [sums | counts] so the cross-worker combine is a single collective
         if self.comm == "p2p" and self.world > 1:
             assert symm is not None, "comm='p2p' needs a SymmetricWorkspace"
             self.acc = symm.alloc(k * d + k, torch.float32)
         else:
             self.acc = torch.zeros(k * d + k, dtype=torch.float32, device=self.dev)
-        self.sums = self.acc[: k * d].view(k, d)
-        self.counts = self.acc[k * d:]
+        self._sums = self.acc[: k * d].view(k, d)
+        self._counts = self.acc[k * d:]
         if self.comm == "p2p" and self.world > 1:
             self.obj = symm.alloc(2, torch.float64)[:1]
             self.obj.zero_()
-            self.C = symm.alloc(k * d, torch.float32).view(k, d)
-            self.C.zero_()
+            self._C = symm.alloc(k * d, torch.float32).view(k, d)
+            self._C.zero_()
         else:
             self.obj = torch.zeros(1, dtype=torch.float64, device=self.dev)
-            self.C = torch.zeros(k, d, dtype=torch.float32, device=self.dev)
+            self._C = torch.zeros(k, d, dtype=torch.float32, device=self.dev)
         self.workspace = None
         if self.dev.type == "cuda":
             need = kops.workspace_bytes(self.n, k, d)
@@ -68,11 +98,34 @@ class KMeansEngine:
             dist.all_reduce(t, group=group)
             self.total_points = float(t.item())
 
+    @property
+    def C(self) -> torch.Tensor:
+        """Current centroids ``[k, d]`` (device)."""
+        return self.fused.centroids if self.fused is not None else self._C
+
+    @property
+    def sums(self) -> torch.Tensor:
+        if self.fused is not None:
+            return self.fused.last_sums[: self.k * self.d].view(self.k, self.d)
+        return self._sums
+
+    @property
+    def counts(self) -> torch.Tensor:
+        if self.fused is not None:
+            return self.fused.last_sums[self.k * self.d:]
+        return self._counts
+
     def set_centroids(self, C: torch.Tensor, non_blocking: bool = True) -> None:
-        self.C.copy_(C.view(self.k, self.d), non_blocking=non_blocking)
+        if self.fused is not None:
+            self.fused.set_centroids(C, non_blocking=non_blocking)
+        else:
+            self._C.copy_(C.view(self.k, self.d), non_blocking=non_blocking)
 
     def step(self, want_obj: bool = True) -> Optional[torch.Tensor]:
         """One Lloyd iteration; returns the (device) Σ min-distance² of the *input* centroids."""
+        if self.fused is not None:
+            self.fused.step(self.X)
+            return self.obj if want_obj else None
         kops.kmeans_step(self.X, self.C, self.sums, self.counts, None,
                          self.obj if want_obj else None, self.workspace, variant=self.variant)
         if self.world > 1 and self.comm == "p2p" and self.d % 4 != 0:

@@ -130,3 +130,97 @@ def kmeans_finalize(sums: torch.Tensor, counts: torch.Tensor, C_out: torch.Tenso
     _native.check(rc, "hb_kmeans_finalize")
     _native.count_launch(1)
     return C_out
+
+
+class FusedKMeans:
+    """One-launch-per-iteration K-means (``csrc/kmeans.cu``: ``assign_tc_pair_kernel<0,1,1>`` + ``fused_tail``).
+
+    The launch that runs the tcgen05 distance GEMM, arg-min and partial-sum accumulation also does Harp's
+    regroup → centroid update → allgather over NVLink peer memory
+    (``ml/java/.../kmeans/regroupallgather/KMeansCollectiveMapper.java:168-185``) and prepares the GEMM operands
+    of the next iteration.  ``state`` is this rank's block of a symmetric slab (same offset on every rank);
+    ``peer_ptrs`` are the device addresses of that block on every rank (for one GPU: just its own).
+    """
+
+    def __init__(self, state: torch.Tensor, peer_ptrs, rank: int, k: int, d: int, keep_empty: bool = False):
+        import ctypes
+
+        lib = _native.lib()
+        lib.hb_kmeans_fused_state_bytes.restype = ctypes.c_size_t
+        lib.hb_kmeans_fused_state_bytes.argtypes = [ctypes.c_int, ctypes.c_int]
+        lib.hb_kmeans_fused_offsets.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+        lib.hb_kmeans_fused_prep.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+        lib.hb_kmeans_fused_init.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+        lib.hb_kmeans_fused_step.argtypes = [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                             ctypes.c_int, ctypes.c_int, ctypes.c_uint, ctypes.c_int, ctypes.c_void_p,
+                                             ctypes.c_void_p]
+        self.lib = lib
+        self.k, self.d = int(k), int(d)
+        self.rank, self.world = int(rank), len(peer_ptrs)
+        self.keep_empty = bool(keep_empty)
+        need = self.state_bytes(k, d)
+        assert state.dtype == torch.uint8 and state.numel() >= need and state.data_ptr() % 256 == 0
+        assert int(peer_ptrs[rank]) == state.data_ptr()
+        self.state = state
+        self._peers = (ctypes.c_void_p * self.world)(*[ctypes.c_void_p(int(p)) for p in peer_ptrs])
+        off = (ctypes.c_ulonglong * 8)()
+        _native.check(lib.hb_kmeans_fused_offsets(k, d, ctypes.cast(off, ctypes.c_void_p)), "hb_kmeans_fused_offsets")
+        o = [int(v) for v in off]
+        kd = k * d
+        self.C = [state[o[i]: o[i] + kd * 4].view(torch.float32).view(k, d) for i in range(2)]
+        self.acc = [state[o[2 + i]: o[2 + i] + (kd + k) * 4].view(torch.float32) for i in range(2)]
+        self.obj_terms = state[o[4]: o[4] + 16].view(torch.float64)
+        self.obj_total = state[o[5]: o[5] + 8].view(torch.float64)
+        self.epoch = 0
+
+    @staticmethod
+    def state_bytes(k: int, d: int) -> int:
+        import ctypes
+
+        lib = _native.lib()
+        lib.hb_kmeans_fused_state_bytes.restype = ctypes.c_size_t
+        lib.hb_kmeans_fused_state_bytes.argtypes = [ctypes.c_int, ctypes.c_int]
+        return int(lib.hb_kmeans_fused_state_bytes(k, d))
+
+    @property
+    def centroids(self) -> torch.Tensor:
+        """The centroid buffer the next step will read (= the result of the previous one)."""
+        return self.C[self.epoch & 1]
+
+    def init(self, C0: Optional[torch.Tensor] = None) -> None:
+        """Zero the state and load ``C0``.  The caller must barrier across ranks before the first ``step``."""
+        if C0 is not None:
+            C0 = C0.to(torch.float32).contiguous()
+        _native.check(self.lib.hb_kmeans_fused_init(_native.ptr(self.state), self.k, self.d, _native.ptr(C0),
+                                                    _native.stream_ptr()), "hb_kmeans_fused_init")
+        _native.count_launch(2)
+        self.epoch = 0
+
+    def set_centroids(self, C: torch.Tensor, non_blocking: bool = True) -> None:
+        """Overwrite the current centroids (every rank must do the same) and rebuild the GEMM operands."""
+        self.centroids.copy_(C.view(self.k, self.d), non_blocking=non_blocking)
+        _native.check(self.lib.hb_kmeans_fused_prep(_native.ptr(self.state), self.k, self.d, self.epoch & 1,
+                                                    _native.stream_ptr()), "hb_kmeans_fused_prep")
+        _native.count_launch(1)
+
+    def step(self, X: torch.Tensor, assign: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """One full Lloyd iteration in one launch; returns the new centroids (a view of the state)."""
+        assert X.dtype == torch.float32 and X.is_contiguous() and X.shape[1] == self.d
+        rc = self.lib.hb_kmeans_fused_step(_native.ptr(X), X.shape[0], self.d, self.k,
+                                           ctypes_cast_void(self._peers), self.rank, self.world, self.epoch,
+                                           1 if self.keep_empty else 0, _native.ptr(assign), _native.stream_ptr())
+        _native.check(rc, "hb_kmeans_fused_step")
+        _native.count_launch(1)
+        self.epoch += 1
+        return self.centroids
+
+    @property
+    def last_sums(self) -> torch.Tensor:
+        """[sums | counts] of this rank from the last step (valid until the step after next)."""
+        return self.acc[(self.epoch - 1) & 1]
+
+
+def ctypes_cast_void(arr):
+    import ctypes
+
+    return ctypes.cast(arr, ctypes.c_void_p)

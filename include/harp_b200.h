@@ -61,6 +61,32 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
 int hb_kmeans_finalize(const float* sums, const float* counts, int k, int d, float* C,
                        int keep_empty, void* stream);
 
+/* ---- Fused K-means iteration: ONE launch per Lloyd iteration, collective included ----
+ *
+ * The launch that runs the tcgen05 distance GEMM, the arg-min and the partial-sum accumulation also
+ * performs the reference's regroup -> centroid update -> allgather
+ * (MJ/kmeans/regroupallgather/KMeansCollectiveMapper.java:168-185) over NVLink peer memory and
+ * prepares the GEMM operands of the next iteration.  Every rank owns a "fused state" block of
+ * hb_kmeans_fused_state_bytes(k, d) bytes, 256-byte aligned, at addresses the peers can load/store
+ * (symmetric memory / CUDA IPC); on one GPU any device buffer works.
+ *
+ *   hb_kmeans_fused_offsets -> out8 = byte offsets inside the block of
+ *       { C[0], C[1], acc[0], acc[1], obj terms (2 doubles), obj total (1 double), ext[0], ext[1] };
+ *       iteration e reads C[e & 1], writes [sums | counts] to acc[e & 1] and the new centroids to C[~e & 1].
+ *   hb_kmeans_fused_init    zeroes the block and loads the initial centroids C0 (device pointer or NULL) into
+ *       C[0].  All ranks must have completed it (host-side barrier) before anyone launches the first step.
+ *   hb_kmeans_fused_prep    rebuilds the operands of C[parity] after the caller overwrote that buffer.
+ *   hb_kmeans_fused_step    one iteration; `epoch` = 0, 1, 2, ... must be the same on every rank.  When the
+ *       launch completes on a rank, its C[~epoch & 1] is whole and the objective total (sum over ranks of the
+ *       sum of min squared distances to the INPUT centroids) is in the block.  Needs hb_kmeans_tc_supported(d, k);
+ *       the grid is one CTA per SM, launched cooperatively because its tail synchronises the CTAs of the launch. */
+size_t hb_kmeans_fused_state_bytes(int k, int d);
+int hb_kmeans_fused_offsets(int k, int d, unsigned long long* out8);
+int hb_kmeans_fused_init(void* state, int k, int d, const float* C0, void* stream);
+int hb_kmeans_fused_prep(void* state, int k, int d, int parity, void* stream);
+int hb_kmeans_fused_step(const float* X, long long n, int d, int k, void* const* peer_state, int rank, int world,
+                         unsigned epoch, int keep_empty, int* assign, void* stream);
+
 /* Same pass as hb_kmeans_step for callers that cannot provide scratch memory: programs that
  * come in through this C ABI from a runtime with no CUDA allocator of its own (JNI/FFI hosts),
  * or whose device memory is already fully claimed by another pool, so a cudaMalloc here would

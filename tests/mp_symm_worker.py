@@ -77,6 +77,20 @@ def main():
         torch.testing.assert_close(o1, o2, rtol=1e-6, atol=1e-6)
         torch.testing.assert_close(e1.C, e2.C, rtol=1e-4, atol=1e-5)
 
+    # one-launch fused iteration (GEMM + arg-min + regroup/update/allgather over NVLink) == NCCL path
+    e3 = KMeansEngine(X, 300, comm="fused", symm=ws); e3.set_centroids(C0)
+    e2.set_centroids(C0)
+    for it in range(5):
+        e2.set_centroids(e3.C.clone()); torch.cuda.synchronize(); dist.barrier()
+        o3 = e3.step().clone(); o2 = e2.step().clone(); torch.cuda.synchronize()
+        torch.testing.assert_close(o3, o2, rtol=1e-6, atol=1e-6)
+        torch.testing.assert_close(e3.C, e2.C, rtol=1e-4, atol=1e-5)
+    # every rank ends up with bit-identical centroids (rank-ordered reduction, one writer per row)
+    mine = e3.C.clone(); ref = mine.clone(); dist.broadcast(ref, src=0)
+    assert torch.equal(mine, ref)
+    if rank == 0:
+        print("fused kmeans ok", flush=True)
+
     # timing of the 5 MB allreduce vs NCCL
     ws.reset()
     n = 10000 * 129

@@ -90,3 +90,39 @@ def test_kmeans_finalize(native_built):
     kmeans_finalize(sums, counts, C2, keep_empty=True)
     ref2 = torch.where(counts[:, None] > 0, sums / counts[:, None].clamp(min=1), torch.full_like(sums, 7.0))
     torch.testing.assert_close(C2, ref2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,d,k,keep", [(20000, 128, 1000, False), (5000, 64, 300, False), (3000, 100, 10, False),
+                                        (1000, 32, 700, True), (1000, 32, 700, False), (100, 128, 5, False)])
+def test_kmeans_fused_iteration_matches_unfused(native_built, n, d, k, keep):
+    """The one-launch iteration (kernel + in-kernel update + next-iteration operands) against the
+    three-launch path, step by step from identical centroids; k > n/… exercises empty clusters."""
+    from harp_b200.models.kmeans import KMeansEngine
+
+    torch.manual_seed(3)
+    X = torch.rand(n, d, device="cuda")
+    C0 = torch.rand(k, d, device="cuda")
+    ef = KMeansEngine(X, k, comm="fused", keep_empty=keep)
+    eu = KMeansEngine(X, k, comm="nccl", keep_empty=keep)
+    assert ef.fused is not None and eu.fused is None
+    ef.set_centroids(C0)
+    for it in range(4):
+        eu.set_centroids(ef.C.clone())
+        of = ef.step().clone()
+        ou = eu.step().clone()
+        torch.cuda.synchronize()
+        torch.testing.assert_close(of, ou, rtol=1e-6, atol=1e-6)
+        torch.testing.assert_close(ef.C, eu.C, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(ef.counts, eu.counts, rtol=0, atol=0)
+    # and against the fp32 reference of one iteration
+    Cin = ef.C.clone()
+    ef.step(); torch.cuda.synchronize()
+    best = torch.cdist(X.double(), Cin.double()).argmin(1)
+    cnt = torch.bincount(best, minlength=k).double()
+    sums = torch.zeros(k, d, dtype=torch.float64, device="cuda").index_add_(0, best, X.double())
+    exp = torch.where(cnt[:, None] > 0, sums / cnt.clamp(min=1)[:, None], Cin.double() if keep else torch.zeros_like(sums))
+    # TF32 products may flip a few boundary points
+    assert (ef.counts.double() - cnt).abs().sum().item() <= 0.01 * n + 2
+    same = ef.counts.double() == cnt
+    torch.testing.assert_close(ef.C.double()[same], exp[same], rtol=5e-3, atol=5e-3)
