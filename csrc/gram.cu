@@ -23,6 +23,7 @@
 #include "../include/harp_b200.h"
 
 #include <math_constants.h>
+#include <string.h>
 
 namespace hb {
 namespace gram {
@@ -80,9 +81,122 @@ __device__ __forceinline__ void decode_unit(long long u, int ntri, int nmt, int&
   tj = ti + t;
 }
 
+// ----------------------------------------------------------------------------
+// Fused partial-result allreduce (FUSED = 1): the launch that computes this rank's XᵀX also sums the
+// ranks' partial Gram matrices over NVLink peer memory, so every rank leaves the launch holding the global
+// result (the reference gathers DAAL partial results on a master and broadcasts the model back,
+// HD/data_comm/HarpDAALComm.java:203-246, e.g. daal_cov/densedistri/COVDaalCollectiveMapper.java:143-176).
+// State block per rank, same offset in every rank's symmetric slab:  GramCtl (256 B) | G[d*d].
+// Tail, run by all CTAs of the launch (one per SM, co-resident):
+//   1. local completion counter (all split-K reductions into the local G are issued);
+//   2. CTA 0 publishes flag1[rank] = epoch+1 on every peer; every CTA waits for all peers' flag1;
+//   3. every rank sums its 1/N row-slice of the upper macro-tile triangle over the peers in rank order
+//      (bit-deterministic, identical on all ranks) and stores it into every peer's G;
+//   4. second counter; its last CTA publishes flag2; every CTA waits for all peers' flag2;
+//   5. lower triangle <- upper triangle, locally.
+// ----------------------------------------------------------------------------
+struct GramCtl {
+  uint32_t done1, done2, pad0[2];
+  uint32_t flag1[HB_MAX_RANKS];
+  uint32_t flag2[HB_MAX_RANKS];
+};
+static_assert(sizeof(GramCtl) <= 256, "GramCtl must fit its 256-byte slot");
+struct GramFused {
+  uint8_t* peer[HB_MAX_RANKS];
+  int rank, world;
+  uint32_t epoch;
+  int pad;
+};
+
+__device__ __forceinline__ void gram_spin(const uint32_t* p, uint32_t target, bool sys, const char* what) {
+  const long long t0 = clock64();
+  while ((int32_t)((sys ? ld_acquire_sys(p) : ld_acquire_gpu(p)) - target) < 0) {
+    if (clock64() - t0 > 20000000000LL) {
+      printf("harp_b200: fused Gram tail timed out waiting for %s (cta %d thread %d)\n", what, blockIdx.x, threadIdx.x);
+      __trap();
+    }
+  }
+}
+
+__device__ __noinline__ void gram_fused_tail(const GramFused& fa, int d) {
+  const int tid = threadIdx.x;
+  const int world = fa.world;
+  const uint32_t target = fa.epoch + 1u;
+  uint8_t* me = fa.peer[fa.rank];
+  GramCtl* ctl = reinterpret_cast<GramCtl*>(me);
+  float* G = reinterpret_cast<float*>(me + 256);
+  // 1.
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    atomicAdd(&ctl->done1, 1u);
+    gram_spin(&ctl->done1, gridDim.x, false, "local CTAs");
+  }
+  __syncthreads();
+  const size_t gtid = blockIdx.x * (size_t)blockDim.x + tid;
+  const size_t gthreads = (size_t)gridDim.x * blockDim.x;
+  const int d4 = d >> 2;
+  if (world > 1) {
+    // 2.
+    if (tid < world) {
+      if (blockIdx.x == 0) {
+        fence_sys();
+        st_release_sys(&reinterpret_cast<GramCtl*>(fa.peer[tid])->flag1[fa.rank], target);
+      }
+      gram_spin(&ctl->flag1[tid], target, true, "peer partial results");
+    }
+    __syncthreads();
+    // 3.
+    const int rows_per = (d + world - 1) / world;
+    const int r0 = min(d, fa.rank * rows_per), r1 = min(d, r0 + rows_per);
+    const size_t total = (size_t)(r1 - r0) * d4;
+    constexpr int PB = 4;
+    for (size_t i = gtid; i < total; i += gthreads) {
+      const int row = r0 + (int)(i / d4);
+      const int c4 = (int)(i % d4);
+      if (c4 * 4 + 3 < (row / MT) * MT) continue;          // below the computed macro-tile triangle
+      const size_t off = 256 + ((size_t)row * d + c4 * 4) * sizeof(float);
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int p0 = 0; p0 < world; p0 += PB) {
+        float4 v[PB];
+#pragma unroll
+        for (int pp = 0; pp < PB; ++pp) {
+          v[pp] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (p0 + pp < world) v[pp] = ld_volatile_f4(fa.peer[p0 + pp] + off);
+        }
+#pragma unroll
+        for (int pp = 0; pp < PB; ++pp) { acc.x += v[pp].x; acc.y += v[pp].y; acc.z += v[pp].z; acc.w += v[pp].w; }
+      }
+      for (int p = 0; p < world; ++p) *reinterpret_cast<float4*>(fa.peer[(fa.rank + p) % world] + off) = acc;
+    }
+    fence_sys();
+  }
+  // 4.
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    const uint32_t old = atomicAdd(&ctl->done2, 1u);
+    if (world > 1 && old == gridDim.x - 1) {          // last CTA of this rank: all its pushes are fenced
+      fence_sys();
+      for (int p = 0; p < world; ++p)
+        st_release_sys(&reinterpret_cast<GramCtl*>(fa.peer[p])->flag2[fa.rank], target);
+    }
+    gram_spin(&ctl->done2, gridDim.x, false, "local CTAs (2)");
+  }
+  if (world > 1 && tid < world) gram_spin(&ctl->flag2[tid], target, true, "peer reduced slices");
+  __syncthreads();
+  // 5.
+  const size_t total = (size_t)d * d;
+  for (size_t idx = gtid; idx < total; idx += gthreads) {
+    const int r = (int)(idx / d), c = (int)(idx % d);
+    if (r > c) G[idx] = ld_volatile_f32(G + (size_t)c * d + r);
+  }
+}
+
+template <int FUSED>
 __global__ void __launch_bounds__(NTHREADS, 1)
 gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int nmt, int ntri,
-               long long rows_per_slab, long long nslabs, float* __restrict__ G) {
+               long long rows_per_slab, long long nslabs, float* __restrict__ G, const GramFused fa) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = smem_u32(smem_raw);
   if ((base & 1023u) != 0) { if (threadIdx.x == 0) printf("harp_b200: smem base not 1024-aligned\n"); __trap(); }
@@ -210,6 +324,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc_1sm(tmem_base, TMEM_COLS);
+  if (FUSED) gram_fused_tail(fa, d);
 }
 
 // Only macro-tiles with tj >= ti were computed: copy the upper triangle onto the lower one.
@@ -308,6 +423,49 @@ __global__ void moments_init_kernel(int d, double* sum, double* sumsq, float* mn
 using namespace hb;
 using namespace hb::gram;
 
+struct GramPlan { CUtensorMap tm; int nmt, ntri, grid; long long rows_per_slab, nslabs; };
+
+// Tensor map + work decomposition of one XᵀX pass (tensor-core path).
+static int gram_plan(GramPlan& P, const float* X, long long n, int d) {
+  // 3-D view of X: dim0 = 32 floats inside a slab, dim1 = rows, dim2 = slab index
+  typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                    CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                    CUtensorMapFloatOOBfill);
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    HB_CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+    HB_REQUIRE(q == cudaDriverEntryPointSuccess && p != nullptr, "cuTensorMapEncodeTiled unavailable");
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  const long long nn = n > 0 ? n : 1;
+  cuuint64_t gdim[3] = {(cuuint64_t)SLAB, (cuuint64_t)nn, (cuuint64_t)(d / SLAB)};
+  cuuint64_t gstr[2] = {(cuuint64_t)d * 4, (cuuint64_t)SLAB * 4};
+  cuuint32_t box[3] = {SLAB, KC, MT / SLAB};
+  cuuint32_t est[3] = {1, 1, 1};
+  CUresult r = fn(&P.tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(X), gdim, gstr, box, est,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  HB_REQUIRE(r == CUDA_SUCCESS, "hb_gram: cuTensorMapEncodeTiled failed (%d)", (int)r);
+  P.nmt = (d + MT - 1) / MT;
+  P.ntri = P.nmt * (P.nmt + 1) / 2;
+  const int sms = sm_count();
+  // row slabs: enough units to balance the grid, each a multiple of KC rows
+  long long nslabs = (5LL * sms + P.ntri - 1) / P.ntri;
+  long long rows_per_slab = ((nn + nslabs - 1) / nslabs + KC - 1) / KC * KC;
+  if (rows_per_slab < 4 * KC) rows_per_slab = 4 * KC;
+  nslabs = n > 0 ? (n + rows_per_slab - 1) / rows_per_slab : 0;
+  P.rows_per_slab = rows_per_slab;
+  P.nslabs = nslabs;
+  const long long nunits = nslabs * P.ntri;
+  P.grid = sms;
+  if ((long long)P.grid > nunits) P.grid = (int)nunits;
+  if (P.grid < 1) P.grid = 1;
+  return 0;
+}
+
 extern "C" {
 
 int hb_gram_tc_supported(int d) { return (d >= 32 && d % 32 == 0 && d <= 16384) ? 1 : 0; }
@@ -322,40 +480,13 @@ int hb_gram(const float* X, long long n, int d, float* G, int flags, void* strea
                   (reinterpret_cast<uintptr_t>(X) & 15) == 0 && (reinterpret_cast<uintptr_t>(G) & 15) == 0 &&
                   n < (1LL << 31);
   if (tc) {
-    // 3-D view of X: dim0 = 32 floats inside a slab, dim1 = rows, dim2 = slab index
-    typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
-                                      CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
-                                      CUtensorMapFloatOOBfill);
-    static EncodeTiledFn fn = nullptr;
-    if (fn == nullptr) {
-      void* p = nullptr;
-      cudaDriverEntryPointQueryResult q;
-      HB_CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
-      HB_REQUIRE(q == cudaDriverEntryPointSuccess && p != nullptr, "cuTensorMapEncodeTiled unavailable");
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-    }
-    CUtensorMap tm;
-    cuuint64_t gdim[3] = {(cuuint64_t)SLAB, (cuuint64_t)n, (cuuint64_t)(d / SLAB)};
-    cuuint64_t gstr[2] = {(cuuint64_t)d * 4, (cuuint64_t)SLAB * 4};
-    cuuint32_t box[3] = {SLAB, KC, MT / SLAB};
-    cuuint32_t est[3] = {1, 1, 1};
-    CUresult r = fn(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(X), gdim, gstr, box, est,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    HB_REQUIRE(r == CUDA_SUCCESS, "hb_gram: cuTensorMapEncodeTiled failed (%d)", (int)r);
-    const int nmt = (d + MT - 1) / MT;
-    const int ntri = nmt * (nmt + 1) / 2;
+    GramPlan P;
+    if (gram_plan(P, X, n, d) != 0) return -1;
     const int sms = sm_count();
-    // row slabs: enough units to balance the grid, each a multiple of KC rows
-    long long nslabs = (5LL * sms + ntri - 1) / ntri;
-    long long rows_per_slab = ((n + nslabs - 1) / nslabs + KC - 1) / KC * KC;
-    if (rows_per_slab < 4 * KC) rows_per_slab = 4 * KC;
-    nslabs = (n + rows_per_slab - 1) / rows_per_slab;
-    const long long nunits = nslabs * ntri;
-    int grid = sms; if ((long long)grid > nunits) grid = (int)nunits;
-    HB_CUDA_OK(cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::total));
-    gram_tc_kernel<<<grid, NTHREADS, Smem::total, stream>>>(tm, n, d, nmt, ntri, rows_per_slab, nslabs, G);
+    HB_CUDA_OK(cudaFuncSetAttribute(gram_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::total));
+    GramFused nofuse;
+    memset(&nofuse, 0, sizeof(nofuse));
+    gram_tc_kernel<0><<<P.grid, NTHREADS, Smem::total, stream>>>(P.tm, n, d, P.nmt, P.ntri, P.rows_per_slab, P.nslabs, G, nofuse);
     HB_CUDA_OK(cudaGetLastError());
     mirror_kernel<<<sms * 2, 256, 0, stream>>>(G, d);
     HB_CUDA_OK(cudaGetLastError());
@@ -372,6 +503,49 @@ int hb_gram(const float* X, long long n, int d, float* G, int flags, void* strea
     mirror32_kernel<<<sm_count() * 2, 256, 0, stream>>>(G, d);
     HB_CUDA_OK(cudaGetLastError());
   }
+  return 0;
+}
+
+size_t hb_gram_fused_state_bytes(int d) { return 256 + (size_t)d * d * sizeof(float); }
+
+// XᵀX of this rank's rows + allreduce over the ranks in ONE launch; the result is left in every rank's state
+// block at byte offset 256 (row-major d x d).  `epoch` = 0, 1, 2, ... per state block, identical on all ranks;
+// the block must be zero-filled once before epoch 0 (and all ranks synchronised) so the flags start at 0.
+int hb_gram_allreduce_fused(const float* X, long long n, int d, void* const* peer_state, int rank, int world,
+                            unsigned epoch, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  HB_REQUIRE(world >= 1 && world <= HB_MAX_RANKS && rank >= 0 && rank < world, "hb_gram_allreduce_fused: bad rank %d / world %d", rank, world);
+  HB_REQUIRE(n >= 0 && n < (1LL << 31) && hb_gram_tc_supported(d), "hb_gram_allreduce_fused: shape (n=%lld, d=%d) not supported", n, d);
+  GramFused fa;
+  memset(&fa, 0, sizeof(fa));
+  for (int i = 0; i < world; ++i) {
+    HB_REQUIRE(peer_state[i] != nullptr && (reinterpret_cast<uintptr_t>(peer_state[i]) & 255) == 0,
+               "hb_gram_allreduce_fused: state pointer of rank %d is null or not 256-byte aligned", i);
+    fa.peer[i] = reinterpret_cast<uint8_t*>(peer_state[i]);
+  }
+  fa.rank = rank; fa.world = world; fa.epoch = epoch;
+  uint8_t* me = fa.peer[rank];
+  float* G = reinterpret_cast<float*>(me + 256);
+  HB_REQUIRE(n == 0 || (X != nullptr && (reinterpret_cast<uintptr_t>(X) & 15) == 0), "hb_gram_allreduce_fused: X must be 16-byte aligned");
+  // counters of this launch + the accumulator; peers stopped touching this block when our previous launch ended
+  HB_CUDA_OK(cudaMemsetAsync(me, 0, 16, stream));
+  HB_CUDA_OK(cudaMemsetAsync(G, 0, (size_t)d * d * sizeof(float), stream));
+  GramPlan P;
+  if (gram_plan(P, n > 0 ? X : G, n, d) != 0) return -1;
+  HB_CUDA_OK(cudaFuncSetAttribute(gram_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::total));
+  // the tail spins on counters fed by the other CTAs of the launch: one CTA per SM, cooperative launch
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)P.grid);
+  cfg.blockDim = dim3(NTHREADS);
+  cfg.dynamicSmemBytes = Smem::total;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  HB_CUDA_OK(cudaLaunchKernelEx(&cfg, gram_tc_kernel<1>, P.tm, n, d, P.nmt, P.ntri, P.rows_per_slab, P.nslabs, G, fa));
   return 0;
 }
 

@@ -98,15 +98,28 @@ def run_workload(args, rank, world, dev):
         n, d = 50_000_000 // world, 1024
         n = min(n, 6_250_000)
         X = torch.randn(n, d, device=dev)
-        G = symm.alloc(d * d, torch.float32).view(d, d) if symm is not None else torch.empty(d, d, device=dev)
+        from .ops.gram import FusedGram
         s = symm.alloc(d, torch.float64) if symm is not None else None
+        fused = None
+        if world == 1 or symm is not None:          # Gram + partial-result allreduce in one launch
+            nb = FusedGram.state_bytes(d)
+            if symm is not None:
+                st = symm.alloc(nb, torch.uint8)
+                fused = FusedGram(st, [p + symm.offset_of(st) for p in symm.peer_ptrs], rank, d)
+            else:
+                st = torch.empty(nb, dtype=torch.uint8, device=dev)
+                fused = FusedGram(st, [st.data_ptr()], 0, d)
+            barrier()
+        G = torch.empty(d, d, device=dev) if fused is None else None
 
         def step():
-            gram(X, out=G)
+            if fused is not None:
+                fused(X)
+            else:
+                gram(X, out=G)
             m = moments(X)
             if world > 1:
                 if symm is not None:
-                    symm.allreduce_sum_(G)
                     s.copy_(m.sum); symm.allreduce_sum_(s)
                 else:
                     dist.all_reduce(G); dist.all_reduce(m.sum)

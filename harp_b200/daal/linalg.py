@@ -17,7 +17,7 @@ from typing import Dict, NamedTuple, Optional, Tuple
 import torch
 import torch.distributed as dist
 
-from ..ops.gram import gram, moments
+from ..ops.gram import fused_gram_for, gram, moments
 
 
 def _allreduce_(t: torch.Tensor, comm, op: str = "sum") -> torch.Tensor:
@@ -37,6 +37,17 @@ def _allreduce_(t: torch.Tensor, comm, op: str = "sum") -> torch.Tensor:
 
 def _f64(t: torch.Tensor) -> torch.Tensor:
     return t.double()
+
+
+def _gram_allreduced(X: torch.Tensor, comm) -> torch.Tensor:
+    """Global ``XᵀX`` in float64.  On CUDA with a tensor-core-sized ``d`` the partial Gram and its allreduce
+    are ONE kernel launch (``ops.gram.FusedGram``); otherwise Gram + ``_allreduce_``."""
+    fg = fused_gram_for(comm, X.shape[1], X.device) if X.dtype == torch.float32 and X.shape[0] < (1 << 31) else None
+    if fg is not None:
+        return _f64(fg(X))
+    G = _f64(gram(X))
+    _allreduce_(G, comm)
+    return G
 
 
 # ---------------------------------------------------------------------------------------
@@ -89,10 +100,10 @@ def _cross_product_partials(X: torch.Tensor, comm) -> Tuple[torch.Tensor, torch.
     """(XᵀX, Σx, n) allreduced — DAAL covariance partial results (nObservations, sum, crossProduct)."""
     if X.layout != torch.strided:
         X = X.to_dense()
-    G = _f64(gram(X))
+    G = _gram_allreduced(X, comm)
     s = moments(X).sum.clone()
     n = torch.tensor([float(X.shape[0])], dtype=torch.float64, device=X.device)
-    _allreduce_(G, comm); _allreduce_(s, comm); _allreduce_(n, comm)
+    _allreduce_(s, comm); _allreduce_(n, comm)
     return G, s, float(n.item())
 
 
@@ -227,9 +238,7 @@ def _normal_eq_partials(X: torch.Tensor, Y: torch.Tensor, comm):
     Z[:, 0] = 1
     Z[:, 1:1 + d] = X
     Z[:, 1 + d:width] = Y
-    G = _f64(gram(Z))[:width, :width].contiguous()
-    _allreduce_(G, comm)
-    return G
+    return _gram_allreduced(Z, comm)[:width, :width].contiguous()
 
 
 def linear_regression_normeq(X: torch.Tensor, Y: torch.Tensor, comm=None, ridge: float = 0.0) -> LinearModel:

@@ -74,3 +74,80 @@ def moments(X: torch.Tensor) -> Moments:
                                  _native.ptr(mx), 0, _native.stream_ptr()), "hb_moments")
     _native.count_launch(2)
     return Moments(s, ss, mn, mx, n)
+
+
+class FusedGram:
+    """``XᵀX`` of this rank's rows **and** the allreduce of the ranks' partial results in one launch
+    (``csrc/gram.cu``: ``gram_tc_kernel<1>`` + ``gram_fused_tail``) — the DAAL-style "partial result →
+    master → broadcast" step (``HD/data_comm/HarpDAALComm.java:203-246``) done over NVLink peer memory by the
+    kernel that produced the partial result.  ``state`` is this rank's block of a symmetric slab (same offset
+    on every rank), ``peer_ptrs`` the device addresses of that block on every rank.  Works on one GPU too
+    (Gram + mirror in one launch)."""
+
+    def __init__(self, state: torch.Tensor, peer_ptrs, rank: int, d: int):
+        lib = _native.lib()
+        _declare(lib)
+        lib.hb_gram_fused_state_bytes.restype = ctypes.c_size_t
+        lib.hb_gram_fused_state_bytes.argtypes = [ctypes.c_int]
+        lib.hb_gram_allreduce_fused.argtypes = [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_void_p,
+                                                ctypes.c_int, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p]
+        assert lib.hb_gram_tc_supported(d), f"fused Gram needs d % 32 == 0 (got {d})"
+        need = self.state_bytes(d)
+        assert state.dtype == torch.uint8 and state.numel() >= need and state.data_ptr() % 256 == 0
+        assert int(peer_ptrs[rank]) == state.data_ptr()
+        self.lib, self.d, self.rank, self.world = lib, int(d), int(rank), len(peer_ptrs)
+        self.state = state
+        self._peers = (ctypes.c_void_p * self.world)(*[ctypes.c_void_p(int(p)) for p in peer_ptrs])
+        self.G = state[256:256 + d * d * 4].view(torch.float32).view(d, d)
+        self.epoch = 0
+        state[:256].zero_()          # flags start at 0; the caller barriers across ranks before the first call
+
+    @staticmethod
+    def state_bytes(d: int) -> int:
+        return 256 + d * d * 4
+
+    def __call__(self, X: torch.Tensor) -> torch.Tensor:
+        """Returns the global Gram matrix (a view of the state, overwritten by the next call)."""
+        assert X.dtype == torch.float32 and X.dim() == 2 and X.shape[1] == self.d
+        X = X.contiguous()
+        rc = self.lib.hb_gram_allreduce_fused(_native.ptr(X), X.shape[0], self.d, ctypes.cast(self._peers, ctypes.c_void_p),
+                                              self.rank, self.world, self.epoch, _native.stream_ptr())
+        _native.check(rc, "hb_gram_allreduce_fused")
+        _native.count_launch(1)
+        self.epoch += 1
+        return self.G
+
+
+def fused_gram_for(comm, d: int, device: torch.device) -> Optional["FusedGram"]:
+    """A cached ``FusedGram`` bound to ``comm``'s symmetric workspace (None when the fused path does not apply:
+    CPU, ``d % 32 != 0``, or several ranks without a symmetric workspace)."""
+    if device.type != "cuda" or d % 32 != 0 or d < 32 or d > 16384:
+        return None
+    world = 1 if comm is None else comm.world
+    symm = None if comm is None else getattr(comm, "symm", None)
+    if world > 1 and symm is None:
+        return None
+    holder = comm if comm is not None else fused_gram_for
+    cache = getattr(holder, "_fused_gram_cache", None)
+    if cache is None:
+        cache = {}
+        setattr(holder, "_fused_gram_cache", cache)
+    key = (d, device.index)
+    if key not in cache:
+        nbytes = FusedGram.state_bytes(d)
+        if world > 1:
+            try:
+                st = symm.alloc(nbytes, torch.uint8)
+            except MemoryError:
+                cache[key] = None
+                return None
+            off = symm.offset_of(st)
+            fg = FusedGram(st, [p + off for p in symm.peer_ptrs], comm.rank, d)
+            torch.cuda.synchronize(device)
+            import torch.distributed as dist
+            dist.barrier(group=comm.group)
+        else:
+            st = torch.empty(nbytes, dtype=torch.uint8, device=device)
+            fg = FusedGram(st, [st.data_ptr()], 0, d)
+        cache[key] = fg
+    return cache[key]

@@ -91,6 +91,23 @@ def main():
     if rank == 0:
         print("fused kmeans ok", flush=True)
 
+    # Gram + partial-result allreduce in one launch == local Gram + NCCL allreduce
+    from harp_b200.ops.gram import FusedGram, gram
+    for d_ in (256, 1024, 96):
+        st = ws.alloc(FusedGram.state_bytes(d_), torch.uint8)
+        fg = FusedGram(st, [p + ws.offset_of(st) for p in ws.peer_ptrs], rank, d_)
+        torch.cuda.synchronize(); dist.barrier()
+        for rep in range(3):
+            Xg = torch.randn(3000 + 500 * rank + 100 * rep, d_, device=dev, generator=g)
+            Gf = fg(Xg).clone()
+            Gr = gram(Xg); dist.all_reduce(Gr); torch.cuda.synchronize()
+            torch.testing.assert_close(Gf, Gr, rtol=1e-5, atol=1e-4 * Gr.abs().max().item())
+            assert torch.equal(Gf, Gf.t())
+            ref = Gf.clone(); dist.broadcast(ref, src=0)
+            assert torch.equal(Gf, ref)                       # rank-ordered sums: identical bits everywhere
+    if rank == 0:
+        print("fused gram ok", flush=True)
+
     # timing of the 5 MB allreduce vs NCCL
     ws.reset()
     n = 10000 * 129
