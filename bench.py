@@ -38,7 +38,7 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="harp_b200", choices=["harp_b200", "reference"])
+    ap.add_argument("--impl", default="harp_b200", choices=["harp_b200", "reference", "nccl_cublas"])
     ap.add_argument("--workload", default="kmeans", choices=["kmeans", "sgd", "lda", "gram"])
     ap.add_argument("--comm", default="auto", choices=["auto", "nccl", "p2p", "fused"])
     ap.add_argument("--points-per-gpu", type=int, default=POINTS_PER_GPU)
@@ -143,6 +143,10 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
+
+    if args.impl == "nccl_cublas":          # library-only arm: cuBLAS + stock torch ops + NCCL, none of our kernels
+        from harp_b200.baseline_arm import run as run_baseline
+        return run_baseline(args, rank, world, dev, ClockSampler)
 
     if args.workload != "kmeans":
         from harp_b200.bench_workloads import run_workload

@@ -60,7 +60,10 @@ struct SgdArgs {
   unsigned long long* trained;   // [1]    ratings updated (atomicAdd)
   unsigned long long deadline_ns;  // time budget in ns measured from kernel entry; 0 = no deadline
   unsigned int ticket_base;
-  int B;
+  int B;                     // CTAs = row-blocks
+  int C;                     // column-blocks (ring schedule: C == B)
+  int dynamic;               // 0 = Latin-square ticket ring, 1 = dynamic: any free column-block not yet visited
+  unsigned int* col_lock;    // [C] dynamic schedule: 0 = free, 1 = held (all 0 between launches)
   int rank;
   float eps, lambda;
 };
@@ -69,25 +72,66 @@ template <int RV>   // float4s per lane: rank <= 128 * RV
 __global__ void __launch_bounds__(SGD_THREADS, 1) sgd_pass_kernel(SgdArgs a) {
   __shared__ int s_next;      // next segment of the current block
   __shared__ int s_stop;
+  __shared__ int s_c;         // column-block of this step
+  __shared__ unsigned s_done[64];   // dynamic schedule: column-blocks this CTA has already visited
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int i = blockIdx.x, B = a.B;
+  const int i = blockIdx.x, B = a.B, C = a.C;
   const int nl4 = a.rank >> 2;
   unsigned long long local_trained = 0;
   bool expired = false;
   const unsigned long long t_end = a.deadline_ns ? globaltimer_ns() + a.deadline_ns : 0ULL;
-  for (int t = 0; t < B; ++t) {
-    const int c = (i + t) % B;
-    // ---- acquire column-block c ----
-    if (threadIdx.x == 0) {
+  if (threadIdx.x < 64) s_done[threadIdx.x] = 0u;
+  __syncthreads();
+  int scan_from = (int)(((long long)i * C) / B);     // staggered start: no contention on the first step
+  for (int t = 0; t < C; ++t) {
+    // ---- acquire a column-block ----
+    if (a.dynamic) {
+      // The reference's Scheduler hands a worker ANY free column block it has not trained yet
+      // (dymoro/Scheduler.java:95-237).  Same here: warp 0 probes 32 candidates at a time and takes the first
+      // free one with a CAS, so a slow neighbour never stalls the ring behind it.
+      if (warp == 0) {
+        int got = -1;
+        while (got < 0) {
+          for (int base = 0; base < C && got < 0; base += 32) {
+            int cand = scan_from + base + lane;
+            const bool valid = base + lane < C;
+            cand %= C;
+            const bool open = valid && !((s_done[cand >> 5] >> (cand & 31)) & 1u) &&
+                              ld_acquire_gpu(a.col_lock + cand) == 0u;
+            unsigned m = __ballot_sync(0xffffffffu, open);
+            while (m != 0u && got < 0) {
+              const int l = __ffs(m) - 1;
+              m &= m - 1;
+              const int cc = __shfl_sync(0xffffffffu, cand, l);
+              unsigned old = 1u;
+              if (lane == 0) old = atomicCAS(a.col_lock + cc, 0u, 1u);
+              old = __shfl_sync(0xffffffffu, old, 0);
+              if (old == 0u) got = cc;
+            }
+          }
+          if (got < 0) __nanosleep(200);
+        }
+        if (lane == 0) {
+          __threadfence();
+          s_done[got >> 5] |= 1u << (got & 31);
+          s_c = got;
+          s_next = a.blk_seg_ptr[(size_t)i * C + got];
+          s_stop = (t_end != 0 && globaltimer_ns() > t_end) ? 1 : 0;
+        }
+        scan_from = (got + 1) % C;
+      }
+    } else if (threadIdx.x == 0) {
+      const int cr = (i + t) % B;
       const unsigned int want = a.ticket_base + (unsigned)t;
-      while (ld_acquire_gpu(a.col_ticket + c) != want) { __nanosleep(64); }
-      const int s0 = a.blk_seg_ptr[(size_t)i * B + c];
-      s_next = s0;
+      while (ld_acquire_gpu(a.col_ticket + cr) != want) { __nanosleep(64); }
+      s_c = cr;
+      s_next = a.blk_seg_ptr[(size_t)i * C + cr];
       s_stop = (t_end != 0 && globaltimer_ns() > t_end) ? 1 : 0;
     }
     __syncthreads();
     expired = (s_stop != 0);
-    const int s_end = a.blk_seg_ptr[(size_t)i * B + c + 1];
+    const int c = s_c;
+    const int s_end = a.blk_seg_ptr[(size_t)i * C + c + 1];
     if (!expired) {
       for (;;) {
         int seg = 0;
@@ -109,6 +153,7 @@ __global__ void __launch_bounds__(SGD_THREADS, 1) sgd_pass_kernel(SgdArgs a) {
         }
         // software pipeline: w of rating k+1 is in flight while rating k is updated
         int row_n = (k0 < k1) ? a.r_row[k0] : 0;
+        float v_n = (k0 < k1) ? a.r_val[k0] : 0.f;
         float4 w_n[RV];
 #pragma unroll
         for (int u = 0; u < RV; ++u)
@@ -119,9 +164,10 @@ __global__ void __launch_bounds__(SGD_THREADS, 1) sgd_pass_kernel(SgdArgs a) {
           float4 w[RV];
 #pragma unroll
           for (int u = 0; u < RV; ++u) w[u] = w_n[u];
-          const float v = a.r_val[k];
+          const float v = v_n;
           if (k + 1 < k1) {
             row_n = a.r_row[k + 1];
+            v_n = a.r_val[k + 1];
 #pragma unroll
             for (int u = 0; u < RV; ++u)
               if (lane + 32 * u < nl4) w_n[u] = ldcg4(a.W + (size_t)row_n * a.rank + (lane + 32 * u) * 4);
@@ -168,7 +214,10 @@ __global__ void __launch_bounds__(SGD_THREADS, 1) sgd_pass_kernel(SgdArgs a) {
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence();
-      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(a.col_ticket + c), "r"(a.ticket_base + (unsigned)t + 1u) : "memory");
+      if (a.dynamic)
+        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(a.col_lock + c), "r"(0u) : "memory");
+      else
+        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(a.col_ticket + c), "r"(a.ticket_base + (unsigned)t + 1u) : "memory");
     }
   }
   if (lane == 0 && local_trained) atomicAdd(a.trained, local_trained);
@@ -244,16 +293,39 @@ int hb_sgd_max_blocks(int rank) {
   return per_sm * sm_count();
 }
 
+static int sgd_launch(SgdArgs& a, void* stream);
+
 int hb_sgd_pass(float* W, float* H, const int* blk_seg_ptr, const int* seg_col, const int* seg_ptr,
                 const int* r_row, const float* r_val, int B, int rank, float eps, float lambda,
                 unsigned int* col_ticket, unsigned int ticket_base, unsigned long long deadline_ns,
                 unsigned long long* trained, void* stream) {
-  HB_REQUIRE(B >= 1 && rank >= 4 && rank % 4 == 0 && rank <= 512, "hb_sgd_pass: need rank %% 4 == 0 and rank <= 512 (got %d)", rank);
-  HB_REQUIRE(B <= hb_sgd_max_blocks(rank), "hb_sgd_pass: B=%d blocks cannot be co-resident (max %d)", B, hb_sgd_max_blocks(rank));
   SgdArgs a;
   a.W = W; a.H = H; a.blk_seg_ptr = blk_seg_ptr; a.seg_col = seg_col; a.seg_ptr = seg_ptr; a.r_row = r_row;
   a.r_val = r_val; a.col_ticket = col_ticket; a.trained = trained; a.deadline_ns = deadline_ns;
-  a.ticket_base = ticket_base; a.B = B; a.rank = rank; a.eps = eps; a.lambda = lambda;
+  a.ticket_base = ticket_base; a.B = B; a.C = B; a.dynamic = 0; a.col_lock = nullptr;
+  a.rank = rank; a.eps = eps; a.lambda = lambda;
+  return sgd_launch(a, stream);
+}
+
+// Dynamic schedule: B row-blocks (CTAs) x C column-blocks (C >= B, C <= 2048); blk_seg_ptr is [B*C + 1] and
+// col_lock [C] must be all zero (it is again when the pass completes).
+int hb_sgd_pass_dynamic(float* W, float* H, const int* blk_seg_ptr, const int* seg_col, const int* seg_ptr,
+                        const int* r_row, const float* r_val, int B, int C, int rank, float eps, float lambda,
+                        unsigned int* col_lock, unsigned long long deadline_ns, unsigned long long* trained,
+                        void* stream) {
+  HB_REQUIRE(C >= B && C <= 2048, "hb_sgd_pass_dynamic: need B <= C <= 2048 (B=%d, C=%d)", B, C);
+  SgdArgs a;
+  a.W = W; a.H = H; a.blk_seg_ptr = blk_seg_ptr; a.seg_col = seg_col; a.seg_ptr = seg_ptr; a.r_row = r_row;
+  a.r_val = r_val; a.col_ticket = nullptr; a.trained = trained; a.deadline_ns = deadline_ns;
+  a.ticket_base = 0; a.B = B; a.C = C; a.dynamic = 1; a.col_lock = col_lock;
+  a.rank = rank; a.eps = eps; a.lambda = lambda;
+  return sgd_launch(a, stream);
+}
+
+static int sgd_launch(SgdArgs& a, void* stream) {
+  const int B = a.B, rank = a.rank;
+  HB_REQUIRE(B >= 1 && rank >= 4 && rank % 4 == 0 && rank <= 512, "hb_sgd_pass: need rank %% 4 == 0 and rank <= 512 (got %d)", rank);
+  HB_REQUIRE(B <= hb_sgd_max_blocks(rank), "hb_sgd_pass: B=%d blocks cannot be co-resident (max %d)", B, hb_sgd_max_blocks(rank));
   void* args[] = {&a};
   const void* fn = rank <= 128 ? (const void*)sgd_pass_kernel<1> : rank <= 256 ? (const void*)sgd_pass_kernel<2>
                                                                                  : (const void*)sgd_pass_kernel<4>;

@@ -1,9 +1,10 @@
 """LDA-CGS engine with model rotation (``ml/java/src/main/java/edu/iu/lda/LDAMPCollectiveMapper.java:183-378``).
 
 Documents (and their dense doc-topic rows) stay on their worker; the word-topic table is sharded by
-word (home worker ``w % N``, slice ``(w // N) % 2``, slice-local row ``w // 2N``) and its two slices
+word (home worker ``w % N``, slice ``(w // N) % S``, slice-local row ``w // SN``) and its S slices
 travel the ring, double-buffered in symmetric memory and pulled over NVLink on a side stream while
-the other slice is being sampled.  Global topic sums are refreshed once per iteration
+the other slice is being sampled (``S = num_slices``: 2 like the reference for large panels, 1 for small
+ones, where one fatter panel per rotation step keeps the block schedule efficient).  Global topic sums are refreshed once per iteration
 (``:442-475``); log-likelihood follows ``CalcLikelihoodTask`` (``:699-752``).
 """
 from __future__ import annotations
@@ -19,7 +20,8 @@ from ..ops import lda as L
 
 class LDAEngine:
     def __init__(self, docs: torch.Tensor, words: torch.Tensor, num_docs_local: int, vocab: int, K: int,
-                 alpha: float, beta: float, *, symm=None, blocks: Optional[int] = None, seed: int = 0, group=None):
+                 alpha: float, beta: float, *, symm=None, blocks: Optional[int] = None, seed: int = 0, group=None,
+                 num_slices: Optional[int] = None):
         self.dev = docs.device
         self.K, self.V = int(K), int(vocab)
         self.alpha, self.beta = float(alpha), float(beta)
@@ -28,11 +30,20 @@ class LDAEngine:
         self.me = dist.get_rank(group) if dist.is_initialized() else 0
         self.symm = symm if self.N > 1 else None
         N = self.N
-        self.cap = max(1, (self.V + 2 * N - 1) // (2 * N))
+        if num_slices is None:
+            ntok_max = float(docs.numel())
+            if dist.is_initialized() and N > 1:
+                t = torch.tensor([ntok_max], dtype=torch.float64, device=self.dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+                ntok_max = float(t.item())
+            num_slices = 2 if (N == 1 or ntok_max / (2.0 * N) >= 4.0e6) else 1
+        self.S = S = int(num_slices)
+        assert S in (1, 2)
+        self.cap = max(1, (self.V + S * N - 1) // (S * N))
         if self.dev.type == "cuda":
             sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
             from ..ops.mf import auto_blocks
-            self.B = int(blocks) if blocks else auto_blocks(docs.numel() / (2.0 * N), min(L.max_blocks(self.K), sms), per_block=32)
+            self.B = int(blocks) if blocks else auto_blocks(docs.numel() / (float(S) * N), min(L.max_blocks(self.K), sms), per_block=32)
         else:
             self.B = int(blocks) if blocks else 2
         self.seed = int(seed)
@@ -41,22 +52,22 @@ class LDAEngine:
         self.ntok = int(docs.numel())
         z = torch.randint(0, self.K, (self.ntok,), device=self.dev, generator=g)
         words = words.to(torch.int64)
-        shard, slc, local = words % N, (words // N) % 2, words // (2 * N)
+        shard, slc, local = words % N, (words // N) % S, words // (S * N)
         self.panels: List[List[L.TokenPanel]] = []
         for s in range(N):
             per = []
-            for k in range(2):
+            for k in range(self.S):
                 m = (shard == s) & (slc == k)
                 per.append(L.build_token_panel(docs[m], local[m], z[m], self.B))
             self.panels.append(per)
         cdt = torch.int32
         self.n_dk = torch.zeros(num_docs_local, self.K, dtype=cdt, device=self.dev)
         for s in range(N):
-            for k in range(2):
+            for k in range(self.S):
                 p = self.panels[s][k]
                 L.count_into(p.tok_doc, p.tok_z, self.K, self.n_dk)
         self.Wbuf: List[List[torch.Tensor]] = []
-        for k in range(2):
+        for k in range(self.S):
             pair = []
             for _ in range(2 if N > 1 else 1):
                 if self.symm is not None:
@@ -66,7 +77,7 @@ class LDAEngine:
                 t.zero_()
                 pair.append(t)
             self.Wbuf.append(pair)
-        self.cur, self.rot = [0, 0], [0, 0]
+        self.cur, self.rot = [0] * S, [0] * S
         if self.dev.type == "cuda":
             self.comm_stream = torch.cuda.Stream(device=self.dev)
             self.ev_compute = [torch.cuda.Event(), torch.cuda.Event()]
@@ -75,7 +86,7 @@ class LDAEngine:
                 e.record()
         # word-topic table: one full rotation in which every worker adds its tokens to the visiting shard
         for _ in range(N):
-            for k in range(2):
+            for k in range(self.S):
                 self._wait_slice(k)
                 p = self.panels[self._visiting(k)][k]
                 L.count_into(p.tok_word, p.tok_z, self.K, self.Wbuf[k][self.cur[k]])
@@ -113,7 +124,7 @@ class LDAEngine:
 
     def _refresh_topic_sums(self) -> None:
         self.topic_sums.zero_()
-        for k in range(2):
+        for k in range(self.S):
             self._wait_slice(k)
             L.topic_sums(self.Wbuf[k][self.cur[k]], self.topic_sums)
         if self.N > 1:
@@ -121,11 +132,11 @@ class LDAEngine:
         self.commons.copy_((1.0 / (self.topic_sums.double() + self.beta * self.V)).float())
 
     def iterate(self, deadline_ms: Optional[float] = None) -> torch.Tensor:
-        """One iteration = N rotations x 2 slices, then the global topic-sum refresh."""
+        """One iteration = N rotations x S slices, then the global topic-sum refresh."""
         self.trained.zero_()
         self.iteration += 1
         for j in range(self.N):
-            for k in range(2):
+            for k in range(self.S):
                 self._wait_slice(k)
                 p = self.panels[self._visiting(k)][k]
                 L.lda_pass(p, self.n_dk, self.Wbuf[k][self.cur[k]], self.commons, self.alpha, self.beta,
@@ -140,12 +151,12 @@ class LDAEngine:
         document side ``Σ_d [Σ_k lgamma(α + n_dk) − lgamma(Kα + n_d)] + D lgamma(Kα) − D K lgamma(α)``."""
         b, a, K, V = self.beta, self.alpha, self.K, self.V
         acc = torch.zeros(1, dtype=torch.float64, device=self.dev)
-        for k in range(2):
+        for k in range(self.S):
             self._wait_slice(k)
             tab = self.Wbuf[k][self.cur[k]].double()
             # only rows that are real words of this shard/slice
             s = self._visiting(k)
-            gid = torch.arange(self.cap, device=self.dev) * (2 * self.N) + k * self.N + s
+            gid = torch.arange(self.cap, device=self.dev) * (self.S * self.N) + k * self.N + s
             tab = tab[gid < V]
             acc += torch.lgamma(tab + b).sum() - tab.shape[0] * K * math.lgamma(b)
         nd = self.n_dk.double()
@@ -159,17 +170,17 @@ class LDAEngine:
 
     def synchronize(self) -> None:
         if self.dev.type == "cuda":
-            for k in range(2):
+            for k in range(self.S):
                 self._wait_slice(k)
             torch.cuda.synchronize(self.dev)
 
     def home_word_rows(self):
         """``(global word ids, count rows)`` of the word-topic rows currently resident."""
         ids, rows = [], []
-        for k in range(2):
+        for k in range(self.S):
             self._wait_slice(k)
             s = self._visiting(k)
-            gid = torch.arange(self.cap, device=self.dev) * (2 * self.N) + k * self.N + s
+            gid = torch.arange(self.cap, device=self.dev) * (self.S * self.N) + k * self.N + s
             keep = gid < self.V
             ids.append(gid[keep]); rows.append(self.Wbuf[k][self.cur[k]][keep])
         return torch.cat(ids), torch.cat(rows)

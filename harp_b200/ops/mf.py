@@ -22,6 +22,7 @@ def _declare(lib) -> None:
     lib.hb_sgd_max_blocks.argtypes = [I]
     lib.hb_sgd_pass.argtypes = [P, P, P, P, P, P, P, I, I, F, F, P, U, ULL, P, P]
     lib.hb_device_time_ns.argtypes = [P, P]
+    lib.hb_sgd_pass_dynamic.argtypes = [P, P, P, P, P, P, P, I, I, I, F, F, P, ctypes.c_ulonglong, P, P]
     lib.hb_mf_sq_err.argtypes = [P, P, P, P, P, LL, I, P, P]
     lib.hb_ccd_update.argtypes = [P, P, P, P, P, P, I, F, P]
     lib._hb_mf_declared = True
@@ -29,15 +30,20 @@ def _declare(lib) -> None:
 
 @dataclass
 class SgdPanel:
-    """Ratings of (this worker's rows) x (one H slice), bucketed B x B, column-sorted inside blocks."""
+    """Ratings of (this worker's rows) x (one H slice), bucketed B x C, column-sorted inside blocks."""
     B: int
-    blk_seg_ptr: torch.Tensor   # int32 [B*B+1]
+    blk_seg_ptr: torch.Tensor   # int32 [B*C+1]
     seg_col: torch.Tensor       # int32 [nseg]
     seg_ptr: torch.Tensor       # int32 [nseg+1]
     r_row: torch.Tensor         # int32 [nnz]
     r_val: torch.Tensor         # float32 [nnz]
-    col_ticket: torch.Tensor    # uint32-as-int32 [B]
+    col_ticket: torch.Tensor    # uint32-as-int32 [C]: ring tickets, or (dynamic schedule) locks that rest at 0
     ticket_base: int = 0
+    C: int = 0                  # column-blocks; 0 / == B -> Latin-square ticket ring, > B -> dynamic schedule
+
+    @property
+    def ncolblocks(self) -> int:
+        return self.C if self.C else self.B
 
     @property
     def nnz(self) -> int:
@@ -50,37 +56,60 @@ def max_blocks(rank: int) -> int:
     return int(lib.hb_sgd_max_blocks(rank))
 
 
-def auto_blocks(nnz_per_panel: float, limit: int, per_block: int = 64) -> int:
+def auto_blocks(nnz_per_panel: float, limit: int, per_block: int = 300) -> int:
     """Blocks per side for a panel: a pass costs ~B hand-overs plus nnz/(B * warps) updates, so small panels
     want fewer, fatter blocks; capped by what one cooperative launch keeps resident."""
     import math
     return int(max(8, min(limit, math.isqrt(max(1, int(nnz_per_panel / per_block))))))
 
 
+def _serpentine_blocks(weight: torch.Tensor, B: int) -> torch.Tensor:
+    """Block id per item: items sorted by weight (descending) are dealt 0..B-1, B-1..0, 0..B-1, ... so every
+    block gets one item of each weight class and the block totals come out nearly equal."""
+    n = weight.numel()
+    order = torch.argsort(weight, descending=True, stable=True)
+    pos = torch.arange(n, device=weight.device)
+    off, rnd = pos % B, pos // B
+    blk_sorted = torch.where(rnd % 2 == 0, off, B - 1 - off)
+    blk = torch.empty(n, dtype=torch.int64, device=weight.device)
+    blk[order] = blk_sorted
+    return blk
+
+
 def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: int, max_run: int = 32,
-                hot_spread: bool = True) -> SgdPanel:
-    """Buckets a COO rating list (worker-local row ids, slice-local column ids).  Row block = row % B,
-    column block = col % B; inside a block ratings are ordered by column (then by original order).
+                hot_spread: bool = True, balance: bool = True, C: Optional[int] = None) -> SgdPanel:
+    """Buckets a COO rating list (worker-local row ids, slice-local column ids).  Rows and columns are dealt
+    to the B row-blocks / column-blocks by weight (``balance=False``: row % B, col % B); inside a block
+    ratings are ordered by column (then by original order).
     Column runs longer than ``max_run`` are cut into sub-runs (flagged in bit 31 of ``seg_col``) so that a
     popular column does not serialise a whole block on one warp."""
     dev = rows.device
     rows = rows.to(torch.int64)
     cols = cols.to(torch.int64)
     n = rows.numel()
+    C = B if not C else int(C)
+    assert C >= B
     if n == 0:
-        z = torch.zeros(B * B + 1, dtype=torch.int32, device=dev)
+        z = torch.zeros(B * C + 1, dtype=torch.int32, device=dev)
         e = torch.zeros(0, dtype=torch.int32, device=dev)
         return SgdPanel(B, z, e, torch.zeros(1, dtype=torch.int32, device=dev), e,
-                        torch.zeros(0, dtype=torch.float32, device=dev), torch.zeros(B, dtype=torch.int32, device=dev))
+                        torch.zeros(0, dtype=torch.float32, device=dev), torch.zeros(C, dtype=torch.int32, device=dev), 0, C)
     ncols = int(cols.max().item()) + 1
     # Hot columns (a blockbuster item, a stop word): if all their ratings sat in ONE column-block, that
     # heavy block would be handed round the ring through all B CTAs one after the other.  Their ratings
     # are dealt round-robin over all column-blocks instead; every run of such a column is flagged shared
     # (bit 31), i.e. its updates are merged with atomics, since several CTAs now work on it at once.
     cnt = torch.bincount(cols, minlength=ncols)
-    hot_thr = max(4 * max_run if max_run else 256, n // (4 * B) if hot_spread else n + 1)
+    hot_thr = max(4 * max_run if max_run else 256, n // (4 * C) if hot_spread else n + 1)
     hot_col = cnt > hot_thr if hot_spread else torch.zeros(ncols, dtype=torch.bool, device=dev)
-    cb = cols % B
+    # The ticket ring couples all CTAs: the pass runs at the pace of the heaviest row-block / column-block.
+    # Rows and columns are therefore dealt to blocks by weight (heaviest first, serpentine order), not by id.
+    if balance and B > 1:
+        row_blk = _serpentine_blocks(torch.bincount(rows), B)
+        col_blk = _serpentine_blocks(torch.where(hot_col, torch.zeros_like(cnt), cnt), C)
+        rb_of, cb = row_blk[rows], col_blk[cols]
+    else:
+        rb_of, cb = rows % B, cols % C
     if bool(hot_col.any()):
         order_c = torch.argsort(cols, stable=True)
         first = torch.zeros(ncols + 1, dtype=torch.int64, device=dev)
@@ -88,8 +117,8 @@ def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: i
         rank_in_col = torch.empty(n, dtype=torch.int64, device=dev)
         rank_in_col[order_c] = torch.arange(n, device=dev) - first[cols[order_c]]
         is_hot = hot_col[cols]
-        cb = torch.where(is_hot, (cols + rank_in_col) % B, cb)
-    blk = (rows % B) * B + cb
+        cb = torch.where(is_hot, (cols + rank_in_col) % C, cb)
+    blk = rb_of * C + cb
     key = blk * ncols + cols
     order = torch.argsort(key, stable=True)
     key_s = key[order]
@@ -112,22 +141,22 @@ def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: i
     seg_blk = uniq // ncols
     seg_col = (uniq % ncols).to(torch.int32)
     seg_col = torch.where(split_flag, seg_col | torch.tensor(-2147483648, dtype=torch.int32, device=dev), seg_col)
-    blk_seg_ptr = torch.searchsorted(seg_blk, torch.arange(B * B + 1, device=dev, dtype=torch.int64)).to(torch.int32)
+    blk_seg_ptr = torch.searchsorted(seg_blk, torch.arange(B * C + 1, device=dev, dtype=torch.int64)).to(torch.int32)
     return SgdPanel(B, blk_seg_ptr.contiguous(), seg_col.contiguous(), seg_ptr.to(torch.int32).contiguous(),
                     rows[order].to(torch.int32).contiguous(), vals[order].to(torch.float32).contiguous(),
-                    torch.zeros(B, dtype=torch.int32, device=dev))
+                    torch.zeros(C, dtype=torch.int32, device=dev), 0, C)
 
 
 def _cpu_sgd_pass(panel: SgdPanel, W, H, eps, lam) -> int:
     # sequential restatement in the kernel's own order: Latin-square steps, blocks, column runs
-    B = panel.B
+    B, C = panel.B, panel.ncolblocks
     bsp, sc, sp = panel.blk_seg_ptr.tolist(), (panel.seg_col & 0x7FFFFFFF).tolist(), panel.seg_ptr.tolist()
     rr, rv = panel.r_row.tolist(), panel.r_val.tolist()
     n = 0
-    for t in range(B):
+    for t in range(C):
         for i in range(B):
-            c = (i + t) % B
-            for s in range(bsp[i * B + c], bsp[i * B + c + 1]):
+            c = (i * C // B + t) % C if C != B else (i + t) % B
+            for s in range(bsp[i * C + c], bsp[i * C + c + 1]):
                 h = H[sc[s]]
                 for k in range(sp[s], sp[s + 1]):
                     w = W[rr[k]]
@@ -154,6 +183,14 @@ def sgd_pass(panel: SgdPanel, W: torch.Tensor, H: torch.Tensor, eps: float, lam:
     if trained is None:
         trained = torch.zeros(1, dtype=torch.int64, device=W.device)
     deadline = int(deadline_ms * 1e6) if deadline_ms is not None else 0     # budget from kernel entry
+    if panel.ncolblocks != panel.B:        # dynamic schedule: any free, not yet visited column-block
+        rc = lib.hb_sgd_pass_dynamic(_native.ptr(W), _native.ptr(H), _native.ptr(panel.blk_seg_ptr), _native.ptr(panel.seg_col),
+                                     _native.ptr(panel.seg_ptr), _native.ptr(panel.r_row), _native.ptr(panel.r_val), panel.B,
+                                     panel.ncolblocks, rank, float(eps), float(lam), _native.ptr(panel.col_ticket), deadline,
+                                     _native.ptr(trained), _native.stream_ptr())
+        _native.check(rc, "hb_sgd_pass_dynamic")
+        _native.count_launch()
+        return trained
     rc = lib.hb_sgd_pass(_native.ptr(W), _native.ptr(H), _native.ptr(panel.blk_seg_ptr), _native.ptr(panel.seg_col),
                          _native.ptr(panel.seg_ptr), _native.ptr(panel.r_row), _native.ptr(panel.r_val), panel.B, rank,
                          float(eps), float(lam), _native.ptr(panel.col_ticket), panel.ticket_base & 0xFFFFFFFF,

@@ -13,8 +13,10 @@ ntok = D * Ldoc
 g = torch.Generator(device="cuda").manual_seed(0)
 docs = torch.arange(D, device="cuda").repeat_interleave(Ldoc)
 words = (torch.rand(ntok, device="cuda", generator=g) ** 3 * V).long() % V        # Zipf-like
-for B in [int(x) for x in (sys.argv[5].split(",") if len(sys.argv) > 5 else ["148"])]:
-    eng = LDAEngine(docs, words, D, V, K, 0.01, 0.01, blocks=B, seed=1)
+import itertools
+Ss = [int(x) for x in (sys.argv[6].split(",") if len(sys.argv) > 6 else ["2"])]
+for B, S in itertools.product([int(x) for x in (sys.argv[5].split(",") if len(sys.argv) > 5 else ["148"])], Ss):
+    eng = LDAEngine(docs, words, D, V, K, 0.01, 0.01, blocks=B, seed=1, num_slices=S)
     for _ in range(2): eng.iterate()
     eng.synchronize()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
@@ -22,6 +24,6 @@ for B in [int(x) for x in (sys.argv[5].split(",") if len(sys.argv) > 5 else ["14
     for _ in range(3): eng.iterate()
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 3
-    print(json.dumps({"B": eng.B, "tokens": ntok, "K": K, "ms_per_iter": ms, "tokens_per_s": ntok / ms * 1e3,
+    print(json.dumps({"B": eng.B, "S": eng.S, "tokens": ntok, "K": K, "ms_per_iter": ms, "tokens_per_s": ntok / ms * 1e3,
                       "ll": eng.log_likelihood()}))
     del eng

@@ -48,6 +48,29 @@ def test_sgd_pass_trains_everything_and_reduces_loss(native_built, rank, B):
     assert int(panel.col_ticket.min()) == int(panel.col_ticket.max()) == 15 * B
 
 
+@pytest.mark.parametrize("rank,B,C", [(32, 16, 32), (128, 148, 296), (64, 37, 100)])
+def test_sgd_pass_dynamic_schedule(native_built, rank, B, C):
+    """Dynamic schedule (any free, not-yet-visited column-block; B row-blocks x C column-blocks): every rating
+    exactly once per pass, locks back at rest, loss goes down like the ring schedule's."""
+    from harp_b200.ops import mf
+    r, c, v = _problem(rank=rank)
+    r, c, v = r.cuda(), c.cuda(), v.cuda()
+    B = min(B, mf.max_blocks(rank))
+    panel = mf.build_panel(r, c, v, B, C=C)
+    assert panel.ncolblocks == C and panel.blk_seg_ptr.numel() == B * C + 1
+    g = torch.Generator(device="cuda").manual_seed(1)
+    W = torch.rand(3000, rank, device="cuda", generator=g) / math.sqrt(rank)
+    H = torch.rand(500, rank, device="cuda", generator=g) / math.sqrt(rank)
+    e0 = float(mf.sq_err(W, H, r, c, v))
+    for it in range(15):
+        n = mf.sgd_pass(panel, W, H, 0.01, 0.02)
+        assert int(n.item()) == r.numel()
+    torch.cuda.synchronize()
+    e1 = float(mf.sq_err(W, H, r, c, v))
+    assert math.isfinite(e1) and e1 < 0.15 * e0, (e0, e1)
+    assert int(panel.col_ticket.abs().max()) == 0
+
+
 def test_sgd_pass_matches_cpu_restatement(native_built):
     """Same panel, same order where it matters: one CTA (B=1) with ratings in distinct rows per column run
     is fully sequential per column, so the GPU result must match the CPU loop closely."""
