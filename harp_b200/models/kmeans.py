@@ -44,7 +44,7 @@ class KMeansEngine:
         self.variant = os.environ.get("HB_KMEANS_VARIANT", "auto")
         k, d = self.k, self.d
         if comm == "auto":
-            fused_ok = (self.dev.type == "cuda" and X.dtype == torch.float32 and d % 4 == 0 and d <= 256
+            fused_ok = (self.dev.type == "cuda" and X.dtype == torch.float32 and kops.tc_supported(d, k)
                         and self.variant in ("auto", "pair") and (self.world == 1 or symm is not None))
             comm = "fused" if fused_ok else ("p2p" if (symm is not None and self.world > 1) else "nccl")
         self.comm = comm

@@ -32,6 +32,11 @@ def workspace_bytes(n: int, k: int, d: int, simt: bool = False) -> int:
     return int(lib.hb_kmeans_workspace_bytes(k, d))
 
 
+def tc_supported(d: int, k: int) -> bool:
+    """Whether the tcgen05 kernels (and so the fused one-launch iteration) take this shape."""
+    return bool(_native.lib().hb_kmeans_tc_supported(int(d), int(k)))
+
+
 def _cpu_step(X, C, sums, counts, assign, obj, zero):
     # exact (x-c)^2 in the tensor's own precision, lowest index wins ties
     d2 = torch.cdist(X.double(), C.double()).pow(2) if X.shape[0] * C.shape[0] <= (1 << 24) else None

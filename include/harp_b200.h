@@ -111,6 +111,15 @@ int hb_kmeans_step_static(const float* X, long long n, int d, const float* C, in
 int hb_gram_tc_supported(int d);
 /* G[d,d] (+)= X^T X for row-major fp32 X[n,d]; TF32 products, fp32 accumulate; full symmetric output. */
 int hb_gram(const float* X, long long n, int d, float* G, int flags, void* stream);
+/* X^T X of this rank's rows AND the allreduce of the ranks' partial results in ONE launch (DAAL's
+ * "partial result -> master -> broadcast", HD/data_comm/HarpDAALComm.java:203-246, done over NVLink peer memory
+ * by the kernel that produced the partial).  Every rank owns a 256-byte-aligned, peer-addressable block of
+ * hb_gram_fused_state_bytes(d) bytes, zero-filled once before epoch 0 (then barrier across ranks); the global
+ * d x d result is left at byte offset 256 of every rank's block.  epoch = 0, 1, 2, ... identical on all ranks.
+ * Needs hb_gram_tc_supported(d) and n < 2^31. */
+size_t hb_gram_fused_state_bytes(int d);
+int hb_gram_allreduce_fused(const float* X, long long n, int d, void* const* peer_state, int rank, int world,
+                            unsigned epoch, void* stream);
 /* Per-column sum / sum of squares (double) and min / max (float) of X[n,d]. */
 int hb_moments(const float* X, long long n, int d, double* sum, double* sumsq, float* mn, float* mx,
                int flags, void* stream);
@@ -129,6 +138,13 @@ int hb_sgd_pass(float* W, float* H, const int* blk_seg_ptr, const int* seg_col, 
                 const int* r_row, const float* r_val, int B, int rank, float eps, float lambda,
                 unsigned int* col_ticket, unsigned int ticket_base, unsigned long long deadline_ns,
                 unsigned long long* trained, void* stream);
+/* Same pass with the reference's dynamic block scheduling (dymoro/Scheduler.java:95-237): B row-blocks (one CTA
+ * each) x C >= B column-blocks (C <= 2048); a CTA takes ANY free column-block it has not visited yet.
+ * blk_seg_ptr is [B*C + 1]; col_lock[C] must be all zero on entry and is all zero again on exit. */
+int hb_sgd_pass_dynamic(float* W, float* H, const int* blk_seg_ptr, const int* seg_col, const int* seg_ptr,
+                        const int* r_row, const float* r_val, int B, int C, int rank, float eps, float lambda,
+                        unsigned int* col_lock, unsigned long long deadline_ns, unsigned long long* trained,
+                        void* stream);
 /* Writes the device wall clock (ns) to *out_dev. */
 int hb_device_time_ns(unsigned long long* out_dev, void* stream);
 /* *sq_err += sum (v - w.h)^2 over a rating list. */

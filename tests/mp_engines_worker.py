@@ -32,7 +32,7 @@ def main():
     eng.synchronize()
     e1 = eng.rmse(r, c, v)
     assert e1 < 0.5 * e0, (e0, e1)
-    assert eng.rot[0] % world == 0 and eng.rot[1] % world == 0
+    assert all(r % world == 0 for r in eng.rot)
     ids = torch.cat([x[0] for x in eng.home_H().values()])
     assert bool((ids % world == rank).all())                       # shards are home again
     # ---- LDA ----
@@ -50,10 +50,24 @@ def main():
     assert ll1 > ll0, (ll0, ll1)
     assert int(lda.topic_sums.sum()) == D * L * world and int(lda.n_dk.sum()) == D * L
     tot = torch.zeros(1, dtype=torch.int64, device=dev)
-    for k in range(2):
+    for k in range(lda.S):
         tot += lda.Wbuf[k][lda.cur[k]].sum()
     dist.all_reduce(tot)
     assert int(tot.item()) == D * L * world
+    # both slice layouts of the rotation (the default picks by panel size)
+    other = 3 - eng.S
+    eng2 = MFSGDEngine(r, c, v, nr, nc, rk, 0.01, 0.02, symm=ws, seed=5, num_slices=other)
+    f0 = eng2.rmse(r, c, v)
+    for it in range(6):
+        assert int(eng2.epoch().item()) == nnz
+    eng2.synchronize()
+    assert eng2.rmse(r, c, v) < 0.7 * f0
+    lda2 = LDAEngine(docs, words, D, V, K, 0.1, 0.01, symm=ws, seed=2, num_slices=3 - lda.S)
+    m0 = lda2.log_likelihood()
+    for it in range(4):
+        assert int(lda2.iterate().item()) == D * L
+    lda2.synchronize()
+    assert lda2.log_likelihood() > m0 and int(lda2.topic_sums.sum()) == D * L * world
     dist.barrier()
     if rank == 0:
         print(f"ENGINES_OK world={world} sgd_rmse {e0:.4f}->{e1:.4f} lda_ll {ll0:.4e}->{ll1:.4e}", flush=True)
