@@ -21,7 +21,7 @@ from ..ops import lda as L
 class LDAEngine:
     def __init__(self, docs: torch.Tensor, words: torch.Tensor, num_docs_local: int, vocab: int, K: int,
                  alpha: float, beta: float, *, symm=None, blocks: Optional[int] = None, seed: int = 0, group=None,
-                 num_slices: Optional[int] = None):
+                 num_slices: Optional[int] = None, dk_dtype: str = "auto"):
         self.dev = docs.device
         self.K, self.V = int(K), int(vocab)
         self.alpha, self.beta = float(alpha), float(beta)
@@ -66,6 +66,15 @@ class LDAEngine:
             for k in range(self.S):
                 p = self.panels[s][k]
                 L.count_into(p.tok_doc, p.tok_z, self.K, self.n_dk)
+        # The sampling kernel is bound by reading one document-topic row per token; when no document is longer
+        # than an int16 can count, the table is kept in 16 bits (dk_dtype="int32" forces the wide table).
+        import os
+        dk_dtype = os.environ.get("HB_LDA_DK", dk_dtype)          # triage knob
+        if dk_dtype == "auto":
+            longest = int(torch.bincount(docs.long(), minlength=1).max().item()) if self.ntok else 0
+            dk_dtype = "int16" if (self.dev.type == "cuda" and longest < 32768) else "int32"
+        if dk_dtype == "int16":
+            self.n_dk = self.n_dk.to(torch.int16)
         self.Wbuf: List[List[torch.Tensor]] = []
         for k in range(self.S):
             pair = []

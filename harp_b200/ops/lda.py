@@ -20,6 +20,7 @@ def _declare(lib) -> None:
                            ctypes.c_ulonglong)
     lib.hb_lda_max_blocks.argtypes = [I]
     lib.hb_lda_pass.argtypes = [P, P, P, P, P, P, P, P, I, I, F, F, ULL, P, U, ULL, P, P]
+    lib.hb_lda_pass_dk16.argtypes = [P, P, P, P, P, P, P, P, I, I, F, F, ULL, P, U, ULL, P, P]
     lib.hb_lda_topic_sums.argtypes = [P, LL, I, P, P]
     lib.hb_lda_count.argtypes = [P, P, LL, I, P, P]
     lib._hb_lda_declared = True
@@ -119,16 +120,19 @@ def lda_pass(panel: TokenPanel, n_dk: torch.Tensor, n_wk: torch.Tensor, commons:
         return out
     lib = _native.lib()
     _declare(lib)
-    assert n_dk.dtype == torch.int32 and n_wk.dtype == torch.int32 and commons.dtype == torch.float32
+    # n_dk may be int16 (documents shorter than 32768 tokens): half the row traffic, the kernel's bound
+    assert n_dk.dtype in (torch.int32, torch.int16) and n_wk.dtype == torch.int32 and commons.dtype == torch.float32
+    assert n_dk.is_contiguous() and n_wk.is_contiguous()
     K = n_dk.shape[1]
     if trained is None:
         trained = torch.zeros(1, dtype=torch.int64, device=n_dk.device)
     deadline = int(deadline_ms * 1e6) if deadline_ms is not None else 0
-    rc = lib.hb_lda_pass(_native.ptr(n_dk), _native.ptr(n_wk), _native.ptr(commons), _native.ptr(panel.blk_seg_ptr),
-                         _native.ptr(panel.seg_word), _native.ptr(panel.seg_ptr), _native.ptr(panel.tok_doc),
-                         _native.ptr(panel.tok_z), panel.B, K, float(alpha), float(beta), int(seed) & 0xFFFFFFFFFFFFFFFF,
-                         _native.ptr(panel.col_ticket), panel.ticket_base & 0xFFFFFFFF, deadline, _native.ptr(trained),
-                         _native.stream_ptr())
+    fn = lib.hb_lda_pass_dk16 if n_dk.dtype == torch.int16 else lib.hb_lda_pass
+    rc = fn(_native.ptr(n_dk), _native.ptr(n_wk), _native.ptr(commons), _native.ptr(panel.blk_seg_ptr),
+            _native.ptr(panel.seg_word), _native.ptr(panel.seg_ptr), _native.ptr(panel.tok_doc),
+            _native.ptr(panel.tok_z), panel.B, K, float(alpha), float(beta), int(seed) & 0xFFFFFFFFFFFFFFFF,
+            _native.ptr(panel.col_ticket), panel.ticket_base & 0xFFFFFFFF, deadline, _native.ptr(trained),
+            _native.stream_ptr())
     _native.check(rc, "hb_lda_pass")
     panel.ticket_base = (panel.ticket_base + panel.B) & 0x7FFFFFFF
     _native.count_launch()

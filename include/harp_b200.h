@@ -164,6 +164,14 @@ int hb_lda_pass(int* n_dk, int* n_wk, const float* commons, const int* blk_seg_p
                 const int* seg_ptr, const int* tok_doc, int* tok_z, int B, int K, float alpha, float beta,
                 unsigned long long seed, unsigned int* col_ticket, unsigned int ticket_base,
                 unsigned long long deadline_ns, unsigned long long* trained, void* stream);
+/* Same pass with the document-topic table held as unsigned 16-bit counts (every document shorter than 65536
+ * tokens; table and rows 8-byte aligned): the kernel is bound by one document-row read per token, so this halves
+ * its traffic, and the next token's row is fetched while the current token is sampled. */
+int hb_lda_pass_dk16(unsigned short* n_dk16, int* n_wk, const float* commons, const int* blk_seg_ptr,
+                     const int* seg_word, const int* seg_ptr, const int* tok_doc, int* tok_z, int B, int K,
+                     float alpha, float beta, unsigned long long seed, unsigned int* col_ticket,
+                     unsigned int ticket_base, unsigned long long deadline_ns, unsigned long long* trained,
+                     void* stream);
 /* sums[k] += sum over words of n_wk[w][k] (int64). */
 int hb_lda_topic_sums(const int* n_wk, long long words, int K, long long* sums, void* stream);
 /* counts[idx0[t] * K + z[t]] += 1 for every token. */

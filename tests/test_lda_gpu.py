@@ -14,11 +14,13 @@ def _corpus(D=400, V=300, K=8, L=60, seed=0):
     return d, w
 
 
-@pytest.mark.parametrize("K", [16, 100, 1000])
-def test_lda_tables_consistent_and_likelihood_improves(native_built, K):
+@pytest.mark.parametrize("K,dk", [(16, "int16"), (100, "int16"), (1000, "int16"), (1000, "int32"), (15, "int16"),
+                                  (15, "int32"), (100, "int32"), (300, "int16"), (1500, "int16")])
+def test_lda_tables_consistent_and_likelihood_improves(native_built, K, dk):
     from harp_b200.models.lda import LDAEngine
     d, w = _corpus(K=8)
-    eng = LDAEngine(d.cuda(), w.cuda(), 400, 300, K, 0.1, 0.01, seed=1)
+    eng = LDAEngine(d.cuda(), w.cuda(), 400, 300, K, 0.1, 0.01, seed=1, dk_dtype=dk)
+    assert eng.n_dk.dtype == (torch.int16 if dk == "int16" else torch.int32)
     ll0 = eng.log_likelihood()
     for it in range(15):
         n = eng.iterate()
@@ -27,7 +29,7 @@ def test_lda_tables_consistent_and_likelihood_improves(native_built, K):
     ll1 = eng.log_likelihood()
     assert ll1 > ll0, (ll0, ll1)
     # tables equal recounts from the assignments
-    nd = torch.zeros_like(eng.n_dk); nw = torch.zeros(eng.cap * 2, K, dtype=torch.int32, device="cuda")
+    nd = torch.zeros(eng.n_dk.shape, dtype=torch.int32, device="cuda")
     tot = 0
     for k in range(2):
         p = eng.panels[0][k]
@@ -36,7 +38,7 @@ def test_lda_tables_consistent_and_likelihood_improves(native_built, K):
         tab.view(-1).index_add_(0, p.tok_word.long() * K + p.tok_z.long(), torch.ones(p.ntok, dtype=torch.int32, device="cuda"))
         assert torch.equal(tab, eng.Wbuf[k][eng.cur[k]])
         tot += p.ntok
-    assert tot == d.numel() and torch.equal(nd, eng.n_dk)
+    assert tot == d.numel() and torch.equal(nd, eng.n_dk.int())
     assert int(eng.topic_sums.sum()) == d.numel() and int(eng.n_dk.min()) >= 0
 
 
