@@ -412,6 +412,65 @@ __global__ void moments_kernel(const float* __restrict__ X, long long n, int d, 
     if (hi >= 0.f) atomicMax(imx, __float_as_int(hi)); else atomicMin(reinterpret_cast<unsigned int*>(imx), __float_as_uint(hi));
   }
 }
+// Same reduction for d % 4 == 0: a lane owns 4 adjacent columns (one 16-byte load per row), a warp a 128-column
+// stripe, four rows are in flight per lane; ~2x the bandwidth of the scalar kernel on wide matrices.
+__global__ void __launch_bounds__(256) moments_vec4_kernel(const float* __restrict__ X, long long n, int d,
+                                                           double* __restrict__ sum, double* __restrict__ sumsq,
+                                                           float* __restrict__ mn, float* __restrict__ mx) {
+  const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int col = (blockIdx.x * 32 + cl) * 4;
+  double ds[4] = {0, 0, 0, 0}, dss[4] = {0, 0, 0, 0};
+  float lo[4], hi[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) { lo[q] = CUDART_INF_F; hi[q] = -CUDART_INF_F; }
+  if (col < d) {
+    const long long stride = (long long)gridDim.y * 8;
+    long long r = blockIdx.y * 8LL + rl;
+    for (; r + 3 * stride < n; r += 4 * stride) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = ld_nc_v4(X + (size_t)(r + u * stride) * d + col);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float e[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          ds[q] += (double)e[q]; dss[q] = fma((double)e[q], (double)e[q], dss[q]);
+          lo[q] = fminf(lo[q], e[q]); hi[q] = fmaxf(hi[q], e[q]);
+        }
+      }
+    }
+    for (; r < n; r += stride) {
+      const float4 v = ld_nc_v4(X + (size_t)r * d + col);
+      const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        ds[q] += (double)e[q]; dss[q] = fma((double)e[q], (double)e[q], dss[q]);
+        lo[q] = fminf(lo[q], e[q]); hi[q] = fmaxf(hi[q], e[q]);
+      }
+    }
+  }
+  __shared__ double sh_s[8][32][4], sh_ss[8][32][4];
+  __shared__ float sh_lo[8][32][4], sh_hi[8][32][4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) { sh_s[rl][cl][q] = ds[q]; sh_ss[rl][cl][q] = dss[q]; sh_lo[rl][cl][q] = lo[q]; sh_hi[rl][cl][q] = hi[q]; }
+  __syncthreads();
+  if (rl < 4 && col < d) {       // warp q of the first four finishes column col + q
+    const int q = rl;
+    double a = 0, b = 0;
+    float l = CUDART_INF_F, h = -CUDART_INF_F;
+    for (int i = 0; i < 8; ++i) {
+      a += sh_s[i][cl][q]; b += sh_ss[i][cl][q];
+      l = fminf(l, sh_lo[i][cl][q]); h = fmaxf(h, sh_hi[i][cl][q]);
+    }
+    atomicAdd(sum + col + q, a);
+    atomicAdd(sumsq + col + q, b);
+    int* imn = reinterpret_cast<int*>(mn + col + q);
+    int* imx = reinterpret_cast<int*>(mx + col + q);
+    if (l >= 0.f) atomicMin(imn, __float_as_int(l)); else atomicMax(reinterpret_cast<unsigned int*>(imn), __float_as_uint(l));
+    if (h >= 0.f) atomicMax(imx, __float_as_int(h)); else atomicMin(reinterpret_cast<unsigned int*>(imx), __float_as_uint(h));
+  }
+}
 __global__ void moments_init_kernel(int d, double* sum, double* sumsq, float* mn, float* mx) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < d) { sum[i] = 0.0; sumsq[i] = 0.0; mn[i] = CUDART_INF_F; mx[i] = -CUDART_INF_F; }
@@ -559,12 +618,14 @@ int hb_moments(const float* X, long long n, int d, double* sum, double* sumsq, f
     HB_CUDA_OK(cudaGetLastError());
   }
   if (n == 0) return 0;
-  const int gx = (d + 31) / 32;
+  const bool vec4 = (d % 4 == 0) && (reinterpret_cast<uintptr_t>(X) & 15) == 0;
+  const int gx = vec4 ? (d / 4 + 31) / 32 : (d + 31) / 32;
   long long gy = (sm_count() * 8 + gx - 1) / gx;
   if (gy > (n + 7) / 8) gy = (n + 7) / 8;
   if (gy < 1) gy = 1;
   if (gy > 65535) gy = 65535;
-  moments_kernel<<<dim3(gx, (unsigned)gy), 256, 0, stream>>>(X, n, d, sum, sumsq, mn, mx);
+  if (vec4) moments_vec4_kernel<<<dim3(gx, (unsigned)gy), 256, 0, stream>>>(X, n, d, sum, sumsq, mn, mx);
+  else moments_kernel<<<dim3(gx, (unsigned)gy), 256, 0, stream>>>(X, n, d, sum, sumsq, mn, mx);
   HB_CUDA_OK(cudaGetLastError());
   return 0;
 }

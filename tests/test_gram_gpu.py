@@ -31,9 +31,10 @@ def test_gram_simt(native_built, n, d):
     torch.testing.assert_close(G.double(), ref, rtol=1e-4, atol=1e-3)
 
 
-def test_moments(native_built):
+@pytest.mark.parametrize("n,d", [(10001, 77), (10001, 128), (50000, 1024), (37, 260), (3, 4)])
+def test_moments(native_built, n, d):
     from harp_b200.ops.gram import moments
-    X = torch.randn(10001, 77, device="cuda") * 3 - 1
+    X = torch.randn(n, d, device="cuda") * 3 - 1
     m = moments(X)
     torch.cuda.synchronize()
     torch.testing.assert_close(m.sum, X.double().sum(0), rtol=1e-9, atol=1e-6)
