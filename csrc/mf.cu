@@ -27,7 +27,12 @@
 namespace hb {
 namespace mf {
 
-constexpr int SGD_THREADS = 512;
+// Threads per CTA.  Rank <= 128 needs few registers: 1024 threads x 1 CTA per SM beat 512 x 2 (same warps per SM,
+// half as many ring steps with 4x larger cells: 17.5 vs 19.8 ms per epoch on the Netflix-shaped bench).
+#ifndef HB_SGD_THREADS
+#define HB_SGD_THREADS 1024
+#endif
+__host__ __device__ constexpr int sgd_threads(int RV) { return RV == 1 ? HB_SGD_THREADS : 512; }
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
@@ -68,8 +73,12 @@ struct SgdArgs {
   float eps, lambda;
 };
 
+#ifndef HB_SGD_PF
+#define HB_SGD_PF 1     // deeper w prefetch measured slower (the pass is bound by random-row DRAM traffic, not latency)
+#endif
 template <int RV>   // float4s per lane: rank <= 128 * RV
-__global__ void __launch_bounds__(SGD_THREADS, 1) sgd_pass_kernel(SgdArgs a) {
+__global__ void __launch_bounds__(sgd_threads(RV), (RV == 1 && sgd_threads(RV) <= 512) ? 2 : 1) sgd_pass_kernel(SgdArgs a) {
+  constexpr int PF = RV == 1 ? HB_SGD_PF : (RV == 2 ? 2 : 1);     // w rows in flight per warp
   __shared__ int s_next;      // next segment of the current block
   __shared__ int s_stop;
   __shared__ int s_c;         // column-block of this step
@@ -151,50 +160,71 @@ __global__ void __launch_bounds__(SGD_THREADS, 1) sgd_pass_kernel(SgdArgs a) {
                                        : make_float4(0.f, 0.f, 0.f, 0.f);
           h0[u] = h[u];
         }
-        // software pipeline: w of rating k+1 is in flight while rating k is updated
-        int row_n = (k0 < k1) ? a.r_row[k0] : 0;
-        float v_n = (k0 < k1) ? a.r_val[k0] : 0.f;
-        float4 w_n[RV];
+        // Row ids and values of the run come in with one coalesced load (lane j holds rating k0 + j); the w rows
+        // of the next PF ratings are kept in flight, so a rating costs 1/PF of a memory round trip, not a whole one.
+        for (int kb = k0; kb < k1; kb += 32) {
+          const int nb = min(32, k1 - kb);
+          const int rows_l = (lane < nb) ? a.r_row[kb + lane] : 0;
+          const float vals_l = (lane < nb) ? a.r_val[kb + lane] : 0.f;
+          // a w row fetched early is stale if one of the PF ratings before it hits the same row (duplicate
+          // (row, col) ratings only): those are flagged in bit 31 and re-read at their turn
+          unsigned dup = 0;
 #pragma unroll
-        for (int u = 0; u < RV; ++u)
-          w_n[u] = (k0 < k1 && lane + 32 * u < nl4) ? ldcg4(a.W + (size_t)row_n * a.rank + (lane + 32 * u) * 4)
-                                                    : make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int k = k0; k < k1; ++k) {
-          const int row = row_n;
-          float4 w[RV];
+          for (int q = 1; q <= PF; ++q) {
+            const int prev = __shfl_up_sync(0xffffffffu, rows_l, q);
+            if (lane >= q && lane < nb && prev == rows_l) dup = 0x80000000u;
+          }
+          const unsigned rows_e = (unsigned)rows_l | dup;
+          float4 wq[PF][RV];
 #pragma unroll
-          for (int u = 0; u < RV; ++u) w[u] = w_n[u];
-          const float v = v_n;
-          if (k + 1 < k1) {
-            row_n = a.r_row[k + 1];
-            v_n = a.r_val[k + 1];
+          for (int q = 0; q < PF; ++q) {
+            const int rq = (int)(__shfl_sync(0xffffffffu, rows_e, q) & 0x7FFFFFFFu);
 #pragma unroll
             for (int u = 0; u < RV; ++u)
-              if (lane + 32 * u < nl4) w_n[u] = ldcg4(a.W + (size_t)row_n * a.rank + (lane + 32 * u) * 4);
+              wq[q][u] = (q < nb && lane + 32 * u < nl4) ? ldcg4(a.W + (size_t)rq * a.rank + (lane + 32 * u) * 4)
+                                                         : make_float4(0.f, 0.f, 0.f, 0.f);
           }
-          float dot = 0.f;
+          for (int j0 = 0; j0 < nb; j0 += PF) {
 #pragma unroll
-          for (int u = 0; u < RV; ++u)
-            dot += w[u].x * h[u].x + w[u].y * h[u].y + w[u].z * h[u].z + w[u].w * h[u].w;
-          const float e = warp_sum(dot) - v;
-          const float ee = a.eps * e, el = a.eps * a.lambda;
+            for (int q = 0; q < PF; ++q) {
+              const int j = j0 + q;
+              if (j < nb) {
+                const unsigned re = __shfl_sync(0xffffffffu, rows_e, j);
+                const int row = (int)(re & 0x7FFFFFFFu);
+                const float v = __shfl_sync(0xffffffffu, vals_l, j);
+                float4 w[RV];
 #pragma unroll
-          for (int u = 0; u < RV; ++u) {
-            // w -= eps (e h + lambda w);  h -= eps (e w_old + lambda h)     (SGDMPTask.java:60-72)
-            float4 wn, hn;
-            wn.x = w[u].x - (ee * h[u].x + el * w[u].x); hn.x = h[u].x - (ee * w[u].x + el * h[u].x);
-            wn.y = w[u].y - (ee * h[u].y + el * w[u].y); hn.y = h[u].y - (ee * w[u].y + el * h[u].y);
-            wn.z = w[u].z - (ee * h[u].z + el * w[u].z); hn.z = h[u].z - (ee * w[u].z + el * h[u].z);
-            wn.w = w[u].w - (ee * h[u].w + el * w[u].w); hn.w = h[u].w - (ee * w[u].w + el * h[u].w);
-            h[u] = hn;
-            if (lane + 32 * u < nl4) stcg4(a.W + (size_t)row * a.rank + (lane + 32 * u) * 4, wn);
-          }
-          // a run may revisit a row only through another run (different column), never within itself,
-          // except for duplicate (row, col) ratings: make the prefetched copy coherent then
-          if (k + 1 < k1 && row_n == row) {
+                for (int u = 0; u < RV; ++u) w[u] = wq[q][u];
+                if (re & 0x80000000u) {
 #pragma unroll
-            for (int u = 0; u < RV; ++u)
-              if (lane + 32 * u < nl4) w_n[u] = ldcg4(a.W + (size_t)row_n * a.rank + (lane + 32 * u) * 4);
+                  for (int u = 0; u < RV; ++u)
+                    if (lane + 32 * u < nl4) w[u] = ldcg4(a.W + (size_t)row * a.rank + (lane + 32 * u) * 4);
+                }
+                if (j + PF < nb) {
+                  const int rn = (int)(__shfl_sync(0xffffffffu, rows_e, j + PF) & 0x7FFFFFFFu);
+#pragma unroll
+                  for (int u = 0; u < RV; ++u)
+                    if (lane + 32 * u < nl4) wq[q][u] = ldcg4(a.W + (size_t)rn * a.rank + (lane + 32 * u) * 4);
+                }
+                float dot = 0.f;
+#pragma unroll
+                for (int u = 0; u < RV; ++u)
+                  dot += w[u].x * h[u].x + w[u].y * h[u].y + w[u].z * h[u].z + w[u].w * h[u].w;
+                const float e = warp_sum(dot) - v;
+                const float ee = a.eps * e, el = a.eps * a.lambda;
+#pragma unroll
+                for (int u = 0; u < RV; ++u) {
+                  // w -= eps (e h + lambda w);  h -= eps (e w_old + lambda h)     (SGDMPTask.java:60-72)
+                  float4 wn, hn;
+                  wn.x = w[u].x - (ee * h[u].x + el * w[u].x); hn.x = h[u].x - (ee * w[u].x + el * h[u].x);
+                  wn.y = w[u].y - (ee * h[u].y + el * w[u].y); hn.y = h[u].y - (ee * w[u].y + el * h[u].y);
+                  wn.z = w[u].z - (ee * h[u].z + el * w[u].z); hn.z = h[u].z - (ee * w[u].z + el * h[u].z);
+                  wn.w = w[u].w - (ee * h[u].w + el * w[u].w); hn.w = h[u].w - (ee * w[u].w + el * h[u].w);
+                  h[u] = hn;
+                  if (lane + 32 * u < nl4) stcg4(a.W + (size_t)row * a.rank + (lane + 32 * u) * 4, wn);
+                }
+              }
+            }
           }
         }
 #pragma unroll
@@ -289,7 +319,8 @@ int hb_sgd_max_blocks(int rank) {
   if (cudaGetDevice(&dev) != cudaSuccess) return 0;
   const void* fn = rank <= 128 ? (const void*)sgd_pass_kernel<1> : rank <= 256 ? (const void*)sgd_pass_kernel<2>
                                                                                  : (const void*)sgd_pass_kernel<4>;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, SGD_THREADS, 0) != cudaSuccess) return 0;
+  const int threads = sgd_threads(rank <= 128 ? 1 : (rank <= 256 ? 2 : 4));
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, 0) != cudaSuccess) return 0;
   return per_sm * sm_count();
 }
 
@@ -330,7 +361,8 @@ static int sgd_launch(SgdArgs& a, void* stream) {
   const void* fn = rank <= 128 ? (const void*)sgd_pass_kernel<1> : rank <= 256 ? (const void*)sgd_pass_kernel<2>
                                                                                  : (const void*)sgd_pass_kernel<4>;
   // cooperative launch: all B CTAs are guaranteed resident, which the ticket ring relies on
-  HB_CUDA_OK(cudaLaunchCooperativeKernel(fn, dim3(B), dim3(SGD_THREADS), args, 0, (cudaStream_t)stream));
+  const int threads = sgd_threads(rank <= 128 ? 1 : (rank <= 256 ? 2 : 4));
+  HB_CUDA_OK(cudaLaunchCooperativeKernel(fn, dim3(B), dim3(threads), args, 0, (cudaStream_t)stream));
   return 0;
 }
 

@@ -22,7 +22,9 @@ class NativeError(RuntimeError):
 
 
 def cuda_lib_path() -> Path:
-    return _PKG / "libharp_b200.so"
+    # HB_CUDA_LIB points at an alternative build of the same library (A/B runs of compile-time knobs)
+    alt = os.environ.get("HB_CUDA_LIB")
+    return Path(alt) if alt else _PKG / "libharp_b200.so"
 
 
 def host_lib_path() -> Path:

@@ -32,7 +32,7 @@ NVCC_FLAGS = [
     "--expt-relaxed-constexpr",
     "-Xptxas", "-v",
     "-I", str(ROOT / "include"),
-] + (["-DHB_GRAM_DEBUG"] if os.environ.get("HB_GRAM_DEBUG") else [])
+] + (["-DHB_GRAM_DEBUG"] if os.environ.get("HB_GRAM_DEBUG") else []) + [f"-D{k}={v}" for k, v in os.environ.items() if k in ("HB_SGD_THREADS", "HB_SGD_PF")]
 GXX_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-pthread", "-Wall", "-I", str(ROOT / "include")]
 
 

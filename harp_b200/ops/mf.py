@@ -56,7 +56,7 @@ def max_blocks(rank: int) -> int:
     return int(lib.hb_sgd_max_blocks(rank))
 
 
-def auto_blocks(nnz_per_panel: float, limit: int, per_block: int = 300) -> int:
+def auto_blocks(nnz_per_panel: float, limit: int, per_block: int = 500) -> int:
     """Blocks per side for a panel: a pass costs ~B hand-overs plus nnz/(B * warps) updates, so small panels
     want fewer, fatter blocks; capped by what one cooperative launch keeps resident."""
     import math
@@ -77,7 +77,7 @@ def _serpentine_blocks(weight: torch.Tensor, B: int) -> torch.Tensor:
 
 
 def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: int, max_run: int = 32,
-                hot_spread: bool = True, balance: bool = True, C: Optional[int] = None) -> SgdPanel:
+                hot_spread: bool = True, balance: bool = True, C: Optional[int] = None, lpt: bool = True) -> SgdPanel:
     """Buckets a COO rating list (worker-local row ids, slice-local column ids).  Rows and columns are dealt
     to the B row-blocks / column-blocks by weight (``balance=False``: row % B, col % B); inside a block
     ratings are ordered by column (then by original order).
@@ -139,6 +139,16 @@ def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: i
     seg_ptr = torch.zeros(uniq.numel() + 1, dtype=torch.int64, device=dev)
     seg_ptr[1:] = torch.cumsum(counts, 0)
     seg_blk = uniq // ncols
+    if lpt and uniq.numel() > 1:
+        # Warps of a CTA claim a block's runs in stored order and the block is over when the last warp finishes:
+        # longest runs first (LPT) leaves only short runs for the end, so the idle tail shrinks from ~half the
+        # longest run to ~half the shortest one.  Ratings keep their order inside a run.
+        perm = torch.argsort(seg_blk * (int(counts.max().item()) + 1) - counts, stable=True)
+        new_ptr = torch.zeros_like(seg_ptr)
+        new_ptr[1:] = torch.cumsum(counts[perm], 0)
+        gather = torch.repeat_interleave(seg_ptr[:-1][perm] - new_ptr[:-1], counts[perm]) + torch.arange(n, device=dev)
+        order = order[gather]
+        uniq, counts, split_flag, seg_blk, seg_ptr = uniq[perm], counts[perm], split_flag[perm], seg_blk[perm], new_ptr
     seg_col = (uniq % ncols).to(torch.int32)
     seg_col = torch.where(split_flag, seg_col | torch.tensor(-2147483648, dtype=torch.int32, device=dev), seg_col)
     blk_seg_ptr = torch.searchsorted(seg_blk, torch.arange(B * C + 1, device=dev, dtype=torch.int64)).to(torch.int32)
