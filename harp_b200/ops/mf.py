@@ -63,15 +63,31 @@ def auto_blocks(nnz_per_panel: float, limit: int, per_block: int = 500) -> int:
     return int(max(8, min(limit, math.isqrt(max(1, int(nnz_per_panel / per_block))))))
 
 
-def _serpentine_blocks(weight: torch.Tensor, B: int) -> torch.Tensor:
-    """Block id per item: items sorted by weight (descending) are dealt 0..B-1, B-1..0, 0..B-1, ... so every
-    block gets one item of each weight class and the block totals come out nearly equal."""
+def _serpentine_blocks(weight: torch.Tensor, B: int, greedy_rounds: int = 64) -> torch.Tensor:
+    """Block id per item, block totals nearly equal.  The ``greedy_rounds * B`` heaviest items are placed one by one
+    on the currently lightest block (LPT, a small host-side heap); the long tail of light items is dealt in
+    alternating direction (0..B-1, B-1..0, ...) over the blocks ordered by the load reached so far."""
+    import heapq
+
     n = weight.numel()
+    dev = weight.device
     order = torch.argsort(weight, descending=True, stable=True)
-    pos = torch.arange(n, device=weight.device)
-    off, rnd = pos % B, pos // B
-    blk_sorted = torch.where(rnd % 2 == 0, off, B - 1 - off)
-    blk = torch.empty(n, dtype=torch.int64, device=weight.device)
+    blk_sorted = torch.empty(n, dtype=torch.int64, device=dev)
+    head = min(n, greedy_rounds * B)
+    w_head = weight[order[:head]].tolist()
+    heap = [(0, b) for b in range(B)]
+    assign = [0] * head
+    for j, w in enumerate(w_head):
+        load, b = heapq.heappop(heap)
+        assign[j] = b
+        heapq.heappush(heap, (load + w, b))
+    blk_sorted[:head] = torch.tensor(assign, dtype=torch.int64, device=dev)
+    if head < n:
+        base = torch.tensor([b for _, b in sorted(heap)], dtype=torch.int64, device=dev)    # lightest block first
+        pos = torch.arange(n - head, device=dev)
+        off, rnd = pos % B, pos // B
+        blk_sorted[head:] = base[torch.where(rnd % 2 == 0, off, B - 1 - off)]
+    blk = torch.empty(n, dtype=torch.int64, device=dev)
     blk[order] = blk_sorted
     return blk
 
