@@ -6,6 +6,8 @@
 Usage: <num of data points> <num of centroids> <vector size> <num of point files per worker>
        <number of map tasks> <num threads> <number of iterations> <work dir> <local points dir>
        [regenerate data: true|false]
+Options: --seed=<n>; --resume=<centroid file> continues from a centroid dump of an earlier run (the reference
+only writes such dumps, KMUtil.storeCentroids; nothing in it reads them back — SURVEY §5.4) and keeps the data.
 """
 from __future__ import annotations
 
@@ -29,6 +31,9 @@ def main(argv=None) -> int:
     n_points, n_cen, vec, files_per_worker, n_maps, _threads, n_iter = (int(x) for x in pos[:7])
     work_dir, local_dir = pos[7], pos[8]
     regenerate = (pos[9].lower() == "true") if len(pos) > 9 else True
+    resume = over.pop("resume", None)
+    if resume is not None:
+        regenerate = False
     rank, world = check_world(n_maps)
     n_files = world * files_per_worker
     if n_points // n_files == 0 or n_cen // world == 0:
@@ -38,7 +43,11 @@ def main(argv=None) -> int:
     cen_dir = os.path.join(work_dir, "centroids")
     out_dir = os.path.join(work_dir, "out")
 
+    resume_copy = os.path.join(work_dir, "resume_centroids")
+
     def prepare():
+        if resume is not None:           # the dump usually lives under cen_dir, which is wiped next
+            shutil.copyfile(resume, resume_copy)
         shutil.rmtree(cen_dir, ignore_errors=True)
         shutil.rmtree(out_dir, ignore_errors=True)
         os.makedirs(cen_dir, exist_ok=True)
@@ -46,8 +55,11 @@ def main(argv=None) -> int:
             shutil.rmtree(data_dir, ignore_errors=True)
             os.makedirs(local_dir, exist_ok=True)
             datagen.generate_kmeans_data(n_points, vec, n_files, data_dir, seed=int(over.get("seed", 0)))
-        datagen.generate_centroids(n_cen, vec, os.path.join(cen_dir, "init_centroids"),
-                                   seed=int(over.get("seed", 0)) + 1)
+        if resume is not None:
+            shutil.copyfile(resume_copy, os.path.join(cen_dir, "init_centroids"))
+        else:
+            datagen.generate_centroids(n_cen, vec, os.path.join(cen_dir, "init_centroids"),
+                                       seed=int(over.get("seed", 0)) + 1)
 
     master_first(prepare)
     conf = {"num_centroids": n_cen, "vector_size": vec, "num_iterations": n_iter,

@@ -66,6 +66,20 @@ def test_kmeans_rotation_matches_regroup_allgather(tmp_path):
     np.testing.assert_allclose(ca, cb, rtol=1e-9, atol=1e-9)
 
 
+def test_kmeans_resume_continues_from_a_centroid_dump(tmp_path):
+    """6 iterations, then --resume for 4 more == 10 iterations in one go (same data, same initial centroids)."""
+    from harp_b200.io import formats as F
+    a, b = tmp_path / "a", tmp_path / "b"
+    args = ["600", "8", "12", "2", "2", "1"]
+    _torchrun(2, ["-m", "harp_b200.launch.kmeans"] + args + ["10", str(a), str(tmp_path / "l")])
+    _torchrun(2, ["-m", "harp_b200.launch.kmeans"] + args + ["6", str(b), str(tmp_path / "l")])
+    _torchrun(2, ["-m", "harp_b200.launch.kmeans"] + args + ["4", str(b), str(tmp_path / "l"),
+                  f"--resume={b / 'centroids' / 'out' / 'output'}"])
+    ca = F.read_centroids_text(str(a / "centroids" / "out" / "output"), 12)
+    cb = F.read_centroids_text(str(b / "centroids" / "out" / "output"), 12)
+    np.testing.assert_allclose(ca, cb, rtol=1e-9, atol=1e-9)
+
+
 def test_secondary_apps_end_to_end(tmp_path):
     """PageRank, iterative SVM, MLR, LDA-CVB (static + push/pull), NN, random forest, subgraph counting
     (allgather + SAHAD rotation), WDA-MDS and the SGX-cost-model K-means on generated inputs, 2 workers."""
