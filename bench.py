@@ -109,6 +109,8 @@ class ClockSampler:
 
 
 def reference_arm(args):
+    if int(os.environ.get("RANK", "0")) != 0:      # launched under torchrun for N > 1: one line, from rank 0
+        return 0
     print(json.dumps({
         "impl": "reference",
         "unavailable": ("chathurawidanage/harp is Java 8 + Maven + Hadoop/YARN 2.6 + Intel DAAL JNI; "

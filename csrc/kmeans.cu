@@ -4,21 +4,21 @@
 // ml/java/.../kmeans/regroupallgather/CenCalcTask.java:67-100, and the contrib
 // variant KmeansMapper.java:173-215) and DAAL's kmeans.DistributedStep1Local.
 //
-// Design (B200-first, not a translation):
-//   * -2·X·Cᵀ runs on the 5th-gen tensor cores: tcgen05.mma kind::tf32 reading
-//     fp32 tiles straight out of shared memory (TMA, SWIZZLE_128B), with the
-//     128x256 fp32 accumulator double-buffered in TMEM.
-//   * A persistent, warp-specialised CTA per SM: warp 0 = TMA producer,
-//     warp 1 = single-thread MMA issuer, warps 2..5 = epilogue.  The point tile
-//     (128 x D) stays resident in smem while all centroid tiles stream past it
-//     out of L2.
-//   * The epilogue pulls distances out of TMEM (tcgen05.ld), adds ‖c‖² from a
-//     small smem ring, keeps the running arg-min, and then folds each point
-//     into sums[argmin]/counts[argmin] with 16-byte vector reductions
-//     (red.global.add.v4.f32) that resolve in L2.  Nothing but the final
-//     [k x d] sums ever goes back to HBM.
-//   * A plain fp32 SIMT kernel is kept as the exact-arithmetic fallback for
-//     shapes the tensor path does not take (d % 4 != 0 or d > 128).
+// Design (B200-first, not a translation).  Three kernels share the building blocks below:
+//   assign_tc_pair_kernel<DBG, EXT, FUSED>   the production path: a cluster of two CTAs drives one
+//       tcgen05.mma.cta_group::2 kind::tf32 pipeline (M256 x N256 x K8) over fp32 tiles that TMA puts in
+//       shared memory (SWIZZLE_128B); the 256x256 fp32 accumulator is double-buffered in TMEM.  Warps 0..7
+//       of each CTA are the epilogue (tcgen05.ld, packed arg-max, fold into sums/counts with
+//       red.global.add.v4.f32 that resolve in L2), warp 8 the TMA producer, warp 9 (leader CTA) the MMA
+//       issuer.  EXT = 1 folds -|c|^2/2 into the GEMM as one extra K = 8 step; FUSED = 1 appends the
+//       regroup -> centroid update -> allgather over NVLink peer memory (fused_tail), i.e. a whole Lloyd
+//       iteration is ONE launch per GPU.
+//   assign_tc_kernel                         the first, single-CTA form (cta_group::1, 4 epilogue warps,
+//       |c|^2 added in the epilogue); kept as fallback for tiny inputs and for hb_kmeans_step_static.
+//   assign_simt_kernel                       plain fp32 SIMT kernel, the exact-arithmetic fallback for shapes
+//       the tensor path does not take (d % 4 != 0 or d > 128).
+// In all of them the point tile stays resident in smem while every centroid tile streams past it out of
+// L2, and nothing but the final [k x d] sums ever goes back to HBM.
 #include "common.cuh"
 #include "../include/harp_b200.h"
 
@@ -667,8 +667,8 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
                       double* __restrict__ obj, const FusedArgs fa) {
   using namespace pair;
   constexpr int dbg = DBG;
-  // Role layout: the SMSP arbiter favours higher warp ids, so the two latency-critical
-  // single-thread roles get the highest ids; epilogue warps 0..7 (two per TMEM quadrant).
+  // Role layout: epilogue warps 0..7 (two per TMEM lane quadrant, which is fixed by warp id % 4), then the
+  // TMA producer and the MMA issuer.
   constexpr int TMA_WARP = 8, MMA_WARP = 9;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = smem_u32(smem_raw);
