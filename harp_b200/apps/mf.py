@@ -129,7 +129,7 @@ class SGDCollectiveMapper(CollectiveMapper):
                 # adjustMiniBatch: pick the per-pass budget that trains ~train_ratio % of a panel
                 stats = self.comm.all_gather_object((dt, n_tr, eng.nnz))
                 rate = sum(s[1] for s in stats) / max(sum(s[0] for s in stats), 1e-9)      # ratings / s / worker
-                per_pass = max(s[2] for s in stats) / (2 * N)
+                per_pass = max(s[2] for s in stats) / (eng.S * N)
                 deadline_ms = max(0.01, 1e3 * per_pass * self.train_ratio / 100.0 / max(rate, 1.0))
             if it % self.rmse_interval == 0 or it == self.num_iterations:
                 rm = eng.rmse(tpos, tmine[:, 1].long(), tmine[:, 2])
