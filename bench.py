@@ -108,6 +108,28 @@ class ClockSampler:
         }
 
 
+def roofline(flops_per_gpu: float, reduce_bytes: int, world: int, ms_per_step: float) -> dict:
+    """Achieved / target for a fused compute+collective step: target = slower of FLOPs / measured GEMM peak and
+    NVLink bytes / measured link rate.  Denominators: MEASURED_PEAKS.json (cuBLAS bf16, sustained figure because the
+    step runs for seconds under the power cap), else the profiling recipe's fallback.  The kernel's products are
+    TF32, whose tensor-pipe rate is half the bf16 rate, so the fraction against half the bf16 figure is given too."""
+    src, bf16 = "fallback", 1400.0
+    try:
+        mp = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+        bf16, src = float(mp.get("bf16_tflops_sustained") or mp["bf16_tflops"]), "measured"
+    except Exception:  # noqa: BLE001
+        pass
+    nvlink_gbs = 770.0                                   # measured peer copy per direction per GPU (recipe)
+    link_bytes = 2.0 * reduce_bytes * (world - 1) / max(world, 1)      # reduce-scatter in + all-gather out
+    t_compute = flops_per_gpu / (bf16 * 1e12) * 1e3
+    t_link = link_bytes / (nvlink_gbs * 1e9) * 1e3
+    target = max(t_compute, t_link)
+    return {"denominator": f"cuBLAS bf16 {bf16:.0f} TFLOP/s sustained, of {src}; NVLink {nvlink_gbs:.0f} GB/s per direction",
+            "target_ms": target, "compute_ms_at_bf16_peak": t_compute, "nvlink_ms": t_link,
+            "fraction_of_bf16_peak": target / ms_per_step,
+            "fraction_of_tf32_rate": min(2.0 * target, max(2.0 * t_compute, t_link)) / ms_per_step}
+
+
 def reference_arm(args):
     if int(os.environ.get("RANK", "0")) != 0:      # launched under torchrun for N > 1: one line, from rank 0
         return 0
@@ -280,6 +302,7 @@ def main():
             "final_mse": final_mse,
             "gpu_launches": launches,
             "clocks": clocks,
+            "roofline": roofline(flops / world, k * (d + 1) * 4, world, ms_per_step),
             "e2e": e2e,
         }
         print(json.dumps(out))
