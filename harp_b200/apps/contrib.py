@@ -20,7 +20,7 @@ from __future__ import annotations
 
 import math
 import os
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 import numpy as np
 import torch

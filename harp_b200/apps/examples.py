@@ -4,7 +4,7 @@ micro-benchmark ``edu.iu.benchmark`` (``BenchmarkMapper.java:96-136``)."""
 from __future__ import annotations
 
 import time
-from typing import Dict, List
+
 
 import torch
 

@@ -31,7 +31,7 @@ Results of float reductions are bit-identical on all ranks (contributions are fo
 from __future__ import annotations
 
 import pickle
-from typing import Any, Callable, Dict, Iterable, List, Optional, Sequence, Tuple
+from typing import Any, Dict, Iterable, List, Optional, Tuple
 
 import torch
 import torch.distributed as dist

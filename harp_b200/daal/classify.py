@@ -10,7 +10,7 @@ runs on the GPU when given CUDA tensors.
 from __future__ import annotations
 
 import math
-from typing import Callable, Dict, List, NamedTuple, Optional, Sequence, Tuple
+from typing import List, NamedTuple, Optional, Tuple
 
 import torch
 

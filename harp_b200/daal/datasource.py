@@ -5,7 +5,7 @@ fan-out uses the host ``DynamicScheduler`` like the reference's ``MTReader`` (``
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional, Sequence, Tuple
+from typing import Dict, Optional, Sequence, Tuple
 
 import numpy as np
 import torch

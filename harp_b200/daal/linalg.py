@@ -12,7 +12,7 @@ Every function takes ``comm`` (a :class:`harp_b200.collective.Comm` or None for 
 from __future__ import annotations
 
 import math
-from typing import Dict, NamedTuple, Optional, Tuple
+from typing import Dict, NamedTuple, Tuple
 
 import torch
 import torch.distributed as dist

@@ -6,7 +6,7 @@ from __future__ import annotations
 
 import itertools
 import math
-from typing import Callable, Dict, FrozenSet, List, NamedTuple, Optional, Sequence, Tuple
+from typing import Dict, FrozenSet, NamedTuple, Optional, Sequence
 
 import torch
 import torch.distributed as dist

@@ -24,7 +24,7 @@ from __future__ import annotations
 import random as _random
 import threading
 import time
-from typing import Any, Dict, Generic, List, Optional, Sequence, TypeVar
+from typing import Any, Dict, List, Optional, Sequence
 
 import torch
 

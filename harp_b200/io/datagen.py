@@ -12,7 +12,7 @@
 from __future__ import annotations
 
 import os
-from typing import List, Optional, Tuple
+from typing import List, Tuple
 
 import numpy as np
 

@@ -16,7 +16,7 @@ from __future__ import annotations
 
 import io
 import struct
-from typing import Any, Callable, Dict, Generic, Hashable, Iterable, Iterator, List, Optional, Tuple, TypeVar
+from typing import Any, Callable, Dict, Hashable, Iterator, List, Optional, Tuple
 
 import torch
 

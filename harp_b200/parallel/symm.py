@@ -19,7 +19,7 @@ everywhere — "symmetric addressing").
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional
+from typing import List
 
 import torch
 import torch.distributed as dist
