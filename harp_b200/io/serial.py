@@ -262,3 +262,86 @@ def encode_table(table) -> Tuple[int, bytes]:
     partition-id field holds the count)."""
     parts = table.get_partitions()
     return len(parts), encode_trans_list(parts)
+
+
+# --------------------------------------------------------------------------------------------------------------
+# Data: one message = head + body  (io/Data.java:31-133, head layout :504-569 / :391-451)
+# --------------------------------------------------------------------------------------------------------------
+UNKNOWN_WORKER_ID = -1
+UNKNOWN_PARTITION_ID = -2147483648          # Constant.UNKNOWN_PARTITION_ID (Integer.MIN_VALUE)
+
+
+class Data:
+    """``bodyType | contextName | workerID | bodySize [| operationName [| partitionID]]`` followed by the body
+    (a ``SIMPLE_LIST`` or a ``PARTITION_LIST``).  For partition lists the partition-id field of the head carries the
+    NUMBER of partitions in the message (``PartitionUtil.java:62-70``)."""
+
+    def __init__(self, body_type: int, context_name: str, worker_id: int, body: Sequence[Any],
+                 operation_name: Optional[str] = None, partition_id: int = UNKNOWN_PARTITION_ID):
+        self.body_type = int(body_type)
+        self.context_name = context_name
+        self.worker_id = int(worker_id)
+        self.body = list(body)
+        self.operation_name = operation_name
+        self.partition_id = int(partition_id)
+
+    @classmethod
+    def of_table(cls, context_name: str, operation_name: str, worker_id: int, table) -> "Data":
+        parts = table.get_partitions()
+        return cls(PARTITION_LIST, context_name, worker_id, parts, operation_name, len(parts))
+
+    # ``Data.isData / isOperationData / isPartitionData`` (``Data.java:264-300``)
+    def is_data(self) -> bool:
+        return (self.body_type in (SIMPLE_LIST, PARTITION_LIST) and self.context_name is not None
+                and self.worker_id != UNKNOWN_WORKER_ID and self.body is not None)
+
+    def is_operation_data(self) -> bool:
+        return self.is_data() and self.operation_name is not None
+
+    def is_partition_data(self) -> bool:
+        return self.is_operation_data() and self.partition_id != UNKNOWN_PARTITION_ID
+
+    def encode_body(self) -> bytes:
+        return encode_trans_list(self.body)
+
+    def encode_head(self, body_size: Optional[int] = None) -> bytes:
+        if not self.is_data():
+            raise ValueError("not a complete Data object")
+        out = Serializer()
+        out.write_byte(self.body_type)
+        out.write_chars(self.context_name)
+        out.write_int(self.worker_id)
+        out.write_int(num_trans_list_bytes(self.body) if body_size is None else body_size)
+        if self.is_operation_data():
+            out.write_chars(self.operation_name)
+            if self.is_partition_data():
+                out.write_int(self.partition_id)
+        head = out.to_bytes()
+        expect = 9 + 4 + 2 * len(self.context_name)
+        if self.is_operation_data():
+            expect += 4 + 2 * len(self.operation_name) + (4 if self.is_partition_data() else 0)
+        assert len(head) == expect                              # Data.java:509-519
+        return head
+
+    def encode(self) -> Tuple[bytes, bytes]:
+        body = self.encode_body()
+        return self.encode_head(len(body)), body
+
+    @classmethod
+    def decode(cls, head: bytes, body: bytes) -> "Data":
+        inp = Deserializer(head)
+        body_type, ctx, wid, size = inp.read_byte(), inp.read_chars(), inp.read_int(), inp.read_int()
+        op = inp.read_chars() if inp.get_pos() < inp.get_length() else None
+        pid = inp.read_int() if inp.get_pos() < inp.get_length() else UNKNOWN_PARTITION_ID
+        if size != len(body):
+            raise ValueError(f"head announces {size} body bytes, got {len(body)}")
+        if body_type == PARTITION_LIST:
+            objs: List[Any] = decode_partition_list(body)
+        elif body_type == SIMPLE_LIST:
+            objs = decode_simple_list(body)
+        else:
+            raise ValueError(f"unknown body type {body_type}")
+        return cls(body_type, ctx, wid, objs, op, pid)
+
+    isData, isOperationData, isPartitionData, encodeHead, encodeBody = (
+        is_data, is_operation_data, is_partition_data, encode_head, encode_body)

@@ -80,3 +80,25 @@ def test_empty_list_is_one_zero_byte_and_partition_lists_carry_ids():
     # payload first, id last (Partition.java:74-78)
     first_len = 2 * 8 + 5
     assert struct.unpack(">i", body[first_len:first_len + 4])[0] in (5, -2)
+
+
+def test_data_message_head_layout_and_round_trip():
+    t = Table(0, ArrayCombiner(Operation.SUM))
+    t.add_partition(Partition(3, IntArray.wrap(torch.tensor([4, 5, 6], dtype=torch.int32))))
+    t.add_partition(Partition(9, IntArray.wrap(torch.tensor([7], dtype=torch.int32))))
+    d = S.Data.of_table("kmeans", "allreduce-1", 2, t)
+    assert d.is_data() and d.is_operation_data() and d.is_partition_data() and d.partition_id == 2
+    head, body = d.encode()
+    assert len(head) == 9 + (4 + 2 * 6) + (4 + 2 * 11) + 4 and head[0] == S.PARTITION_LIST
+    back = S.Data.decode(head, body)
+    assert (back.context_name, back.operation_name, back.worker_id, back.partition_id) == ("kmeans", "allreduce-1", 2, 2)
+    assert {p.id(): p.get().get().tolist() for p in back.body} == {3: [4, 5, 6], 9: [7]}
+    ev = S.Data(S.SIMPLE_LIST, "ctx", 0, [DoubleArray.wrap(torch.tensor([1.0], dtype=torch.float64))])
+    assert ev.is_data() and not ev.is_operation_data() and not ev.is_partition_data()
+    h2, b2 = ev.encode()
+    assert len(h2) == 9 + 4 + 2 * 3
+    e2 = S.Data.decode(h2, b2)
+    assert e2.operation_name is None and e2.body[0].get().tolist() == [1.0]
+    assert not S.Data(S.SIMPLE_LIST, "ctx", S.UNKNOWN_WORKER_ID, []).is_data()
+    with pytest.raises(ValueError):
+        S.Data.decode(h2, b2 + b"\x00")
