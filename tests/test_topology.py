@@ -40,3 +40,34 @@ def test_workers_ids_follow_the_reference_rules(tmp_path):
 def test_workers_from_a_single_process():
     w = Workers.from_distributed()
     assert w.is_the_only_worker() and w.is_master() and w.get_next_id() == 0 and w.get_max_id() == 0
+
+
+def test_driver_turns_a_nodes_file_into_torchrun_commands(tmp_path, capsys):
+    import pytest
+    from harp_b200.launch import driver
+    p = tmp_path / "nodes"
+    p.write_text("#0\n127.0.0.1\n127.0.0.1\n#1\n127.0.0.1\n127.0.0.1\n")          # core/scripts/nodes: 4 local workers
+    (host, cmd), = driver.plan(Nodes.from_file(str(p)), ["-m", "harp_b200.launch.kmeans", "1000"], 29611)
+    assert host == "127.0.0.1" and "--nproc-per-node=4" in cmd and "--nnodes=1" in cmd
+    assert cmd[cmd.index("--master-addr") + 1] == "127.0.0.1" and cmd[-3:] == ["-m", "harp_b200.launch.kmeans", "1000"]
+    two = driver.plan(Nodes.from_lines(["#0", "n1", "n1", "#1", "n2", "n2"]), ["x.py"])
+    assert [h for h, _ in two] == ["n1", "n2"]
+    assert "--node-rank=1" in two[1][1] and "--rdzv-endpoint=n1:29500" in two[1][1] and "--nproc-per-node=2" in two[0][1]
+    with pytest.raises(ValueError):
+        driver.plan(Nodes.from_lines(["#0", "a", "a", "b"]), ["x.py"])
+    assert driver.main(["--nodes", str(p), "--dry-run", "--", "-m", "harp_b200.launch.kmeans"]) == 0
+    assert "torch.distributed.run" in capsys.readouterr().out
+
+
+def test_driver_runs_local_workers(tmp_path):
+    import subprocess, sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    p = tmp_path / "nodes"
+    p.write_text("#0\n127.0.0.1\n127.0.0.1\n")
+    prog = tmp_path / "hello.py"
+    prog.write_text("import os\nopen(os.path.join(os.path.dirname(__file__), 'r' + os.environ['RANK']), 'w').write(os.environ['WORLD_SIZE'])\n")
+    res = subprocess.run([sys.executable, "-m", "harp_b200.launch.driver", "--nodes", str(p), "--master-port", "29612", "--", str(prog)],
+                         cwd=str(root), capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stderr[-2000:]
+    assert (tmp_path / "r0").read_text() == "2" and (tmp_path / "r1").read_text() == "2"
