@@ -80,6 +80,16 @@ def test_kmeans_resume_continues_from_a_centroid_dump(tmp_path):
     np.testing.assert_allclose(ca, cb, rtol=1e-9, atol=1e-9)
 
 
+def test_numpy_session_api():
+    """python/harp_session.py of the reference (a py4j stub there): barrier / broadcast / allreduce / reduce /
+    allgather on NumPy arrays, 1 and 3 workers."""
+    out = _torchrun(3, [str(ROOT / "tests" / "mp_session_worker.py")])
+    assert "SESSION_OK 3" in out
+    res = subprocess.run([sys.executable, str(ROOT / "tests" / "mp_session_worker.py")], capture_output=True, text=True,
+                         timeout=300, cwd=str(ROOT), env=dict(os.environ, PYTHONPATH=str(ROOT)))
+    assert res.returncode == 0 and "SESSION_OK 1" in res.stdout, res.stdout + res.stderr[-2000:]
+
+
 def test_secondary_apps_end_to_end(tmp_path):
     """PageRank, iterative SVM, MLR, LDA-CVB (static + push/pull), NN, random forest, subgraph counting
     (allgather + SAHAD rotation), WDA-MDS and the SGX-cost-model K-means on generated inputs, 2 workers."""
