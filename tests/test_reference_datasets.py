@@ -1,0 +1,96 @@
+"""The DAAL-style algorithms on the sample data that ships with the reference (``datasets/daal_*``), the inputs of
+its ``ml/daal/test_scripts/harp-daal-*.sh`` acceptance scripts.  Those scripts only check that the job completes;
+here the results are compared with NumPy or with the ground-truth files that sit next to the data.  Skipped when
+the reference tree is not mounted (nothing is copied into this repository)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from harp_b200.daal import classify, linalg, models
+
+BASE = os.environ.get("HARP_REFERENCE_DATASETS", "/root/reference/datasets")
+pytestmark = pytest.mark.skipif(not os.path.isdir(os.path.join(BASE, "daal_cov")),
+                                reason="reference data sets not available")
+
+
+def _csv(path, ncols=None):
+    with open(path) as f:
+        first = f.readline()
+    n = ncols or len([x for x in first.strip().split(",") if x])
+    return np.loadtxt(path, delimiter=",", usecols=range(n), ndmin=2)
+
+
+def _dir(rel, ncols=None):
+    return [_csv(f, ncols) for f in sorted(glob.glob(os.path.join(BASE, rel, "*.csv")))]
+
+
+def test_covariance_moments_pca_on_daal_cov_dense():
+    parts = _dir("daal_cov/daal_cov_dense")
+    assert len(parts) == 4
+    X = np.concatenate(parts)
+    Xt = torch.from_numpy(X)
+    res = linalg.covariance(Xt)
+    np.testing.assert_allclose(res.covariance.numpy(), np.cov(X, rowvar=False), rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose(res.mean.numpy(), X.mean(0), rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(res.correlation.numpy(), np.corrcoef(X, rowvar=False), rtol=1e-9, atol=1e-9)
+    mom = linalg.low_order_moments(Xt)
+    np.testing.assert_allclose(mom.variance.numpy(), X.var(0, ddof=1), rtol=1e-9)
+    np.testing.assert_allclose(mom.minimum.numpy(), X.min(0)); np.testing.assert_allclose(mom.maximum.numpy(), X.max(0))
+    pca = linalg.pca_correlation(Xt)
+    want = np.sort(np.linalg.eigvalsh(np.corrcoef(X, rowvar=False)))[::-1]
+    np.testing.assert_allclose(pca.eigenvalues.numpy(), want, rtol=1e-8, atol=1e-10)
+
+
+def test_linear_and_ridge_regression_against_the_ground_truth_file():
+    tr = np.concatenate(_dir("daal_reg/train", 12))
+    te = _csv(os.path.join(BASE, "daal_reg/test/linear_regression_test.csv"), 12)
+    gt = _csv(os.path.join(BASE, "daal_reg/groundTruth/linear_regression_test_groundTruth.csv"), 2)
+    X, Y = torch.from_numpy(tr[:, :10]), torch.from_numpy(tr[:, 10:])
+    beta_np, *_ = np.linalg.lstsq(np.hstack([np.ones((len(tr), 1)), tr[:, :10]]), tr[:, 10:], rcond=None)
+    for fit in (linalg.linear_regression_normeq, linalg.linear_regression_qr, linalg.ridge_regression):
+        m = fit(X, Y)
+        pred = m.predict(torch.from_numpy(te[:, :10])).numpy()
+        assert np.abs(pred - gt).max() < 1e-2 * np.abs(gt).max()           # the file holds noisy targets
+        if fit is not linalg.ridge_regression:
+            np.testing.assert_allclose(pred, np.hstack([np.ones((len(te), 1)), te[:, :10]]) @ beta_np, rtol=1e-7, atol=1e-6)
+
+
+def test_qr_and_svd_on_daal_qr_dense():
+    parts = _dir("daal_qr/daal_qr_dense")
+    X = torch.from_numpy(np.concatenate(parts))
+    qr = linalg.qr_distributed(X)
+    Q, R = (qr.Q, qr.R) if hasattr(qr, "Q") else qr
+    torch.testing.assert_close(Q @ R, X, rtol=1e-9, atol=1e-9)
+    torch.testing.assert_close(Q.t() @ Q, torch.eye(Q.shape[1], dtype=Q.dtype), rtol=1e-9, atol=1e-9)
+    sv = linalg.svd_distributed(X)
+    S = sv.S if hasattr(sv, "S") else sv[1]
+    np.testing.assert_allclose(np.sort(S.numpy())[::-1], np.linalg.svd(X.numpy(), compute_uv=False), rtol=1e-9)
+
+
+def test_naive_bayes_and_neural_network_reach_the_ground_truth_labels():
+    tr = np.concatenate(_dir("daal_naive/densedistri/train", 21))
+    te = _csv(glob.glob(os.path.join(BASE, "daal_naive/densedistri/test/*.csv"))[0], 21)
+    gt = _csv(glob.glob(os.path.join(BASE, "daal_naive/densedistri/groundTruth/*.csv"))[0], 1)[:, 0]
+    nb = classify.naive_bayes_train(torch.from_numpy(tr[:, :20]), torch.from_numpy(tr[:, 20]).long(), 20)
+    assert float((nb.predict(torch.from_numpy(te[:, :20])).numpy() == gt).mean()) > 0.98
+    tr = np.concatenate(_dir("daal_nn/train", 21))
+    te = _csv(os.path.join(BASE, "daal_nn/test/neural_network_test.csv"), 20)
+    gt = _csv(os.path.join(BASE, "daal_nn/groundTruth/neural_network_test_ground_truth.csv"), 1)[:, 0]
+    net = models.MLP([20, 20, 40, 2], seed=1)
+    net.train(torch.tensor(tr[:, :20], dtype=torch.float32), torch.tensor(tr[:, 20], dtype=torch.long), epochs=20,
+              batch_size=50, lr=0.05)
+    assert float((net.predict(torch.tensor(te, dtype=torch.float32)).numpy() == gt).mean()) > 0.97
+
+
+def test_kmeans_on_daal_kmeans_dense_is_monotone_and_matches_the_oracle():
+    from oracle import kmeans as oracle
+    X = np.concatenate(_dir("daal_kmeans/densedistri"))
+    init = X[:10].copy()
+    got = models.kmeans_daal(torch.from_numpy(X), torch.from_numpy(init), 8, None, "allreduce")
+    C = got.centroids if hasattr(got, "centroids") else got[0]
+    want, hist = oracle.run(X, init, 8)
+    np.testing.assert_allclose(C.numpy(), want, rtol=1e-9, atol=1e-9)
+    assert all(a >= b - 1e-6 for a, b in zip(hist, hist[1:]))
