@@ -78,15 +78,11 @@ class BinarySVM(NamedTuple):
         return Kx @ self.coef + self.bias
 
 
-def svm_train_binary(X: torch.Tensor, y: torch.Tensor, C: float = 1.0, kernel: str = "linear", sigma: float = 1.0,
-                     tol: float = 1e-3, max_iter: int = 20000) -> BinarySVM:
-    """C-SVC dual by SMO on a precomputed kernel matrix (labels in {-1, +1})."""
-    Xd = _dense(X).double()
-    y = y.double()
-    n = Xd.shape[0]
-    K = kernel_linear(Xd) if kernel == "linear" else kernel_rbf(Xd, None, sigma)
-    alpha = torch.zeros(n, dtype=torch.float64, device=Xd.device)
-    grad = -torch.ones(n, dtype=torch.float64, device=Xd.device)          # ∇ of ½αᵀQα − eᵀα, Q = yyᵀ∘K
+def _smo_torch(K: torch.Tensor, y: torch.Tensor, C: float, tol: float, max_iter: int):
+    """Plain tensor restatement of the SMO loop (fallback when neither native library is built)."""
+    n = K.shape[0]
+    alpha = torch.zeros(n, dtype=torch.float64, device=K.device)
+    grad = -torch.ones(n, dtype=torch.float64, device=K.device)          # ∇ of ½αᵀQα − eᵀα, Q = yyᵀ∘K
     for _ in range(max_iter):
         up = ((y > 0) & (alpha < C)) | ((y < 0) & (alpha > 0))
         lo = ((y > 0) & (alpha > 0)) | ((y < 0) & (alpha < C))
@@ -99,16 +95,53 @@ def svm_train_binary(X: torch.Tensor, y: torch.Tensor, C: float = 1.0, kernel: s
         yi, yj = float(y[i]), float(y[j])
         eta = float(K[i, i] + K[j, j] - 2 * K[i, j])
         eta = eta if eta > 1e-12 else 1e-12
-        # move along the feasible direction, clipped to the box
         delta = float(fi[i] - fj[j]) / eta
         ai, aj = float(alpha[i]), float(alpha[j])
-        # alpha_i += y_i t, alpha_j -= y_j t with t >= 0
-        t_max_i = (C - ai) if yi > 0 else ai
+        t_max_i = (C - ai) if yi > 0 else ai                # alpha_i += y_i t, alpha_j -= y_j t with t >= 0
         t_max_j = aj if yj > 0 else (C - aj)
         t = min(delta, t_max_i, t_max_j)
         alpha[i] = ai + yi * t
         alpha[j] = aj - yj * t
-        grad += t * (y * K[:, i]) * 1.0 - t * (y * K[:, j]) * 1.0
+        grad += t * y * (K[:, i] - K[:, j])
+    return alpha, grad
+
+
+def _smo_solve(K: torch.Tensor, y: torch.Tensor, C: float, tol: float, max_iter: int):
+    """``(alpha, grad)`` of the C-SVC dual.  The whole SMO loop runs natively: one CUDA kernel launch for device
+    tensors (``csrc/svm.cu``), the C++ host solver for CPU tensors (``csrc/host/smo.cpp``)."""
+    import ctypes
+
+    from .. import _native
+    n = K.shape[0]
+    alpha = torch.empty(n, dtype=torch.float64, device=K.device)
+    grad = torch.empty(n, dtype=torch.float64, device=K.device)
+    if n == 0:
+        return alpha, grad
+    P = ctypes.c_void_p
+    if K.device.type == "cuda" and _native.have_cuda_lib():
+        lib = _native.lib()
+        lib.hb_smo_binary.argtypes = [P, P, ctypes.c_int, ctypes.c_double, ctypes.c_double, ctypes.c_int, P, P, P, P]
+        _native.check(lib.hb_smo_binary(_native.ptr(K), _native.ptr(y), n, C, tol, max_iter, _native.ptr(alpha),
+                                        _native.ptr(grad), None, _native.stream_ptr()), "hb_smo_binary")
+        _native.count_launch()
+        return alpha, grad
+    if K.device.type == "cpu" and _native.have_host_lib():
+        lib = _native.host()
+        lib.hh_smo_binary.restype = ctypes.c_longlong
+        lib.hh_smo_binary.argtypes = [P, P, ctypes.c_longlong, ctypes.c_double, ctypes.c_double, ctypes.c_longlong, P, P]
+        lib.hh_smo_binary(_native.ptr(K), _native.ptr(y), n, C, tol, max_iter, _native.ptr(alpha), _native.ptr(grad))
+        return alpha, grad
+    return _smo_torch(K, y, C, tol, max_iter)
+
+
+def svm_train_binary(X: torch.Tensor, y: torch.Tensor, C: float = 1.0, kernel: str = "linear", sigma: float = 1.0,
+                     tol: float = 1e-3, max_iter: int = 20000) -> BinarySVM:
+    """C-SVC dual by SMO on a precomputed kernel matrix (labels in {-1, +1})."""
+    Xd = _dense(X).double()
+    y = y.double()
+    n = Xd.shape[0]
+    K = kernel_linear(Xd) if kernel == "linear" else kernel_rbf(Xd, None, sigma)
+    alpha, grad = _smo_solve(K.contiguous(), y.contiguous(), float(C), float(tol), int(max_iter))
     sv_mask = alpha > 1e-8
     free = sv_mask & (alpha < C - 1e-8)
     f = -y * grad

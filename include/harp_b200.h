@@ -177,6 +177,15 @@ int hb_lda_topic_sums(const int* n_wk, long long words, int K, long long* sums, 
 /* counts[idx0[t] * K + z[t]] += 1 for every token. */
 int hb_lda_count(const int* idx0, const int* z, long long n, int K, int* counts, void* stream);
 
+/* ---- SVM training (csrc/svm.cu) — DAAL svm::training::Batch (Boser) behind
+ * MD/daal_svm/MultiClassDenseBatch/SVMDaalCollectiveMapper.java:150-199 ------------------------ */
+/* The whole SMO loop (maximal-violating-pair rule) of one binary C-SVC problem in ONE launch of one CTA:
+ * K[n,n] row-major symmetric fp64 kernel matrix, y in {-1,+1}; outputs alpha[n], grad[n] (= Q alpha - e) and the
+ * number of steps taken (*iters_out, device int, may be NULL).  Stream-ordered, nothing is read back; independent
+ * problems (one-vs-one pairs) can run on separate streams. */
+int hb_smo_binary(const double* K, const double* y, int n, double C, double tol, int max_iter, double* alpha,
+                  double* grad, int* iters_out, void* stream);
+
 /* ---- NVLink peer-memory collectives (csrc/coll.cu) ------------------------
  * Replace the TCP collectives of HC/collective/*.java.  Every rank passes the
  * same table `peer_ptrs[world]` of peer-mapped slab base addresses (index =

@@ -94,3 +94,16 @@ def test_kmeans_on_daal_kmeans_dense_is_monotone_and_matches_the_oracle():
     want, hist = oracle.run(X, init, 8)
     np.testing.assert_allclose(C.numpy(), want, rtol=1e-9, atol=1e-9)
     assert all(a >= b - 1e-6 for a, b in zip(hist, hist[1:]))
+
+
+def test_multiclass_svm_and_boosting_on_the_reference_samples():
+    tr = np.concatenate(_dir("daal_svm/multidense/train"))
+    te = np.concatenate(_dir("daal_svm/multidense/test"))
+    m = classify.svm_train_multiclass(torch.from_numpy(tr[:, :-1]), torch.from_numpy(tr[:, -1]).long())
+    acc = float((m.predict(torch.from_numpy(te[:, :-1])).numpy() == te[:, -1]).mean())
+    assert acc > 0.85, acc                                   # scikit-learn SVC(kernel="linear", C=1): 0.873
+    for name, fit in (("adaboost", classify.adaboost_train), ("brownboost", classify.brownboost_train)):
+        tr = np.concatenate([_csv(f) for f in sorted(glob.glob(os.path.join(BASE, f"daal_{name}/train/*")))])
+        te = _csv(glob.glob(os.path.join(BASE, f"daal_{name}/test/*.csv"))[0])
+        pred = fit(torch.from_numpy(tr[:, :-1]), torch.from_numpy(tr[:, -1])).predict(torch.from_numpy(te[:, :-1]))
+        assert float((pred.numpy().reshape(-1) == te[:, -1]).mean()) > 0.97, name
