@@ -110,11 +110,30 @@ def _cpu_pass(panel: TokenPanel, n_dk, n_wk, commons, alpha, beta, seed) -> int:
     return n
 
 
+def _host_pass(panel: TokenPanel, n_dk, n_wk, commons, alpha, beta, seed) -> int:
+    """The sequential sampler in C++ (``csrc/host/mf_host.cpp::hh_lda_pass``, counter-based RNG like the device
+    kernel); falls back to the Python loop when the host library is missing or the tables are not int32/int16."""
+    ok = (_native.have_host_lib() and n_wk.dtype == torch.int32 and n_dk.dtype in (torch.int32, torch.int16)
+          and n_dk.is_contiguous() and n_wk.is_contiguous() and panel.tok_z.dtype == torch.int32
+          and commons.dtype == torch.float32)
+    if not ok:
+        return _cpu_pass(panel, n_dk, n_wk, commons, alpha, beta, seed)
+    lib = _native.host()
+    P = ctypes.c_void_p
+    lib.hh_lda_pass.restype = ctypes.c_longlong
+    lib.hh_lda_pass.argtypes = [P, ctypes.c_int, P, P, P, P, P, P, P, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                                ctypes.c_double, ctypes.c_ulonglong]
+    keep = [t.contiguous() for t in (commons, panel.blk_seg_ptr, panel.seg_word, panel.seg_ptr, panel.tok_doc)]
+    return int(lib.hh_lda_pass(_native.ptr(n_dk), 1 if n_dk.dtype == torch.int16 else 0, _native.ptr(n_wk),
+                               *[_native.ptr(t) for t in keep], _native.ptr(panel.tok_z), panel.B, n_dk.shape[1],
+                               float(alpha), float(beta), int(seed) & 0xFFFFFFFFFFFFFFFF))
+
+
 def lda_pass(panel: TokenPanel, n_dk: torch.Tensor, n_wk: torch.Tensor, commons: torch.Tensor, alpha: float,
              beta: float, seed: int, deadline_ms: Optional[float] = None,
              trained: Optional[torch.Tensor] = None) -> torch.Tensor:
     if n_dk.device.type != "cuda":
-        n = _cpu_pass(panel, n_dk, n_wk, commons, alpha, beta, seed)
+        n = _host_pass(panel, n_dk, n_wk, commons, alpha, beta, seed)
         out = trained if trained is not None else torch.zeros(1, dtype=torch.int64)
         out += n
         return out

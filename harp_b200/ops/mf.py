@@ -194,11 +194,28 @@ def _cpu_sgd_pass(panel: SgdPanel, W, H, eps, lam) -> int:
     return n
 
 
+def _host_sgd_pass(panel: SgdPanel, W, H, eps, lam) -> int:
+    """The same sequential pass in C++ (``csrc/host/mf_host.cpp::hh_sgd_pass``); the Python loop above stays as its
+    oracle and as the fallback when the host library is not built or the tensors are not plain fp32/fp64."""
+    ok = (_native.have_host_lib() and W.dtype == H.dtype and W.dtype in (torch.float32, torch.float64)
+          and W.is_contiguous() and H.is_contiguous() and panel.r_val.dtype == torch.float32)
+    if not ok:
+        return _cpu_sgd_pass(panel, W, H, eps, lam)
+    lib = _native.host()
+    P = ctypes.c_void_p
+    lib.hh_sgd_pass.restype = ctypes.c_longlong
+    lib.hh_sgd_pass.argtypes = [P, P, ctypes.c_int, P, P, P, P, P, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                                ctypes.c_double, ctypes.c_int]
+    keep = [t.contiguous() for t in (panel.blk_seg_ptr, panel.seg_col, panel.seg_ptr, panel.r_row, panel.r_val)]
+    return int(lib.hh_sgd_pass(_native.ptr(W), _native.ptr(H), W.shape[1], *[_native.ptr(t) for t in keep], panel.B,
+                               panel.ncolblocks, float(eps), float(lam), 1 if W.dtype == torch.float64 else 0))
+
+
 def sgd_pass(panel: SgdPanel, W: torch.Tensor, H: torch.Tensor, eps: float, lam: float,
              deadline_ms: Optional[float] = None, trained: Optional[torch.Tensor] = None) -> torch.Tensor:
     """One pass over the panel; returns a 1-element int64 tensor with the number of ratings trained."""
     if W.device.type != "cuda":
-        n = _cpu_sgd_pass(panel, W, H, eps, lam)
+        n = _host_sgd_pass(panel, W, H, eps, lam)
         out = trained if trained is not None else torch.zeros(1, dtype=torch.int64)
         out += n
         return out

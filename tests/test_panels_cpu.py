@@ -118,3 +118,47 @@ def test_engines_single_process_both_slice_layouts(S):
     for _ in range(6):
         assert int(lda.iterate().item()) == D * L
     assert lda.log_likelihood() > ll0 and int(lda.n_dk.sum()) == D * L
+
+
+@pytest.mark.parametrize("dtype,B,C", [(torch.float64, 1, None), (torch.float64, 6, None), (torch.float32, 5, 9)])
+def test_host_cpp_sgd_pass_equals_the_python_loop(dtype, B, C):
+    """csrc/host/mf_host.cpp::hh_sgd_pass against the Python restatement it replaces on the CPU path."""
+    from harp_b200 import _native
+    if not _native.have_host_lib():
+        pytest.skip("host library not built")
+    r, c, v = _ratings(nr=200, nc=50, nnz=3000, seed=7)
+    p = mf.build_panel(r, c, v, B, C=C)
+    g = torch.Generator().manual_seed(0)
+    W = (torch.rand(200, 8, generator=g, dtype=torch.float64) * 0.3).to(dtype)
+    H = (torch.rand(50, 8, generator=g, dtype=torch.float64) * 0.3).to(dtype)
+    W1, H1, W2, H2 = W.clone(), H.clone(), W.clone(), H.clone()
+    n1 = mf._cpu_sgd_pass(p, W1, H1, 0.02, 0.05)
+    n2 = mf._host_sgd_pass(p, W2, H2, 0.02, 0.05)
+    assert n1 == n2 == 3000
+    tol = dict(rtol=1e-12, atol=1e-13) if dtype == torch.float64 else dict(rtol=2e-4, atol=2e-5)
+    torch.testing.assert_close(W2, W1, **tol)          # fp32 tables: the C++ pass accumulates in double
+    torch.testing.assert_close(H2, H1, **tol)
+
+
+@pytest.mark.parametrize("dk", [torch.int32, torch.int16])
+def test_host_cpp_lda_pass_keeps_the_tables_consistent(dk):
+    from harp_b200 import _native
+    from harp_b200.ops import lda as L
+    if not _native.have_host_lib():
+        pytest.skip("host library not built")
+    g = torch.Generator().manual_seed(3)
+    D, V, K, n = 60, 40, 7, 2500
+    docs = torch.randint(0, D, (n,), generator=g); words = torch.randint(0, V, (n,), generator=g)
+    z = torch.randint(0, K, (n,), generator=g)
+    panel = L.build_token_panel(docs, words, z, 3)
+    n_dk = torch.zeros(D, K, dtype=torch.int32); n_wk = torch.zeros(V, K, dtype=torch.int32)
+    L.count_into(panel.tok_doc, panel.tok_z, K, n_dk); L.count_into(panel.tok_word, panel.tok_z, K, n_wk)
+    n_dk = n_dk.to(dk)
+    commons = (1.0 / (n_wk.sum(0).double() + 0.01 * V)).float()
+    before = panel.tok_z.clone()
+    for it in range(3):
+        assert L._host_pass(panel, n_dk, n_wk, commons, 0.1, 0.01, 11 + it) == n
+    assert not torch.equal(before, panel.tok_z)
+    nd = torch.zeros(D, K, dtype=torch.int32); nw = torch.zeros(V, K, dtype=torch.int32)
+    L.count_into(panel.tok_doc, panel.tok_z, K, nd); L.count_into(panel.tok_word, panel.tok_z, K, nw)
+    assert torch.equal(nd, n_dk.int()) and torch.equal(nw, n_wk) and int(n_dk.min()) >= 0
