@@ -75,7 +75,51 @@ class Initialize:
     def app_args(self) -> List[str]:
         return self.args[self.SYS_ARG_NUM:]
 
-    loadDistributedLibs, loadSysArgs, getSysArgNum = load_distributed_libs, load_sys_args, get_sys_arg_num
+    def create_job(self, job_name: str, launcher_cls, mapper_cls) -> "Job":
+        """``Initialize.createJob`` (``Initialize.java:132-162``): a job that deals the files of ``inputDir`` to the
+        workers like ``MultiFileInputFormat`` and runs ``mapper_cls`` on each.  The Hadoop knobs it sets there
+        (framework name, memory, JVM options, task timeout, zero reducers) have no counterpart under torchrun; the
+        number of map tasks is checked against the world size when the job runs."""
+        if self.sys is None:
+            self.load_sys_args()
+        return Job(job_name, launcher_cls, mapper_cls, dict(self.conf), self.sys.input_dir,
+                   os.path.join(self.sys.work_dir, "output"), self.sys.num_mappers)
+
+    loadDistributedLibs, loadSysArgs, getSysArgNum, createJob = (load_distributed_libs, load_sys_args, get_sys_arg_num,
+                                                                 create_job)
+
+
+class Job:
+    """What ``createJob`` returns: enough of ``org.apache.hadoop.mapreduce.Job`` for the reference's launchers
+    (``job.waitForCompletion(true)``, ``job.isSuccessful()``)."""
+
+    def __init__(self, name: str, launcher_cls, mapper_cls, conf: Dict[str, Any], input_path: str, output_path: str,
+                 num_map_tasks: int):
+        self.name, self.launcher_cls, self.mapper_cls = name, launcher_cls, mapper_cls
+        self.conf, self.input_path, self.output_path, self.num_map_tasks = conf, input_path, output_path, num_map_tasks
+        self.mapper = None
+        self._ok = False
+
+    def get_configuration(self) -> Dict[str, Any]:
+        return self.conf
+
+    def wait_for_completion(self, verbose: bool = True) -> bool:
+        from ..launch.common import check_world, run_mapper
+        check_world(self.num_map_tasks)
+        self.mapper = self.mapper_cls()
+        try:
+            run_mapper(self.mapper, self.input_path, self.conf, self.output_path)
+            self._ok = True
+        except Exception:  # noqa: BLE001
+            self._ok = False
+            if verbose:
+                raise
+        return self._ok
+
+    def is_successful(self) -> bool:
+        return self._ok
+
+    getConfiguration, waitForCompletion, isSuccessful = get_configuration, wait_for_completion, is_successful
 
 
 class Service:

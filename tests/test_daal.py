@@ -165,3 +165,27 @@ def test_kmeans_em_als_apriori_solvers_nn():
     net = M.MLP([5, 16, 3], seed=0, dtype=torch.float64)
     h = net.train(Xb, y, epochs=30, batch_size=32, lr=0.1)
     assert h[-1] < h[0] and float((net.predict(Xb) == y).double().mean()) > 0.95
+
+
+def test_initialize_create_job_runs_a_mapper(tmp_path):
+    """``Initialize.createJob(...).waitForCompletion(true)`` — the launcher idiom of every Harp-DAAL app."""
+    import os
+    import numpy as np
+    from harp_b200.daal.initialize import DataGenerator, Initialize
+    from harp_b200.mapper import CollectiveMapper
+
+    os.environ["HARP_FORCE_CPU"] = "1"
+    files = DataGenerator.generate_dense_data_multi(40, 3, 2, str(tmp_path / "in"))
+    assert len(files) == 2
+
+    class CountRows(CollectiveMapper):
+        def map_collective(self, reader, context):
+            self.rows = 0
+            while reader.next_key_value():
+                self.rows += len(np.loadtxt(reader.get_current_value(), delimiter=",", ndmin=2))
+
+    init = Initialize({}, ["1", "2", "1000", "3", str(tmp_path / "in"), str(tmp_path / "work"), "extra"])
+    init.loadDistributedLibs()
+    job = init.createJob("count", None, CountRows)
+    assert init.getSysArgNum() == 6 and init.app_args() == ["extra"] and job.getConfiguration()["num_iterations"] == 3
+    assert job.waitForCompletion(True) and job.isSuccessful() and job.mapper.rows == 40
