@@ -107,3 +107,55 @@ def test_multiclass_svm_and_boosting_on_the_reference_samples():
         te = _csv(glob.glob(os.path.join(BASE, f"daal_{name}/test/*.csv"))[0])
         pred = fit(torch.from_numpy(tr[:, :-1]), torch.from_numpy(tr[:, -1])).predict(torch.from_numpy(te[:, :-1]))
         assert float((pred.numpy().reshape(-1) == te[:, -1]).mean()) > 0.97, name
+
+
+BATCH_RUNS = [
+    ("svm", "daal_svm/multidense/train", ["20", "daal_svm/multidense/test/svm_multi_class_test_dense.csv"], "test_accuracy", 0.85),
+    ("adaboost", "daal_adaboost/train", ["20", "daal_adaboost/test/adaboost_test.csv"], "test_accuracy", 0.97),
+    ("brownboost", "daal_brownboost/train", ["20", "daal_brownboost/test/brownboost_test.csv"], "test_accuracy", 0.97),
+    ("logitboost", "daal_logitboost/train", ["20", "5", "daal_logitboost/test/logitboost_test.csv"], "test_accuracy", 0.97),
+    ("stump", "daal_stump/train", ["20", "daal_stump/test/stump_test.csv"], "test_accuracy", 0.97),
+    ("dtree_cls_traverse", "daal_dtree/train", ["5"], "nodes", None),
+    ("dforest_reg", "daal_dforest/regdensebatch/train", ["13", "daal_dforest/regdensebatch/test/df_regression_test.csv"], "test_rmse", None),
+    ("em", "daal_em/batchdense/train", ["3", "2"], "weights", None),
+    ("als_batch", "daal_als/implicitdense/train", ["5"], None, None),
+    ("ar", "daal_ar/batchdense/train", ["0.01", "0.6"], "n_itemsets", None),
+    ("cholesky", "daal_cholesky/train", ["5"], None, None),
+    ("pivoted_qr", "daal_pivoted_qr/train", [], None, None),
+    ("sorting", "daal_sorting/train", [], None, None),
+    ("quantile", "daal_quantile/train", [], None, None),
+    ("zscore", "daal_normalization/train", [], None, None),
+    ("minmax", "daal_normalization/train", [], None, None),
+    ("outlier_uni", "daal_outlier/train", [], None, None),
+    ("outlier_multi", "daal_outlier/train", [], None, None),
+    ("outlier_bacon", "daal_outlier/train", [], None, None),
+    ("kernel_lin", "daal_kernelfunc/densebatch", [], None, None),
+    ("kernel_rbf", "daal_kernelfunc/densebatch", [], None, None),
+    ("mse", "daal_optimization_solvers/mse/train", ["3"], "gradient_norm", None),
+    ("lbfgs", "daal_optimization_solvers/lbfgs/train", ["10"], None, None),
+    ("sgd_moment", "daal_optimization_solvers/mse/train", ["3"], None, None),
+    ("adagrad", "daal_optimization_solvers/mse/train", ["3"], None, None),
+    ("quality_linreg", "daal_quality_metrics/linregmetrics/train", ["10"], "rms", None),
+    ("quality_svm", "daal_quality_metrics/svmmultimetrics/train", ["20", "daal_quality_metrics/svmmultimetrics/test"], None, None),
+    ("knn", "daal_knn/batchdense/train", ["5", "5", "daal_knn/batchdense/test"], "test_accuracy", 0.93),
+    ("dforest_cls_traverse", "daal_dforest/clsdensebatch/train", ["3", "daal_dforest/clsdensebatch/test"], "test_accuracy", 0.5),
+    ("dtree_reg", "daal_dtree/train", ["5"], None, None),
+]
+
+
+@pytest.mark.parametrize("algo,indir,app,key,minimum", BATCH_RUNS, ids=[r[0] for r in BATCH_RUNS])
+def test_every_batch_launcher_runs_on_its_reference_sample(tmp_path, monkeypatch, capsys, algo, indir, app, key, minimum):
+    """One CLI run per remaining ``*DaalLauncher`` of the reference (``ml/daal/test_scripts/harp-daal-*.sh`` only
+    check that the job completes; accuracies are asserted where the sample has labels)."""
+    from harp_b200.launch import daal as launcher
+    monkeypatch.setenv("HARP_FORCE_CPU", "1")
+    app = [os.path.join(BASE, x) if x.startswith("daal_") else x for x in app]
+    work = tmp_path / "work"
+    assert launcher.main([algo, "1", "2", "1000", "5", os.path.join(BASE, indir), str(work)] + app) == 0
+    out = capsys.readouterr().out
+    assert f"Harp-DAAL {algo} finished" in out and (work / f"{algo}.out").exists()
+    if key is not None:
+        assert f"{algo}.{key}" in out or key in (work / f"{algo}.out").read_text()
+    if minimum is not None:
+        line = [l for l in out.splitlines() if l.startswith(f"{algo}.{key}:")][0]
+        assert float(line.split(":")[1]) > minimum, line
