@@ -155,7 +155,9 @@ def read_csr(path: str) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
         lines = [ln for ln in f.read().split(b"\n") if ln.strip()]
     assert len(lines) >= 3, f"{path}: DAAL CSR needs 3 lines"
     ro = _parse_numbers(lines[0]).astype(np.int64) - 1
-    ci = _parse_numbers(lines[1]).astype(np.int64) - 1
+    ci = _parse_numbers(lines[1]).astype(np.int64)
+    if ci.size == 0 or ci.min() >= 1:      # one-based, as DAAL writes them; a 0 marks a zero-based file (the
+        ci = ci - 1                        # reference's own datasets/daal_kernelfunc/csrbatch sample is one)
     va = _parse_numbers(lines[2])
     return ro, ci, va
 

@@ -27,6 +27,13 @@ width used for the reported accuracy / error:
   mse | sgd | sgd_mini | sgd_moment | lbfgs | adagrad               <featureDim>   (daal_optimization_solvers)
   quality_svm | quality_linreg     <featureDim> <testFile>          (daal_quality_metrics)
 
+CSR inputs (DAAL's three-line CSR text files, one block of rows per file — the reference's ``csr*`` launchers):
+
+  cov_csr | pca_csr | mom_csr                                       (daal_cov/csrdistri, daal_pca/corcsrdistr, daal_mom/csrdistri)
+  kmeans_csr                       <nCentroids>                     (daal_kmeans/allreducecsr)
+  svm_csr                          <trainLabels> [testCsr testLabels]   (daal_svm/MultiClassCSRBatch)
+  kernel_lin_csr | kernel_rbf_csr                                   (daal_kernel_func/{Lin,Rbf}CSRBatch)
+
 Input = comma-separated dense CSV files dealt to workers like ``MultiFileInputFormat``; results are
 printed by rank 0 and written under ``<workDir>``.
 """
@@ -81,6 +88,31 @@ class DaalMapper(CollectiveMapper):
             hist = net.train(X, Y[:, 0].long(), c["num_iterations"], int(a[2]) if len(a) > 2 else 64,
                              float(a[3]) if len(a) > 3 else 0.1, comm)
             self.result = (net, hist)
+        elif algo in ("cov_csr", "pca_csr", "mom_csr", "kmeans_csr"):
+            X = ds.load_csr_numeric_table(files)                      # this worker's rows, sparse CSR
+            if algo == "kmeans_csr":
+                k = int(a[0])
+                Xd = X.to_dense().double()
+                g = torch.Generator().manual_seed(0)
+                init = torch.rand(k, Xd.shape[1], generator=g, dtype=torch.float64).to(self.device) * float(Xd.abs().max() or 1.0)
+                self.result = models.kmeans_daal(Xd, init, c["num_iterations"], comm, "allreduce")
+            else:
+                self.result = {"cov_csr": linalg.covariance, "pca_csr": linalg.pca_correlation,
+                               "mom_csr": linalg.low_order_moments}[algo](X, comm)
+        elif algo in ("svm_csr", "kernel_lin_csr", "kernel_rbf_csr"):
+            every = self._all_files(files)
+            X = ds.load_csr_numeric_table(every)
+            if algo == "svm_csr":
+                y = ds.create_dense_numeric_table([a[0]], 1)[:, 0].long()
+                m = classify.svm_train_multiclass(X.to_dense(), y)
+                out = {"n_pairs": len(m.pairs)}
+                if len(a) > 2:
+                    Xt = ds.load_csr_numeric_table([a[1]], X.shape[1])
+                    yt = ds.create_dense_numeric_table([a[2]], 1)[:, 0].long()
+                    out["test_accuracy"] = float((m.predict(Xt.to_dense()) == yt).double().mean())
+                self.result = out
+            else:
+                self.result = (classify.kernel_linear if algo == "kernel_lin_csr" else classify.kernel_rbf)(X)
         elif algo in BATCH:
             self.result = self.run_batch(algo, a, files, ds)
         else:

@@ -140,6 +140,15 @@ BATCH_RUNS = [
     ("knn", "daal_knn/batchdense/train", ["5", "5", "daal_knn/batchdense/test"], "test_accuracy", 0.93),
     ("dforest_cls_traverse", "daal_dforest/clsdensebatch/train", ["3", "daal_dforest/clsdensebatch/test"], "test_accuracy", 0.5),
     ("dtree_reg", "daal_dtree/train", ["5"], None, None),
+    ("cov_csr", "daal_cov/daal_cov_csr", [], "covariance", None),
+    ("pca_csr", "daal_pca/daal_pca_csr", [], "eigenvalues", None),
+    ("mom_csr", "daal_mom/daal_mom_csr", [], "variance", None),
+    ("kmeans_csr", "daal_kmeans/csrdistri", ["10"], None, None),
+    ("svm_csr", "daal_svm/multicsr/train", ["daal_svm/multicsr/trainTruth/svm_multi_class_train_labels.csv",
+                                            "daal_svm/multicsr/test/svm_multi_class_test_csr.csv",
+                                            "daal_svm/multicsr/testTruth/svm_multi_class_test_labels.csv"], "test_accuracy", 0.8),
+    ("kernel_lin_csr", "daal_kernelfunc/csrbatch", [], None, None),
+    ("kernel_rbf_csr", "daal_kernelfunc/csrbatch", [], None, None),
 ]
 
 
