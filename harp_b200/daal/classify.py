@@ -266,16 +266,23 @@ class DecisionTree:
 
     def _best_split(self, X, y):
         n, d = X.shape
+        # feature sub-sampling: `max_features` candidates, but features that are constant in this node do not
+        # count — the search goes on through the permutation until that many splittable ones were tried
+        limit = d
         feats = torch.arange(d)
         if self.max_features and self.max_features < d:
-            feats = torch.randperm(d, generator=self.rng)[: self.max_features]
+            feats, limit = torch.randperm(d, generator=self.rng), self.max_features
         best = (None, None, float("inf"))
+        tried = 0
         for f in feats.tolist():
+            if tried >= limit:
+                break
             xs, order = torch.sort(X[:, f])
             ys = y[order]
             valid = xs[1:] > xs[:-1]
             if not bool(valid.any()):
                 continue
+            tried += 1
             nl = torch.arange(1, n, dtype=torch.float64, device=X.device)
             nr = n - nl
             if self.task == "classification":

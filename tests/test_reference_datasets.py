@@ -138,7 +138,7 @@ BATCH_RUNS = [
     ("quality_linreg", "daal_quality_metrics/linregmetrics/train", ["10"], "rms", None),
     ("quality_svm", "daal_quality_metrics/svmmultimetrics/train", ["20", "daal_quality_metrics/svmmultimetrics/test"], None, None),
     ("knn", "daal_knn/batchdense/train", ["5", "5", "daal_knn/batchdense/test"], "test_accuracy", 0.93),
-    ("dforest_cls_traverse", "daal_dforest/clsdensebatch/train", ["3", "daal_dforest/clsdensebatch/test"], "test_accuracy", 0.5),
+    ("dforest_cls_traverse", "daal_dforest/clsdensebatch/train", ["3", "daal_dforest/clsdensebatch/test"], "test_accuracy", 0.7),
     ("dtree_reg", "daal_dtree/train", ["5"], None, None),
     ("cov_csr", "daal_cov/daal_cov_csr", [], "covariance", None),
     ("pca_csr", "daal_pca/daal_pca_csr", [], "eigenvalues", None),
