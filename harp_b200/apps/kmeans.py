@@ -45,6 +45,10 @@ class KMeansRegroupAllgatherMapper(CollectiveMapper):
         self.cen_file = c["centroid_file"]
         self.out_file = c.get("out_file")
         self.cen_vec_size = self.vector_size + 1
+        # "table": the reference's structure (partial-sum table -> regroup -> divide -> allgather per iteration);
+        # "device": the iterations run in models.kmeans.KMeansEngine — on GPUs one fused launch per iteration with
+        # the regroup/update/allgather done in-kernel over NVLink, on CPUs sums + allreduce
+        self.engine_mode = str(c.get("engine", "table"))
         self.timings: Dict[str, float] = {"compute": 0.0, "regroup": 0.0, "allgather": 0.0}
 
     def map_collective(self, reader: KeyValReader, context: Context) -> None:
@@ -99,6 +103,21 @@ class KMeansRegroupAllgatherMapper(CollectiveMapper):
         dt = _work_dtype(self.device)
         sizes = [cen_table.get_partition(p).get().numel() // v for p in sorted(cen_table.get_partition_ids())]
         self.objective_history: List[float] = []
+        if self.engine_mode == "device":
+            from ..models.kmeans import KMeansEngine
+            t0 = time.perf_counter()
+            eng = KMeansEngine(points, K, comm="auto", symm=self.symm)
+            eng.set_centroids(self._centroids_of(cen_table).to(points.dtype))
+            for it in range(self.num_iterations):
+                obj = eng.step()
+                self.objective_history.append(float(obj.item()))       # global objective (sum over workers)
+                context.progress()
+            self.timings["compute"] += time.perf_counter() - t0
+            self.centroids = eng.C.clone()
+            LOG.info("[rank %d] device engine (%s): %.3f s", self.get_self_id(), eng.comm, self.timings["compute"])
+            if self.is_master() and self.out_file:
+                F.write_centroids_text(self.out_file, self.centroids.double().cpu().numpy())
+            return
         for it in range(self.num_iterations):
             t0 = time.perf_counter()
             C = self._centroids_of(cen_table)

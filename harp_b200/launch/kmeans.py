@@ -6,7 +6,8 @@
 Usage: <num of data points> <num of centroids> <vector size> <num of point files per worker>
        <number of map tasks> <num threads> <number of iterations> <work dir> <local points dir>
        [regenerate data: true|false]
-Options: --seed=<n>; --resume=<centroid file> continues from a centroid dump of an earlier run (the reference
+Options: --seed=<n>; --engine=device runs the iterations in ``models.kmeans.KMeansEngine`` (one fused launch per
+iteration on GPUs) instead of the reference's table regroup/allgather structure (default ``--engine=table``); --resume=<centroid file> continues from a centroid dump of an earlier run (the reference
 only writes such dumps, KMUtil.storeCentroids; nothing in it reads them back — SURVEY §5.4) and keeps the data.
 """
 from __future__ import annotations

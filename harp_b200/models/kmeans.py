@@ -72,12 +72,13 @@ class KMeansEngine:
                 dist.all_reduce(t, group=group)
                 self.total_points = float(t.item())
             return
+        wdt = torch.float32 if self.dev.type == "cuda" else X.dtype      # the CPU path keeps the input precision
         # one slab [sums | counts] so the cross-worker combine is a single collective
         if self.comm == "p2p" and self.world > 1:
             assert symm is not None, "comm='p2p' needs a SymmetricWorkspace"
             self.acc = symm.alloc(k * d + k, torch.float32)
         else:
-            self.acc = torch.zeros(k * d + k, dtype=torch.float32, device=self.dev)
+            self.acc = torch.zeros(k * d + k, dtype=wdt, device=self.dev)
         self._sums = self.acc[: k * d].view(k, d)
         self._counts = self.acc[k * d:]
         if self.comm == "p2p" and self.world > 1:
@@ -87,7 +88,7 @@ class KMeansEngine:
             self._C.zero_()
         else:
             self.obj = torch.zeros(1, dtype=torch.float64, device=self.dev)
-            self._C = torch.zeros(k, d, dtype=torch.float32, device=self.dev)
+            self._C = torch.zeros(k, d, dtype=wdt, device=self.dev)
         self.workspace = None
         if self.dev.type == "cuda":
             need = kops.workspace_bytes(self.n, k, d)

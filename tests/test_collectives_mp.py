@@ -66,6 +66,19 @@ def test_kmeans_rotation_matches_regroup_allgather(tmp_path):
     np.testing.assert_allclose(ca, cb, rtol=1e-9, atol=1e-9)
 
 
+def test_kmeans_launcher_device_engine_matches_the_table_path(tmp_path):
+    """--engine=device runs the iterations in KMeansEngine (sums + allreduce here on CPU, the fused NVLink kernel on
+    GPUs) instead of the table regroup/allgather; same centroids."""
+    from harp_b200.io import formats as F
+    a, b = tmp_path / "a", tmp_path / "b"
+    args = ["600", "8", "12", "2", "2", "1", "6"]
+    _torchrun(2, ["-m", "harp_b200.launch.kmeans"] + args + [str(a), str(tmp_path / "l")])
+    _torchrun(2, ["-m", "harp_b200.launch.kmeans"] + args + [str(b), str(tmp_path / "l"), "--engine=device"])
+    ca = F.read_centroids_text(str(a / "centroids" / "out" / "output"), 12)
+    cb = F.read_centroids_text(str(b / "centroids" / "out" / "output"), 12)
+    np.testing.assert_allclose(ca, cb, rtol=1e-9, atol=1e-9)
+
+
 def test_kmeans_resume_continues_from_a_centroid_dump(tmp_path):
     """6 iterations, then --resume for 4 more == 10 iterations in one go (same data, same initial centroids)."""
     from harp_b200.io import formats as F
