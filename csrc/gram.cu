@@ -593,8 +593,7 @@ int hb_gram_allreduce_fused(const float* X, long long n, int d, void* const* pee
   if (gram_plan(P, n > 0 ? X : G, n, d) != 0) return -1;
   HB_CUDA_OK(cudaFuncSetAttribute(gram_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::total));
   // the tail spins on counters fed by the other CTAs of the launch: one CTA per SM, cooperative launch
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof(cfg));
+  cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)P.grid);
   cfg.blockDim = dim3(NTHREADS);
   cfg.dynamicSmemBytes = Smem::total;

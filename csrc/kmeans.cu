@@ -1286,8 +1286,7 @@ int hb_kmeans_fused_step(const float* X, long long n, int d, int k, void* const*
   if (nclusters < 1) nclusters = 1;
   // The tail spins on counters fed by the other CTAs of this launch, so all of them must be resident at once:
   // one CTA per SM, never more CTAs than SMs, and a cooperative launch so the driver refuses otherwise.
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof(cfg));
+  cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(2 * nclusters));
   cfg.blockDim = dim3(pair::NTHREADS2);
   cfg.dynamicSmemBytes = pair::Smem::total;

@@ -187,7 +187,7 @@ int hb_smo_binary(const double* K, const double* y, int n, double C, double tol,
                   double* grad, int* iters_out, void* stream);
 
 /* ---- NVLink peer-memory collectives (csrc/coll.cu) ------------------------
- * Replace the TCP collectives of HC/collective/*.java.  Every rank passes the
+ * Replace the TCP collectives of HC/collective/<Op>Collective.java.  Every rank passes the
  * same table `peer_ptrs[world]` of peer-mapped slab base addresses (index =
  * rank; entry `rank` is the local slab), the same byte offsets into the slab,
  * and the same `ticket`.  Tickets must grow by at least 2 per call on a given
