@@ -144,6 +144,11 @@ class Deserializer:
 # --------------------------------------------------------------------------------------------------------------
 # Simple objects: typed arrays and writables
 # --------------------------------------------------------------------------------------------------------------
+def _utf16_len(s: str) -> int:
+    """``String.length()`` of Java: UTF-16 code units (characters outside the BMP count twice)."""
+    return len(s.encode("utf-16-be")) // 2
+
+
 def _tensor_of(obj: Any) -> Optional[torch.Tensor]:
     if isinstance(obj, Array):
         return obj.get()
@@ -159,7 +164,7 @@ def num_encode_bytes(obj: Any) -> int:
     if t is not None:
         return t.numel() * t.element_size() + 5
     if isinstance(obj, Writable):
-        return 1 + 4 + 2 * len(writable_name(obj)) + obj.get_num_write_bytes()
+        return 1 + 4 + 2 * _utf16_len(writable_name(obj)) + obj.get_num_write_bytes()
     raise TypeError(f"not a Harp Simple object: {type(obj)!r}")
 
 
@@ -317,9 +322,9 @@ class Data:
             if self.is_partition_data():
                 out.write_int(self.partition_id)
         head = out.to_bytes()
-        expect = 9 + 4 + 2 * len(self.context_name)
+        expect = 9 + 4 + 2 * _utf16_len(self.context_name)
         if self.is_operation_data():
-            expect += 4 + 2 * len(self.operation_name) + (4 if self.is_partition_data() else 0)
+            expect += 4 + 2 * _utf16_len(self.operation_name) + (4 if self.is_partition_data() else 0)
         assert len(head) == expect                              # Data.java:509-519
         return head
 

@@ -1,0 +1,83 @@
+"""Property tests (hypothesis) of the L1 data model against plain-Python models: a Table is "union of ids, combine
+on collision" (SURVEY §9.1 item 1), the partitioner is |id % N| with the sign rule for negative ids (item 5), KV
+tables are dictionaries with a combiner, and the wire format round-trips arbitrary arrays."""
+import numpy as np
+import torch
+from hypothesis import given, settings, strategies as st
+
+from harp_b200.io import serial as S
+from harp_b200.keyval import Int2LongKVTable, TypeCombiner
+from harp_b200.partition import ArrayCombiner, Operation, Partition, Partitioner, PartitionStatus, Table
+from harp_b200.resource import DoubleArray, IntArray, LongArray
+
+OPS = {Operation.SUM: lambda a, b: a + b, Operation.MAX: np.maximum, Operation.MIN: np.minimum,
+       Operation.MULTIPLY: lambda a, b: a * b, Operation.MINUS: lambda a, b: a - b}
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.sampled_from(list(OPS)), st.lists(st.tuples(st.integers(-20, 20), st.lists(st.integers(-50, 50), min_size=3, max_size=3)),
+                                            min_size=0, max_size=25))
+def test_table_is_union_of_ids_with_combine_on_collision(op, adds):
+    table, model = Table(0, ArrayCombiner(op)), {}
+    for pid, vals in adds:
+        status = table.add_partition(Partition(pid, torch.tensor(vals, dtype=torch.int64)))
+        if pid in model:
+            assert status is PartitionStatus.COMBINED
+            model[pid] = OPS[op](model[pid], np.array(vals))
+        else:
+            assert status is PartitionStatus.ADDED
+            model[pid] = np.array(vals)
+    assert sorted(table.get_partition_ids()) == sorted(model) and table.get_num_partitions() == len(model)
+    for pid, want in model.items():
+        assert table.get_partition(pid).get().tolist() == want.tolist()
+
+
+@settings(max_examples=100, deadline=None)
+@given(st.integers(1, 64), st.integers(-10 ** 6, 10 ** 6))
+def test_partitioner_matches_the_java_remainder_rule(n, pid):
+    # Java: id % N keeps the sign of id; negative results are negated (Partitioner.java:36-43)
+    java_rem = abs(pid) % n * (1 if pid >= 0 else -1)
+    assert Partitioner(n).get_worker_id(pid) == (java_rem if java_rem >= 0 else -java_rem)
+    ids = torch.tensor([pid, -pid, pid + n])
+    got = Partitioner(n).worker_ids(ids).tolist() if hasattr(Partitioner(n), "worker_ids") else None
+    if got is not None:
+        assert got == [Partitioner(n).get_worker_id(int(i)) for i in ids.tolist()]
+
+
+@settings(max_examples=50, deadline=None)
+@given(st.lists(st.tuples(st.integers(-30, 30), st.integers(-1000, 1000)), max_size=60))
+def test_kv_table_is_a_dict_with_a_combiner(pairs):
+    t, model = Int2LongKVTable(0, TypeCombiner("sum")), {}
+    for k, v in pairs:
+        t.add_key_val(k, v)
+        model[k] = model.get(k, 0) + v
+    assert t.num_keys() == len(model)
+    for k, v in model.items():
+        assert t.get_val(k) == v
+    if model:
+        keys = torch.tensor(sorted(model)); vals = torch.ones(len(model), dtype=torch.int64)
+        t.add_batch(keys, vals)
+        assert all(t.get_val(k) == model[k] + 1 for k in model)
+
+
+@settings(max_examples=50, deadline=None)
+@given(st.lists(st.tuples(st.integers(-2 ** 31, 2 ** 31 - 1), st.sampled_from(["d", "i", "l"]),
+                          st.lists(st.integers(-2 ** 31, 2 ** 31 - 1), max_size=12)), max_size=8))
+def test_partition_lists_round_trip_through_the_wire_format(parts):
+    cls = {"d": (DoubleArray, torch.float64), "i": (IntArray, torch.int32), "l": (LongArray, torch.int64)}
+    objs = [Partition(pid, cls[k][0].wrap(torch.tensor(vals, dtype=cls[k][1]))) for pid, k, vals in parts]
+    data = S.encode_trans_list(objs)
+    assert len(data) == S.num_trans_list_bytes(objs)
+    back = S.decode_partition_list(data)
+    assert [p.id() for p in back] == [p.id() for p in objs]
+    for a, b in zip(back, objs):
+        assert type(a.get()) is type(b.get()) and torch.equal(a.get().get(), b.get().get())
+
+
+@settings(max_examples=30, deadline=None)
+@given(st.text(max_size=20), st.text(max_size=20), st.integers(0, 1000))
+def test_data_heads_round_trip_any_names(ctx, op, wid):
+    d = S.Data(S.SIMPLE_LIST, ctx, wid, [IntArray.wrap(torch.tensor([1], dtype=torch.int32))], op)
+    head, body = d.encode()
+    e = S.Data.decode(head, body)
+    assert (e.context_name, e.operation_name, e.worker_id) == (ctx, op, wid)
