@@ -17,7 +17,10 @@
 // the CPU code would diverge across lanes).  Count updates are integer atomics, so the tables stay
 // exactly consistent with the assignments even where two warps of a CTA meet on a document.
 #include "common.cuh"
+#include "rotate_ring.cuh"
 #include "../include/harp_b200.h"
+
+#include <string.h>
 
 namespace hb {
 namespace lda {
@@ -336,6 +339,133 @@ template <int KJ, bool DK16> constexpr int lda_smem_warps() {
   return (KJ * 32 * (4 + (DK16 ? 4 : 8)) * 24 + KJ * 32 * 4 <= 200 * 1024) ? 24 : 16;
 }
 
+// One word run of a cell, sampled by one warp with its phi vector and two document-row buffers in shared memory.
+// `a` provides n_dk, n_wk, seg_word, seg_ptr, tok_doc, tok_z, seed, alpha, beta; `salt` decorrelates the random
+// streams of different row-blocks.  Returns the number of tokens of the run.
+template <int KJ, bool DK16, typename Core>
+__device__ __forceinline__ unsigned long long lda_run_segment_smem(const Core& a, int seg, int lane, int K, int salt,
+                                                                    float* phi, uint8_t* rowbuf, const float* s_cm) {
+  constexpr int KS = 32 * KJ;
+  constexpr int KP = KJ / 2;
+  constexpr int ROWB = DK16 ? KS * 2 : KS * 4;
+  const uint32_t rowbuf_s = smem_u32(rowbuf);
+  const int row_bytes = DK16 ? K * 2 : K * 4;
+  const int nchunks = row_bytes >> 4;
+  const int i = salt;
+  auto issue_row = [&](int d, int buf) {
+    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.n_dk) + (size_t)d * row_bytes;
+    for (int ch = lane; ch < nchunks; ch += 32) cp_async16(rowbuf_s + buf * ROWB + ch * 16, src + ch * 16);
+    cp_async_commit();
+  };
+  auto row_add = [&](int buf, int z, int delta) {    // one lane: counts[z] += delta in the shared copy, clamped at 0
+    if (DK16) {
+      unsigned short* e = reinterpret_cast<unsigned short*>(rowbuf + buf * ROWB) + z;
+      const int v = (int)*e + delta;
+      *e = (unsigned short)max(v, 0);
+    } else {
+      int* e = reinterpret_cast<int*>(rowbuf + buf * ROWB) + z;
+      *e = max(*e + delta, 0);
+    }
+  };
+  const int word = a.seg_word[seg] & 0x7FFFFFFF;
+  const int k0 = a.seg_ptr[seg], k1 = a.seg_ptr[seg + 1];
+  int* wrow = a.n_wk + (size_t)word * K;
+  __syncwarp();
+#pragma unroll 4
+  for (int k = lane; k < KS; k += 32) phi[k] = (k < K) ? ((float)ldcg_i32(wrow + k) + a.beta) * s_cm[k] : 0.f;
+  __syncwarp();
+  for (int kb = k0; kb < k1; kb += 32) {
+    const int nb = min(32, k1 - kb);
+    const int docs_l = (lane < nb) ? a.tok_doc[kb + lane] : 0;
+    const int zs_l = (lane < nb) ? a.tok_z[kb + lane] : 0;
+    int znew_l = zs_l;
+    int pend_doc = -1, pend_new = 0, pend_old = 0;      // table moves the row fetched ahead may have missed
+    issue_row(__shfl_sync(0xffffffffu, docs_l, 0), 0);
+    for (int j = 0; j < nb; ++j) {
+      const int d = __shfl_sync(0xffffffffu, docs_l, j);
+      const int zold = __shfl_sync(0xffffffffu, zs_l, j);
+      const int tk = kb + j;
+      const int buf = j & 1;
+      if (j + 1 < nb) {
+        issue_row(__shfl_sync(0xffffffffu, docs_l, j + 1), buf ^ 1);
+        cp_async_wait<1>();
+      } else {
+        cp_async_wait<0>();
+      }
+      __syncwarp();
+      // take the token out of both factors (shared copies only; the tables move once, below)
+      if (lane == 0) {
+        if (pend_doc == d) { row_add(buf, pend_new, 1); row_add(buf, pend_old, -1); }
+        phi[zold] -= s_cm[zold];
+        row_add(buf, zold, -1);
+      }
+      __syncwarp();
+      // p_k = (n_dk + alpha) * phi_k, running prefix over this lane's topics (2m, 2m+1), m = lane + 32 jp
+      float cpre[KJ];
+      float run = 0.f;
+      const float2* phi2 = reinterpret_cast<const float2*>(phi);
+#pragma unroll
+      for (int jp = 0; jp < KP; ++jp) {
+        const int m = lane + 32 * jp;
+        const float2 ph = phi2[m];
+        float n0, n1;
+        if (DK16) {
+          const unsigned w = reinterpret_cast<const unsigned*>(rowbuf + buf * ROWB)[m];
+          n0 = (float)(w & 0xFFFFu); n1 = (float)(w >> 16);
+        } else {
+          const int2 w = reinterpret_cast<const int2*>(rowbuf + buf * ROWB)[m];
+          n0 = (float)w.x; n1 = (float)w.y;
+        }
+        run = fmaf(n0 + a.alpha, ph.x, run); cpre[2 * jp] = run;
+        run = fmaf(n1 + a.alpha, ph.y, run); cpre[2 * jp + 1] = run;
+      }
+      float cum = run;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const float v = __shfl_up_sync(0xffffffffu, cum, o);
+        if (lane >= o) cum += v;
+      }
+      const float total = __shfl_sync(0xffffffffu, cum, 31);
+      const float u = uniform01(a.seed, (unsigned long long)tk * 2654435761ULL + (unsigned long long)i) * total;
+      const unsigned int ball = __ballot_sync(0xffffffffu, cum > u);
+      const int L = ball ? (__ffs(ball) - 1) : 31;
+      const float target = u - (cum - run);                  // position inside this lane's stretch
+      unsigned mask = 0u;
+#pragma unroll
+      for (int q = 0; q < KJ; ++q) mask |= (cpre[q] > target) ? (1u << q) : 0u;
+      int zmine = zold;
+      if (mask != 0u) {
+        const int q = __ffs(mask) - 1;
+        const int k = 2 * (lane + 32 * (q >> 1)) + (q & 1);
+        if (k < K) zmine = k;
+      }
+      const int znew = __shfl_sync(0xffffffffu, zmine, L);
+      // put the token back with its new topic; the count tables only move when the topic changed
+      if (lane == 0) {
+        phi[znew] += s_cm[znew];
+        if (znew != zold) {
+          atomicAdd(wrow + znew, 1);
+          atomicSub(wrow + zold, 1);
+          if (DK16) {
+            int* d32 = reinterpret_cast<int*>(reinterpret_cast<unsigned short*>(a.n_dk) + (size_t)d * K);
+            atomicAdd(d32 + (znew >> 1), (znew & 1) ? 65536 : 1);       // rows are 16-byte aligned here
+            atomicSub(d32 + (zold >> 1), (zold & 1) ? 65536 : 1);
+          } else {
+            int* drow = a.n_dk + (size_t)d * K;
+            atomicAdd(drow + znew, 1);
+            atomicSub(drow + zold, 1);
+          }
+        }
+      }
+      // the next token's row was requested before these table moves: remember them in case it is the same document
+      pend_doc = (znew != zold) ? d : -1; pend_new = znew; pend_old = zold;
+      if (lane == j) znew_l = znew;
+    }
+    if (lane < nb) a.tok_z[kb + lane] = znew_l;
+  }
+  return (unsigned long long)(k1 - k0);
+}
+
 template <int KJ, bool DK16>
 __global__ void __launch_bounds__(32 * lda_smem_warps<KJ, DK16>(), 1) lda_pass_smem_kernel(LdaArgs a) {
   constexpr int KS = 32 * KJ;                       // padded topic count
@@ -356,26 +486,7 @@ __global__ void __launch_bounds__(32 * lda_smem_warps<KJ, DK16>(), 1) lda_pass_s
   for (int k = threadIdx.x; k < NW * 2 * ROWB / 4; k += blockDim.x) reinterpret_cast<int*>(s_row_all)[k] = 0;
   float* phi = s_phi_all + warp * KS;
   uint8_t* rowbuf = s_row_all + (size_t)warp * 2 * ROWB;
-  const uint32_t rowbuf_s = smem_u32(rowbuf);
-  const int row_bytes = DK16 ? K * 2 : K * 4;       // a whole number of 16-byte chunks (host-checked)
-  const int nchunks = row_bytes >> 4;
   __syncthreads();
-
-  auto issue_row = [&](int d, int buf) {
-    const uint8_t* src = reinterpret_cast<const uint8_t*>(a.n_dk) + (size_t)d * row_bytes;
-    for (int ch = lane; ch < nchunks; ch += 32) cp_async16(rowbuf_s + buf * ROWB + ch * 16, src + ch * 16);
-    cp_async_commit();
-  };
-  auto row_add = [&](int buf, int z, int delta) {    // one lane: counts[z] += delta in the shared copy, clamped at 0
-    if (DK16) {
-      unsigned short* e = reinterpret_cast<unsigned short*>(rowbuf + buf * ROWB) + z;
-      const int v = (int)*e + delta;
-      *e = (unsigned short)max(v, 0);
-    } else {
-      int* e = reinterpret_cast<int*>(rowbuf + buf * ROWB) + z;
-      *e = max(*e + delta, 0);
-    }
-  };
 
   for (int t = 0; t < B; ++t) {
     const int c = (i + t) % B;
@@ -394,103 +505,7 @@ __global__ void __launch_bounds__(32 * lda_smem_warps<KJ, DK16>(), 1) lda_pass_s
         if (lane == 0) seg = atomicAdd(&s_next, 1);
         seg = __shfl_sync(0xffffffffu, seg, 0);
         if (seg >= s_end) break;
-        const int word = a.seg_word[seg] & 0x7FFFFFFF;
-        const int k0 = a.seg_ptr[seg], k1 = a.seg_ptr[seg + 1];
-        int* wrow = a.n_wk + (size_t)word * K;
-        __syncwarp();
-#pragma unroll 4
-        for (int k = lane; k < KS; k += 32) phi[k] = (k < K) ? ((float)ldcg_i32(wrow + k) + a.beta) * s_cm[k] : 0.f;
-        __syncwarp();
-        for (int kb = k0; kb < k1; kb += 32) {
-          const int nb = min(32, k1 - kb);
-          const int docs_l = (lane < nb) ? a.tok_doc[kb + lane] : 0;
-          const int zs_l = (lane < nb) ? a.tok_z[kb + lane] : 0;
-          int znew_l = zs_l;
-          int pend_doc = -1, pend_new = 0, pend_old = 0;      // table moves the row fetched ahead may have missed
-          issue_row(__shfl_sync(0xffffffffu, docs_l, 0), 0);
-          for (int j = 0; j < nb; ++j) {
-            const int d = __shfl_sync(0xffffffffu, docs_l, j);
-            const int zold = __shfl_sync(0xffffffffu, zs_l, j);
-            const int tk = kb + j;
-            const int buf = j & 1;
-            if (j + 1 < nb) {
-              issue_row(__shfl_sync(0xffffffffu, docs_l, j + 1), buf ^ 1);
-              cp_async_wait<1>();
-            } else {
-              cp_async_wait<0>();
-            }
-            __syncwarp();
-            // take the token out of both factors (shared copies only; the tables move once, below)
-            if (lane == 0) {
-              if (pend_doc == d) { row_add(buf, pend_new, 1); row_add(buf, pend_old, -1); }
-              phi[zold] -= s_cm[zold];
-              row_add(buf, zold, -1);
-            }
-            __syncwarp();
-            // p_k = (n_dk + alpha) * phi_k, running prefix over this lane's topics (2m, 2m+1), m = lane + 32 jp
-            float cpre[KJ];
-            float run = 0.f;
-            const float2* phi2 = reinterpret_cast<const float2*>(phi);
-#pragma unroll
-            for (int jp = 0; jp < KP; ++jp) {
-              const int m = lane + 32 * jp;
-              const float2 ph = phi2[m];
-              float n0, n1;
-              if (DK16) {
-                const unsigned w = reinterpret_cast<const unsigned*>(rowbuf + buf * ROWB)[m];
-                n0 = (float)(w & 0xFFFFu); n1 = (float)(w >> 16);
-              } else {
-                const int2 w = reinterpret_cast<const int2*>(rowbuf + buf * ROWB)[m];
-                n0 = (float)w.x; n1 = (float)w.y;
-              }
-              run = fmaf(n0 + a.alpha, ph.x, run); cpre[2 * jp] = run;
-              run = fmaf(n1 + a.alpha, ph.y, run); cpre[2 * jp + 1] = run;
-            }
-            float cum = run;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-              const float v = __shfl_up_sync(0xffffffffu, cum, o);
-              if (lane >= o) cum += v;
-            }
-            const float total = __shfl_sync(0xffffffffu, cum, 31);
-            const float u = uniform01(a.seed, (unsigned long long)tk * 2654435761ULL + (unsigned long long)i) * total;
-            const unsigned int ball = __ballot_sync(0xffffffffu, cum > u);
-            const int L = ball ? (__ffs(ball) - 1) : 31;
-            const float target = u - (cum - run);                  // position inside this lane's stretch
-            unsigned mask = 0u;
-#pragma unroll
-            for (int q = 0; q < KJ; ++q) mask |= (cpre[q] > target) ? (1u << q) : 0u;
-            int zmine = zold;
-            if (mask != 0u) {
-              const int q = __ffs(mask) - 1;
-              const int k = 2 * (lane + 32 * (q >> 1)) + (q & 1);
-              if (k < K) zmine = k;
-            }
-            const int znew = __shfl_sync(0xffffffffu, zmine, L);
-            // put the token back with its new topic; the count tables only move when the topic changed
-            if (lane == 0) {
-              phi[znew] += s_cm[znew];
-              if (znew != zold) {
-                atomicAdd(wrow + znew, 1);
-                atomicSub(wrow + zold, 1);
-                if (DK16) {
-                  int* d32 = reinterpret_cast<int*>(reinterpret_cast<unsigned short*>(a.n_dk) + (size_t)d * K);
-                  atomicAdd(d32 + (znew >> 1), (znew & 1) ? 65536 : 1);       // rows are 16-byte aligned here
-                  atomicSub(d32 + (zold >> 1), (zold & 1) ? 65536 : 1);
-                } else {
-                  int* drow = a.n_dk + (size_t)d * K;
-                  atomicAdd(drow + znew, 1);
-                  atomicSub(drow + zold, 1);
-                }
-              }
-            }
-            // the next token's row was requested before these table moves: remember them in case it is the same document
-            pend_doc = (znew != zold) ? d : -1; pend_new = znew; pend_old = zold;
-            if (lane == j) znew_l = znew;
-          }
-          if (lane < nb) a.tok_z[kb + lane] = znew_l;
-        }
-        if (lane == 0) local_trained += (unsigned long long)(k1 - k0);
+        local_trained += lda_run_segment_smem<KJ, DK16>(a, seg, lane, K, i, phi, rowbuf, s_cm);
       }
     }
     __syncthreads();
@@ -500,6 +515,175 @@ __global__ void __launch_bounds__(32 * lda_smem_warps<KJ, DK16>(), 1) lda_pass_s
     }
   }
   if (lane == 0 && local_trained) atomicAdd(a.trained, local_trained);
+}
+
+// ----------------------------------------------------------------------------
+// Whole-iteration kernel: N rotation steps x S word-topic slices in ONE cooperative launch; the last warp of
+// every CTA is the communication warp of rotate_ring.cuh, pulling the next use of the other slice over NVLink
+// while the sampling warps work (LDAMPCollectiveMapper.java:263-300 — `for j < N: for k < numModelSlices:
+// getSplitMap(k); schedule(); rotate(k)`).  Workers are clusters of `cs` CTAs exactly as in the MF-SGD epoch
+// kernel (csrc/mf.cu): few, fat workers keep the ticket ring short when the panels are small.
+// ----------------------------------------------------------------------------
+struct LdaPanelDesc {
+  const int* blk_seg_ptr;
+  const int* seg_word;
+  const int* seg_ptr;
+  const int* tok_doc;
+  int* tok_z;
+  unsigned int* col_ticket;
+};
+
+struct LdaEpochArgs {
+  void* n_dk;
+  const float* commons;
+  const LdaPanelDesc* panels;
+  const int* panel_of_step;
+  unsigned long long* trained;
+  unsigned long long deadline_ns;
+  unsigned long long seed;
+  unsigned int ticket_epoch;
+  int cs, K;
+  float alpha, beta;
+  rot::RingArgs ring;
+};
+
+struct LdaCore {
+  int* n_dk; int* n_wk;
+  const int* seg_word; const int* seg_ptr; const int* tok_doc; int* tok_z;
+  unsigned long long seed; float alpha, beta;
+};
+
+__device__ __forceinline__ void lmbar_arrive_remote(uint32_t bar, uint32_t cta) {
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+      "}\n" ::"r"(bar), "r"(cta) : "memory");
+}
+__device__ __forceinline__ void lst_remote_u32(uint32_t addr, uint32_t cta, uint32_t v) {
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n"
+      "st.shared::cluster.u32 [ra], %2;\n"
+      "}\n" ::"r"(addr), "r"(cta), "r"(v) : "memory");
+}
+__device__ __forceinline__ void lmbar_wait_acq_cluster(uint32_t bar, uint32_t parity) {
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+        "selp.b32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    if (ok) break;
+  }
+}
+
+template <int KJ, bool DK16>
+__global__ void __launch_bounds__(32 * (lda_smem_warps<KJ, DK16>() + 1), 1)
+lda_epoch_kernel(const __grid_constant__ LdaEpochArgs a) {
+  constexpr int KS = 32 * KJ;
+  constexpr int NW = lda_smem_warps<KJ, DK16>();         // sampling warps; warp NW is the communication warp
+  constexpr int ROWB = DK16 ? KS * 2 : KS * 4;
+  extern __shared__ __align__(16) uint8_t lsm[];
+  float* s_cm = reinterpret_cast<float*>(lsm);
+  float* s_phi_all = s_cm + KS;
+  uint8_t* s_row_all = reinterpret_cast<uint8_t*>(s_phi_all + NW * KS);
+  __shared__ __align__(8) unsigned long long s_bar[2];
+  __shared__ unsigned int s_flags;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cs = (uint32_t)a.cs;
+  const uint32_t crank = cs > 1 ? cluster_ctarank() : 0u;
+  const int worker = blockIdx.x / cs, B = gridDim.x / cs, K = a.K;
+  const uint32_t bar_go = smem_u32(&s_bar[0]), bar_done = smem_u32(&s_bar[1]);
+  const bool ring_on = a.ring.world > 0;
+  if (threadIdx.x == 0) {
+    mbar_init(bar_go, 1);
+    mbar_init(bar_done, cs);
+    s_flags = 0u;
+    fence_barrier_init();
+  }
+  for (int k = threadIdx.x; k < KS; k += blockDim.x) s_cm[k] = (k < K) ? a.commons[k] : 0.f;
+  for (int k = threadIdx.x; k < NW * 2 * ROWB / 4; k += blockDim.x) reinterpret_cast<int*>(s_row_all)[k] = 0;
+  if (cs > 1) cluster_sync_all(); else __syncthreads();
+
+  if (warp == NW) {
+    if (ring_on) rot::comm_warp_loop(a.ring);
+  } else {
+    float* phi = s_phi_all + warp * KS;
+    uint8_t* rowbuf = s_row_all + (size_t)warp * 2 * ROWB;
+    const int wid = (int)crank * NW + warp, nw = (int)cs * NW;
+    const bool leader = (crank == 0u && threadIdx.x == 0);
+    rot::RingCtl* ctl = ring_on ? rot::ctl_of(a.ring, a.ring.rank) : nullptr;
+    unsigned long long local_trained = 0;
+    uint32_t ph_go = 0, ph_done = 0;
+    bool dead = false;
+    const unsigned int tbase = a.ticket_epoch * (unsigned)B;
+    for (int g = 0; g < a.ring.steps && !dead; ++g) {
+      const LdaPanelDesc pd = a.panels[a.panel_of_step[g]];
+      LdaCore core;
+      core.n_dk = reinterpret_cast<int*>(a.n_dk);
+      core.n_wk = ring_on ? reinterpret_cast<int*>(rot::slice_ptr(a.ring, g))
+                          : reinterpret_cast<int*>(a.ring.peer[0] + a.ring.off_buf[g % a.ring.S][0]);
+      core.seg_word = pd.seg_word; core.seg_ptr = pd.seg_ptr; core.tok_doc = pd.tok_doc; core.tok_z = pd.tok_z;
+      core.seed = a.seed + (unsigned long long)g * 0x9E3779B97F4A7C15ULL; core.alpha = a.alpha; core.beta = a.beta;
+      const unsigned long long t_end = a.deadline_ns ? globaltimer_ns() + a.deadline_ns : 0ULL;
+      for (int t = 0; t < B; ++t) {
+        const int c = (worker + t) % B;
+        if (leader) {
+          unsigned int fl = 0u;
+          if (t == 0 && ring_on && !rot::wait_slice(a.ring, g)) fl = 2u;
+          if (fl == 0u) {
+            const unsigned int want = tbase + (unsigned)t;
+            if (ld_acquire_gpu(pd.col_ticket + c) != want) {
+              const unsigned long long t0 = rot::now_ns();
+              unsigned spins = 0;
+              while (ld_acquire_gpu(pd.col_ticket + c) != want) {
+                __nanosleep(32);
+                if ((++spins & 255u) == 0u && ring_on) {
+                  if (rot::aborted(ctl)) { fl = 2u; break; }
+                  if (a.ring.timeout_ns != 0ULL && rot::now_ns() - t0 > a.ring.timeout_ns) {
+                    if (atomicCAS(&ctl->error, 0u, (unsigned)rot::ERR_TICKET) == 0u) ctl->error_detail = (unsigned)g;
+                    fl = 2u; break;
+                  }
+                }
+              }
+            }
+          }
+          if (fl == 0u && t_end != 0ULL && globaltimer_ns() > t_end) fl = 1u;
+          for (uint32_t q = 0; q < cs; ++q) {
+            if (cs > 1) { lst_remote_u32(smem_u32(&s_flags), q, fl); lmbar_arrive_remote(bar_go, q); }
+            else { s_flags = fl; mbar_arrive(bar_go); }
+          }
+        }
+        lmbar_wait_acq_cluster(bar_go, ph_go);
+        ph_go ^= 1u;
+        const unsigned int fl = *reinterpret_cast<volatile unsigned int*>(&s_flags);
+        if (!(fl & 3u)) {
+          const int s0 = pd.blk_seg_ptr[(size_t)worker * B + c], s1 = pd.blk_seg_ptr[(size_t)worker * B + c + 1];
+          for (int seg = s0 + wid; seg < s1; seg += nw)
+            local_trained += lda_run_segment_smem<KJ, DK16>(core, seg, lane, K, worker, phi, rowbuf, s_cm);
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * NW) : "memory");
+        if (threadIdx.x == 0) {
+          __threadfence();
+          if (cs > 1) lmbar_arrive_remote(bar_done, 0); else mbar_arrive(bar_done);
+        }
+        if (leader) {
+          lmbar_wait_acq_cluster(bar_done, ph_done);
+          ph_done ^= 1u;
+          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(pd.col_ticket + c), "r"(tbase + (unsigned)t + 1u) : "memory");
+        }
+        if (fl & 2u) { dead = true; break; }
+      }
+      if (threadIdx.x == 0 && ring_on && !dead) rot::step_done(a.ring, g);
+    }
+    if (lane == 0 && local_trained) atomicAdd(a.trained, local_trained);
+  }
+  if (cs > 1) cluster_sync_all(); else __syncthreads();
 }
 
 template <int KJ, bool DK16> constexpr size_t lda_smem_bytes() {
@@ -600,6 +784,64 @@ int hb_lda_pass_dk16(unsigned short* n_dk16, int* n_wk, const float* commons, co
                      unsigned long long deadline_ns, unsigned long long* trained, void* stream) {
   return lda_launch(n_dk16, true, n_wk, commons, blk_seg_ptr, seg_word, seg_ptr, tok_doc, tok_z, B, K, alpha, beta, seed,
                     col_ticket, ticket_base, deadline_ns, trained, stream);
+}
+
+// ---- whole-iteration launch (rotation fused); see hb_sgd_epoch for the ring arguments ----
+static const void* lda_epoch_fn(int K, bool dk16, size_t* smem, int* threads) {
+#define HB_LDA_EPICK(KJ_)                                                                                       \
+  do {                                                                                                           \
+    if (dk16) { *smem = lda_smem_bytes<KJ_, true>(); *threads = 32 * (lda_smem_warps<KJ_, true>() + 1); return (const void*)lda_epoch_kernel<KJ_, true>; }   \
+    *smem = lda_smem_bytes<KJ_, false>(); *threads = 32 * (lda_smem_warps<KJ_, false>() + 1); return (const void*)lda_epoch_kernel<KJ_, false>;              \
+  } while (0)
+  if (K <= 256) HB_LDA_EPICK(8);
+  if (K <= 512) HB_LDA_EPICK(16);
+  HB_LDA_EPICK(32);
+#undef HB_LDA_EPICK
+}
+
+// 1 when the whole-iteration kernel handles (K, table width): rows must be whole 16-byte chunks, K <= 1024.
+int hb_lda_epoch_supported(int K, int dk16) { return (K >= 2 && K <= 1024 && (dk16 ? K % 8 == 0 : K % 4 == 0)) ? 1 : 0; }
+
+int hb_lda_epoch_max_workers(int K, int dk16, int cs) {
+  if (cs < 1 || cs > 8 || (cs & (cs - 1)) != 0 || !hb_lda_epoch_supported(K, dk16)) return 0;
+  size_t smem = 0; int threads = 0;
+  const void* fn = lda_epoch_fn(K, dk16 != 0, &smem, &threads);
+  if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+  if (cs == 1) return sm_count();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(sm_count() / cs * cs));
+  cfg.blockDim = dim3((unsigned)threads);
+  cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, fn, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int hb_lda_epoch(void* n_dk, int dk16, const float* commons, const void* panels_dev, const int* panel_of_step_dev,
+                 int steps, int S, int workers, int cs, int K, float alpha, float beta, unsigned long long seed,
+                 unsigned ticket_epoch, unsigned long long deadline_ns, unsigned long long* trained,
+                 void* const* peer_state, int my_rank, int world, unsigned long long off_ctl,
+                 const unsigned long long* off_buf4, const unsigned long long* bytes2, const int* src_rank_dev,
+                 unsigned cnt_base, const unsigned* par_base2, unsigned long long timeout_ns, void* stream) {
+  HB_REQUIRE(hb_lda_epoch_supported(K, dk16), "hb_lda_epoch: K=%d (dk16=%d) not supported (need K <= 1024, rows of whole 16-byte chunks)", K, dk16);
+  HB_REQUIRE(workers >= 1 && workers <= hb_lda_epoch_max_workers(K, dk16, cs),
+             "hb_lda_epoch: %d workers of %d CTAs cannot be co-resident (max %d)", workers, cs, hb_lda_epoch_max_workers(K, dk16, cs));
+  HB_REQUIRE((reinterpret_cast<uintptr_t>(n_dk) & 15) == 0, "hb_lda_epoch: the document-topic table must be 16-byte aligned");
+  LdaEpochArgs a;
+  memset(&a, 0, sizeof(a));
+  if (rot::fill_ring(a.ring, peer_state, my_rank, world, S, steps, off_ctl, off_buf4, bytes2, src_rank_dev, cnt_base,
+                     par_base2, timeout_ns) != 0) return -2;
+  a.n_dk = n_dk; a.commons = commons; a.panels = reinterpret_cast<const LdaPanelDesc*>(panels_dev);
+  a.panel_of_step = panel_of_step_dev; a.trained = trained; a.deadline_ns = deadline_ns; a.seed = seed;
+  a.ticket_epoch = ticket_epoch; a.cs = cs; a.K = K; a.alpha = alpha; a.beta = beta;
+  size_t smem = 0; int threads = 0;
+  const void* fn = lda_epoch_fn(K, dk16 != 0, &smem, &threads);
+  HB_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  return rot::launch_epoch(fn, threads, smem, workers, cs, a, stream);
 }
 
 int hb_lda_topic_sums(const int* n_wk, long long words, int K, long long* sums, void* stream) {

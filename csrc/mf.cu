@@ -20,9 +20,11 @@
 // intra-block collision is resolved last-writer-wins.  A %globaltimer deadline gives the
 // reference's timer-bounded partial pass; the number of ratings actually trained is returned.
 #include "common.cuh"
+#include "rotate_ring.cuh"
 #include "../include/harp_b200.h"
 
 #include <cooperative_groups.h>
+#include <string.h>
 
 namespace hb {
 namespace mf {
@@ -76,9 +78,106 @@ struct SgdArgs {
 #ifndef HB_SGD_PF
 #define HB_SGD_PF 1     // deeper w prefetch measured slower (the pass is bound by random-row DRAM traffic, not latency)
 #endif
+// One column run (segment) of a block: h stays in registers, the run's ratings are trained in order.
+// Returns the number of ratings of the run (same value in every lane).
+template <int RV, typename Core>
+__device__ __forceinline__ unsigned long long sgd_run_segment(const Core& a, int seg, int lane, int nl4) {
+  constexpr int PF = RV == 1 ? HB_SGD_PF : (RV == 2 ? 2 : 1);     // w rows in flight per warp
+    // bit 31 of seg_col marks a sub-run of a long column run that was split so that several warps
+    // can work on a popular column at once; such sub-runs merge their h deltas additively
+    const int col_raw = a.seg_col[seg];
+    const bool shared_col = col_raw < 0;
+    const int col = col_raw & 0x7FFFFFFF;
+    const int k0 = a.seg_ptr[seg], k1 = a.seg_ptr[seg + 1];
+    float4 h[RV], h0[RV];
+#pragma unroll
+    for (int u = 0; u < RV; ++u) {
+      h[u] = (lane + 32 * u < nl4) ? ldcg4(a.H + (size_t)col * a.rank + (lane + 32 * u) * 4)
+                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+      h0[u] = h[u];
+    }
+    // Row ids and values of the run come in with one coalesced load (lane j holds rating k0 + j); the w rows
+    // of the next PF ratings are kept in flight, so a rating costs 1/PF of a memory round trip, not a whole one.
+    for (int kb = k0; kb < k1; kb += 32) {
+      const int nb = min(32, k1 - kb);
+      const int rows_l = (lane < nb) ? a.r_row[kb + lane] : 0;
+      const float vals_l = (lane < nb) ? a.r_val[kb + lane] : 0.f;
+      // a w row fetched early is stale if one of the PF ratings before it hits the same row (duplicate
+      // (row, col) ratings only): those are flagged in bit 31 and re-read at their turn
+      unsigned dup = 0;
+#pragma unroll
+      for (int q = 1; q <= PF; ++q) {
+        const int prev = __shfl_up_sync(0xffffffffu, rows_l, q);
+        if (lane >= q && lane < nb && prev == rows_l) dup = 0x80000000u;
+      }
+      const unsigned rows_e = (unsigned)rows_l | dup;
+      float4 wq[PF][RV];
+#pragma unroll
+      for (int q = 0; q < PF; ++q) {
+        const int rq = (int)(__shfl_sync(0xffffffffu, rows_e, q) & 0x7FFFFFFFu);
+#pragma unroll
+        for (int u = 0; u < RV; ++u)
+          wq[q][u] = (q < nb && lane + 32 * u < nl4) ? ldcg4(a.W + (size_t)rq * a.rank + (lane + 32 * u) * 4)
+                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      for (int j0 = 0; j0 < nb; j0 += PF) {
+#pragma unroll
+        for (int q = 0; q < PF; ++q) {
+          const int j = j0 + q;
+          if (j < nb) {
+            const unsigned re = __shfl_sync(0xffffffffu, rows_e, j);
+            const int row = (int)(re & 0x7FFFFFFFu);
+            const float v = __shfl_sync(0xffffffffu, vals_l, j);
+            float4 w[RV];
+#pragma unroll
+            for (int u = 0; u < RV; ++u) w[u] = wq[q][u];
+            if (re & 0x80000000u) {
+#pragma unroll
+              for (int u = 0; u < RV; ++u)
+                if (lane + 32 * u < nl4) w[u] = ldcg4(a.W + (size_t)row * a.rank + (lane + 32 * u) * 4);
+            }
+            if (j + PF < nb) {
+              const int rn = (int)(__shfl_sync(0xffffffffu, rows_e, j + PF) & 0x7FFFFFFFu);
+#pragma unroll
+              for (int u = 0; u < RV; ++u)
+                if (lane + 32 * u < nl4) wq[q][u] = ldcg4(a.W + (size_t)rn * a.rank + (lane + 32 * u) * 4);
+            }
+            float dot = 0.f;
+#pragma unroll
+            for (int u = 0; u < RV; ++u)
+              dot += w[u].x * h[u].x + w[u].y * h[u].y + w[u].z * h[u].z + w[u].w * h[u].w;
+            const float e = warp_sum(dot) - v;
+            const float ee = a.eps * e, el = a.eps * a.lambda;
+#pragma unroll
+            for (int u = 0; u < RV; ++u) {
+              // w -= eps (e h + lambda w);  h -= eps (e w_old + lambda h)     (SGDMPTask.java:60-72)
+              float4 wn, hn;
+              wn.x = w[u].x - (ee * h[u].x + el * w[u].x); hn.x = h[u].x - (ee * w[u].x + el * h[u].x);
+              wn.y = w[u].y - (ee * h[u].y + el * w[u].y); hn.y = h[u].y - (ee * w[u].y + el * h[u].y);
+              wn.z = w[u].z - (ee * h[u].z + el * w[u].z); hn.z = h[u].z - (ee * w[u].z + el * h[u].z);
+              wn.w = w[u].w - (ee * h[u].w + el * w[u].w); hn.w = h[u].w - (ee * w[u].w + el * h[u].w);
+              h[u] = hn;
+              if (lane + 32 * u < nl4) stcg4(a.W + (size_t)row * a.rank + (lane + 32 * u) * 4, wn);
+            }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < RV; ++u) {
+      if (lane + 32 * u < nl4) {
+        float* hp = a.H + (size_t)col * a.rank + (lane + 32 * u) * 4;
+        if (shared_col)
+          red_add_v4(hp, make_float4(h[u].x - h0[u].x, h[u].y - h0[u].y, h[u].z - h0[u].z, h[u].w - h0[u].w));
+        else
+          stcg4(hp, h[u]);
+      }
+    }
+    return (unsigned long long)(k1 - k0);
+}
+
 template <int RV>   // float4s per lane: rank <= 128 * RV
 __global__ void __launch_bounds__(sgd_threads(RV), (RV == 1 && sgd_threads(RV) <= 512) ? 2 : 1) sgd_pass_kernel(SgdArgs a) {
-  constexpr int PF = RV == 1 ? HB_SGD_PF : (RV == 2 ? 2 : 1);     // w rows in flight per warp
   __shared__ int s_next;      // next segment of the current block
   __shared__ int s_stop;
   __shared__ int s_c;         // column-block of this step
@@ -147,97 +246,7 @@ __global__ void __launch_bounds__(sgd_threads(RV), (RV == 1 && sgd_threads(RV) <
         if (lane == 0) seg = atomicAdd(&s_next, 1);
         seg = __shfl_sync(0xffffffffu, seg, 0);
         if (seg >= s_end) break;
-        // bit 31 of seg_col marks a sub-run of a long column run that was split so that several warps
-        // can work on a popular column at once; such sub-runs merge their h deltas additively
-        const int col_raw = a.seg_col[seg];
-        const bool shared_col = col_raw < 0;
-        const int col = col_raw & 0x7FFFFFFF;
-        const int k0 = a.seg_ptr[seg], k1 = a.seg_ptr[seg + 1];
-        float4 h[RV], h0[RV];
-#pragma unroll
-        for (int u = 0; u < RV; ++u) {
-          h[u] = (lane + 32 * u < nl4) ? ldcg4(a.H + (size_t)col * a.rank + (lane + 32 * u) * 4)
-                                       : make_float4(0.f, 0.f, 0.f, 0.f);
-          h0[u] = h[u];
-        }
-        // Row ids and values of the run come in with one coalesced load (lane j holds rating k0 + j); the w rows
-        // of the next PF ratings are kept in flight, so a rating costs 1/PF of a memory round trip, not a whole one.
-        for (int kb = k0; kb < k1; kb += 32) {
-          const int nb = min(32, k1 - kb);
-          const int rows_l = (lane < nb) ? a.r_row[kb + lane] : 0;
-          const float vals_l = (lane < nb) ? a.r_val[kb + lane] : 0.f;
-          // a w row fetched early is stale if one of the PF ratings before it hits the same row (duplicate
-          // (row, col) ratings only): those are flagged in bit 31 and re-read at their turn
-          unsigned dup = 0;
-#pragma unroll
-          for (int q = 1; q <= PF; ++q) {
-            const int prev = __shfl_up_sync(0xffffffffu, rows_l, q);
-            if (lane >= q && lane < nb && prev == rows_l) dup = 0x80000000u;
-          }
-          const unsigned rows_e = (unsigned)rows_l | dup;
-          float4 wq[PF][RV];
-#pragma unroll
-          for (int q = 0; q < PF; ++q) {
-            const int rq = (int)(__shfl_sync(0xffffffffu, rows_e, q) & 0x7FFFFFFFu);
-#pragma unroll
-            for (int u = 0; u < RV; ++u)
-              wq[q][u] = (q < nb && lane + 32 * u < nl4) ? ldcg4(a.W + (size_t)rq * a.rank + (lane + 32 * u) * 4)
-                                                         : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-          for (int j0 = 0; j0 < nb; j0 += PF) {
-#pragma unroll
-            for (int q = 0; q < PF; ++q) {
-              const int j = j0 + q;
-              if (j < nb) {
-                const unsigned re = __shfl_sync(0xffffffffu, rows_e, j);
-                const int row = (int)(re & 0x7FFFFFFFu);
-                const float v = __shfl_sync(0xffffffffu, vals_l, j);
-                float4 w[RV];
-#pragma unroll
-                for (int u = 0; u < RV; ++u) w[u] = wq[q][u];
-                if (re & 0x80000000u) {
-#pragma unroll
-                  for (int u = 0; u < RV; ++u)
-                    if (lane + 32 * u < nl4) w[u] = ldcg4(a.W + (size_t)row * a.rank + (lane + 32 * u) * 4);
-                }
-                if (j + PF < nb) {
-                  const int rn = (int)(__shfl_sync(0xffffffffu, rows_e, j + PF) & 0x7FFFFFFFu);
-#pragma unroll
-                  for (int u = 0; u < RV; ++u)
-                    if (lane + 32 * u < nl4) wq[q][u] = ldcg4(a.W + (size_t)rn * a.rank + (lane + 32 * u) * 4);
-                }
-                float dot = 0.f;
-#pragma unroll
-                for (int u = 0; u < RV; ++u)
-                  dot += w[u].x * h[u].x + w[u].y * h[u].y + w[u].z * h[u].z + w[u].w * h[u].w;
-                const float e = warp_sum(dot) - v;
-                const float ee = a.eps * e, el = a.eps * a.lambda;
-#pragma unroll
-                for (int u = 0; u < RV; ++u) {
-                  // w -= eps (e h + lambda w);  h -= eps (e w_old + lambda h)     (SGDMPTask.java:60-72)
-                  float4 wn, hn;
-                  wn.x = w[u].x - (ee * h[u].x + el * w[u].x); hn.x = h[u].x - (ee * w[u].x + el * h[u].x);
-                  wn.y = w[u].y - (ee * h[u].y + el * w[u].y); hn.y = h[u].y - (ee * w[u].y + el * h[u].y);
-                  wn.z = w[u].z - (ee * h[u].z + el * w[u].z); hn.z = h[u].z - (ee * w[u].z + el * h[u].z);
-                  wn.w = w[u].w - (ee * h[u].w + el * w[u].w); hn.w = h[u].w - (ee * w[u].w + el * h[u].w);
-                  h[u] = hn;
-                  if (lane + 32 * u < nl4) stcg4(a.W + (size_t)row * a.rank + (lane + 32 * u) * 4, wn);
-                }
-              }
-            }
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < RV; ++u) {
-          if (lane + 32 * u < nl4) {
-            float* hp = a.H + (size_t)col * a.rank + (lane + 32 * u) * 4;
-            if (shared_col)
-              red_add_v4(hp, make_float4(h[u].x - h0[u].x, h[u].y - h0[u].y, h[u].z - h0[u].z, h[u].w - h0[u].w));
-            else
-              stcg4(hp, h[u]);
-          }
-        }
-        if (lane == 0) local_trained += (unsigned long long)(k1 - k0);
+        local_trained += sgd_run_segment<RV>(a, seg, lane, nl4);
       }
     }
     // ---- release column-block c to the next CTA in the ring ----
@@ -251,6 +260,180 @@ __global__ void __launch_bounds__(sgd_threads(RV), (RV == 1 && sgd_threads(RV) <
     }
   }
   if (lane == 0 && local_trained) atomicAdd(a.trained, local_trained);
+}
+
+// ----------------------------------------------------------------------------
+// Whole-epoch kernel: N rotation steps x S model slices in ONE cooperative launch, with the model
+// rotation done by a communication warp per CTA over NVLink peer memory (rotate_ring.cuh) while the
+// other warps train (SGDCollectiveMapper.java:263-277 — `for j < N: for k < numModelSlices:
+// getSplitMap(k); schedule(); rotate(k)` — plus Rotator.java:53-67 / RotateTask.java:107-124).
+//
+// A *worker* (the unit that owns a row-block and is handed column-blocks through the ticket ring) is a
+// thread-block cluster of CS CTAs: small panels (many GPUs) want FEW, FAT workers — a pass costs B hand-overs
+// plus nnz / (B * warps-per-worker) updates, so with 4 or 8 SMs per worker the ring has 37 or 18 steps
+// instead of 148 while all SMs stay busy.  Inside a worker the cell's column runs are dealt to the
+// CS x 31 training warps round-robin (runs are stored longest first, so the deal is balanced); the
+// hand-over inside the cluster goes through two mbarriers in distributed shared memory, the hand-over
+// between workers through the acquire/release column tickets in global memory.
+// ----------------------------------------------------------------------------
+struct SgdPanelDesc {
+  const int* blk_seg_ptr;    // [B*B + 1]
+  const int* seg_col;
+  const int* seg_ptr;
+  const int* r_row;
+  const float* r_val;
+  unsigned int* col_ticket;  // [B], holds ticket_epoch * B between launches
+};
+
+struct SgdEpochArgs {
+  float* W;
+  const SgdPanelDesc* panels;      // device array
+  const int* panel_of_step;        // [steps] index into panels
+  unsigned long long* trained;
+  unsigned long long deadline_ns;  // per step, 0 = none
+  unsigned int ticket_epoch;       // launches of this kernel so far (every panel is visited once per launch)
+  int cs;                          // CTAs per worker (cluster size)
+  int rank;
+  float eps, lambda;
+  rot::RingArgs ring;
+};
+
+struct SgdCore {
+  float* W; float* H;
+  const int* seg_col; const int* seg_ptr; const int* r_row; const float* r_val;
+  int rank; float eps, lambda;
+};
+
+constexpr int EPOCH_THREADS = 1024;
+constexpr int EPOCH_COMM_WARP = EPOCH_THREADS / 32 - 1;      // last warp = communication warp
+constexpr int EPOCH_TRAIN_THREADS = EPOCH_THREADS - 32;
+
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t cta) {
+  // release at cluster scope: the arriving thread's prior writes (and, through the CTA barrier before it,
+  // its CTA's) are visible to whoever acquires the barrier phase
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+      "}\n" ::"r"(bar), "r"(cta) : "memory");
+}
+__device__ __forceinline__ void st_remote_u32(uint32_t addr, uint32_t cta, uint32_t v) {
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n"
+      "st.shared::cluster.u32 [ra], %2;\n"
+      "}\n" ::"r"(addr), "r"(cta), "r"(v) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_acq_cluster(uint32_t bar, uint32_t parity) {
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+        "selp.b32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    if (ok) break;
+  }
+}
+
+template <int RV>
+__global__ void __launch_bounds__(EPOCH_THREADS, 1) sgd_epoch_kernel(const __grid_constant__ SgdEpochArgs a) {
+  __shared__ __align__(8) unsigned long long s_bar[2];    // [0] go (1 arrival), [1] done (cs arrivals; used in the leader)
+  __shared__ unsigned int s_flags;                        // bit 0: stop (deadline), bit 1: abort
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cs = (uint32_t)a.cs;
+  const uint32_t crank = cs > 1 ? cluster_ctarank() : 0u;
+  const int worker = blockIdx.x / cs, B = gridDim.x / cs;
+  const uint32_t bar_go = smem_u32(&s_bar[0]), bar_done = smem_u32(&s_bar[1]);
+  const int nl4 = a.rank >> 2;
+  const bool ring_on = a.ring.world > 0;
+  if (threadIdx.x == 0) {
+    mbar_init(bar_go, 1);
+    mbar_init(bar_done, cs);
+    s_flags = 0u;
+    fence_barrier_init();
+  }
+  if (cs > 1) cluster_sync_all(); else __syncthreads();
+
+  if (warp == EPOCH_COMM_WARP) {
+    if (ring_on) rot::comm_warp_loop(a.ring);
+  } else {
+    const int wid = (int)crank * (EPOCH_TRAIN_THREADS / 32) + warp;      // training warp id inside the worker
+    const int nw = (int)cs * (EPOCH_TRAIN_THREADS / 32);
+    const bool leader = (crank == 0u && threadIdx.x == 0);
+    rot::RingCtl* ctl = ring_on ? rot::ctl_of(a.ring, a.ring.rank) : nullptr;
+    unsigned long long local_trained = 0;
+    uint32_t ph_go = 0, ph_done = 0;
+    bool dead = false;
+    const unsigned int tbase = a.ticket_epoch * (unsigned)B;
+    for (int g = 0; g < a.ring.steps && !dead; ++g) {
+      const SgdPanelDesc pd = a.panels[a.panel_of_step[g]];
+      SgdCore core;
+      core.W = a.W;
+      core.H = ring_on ? reinterpret_cast<float*>(rot::slice_ptr(a.ring, g))
+                       : reinterpret_cast<float*>(a.ring.peer[0] + a.ring.off_buf[g % a.ring.S][0]);
+      core.seg_col = pd.seg_col; core.seg_ptr = pd.seg_ptr; core.r_row = pd.r_row; core.r_val = pd.r_val;
+      core.rank = a.rank; core.eps = a.eps; core.lambda = a.lambda;
+      const unsigned long long t_end = a.deadline_ns ? globaltimer_ns() + a.deadline_ns : 0ULL;
+      for (int t = 0; t < B; ++t) {
+        const int c = (worker + t) % B;
+        if (leader) {
+          unsigned int fl = 0u;
+          if (t == 0 && ring_on && !rot::wait_slice(a.ring, g)) fl = 2u;
+          if (fl == 0u) {
+            // column-block c is ours once its previous holder has released it
+            const unsigned int want = tbase + (unsigned)t;
+            if (ld_acquire_gpu(pd.col_ticket + c) != want) {
+              const unsigned long long t0 = rot::now_ns();
+              unsigned spins = 0;
+              while (ld_acquire_gpu(pd.col_ticket + c) != want) {
+                __nanosleep(32);
+                if ((++spins & 255u) == 0u && ring_on) {
+                  if (rot::aborted(ctl)) { fl = 2u; break; }
+                  if (a.ring.timeout_ns != 0ULL && rot::now_ns() - t0 > a.ring.timeout_ns) {
+                    if (atomicCAS(&ctl->error, 0u, (unsigned)rot::ERR_TICKET) == 0u) ctl->error_detail = (unsigned)g;
+                    fl = 2u; break;
+                  }
+                }
+              }
+            }
+          }
+          if (fl == 0u && t_end != 0ULL && globaltimer_ns() > t_end) fl = 1u;
+          for (uint32_t q = 0; q < cs; ++q) {
+            if (cs > 1) { st_remote_u32(smem_u32(&s_flags), q, fl); mbar_arrive_remote(bar_go, q); }
+            else { s_flags = fl; mbar_arrive(bar_go); }
+          }
+        }
+        mbar_wait_acq_cluster(bar_go, ph_go);      // unbounded: the leader may be waiting for a peer GPU
+        ph_go ^= 1u;
+        const unsigned int fl = *reinterpret_cast<volatile unsigned int*>(&s_flags);
+        if (!(fl & 3u)) {
+          const int s0 = pd.blk_seg_ptr[(size_t)worker * B + c], s1 = pd.blk_seg_ptr[(size_t)worker * B + c + 1];
+          for (int seg = s0 + wid; seg < s1; seg += nw) local_trained += sgd_run_segment<RV>(core, seg, lane, nl4);
+        }
+        // ---- hand the column-block on ----
+        asm volatile("bar.sync 1, %0;" ::"n"(EPOCH_TRAIN_THREADS) : "memory");
+        if (threadIdx.x == 0) {
+          __threadfence();
+          if (cs > 1) mbar_arrive_remote(bar_done, 0); else mbar_arrive(bar_done);
+        }
+        if (leader) {
+          mbar_wait_acq_cluster(bar_done, ph_done);
+          ph_done ^= 1u;
+          // tickets keep moving even when the step was cut short (deadline / abort) so nobody waits for ever
+          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(pd.col_ticket + c), "r"(tbase + (unsigned)t + 1u) : "memory");
+        }
+        if (fl & 2u) { dead = true; break; }
+      }
+      if (threadIdx.x == 0 && ring_on && !dead) rot::step_done(a.ring, g);
+    }
+    if (lane == 0 && local_trained) atomicAdd(a.trained, local_trained);
+  }
+  // nobody leaves while a cluster peer may still arrive on its barriers
+  if (cs > 1) cluster_sync_all(); else __syncthreads();
 }
 
 // Σ (v - w·h)^2 over a rating list; one warp per rating.
@@ -364,6 +547,60 @@ static int sgd_launch(SgdArgs& a, void* stream) {
   const int threads = sgd_threads(rank <= 128 ? 1 : (rank <= 256 ? 2 : 4));
   HB_CUDA_OK(cudaLaunchCooperativeKernel(fn, dim3(B), dim3(threads), args, 0, (cudaStream_t)stream));
   return 0;
+}
+
+// ---- whole-epoch launch (rotation fused) ----
+static const void* sgd_epoch_fn(int rank) {
+  return rank <= 128 ? (const void*)sgd_epoch_kernel<1> : rank <= 256 ? (const void*)sgd_epoch_kernel<2>
+                                                                         : (const void*)sgd_epoch_kernel<4>;
+}
+
+// How many workers (clusters of `cs` CTAs, one CTA per SM) one cooperative launch keeps resident.
+int hb_sgd_epoch_max_workers(int rank, int cs) {
+  if (cs < 1 || cs > 8 || (cs & (cs - 1)) != 0) return 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(sm_count() / cs * cs));
+  cfg.blockDim = dim3(EPOCH_THREADS);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cs == 1) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sgd_epoch_fn(rank), EPOCH_THREADS, 0) != cudaSuccess) return 0;
+    return per_sm > 0 ? sm_count() : 0;
+  }
+  if (cudaOccupancyMaxActiveClusters(&n, sgd_epoch_fn(rank), &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int hb_ring_ctl_bytes(void) { return (int)sizeof(rot::RingCtl); }
+
+// One epoch = `steps` panel passes (step g trains panel panel_of_step[g] against slice g % S) in ONE launch.
+//   panels: device array of 6-pointer descriptors {blk_seg_ptr, seg_col, seg_ptr, r_row, r_val, col_ticket};
+//   every panel must be bucketed with B = `workers` blocks per side and is visited exactly once per launch
+//   (its tickets advance by B), ticket_epoch = number of earlier launches on these panels.
+//   world == 0: no ring, peer_state[0] + off_buf4[2k] is slice k.  world >= 1: symmetric ring state of every
+//   rank (world == 1 is a loop-back ring onto this rank's own buffers).
+int hb_sgd_epoch(float* W, const void* panels_dev, const int* panel_of_step_dev, int steps, int S, int workers,
+                 int cs, int rank, float eps, float lambda, unsigned ticket_epoch, unsigned long long deadline_ns,
+                 unsigned long long* trained, void* const* peer_state, int my_rank, int world,
+                 unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
+                 const int* src_rank_dev, unsigned cnt_base, const unsigned* par_base2,
+                 unsigned long long timeout_ns, void* stream) {
+  HB_REQUIRE(rank >= 4 && rank % 4 == 0 && rank <= 512, "hb_sgd_epoch: need rank %% 4 == 0 and rank <= 512 (got %d)", rank);
+  HB_REQUIRE(workers >= 1 && workers <= hb_sgd_epoch_max_workers(rank, cs),
+             "hb_sgd_epoch: %d workers of %d CTAs cannot be co-resident (max %d)", workers, cs, hb_sgd_epoch_max_workers(rank, cs));
+  SgdEpochArgs a;
+  memset(&a, 0, sizeof(a));
+  if (rot::fill_ring(a.ring, peer_state, my_rank, world, S, steps, off_ctl, off_buf4, bytes2, src_rank_dev, cnt_base,
+                par_base2, timeout_ns) != 0) return -2;
+  a.W = W; a.panels = reinterpret_cast<const SgdPanelDesc*>(panels_dev); a.panel_of_step = panel_of_step_dev;
+  a.trained = trained; a.deadline_ns = deadline_ns; a.ticket_epoch = ticket_epoch; a.cs = cs; a.rank = rank;
+  a.eps = eps; a.lambda = lambda;
+  return rot::launch_epoch(sgd_epoch_fn(rank), EPOCH_THREADS, 0, workers, cs, a, stream);
 }
 
 // Device wall clock (ns) usable as a deadline base for hb_sgd_pass.

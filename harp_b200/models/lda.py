@@ -16,12 +16,15 @@ import torch
 import torch.distributed as dist
 
 from ..ops import lda as L
+from ..ops import mf as _mf
+from ..parallel.ring import RingSchedule, RingState
 
 
 class LDAEngine:
     def __init__(self, docs: torch.Tensor, words: torch.Tensor, num_docs_local: int, vocab: int, K: int,
                  alpha: float, beta: float, *, symm=None, blocks: Optional[int] = None, seed: int = 0, group=None,
-                 num_slices: Optional[int] = None, dk_dtype: str = "auto"):
+                 num_slices: Optional[int] = None, dk_dtype: str = "auto", fused: Optional[bool] = None,
+                 cluster: Optional[int] = None, loopback: bool = False, max_run: Optional[int] = None):
         self.dev = docs.device
         self.K, self.V = int(K), int(vocab)
         self.alpha, self.beta = float(alpha), float(beta)
@@ -30,22 +33,44 @@ class LDAEngine:
         self.me = dist.get_rank(group) if dist.is_initialized() else 0
         self.symm = symm if self.N > 1 else None
         N = self.N
-        if num_slices is None:
-            ntok_max = float(docs.numel())
-            if dist.is_initialized() and N > 1:
-                t = torch.tensor([ntok_max], dtype=torch.float64, device=self.dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
-                ntok_max = float(t.item())
-            num_slices = 2 if (N == 1 or ntok_max / (2.0 * N) >= 4.0e6) else 1
-        self.S = S = int(num_slices)
+        import os
+        cuda = self.dev.type == "cuda"
+        self.S = S = int(num_slices) if num_slices else 2          # two slices in flight, like the reference
         assert S in (1, 2)
         self.cap = max(1, (self.V + S * N - 1) // (S * N))
-        if self.dev.type == "cuda":
+        ntok_max = float(docs.numel())
+        if dist.is_initialized() and N > 1:
+            t = torch.tensor([ntok_max], dtype=torch.float64, device=self.dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+            ntok_max = float(t.item())
+        per_panel = ntok_max / (float(S) * N)
+        # The sampling kernel is bound by reading one document-topic row per token; when no document is longer
+        # than an int16 can count, the table is kept in 16 bits (dk_dtype="int32" forces the wide table).
+        dk_dtype = os.environ.get("HB_LDA_DK", dk_dtype)          # triage knob
+        if dk_dtype == "auto":
+            longest = int(torch.bincount(docs.long(), minlength=1).max().item()) if docs.numel() else 0
+            dk_dtype = "int16" if (cuda and longest < 32768) else "int32"
+        self.dk16 = dk_dtype == "int16"
+        if fused is None:
+            fused = (cuda and (N == 1 or self.symm is not None) and os.environ.get("HB_LDA_FUSED", "1") != "0"
+                     and L.epoch_supported(self.K, self.dk16))
+        self.fused = bool(fused)
+        self.cs = 1
+        if cuda and self.fused:
+            self.cs = int(cluster) if cluster else _mf.pick_cluster(per_panel * 8)    # a token costs ~8x a rating
+            mx = L.epoch_max_workers(self.K, self.dk16, self.cs)
+            while mx < 1 and self.cs > 1:
+                self.cs //= 2
+                mx = L.epoch_max_workers(self.K, self.dk16, self.cs)
+            self.B = max(1, min(int(blocks) if blocks else mx, mx))
+            if max_run is None:
+                max_run = max(8, min(64, int(per_panel / (self.B * self.B) / (2.0 * self.cs * 24))))
+        elif cuda:
             sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
-            from ..ops.mf import auto_blocks
-            self.B = int(blocks) if blocks else auto_blocks(docs.numel() / (float(S) * N), min(L.max_blocks(self.K), sms), per_block=32)
+            self.B = int(blocks) if blocks else _mf.auto_blocks(per_panel, min(L.max_blocks(self.K), sms), per_block=32)
         else:
             self.B = int(blocks) if blocks else 2
+        self.max_run = int(max_run) if max_run else 64
         self.seed = int(seed)
         self.iteration = 0
         g = torch.Generator(device=self.dev).manual_seed(seed + 31 * self.me)
@@ -58,7 +83,7 @@ class LDAEngine:
             per = []
             for k in range(self.S):
                 m = (shard == s) & (slc == k)
-                per.append(L.build_token_panel(docs[m], local[m], z[m], self.B))
+                per.append(L.build_token_panel(docs[m], local[m], z[m], self.B, max_run=self.max_run))
             self.panels.append(per)
         cdt = torch.int32
         self.n_dk = torch.zeros(num_docs_local, self.K, dtype=cdt, device=self.dev)
@@ -66,27 +91,18 @@ class LDAEngine:
             for k in range(self.S):
                 p = self.panels[s][k]
                 L.count_into(p.tok_doc, p.tok_z, self.K, self.n_dk)
-        # The sampling kernel is bound by reading one document-topic row per token; when no document is longer
-        # than an int16 can count, the table is kept in 16 bits (dk_dtype="int32" forces the wide table).
-        import os
-        dk_dtype = os.environ.get("HB_LDA_DK", dk_dtype)          # triage knob
-        if dk_dtype == "auto":
-            longest = int(torch.bincount(docs.long(), minlength=1).max().item()) if self.ntok else 0
-            dk_dtype = "int16" if (self.dev.type == "cuda" and longest < 32768) else "int32"
-        if dk_dtype == "int16":
+        if self.dk16:
             self.n_dk = self.n_dk.to(torch.int16)
-        self.Wbuf: List[List[torch.Tensor]] = []
-        for k in range(self.S):
-            pair = []
-            for _ in range(2 if N > 1 else 1):
-                if self.symm is not None:
-                    t = self.symm.alloc(self.cap * self.K, cdt).view(self.cap, self.K)
-                else:
-                    t = torch.empty(self.cap, self.K, dtype=cdt, device=self.dev)
-                t.zero_()
-                pair.append(t)
-            self.Wbuf.append(pair)
-        self.cur, self.rot = [0] * S, [0] * S
+        self.ring = None
+        self._cur = [0] * S
+        self.sched = [RingSchedule(N, None) for _ in range(S)]     # plain ring (LDAMPCollectiveMapper.java:255-259)
+        if cuda:
+            self.ring = RingState(self.dev, self.cap * self.K, cdt, S, symm=self.symm, rank=self.me, world=N,
+                                  loopback=loopback)
+            self.Wbuf = [[b_.view(self.cap, self.K) for b_ in pair] for pair in self.ring.buf]
+        else:
+            self.Wbuf = [[torch.zeros(self.cap, self.K, dtype=cdt, device=self.dev) for _ in range(2 if N > 1 else 1)]
+                         for _ in range(S)]
         if self.dev.type == "cuda":
             self.comm_stream = torch.cuda.Stream(device=self.dev)
             self.ev_compute = [torch.cuda.Event(), torch.cuda.Event()]
@@ -103,20 +119,35 @@ class LDAEngine:
         self.topic_sums = torch.zeros(self.K, dtype=torch.int64, device=self.dev)
         self.commons = torch.zeros(self.K, dtype=torch.float32, device=self.dev)
         self.trained = torch.zeros(1, dtype=torch.int64, device=self.dev)
+        self.epochs_fused = 0
+        self._tables = {}
+        if cuda:
+            self.desc = L.panel_descriptors([self.panels[s][k] for s in range(N) for k in range(S)])
         self._refresh_topic_sums()
+        if dist.is_initialized() and N > 1:
+            dist.barrier(group=group)
+
+    @property
+    def cur(self) -> List[int]:
+        return self.ring.cur if self.ring is not None else self._cur
+
+    @property
+    def rot(self) -> List[int]:
+        return [s.rotations for s in self.sched]
 
     def _visiting(self, k: int) -> int:
-        return (self.me - self.rot[k]) % self.N
+        return self.sched[k].shard_at[self.me]
 
     def _wait_slice(self, k: int) -> None:
         if self.N > 1 and self.symm is not None and self.dev.type == "cuda":
             torch.cuda.current_stream().wait_event(self.ev_comm[k])
 
     def _rotate(self, k: int) -> None:
+        srcs = self.sched[k].rotate()
         if self.N == 1:
             return
         src, dst = self.Wbuf[k][self.cur[k]], self.Wbuf[k][1 - self.cur[k]]
-        pred = (self.me - 1) % self.N
+        pred, succ = srcs[self.me], srcs.index(self.me)
         if self.symm is not None and self.dev.type == "cuda":
             self.ev_compute[k].record()
             with torch.cuda.stream(self.comm_stream):
@@ -124,12 +155,11 @@ class LDAEngine:
                 self.symm.rotate_(dst, src, pred)
                 self.ev_comm[k].record()
         else:
-            ops = [dist.P2POp(dist.isend, src.contiguous(), (self.me + 1) % self.N, group=self.group),
+            ops = [dist.P2POp(dist.isend, src.contiguous(), succ, group=self.group),
                    dist.P2POp(dist.irecv, dst, pred, group=self.group)]
             for r in dist.batch_isend_irecv(ops):
                 r.wait()
         self.cur[k] ^= 1
-        self.rot[k] += 1
 
     def _refresh_topic_sums(self) -> None:
         self.topic_sums.zero_()
@@ -144,6 +174,32 @@ class LDAEngine:
         """One iteration = N rotations x S slices, then the global topic-sum refresh."""
         self.trained.zero_()
         self.iteration += 1
+        if self.fused and self.dev.type == "cuda":
+            N, S = self.N, self.S
+            pos_l, src_l = [], []
+            for _ in range(N):
+                for k in range(S):
+                    pos_l.append(self.sched[k].shard_at[self.me] * S + k)
+                    src_l.append(self.sched[k].rotate()[self.me])
+            for k in range(S):
+                self._wait_slice(k)
+            key = tuple(pos_l + src_l)
+            pos = self._tables.get(key)
+            if pos is None:
+                pos = torch.tensor(key, dtype=torch.int32).to(self.dev)
+                self._tables[key] = pos
+            steps = N * S
+            L.lda_epoch(self.n_dk, self.commons, self.desc, pos[:steps], steps, S, self.B, self.cs, self.alpha, self.beta,
+                        self.seed * 1000003 + self.iteration * 7919 + 104729 * self.me, self.epochs_fused, deadline_ms,
+                        self.trained, self.ring, pos[steps:])
+            self.epochs_fused += 1
+            self.ring.advance(N)
+            tb = (self.epochs_fused * self.B) & 0x7FFFFFFF
+            for per in self.panels:
+                for p in per:
+                    p.ticket_base = tb
+            self._refresh_topic_sums()
+            return self.trained
         for j in range(self.N):
             for k in range(self.S):
                 self._wait_slice(k)
@@ -182,6 +238,8 @@ class LDAEngine:
             for k in range(self.S):
                 self._wait_slice(k)
             torch.cuda.synchronize(self.dev)
+            if self.ring is not None and self.fused:
+                self.ring.check()
 
     def home_word_rows(self):
         """``(global word ids, count rows)`` of the word-topic rows currently resident."""

@@ -6,28 +6,34 @@ a ring; while slice k is being trained on, slice 1-k is in flight to the next wo
 (``dymoro/Rotator.java:53-67``).  One epoch = N rotations x 2 slices, so every H column meets every
 worker's ratings exactly once.
 
-Here: column j has home worker ``j % N``, slice ``(j // N) % S`` and slice-local index ``j // SN``
-(``S = num_slices``: 2 like the reference when panels are large; 1 when they are small — over NVLink a slice
-moves in microseconds, and one fatter panel per rotation step keeps the block schedule efficient).
-Each slice has a ping-pong pair of buffers in the symmetric workspace; the rotation is a peer *pull*
-over NVLink (``SymmetricWorkspace.rotate_``) issued on a side stream, overlapping the SGD kernel of
-the other slice.  The per-panel block schedule and the update itself are ``ops.mf.sgd_pass``.
+Here: column j has home worker ``j % N``, slice ``(j // N) % S`` and slice-local index ``j // SN``; always
+``S = 2`` slices in flight like the reference.  On GPUs a whole epoch is ONE cooperative launch
+(``csrc/mf.cu::sgd_epoch_kernel``): 2N panel passes back to back, and in every CTA a communication warp pulls
+the next use of the other slice from the source rank's symmetric slab over NVLink while the training warps
+work (``csrc/rotate_ring.cuh``).  Rotation orders may be randomised like the reference's
+(``dymoro/RotationUtil.java:58-90``): the per-step source ranks come from ``parallel.ring.RingSchedule``.
+The older path — one launch per panel, rotation as a separate pull kernel on a side stream — is kept for CPU
+tensors (gloo) and as the ``fused=False`` A/B arm; the RMSE pass uses it too.
 """
 from __future__ import annotations
 
 import math
-from typing import Dict, List, Optional, Tuple
+import os
+from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
 import torch.distributed as dist
 
 from ..ops import mf
+from ..parallel.ring import RingSchedule, RingState
 
 
 class MFSGDEngine:
     def __init__(self, rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, num_rows_local: int,
                  num_cols: int, rank: int, eps: float, lam: float, *, symm=None, blocks: Optional[int] = None,
-                 seed: int = 0, group=None, num_slices: Optional[int] = None):
+                 seed: int = 0, group=None, num_slices: Optional[int] = None, fused: Optional[bool] = None,
+                 cluster: Optional[int] = None, orders: Optional[Sequence[int]] = None, loopback: bool = False,
+                 max_run: Optional[int] = None):
         self.dev = rows.device
         self.rank_k = int(rank)
         self.eps, self.lam = float(eps), float(lam)
@@ -38,41 +44,54 @@ class MFSGDEngine:
         self.num_cols = int(num_cols)
         self.num_rows_local = int(num_rows_local)
         N = self.N
-        if num_slices is None:
-            # two slices (compute one while the other travels) only pay off while a half panel is still big
-            nnz_max = float(rows.numel())
-            if dist.is_initialized() and N > 1:
-                t = torch.tensor([nnz_max], dtype=torch.float64, device=self.dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
-                nnz_max = float(t.item())
-            num_slices = 2 if (N == 1 or nnz_max / (2.0 * N) >= 4.0e6) else 1
-        self.S = S = int(num_slices)
+        cuda = self.dev.type == "cuda"
+        self.S = S = int(num_slices) if num_slices else 2        # two slices in flight, like the reference
         assert S in (1, 2)
+        if fused is None:
+            fused = cuda and (N == 1 or self.symm is not None) and os.environ.get("HB_SGD_FUSED", "1") != "0"
+        self.fused = bool(fused)
         self.cap = max(1, (self.num_cols + S * N - 1) // (S * N))          # columns per (shard, slice)
-        if self.dev.type == "cuda":
+        nnz_max = float(rows.numel())
+        if dist.is_initialized() and N > 1:
+            t = torch.tensor([nnz_max], dtype=torch.float64, device=self.dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+            nnz_max = float(t.item())
+        per_panel = nnz_max / (float(S) * N)
+        self.cs = 1
+        if cuda and self.fused:
+            # worker = cluster of cs CTAs; B = as many workers as one cooperative launch keeps resident
+            self.cs = int(cluster) if cluster else mf.pick_cluster(per_panel)
+            mx = mf.epoch_max_workers(self.rank_k, self.cs)
+            while mx < 1 and self.cs > 1:
+                self.cs //= 2
+                mx = mf.epoch_max_workers(self.rank_k, self.cs)
+            self.B = int(blocks) if blocks else mx
+            self.B = max(1, min(self.B, mx))
+            if max_run is None:
+                max_run = mf.pick_max_run(per_panel, self.B, self.cs)
+        elif cuda:
             mx = mf.max_blocks(self.rank_k)
             sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
-            self.B = int(blocks) if blocks else mf.auto_blocks(rows.numel() / (float(S) * N), min(mx, 2 * sms))
+            self.B = int(blocks) if blocks else mf.auto_blocks(per_panel, min(mx, 2 * sms))
         else:
             self.B = int(blocks) if blocks else 4
+        self.max_run = int(max_run) if max_run else 32
         g = torch.Generator(device=self.dev).manual_seed(seed + 7919 * self.me)
         scale = 1.0 / math.sqrt(self.rank_k)
-        dt = torch.float32 if self.dev.type == "cuda" else torch.float64
+        dt = torch.float32 if cuda else torch.float64
         self.dt = dt
         self.W = (torch.rand(self.num_rows_local, self.rank_k, device=self.dev, generator=g, dtype=dt) * scale).contiguous()
-        # H slices: ping-pong buffers (symmetric memory when rotating)
-        self.Hbuf: List[List[torch.Tensor]] = []
-        for k in range(S):
-            pair = []
-            for _ in range(2 if N > 1 else 1):
-                if self.symm is not None:
-                    t = self.symm.alloc(self.cap * self.rank_k, dt).view(self.cap, self.rank_k)
-                else:
-                    t = torch.empty(self.cap, self.rank_k, dtype=dt, device=self.dev)
-                pair.append(t)
-            self.Hbuf.append(pair)
-        self.cur = [0] * S
-        self.rot = [0] * S
+        # H slices: control block + ping-pong buffers, one allocation (symmetric memory when there are peers)
+        self.ring = None
+        if cuda:
+            self.ring = RingState(self.dev, self.cap * self.rank_k, dt, S, symm=self.symm, rank=self.me, world=N,
+                                  loopback=loopback)
+            self.Hbuf = [[b.view(self.cap, self.rank_k) for b in pair] for pair in self.ring.buf]
+        else:
+            self.Hbuf = [[torch.empty(self.cap, self.rank_k, dtype=dt, device=self.dev) for _ in range(2 if N > 1 else 1)]
+                         for _ in range(S)]
+        self._cur = [0] * S
+        self.sched = [RingSchedule(N, orders) for _ in range(S)]        # every slice walks the same order array
         gh = torch.Generator(device=self.dev).manual_seed(seed + 104729)      # same H init on every rank, then
         for k in range(S):                                                    # each keeps its own shard
             full = torch.rand(N, self.cap, self.rank_k, device=self.dev, generator=gh, dtype=dt) * scale
@@ -88,28 +107,46 @@ class MFSGDEngine:
             per = []
             for k in range(S):
                 m = (shard == s) & (slc == k)
-                per.append(mf.build_panel(rows[m], local[m], vals[m], self.B))
+                per.append(mf.build_panel(rows[m], local[m], vals[m], self.B, max_run=self.max_run))
             self.panels.append(per)
         self.trained = torch.zeros(1, dtype=torch.int64, device=self.dev)
-        if self.dev.type == "cuda":
+        self.epochs_fused = 0
+        self._tables: Dict[tuple, torch.Tensor] = {}
+        if cuda:
+            self.desc = mf.panel_descriptors([self.panels[s][k] for s in range(N) for k in range(S)])
             self.comm_stream = torch.cuda.Stream(device=self.dev)
             self.ev_compute = [torch.cuda.Event(), torch.cuda.Event()]
             self.ev_comm = [torch.cuda.Event(), torch.cuda.Event()]
             for e in self.ev_comm:
                 e.record()
+            torch.cuda.synchronize(self.dev)
         self.comm_time_hidden = True
+        if dist.is_initialized() and N > 1:
+            dist.barrier(group=group)       # nobody starts a device collective before every rank's state exists
+
+    # cur parity lives in the ring state when there is one
+    @property
+    def cur(self) -> List[int]:
+        return self.ring.cur if self.ring is not None else self._cur
+
+    @property
+    def rot(self) -> List[int]:
+        return [s.rotations for s in self.sched]
 
     # ------------------------------------------------------------------------------------
     def _visiting_shard(self, k: int) -> int:
-        return (self.me - self.rot[k]) % self.N
+        return self.sched[k].shard_at[self.me]
 
     def _rotate(self, k: int) -> None:
-        """slice k moves to the next worker: every worker pulls its predecessor's copy."""
+        """slice k moves on: every worker pulls the copy of the worker the rotation map names as its source."""
         if self.N == 1:
+            self.sched[k].rotate()
             return
         src = self.Hbuf[k][self.cur[k]]
         dst = self.Hbuf[k][1 - self.cur[k]]
-        pred = (self.me - 1) % self.N
+        srcs = self.sched[k].rotate()
+        pred = srcs[self.me]
+        succ = srcs.index(self.me)
         if self.symm is not None and self.dev.type == "cuda":
             self.ev_compute[k].record()
             with torch.cuda.stream(self.comm_stream):
@@ -119,20 +156,47 @@ class MFSGDEngine:
         else:
             # gloo / NCCL send-recv ring (baseline path and CPU tests)
             send = src.contiguous()
-            ops = [dist.P2POp(dist.isend, send, (self.me + 1) % self.N, group=self.group),
+            ops = [dist.P2POp(dist.isend, send, succ, group=self.group),
                    dist.P2POp(dist.irecv, dst, pred, group=self.group)]
             for r in dist.batch_isend_irecv(ops):
                 r.wait()
         self.cur[k] ^= 1
-        self.rot[k] += 1
 
     def _wait_slice(self, k: int) -> None:
         if self.N > 1 and self.symm is not None and self.dev.type == "cuda":
             torch.cuda.current_stream().wait_event(self.ev_comm[k])
 
+    def _epoch_fused(self, deadline_ms: Optional[float]) -> None:
+        """The whole epoch as one launch; the per-step panel / source-rank tables come from the schedules."""
+        N, S = self.N, self.S
+        panel_of_step, src_of_step = [], []
+        for _ in range(N):
+            for k in range(S):
+                panel_of_step.append(self.sched[k].shard_at[self.me] * S + k)
+                src_of_step.append(self.sched[k].rotate()[self.me])
+        for k in range(S):
+            self._wait_slice(k)
+        key = tuple(panel_of_step + src_of_step)
+        pos = self._tables.get(key)
+        if pos is None:                        # the plain ring repeats the same tables every epoch
+            pos = torch.tensor(key, dtype=torch.int32).to(self.dev)
+            self._tables[key] = pos
+        steps = N * S
+        mf.sgd_epoch(self.W, self.desc, pos[:steps], steps, S, self.B, self.cs, self.eps, self.lam, self.epochs_fused,
+                     deadline_ms, self.trained, self.ring, pos[steps:])
+        self.epochs_fused += 1
+        self.ring.advance(N)
+        tb = (self.epochs_fused * self.B) & 0x7FFFFFFF
+        for per in self.panels:
+            for p in per:
+                p.ticket_base = tb
+
     def epoch(self, deadline_ms: Optional[float] = None) -> torch.Tensor:
         """N rotations x S slices (``SGDCollectiveMapper.java:263-277``). Returns the trained-rating counter."""
         self.trained.zero_()
+        if self.fused and self.dev.type == "cuda":
+            self._epoch_fused(deadline_ms)
+            return self.trained
         for _ in range(self.N):
             for k in range(self.S):
                 self._wait_slice(k)
@@ -170,6 +234,8 @@ class MFSGDEngine:
             for k in range(self.S):
                 self._wait_slice(k)
             torch.cuda.synchronize(self.dev)
+            if self.ring is not None and self.fused:
+                self.ring.check()
 
     def home_H(self) -> Dict[int, torch.Tensor]:
         """The H columns currently held by this worker as ``{global column id: vector}`` blocks

@@ -23,6 +23,10 @@ def _declare(lib) -> None:
     lib.hb_lda_pass_dk16.argtypes = [P, P, P, P, P, P, P, P, I, I, F, F, ULL, P, U, ULL, P, P]
     lib.hb_lda_topic_sums.argtypes = [P, LL, I, P, P]
     lib.hb_lda_count.argtypes = [P, P, LL, I, P, P]
+    lib.hb_lda_epoch_supported.argtypes = [I, I]
+    lib.hb_lda_epoch_max_workers.argtypes = [I, I, I]
+    lib.hb_lda_epoch.argtypes = [P, I, P, P, P, I, I, I, I, I, F, F, ULL, U, ULL, P,
+                                 P, I, I, ULL, P, P, P, U, P, ULL, P]
     lib._hb_lda_declared = True
 
 
@@ -48,6 +52,39 @@ def max_blocks(K: int) -> int:
     lib = _native.lib()
     _declare(lib)
     return int(lib.hb_lda_max_blocks(K))
+
+
+def epoch_supported(K: int, dk16: bool) -> bool:
+    lib = _native.lib()
+    _declare(lib)
+    return bool(lib.hb_lda_epoch_supported(int(K), 1 if dk16 else 0))
+
+
+def epoch_max_workers(K: int, dk16: bool, cs: int) -> int:
+    lib = _native.lib()
+    _declare(lib)
+    return int(lib.hb_lda_epoch_max_workers(int(K), 1 if dk16 else 0, int(cs)))
+
+
+def panel_descriptors(panels) -> torch.Tensor:
+    """Device array of the 6-pointer descriptors of ``lda_epoch_kernel`` (``LdaPanelDesc``)."""
+    rows = [[t.data_ptr() for t in (p.blk_seg_ptr, p.seg_word, p.seg_ptr, p.tok_doc, p.tok_z, p.col_ticket)] for p in panels]
+    return torch.tensor(rows, dtype=torch.int64, device=panels[0].tok_doc.device)
+
+
+def lda_epoch(n_dk: torch.Tensor, commons: torch.Tensor, desc: torch.Tensor, panel_of_step: torch.Tensor, steps: int,
+              S: int, workers: int, cs: int, alpha: float, beta: float, seed: int, ticket_epoch: int,
+              deadline_ms: Optional[float], trained: torch.Tensor, ring, src_dev: Optional[torch.Tensor]) -> None:
+    """One launch = a whole iteration's ``steps`` panel passes with the rotation done in-kernel (``hb_lda_epoch``)."""
+    lib = _native.lib()
+    _declare(lib)
+    deadline = int(deadline_ms * 1e6) if deadline_ms is not None else 0
+    rc = lib.hb_lda_epoch(_native.ptr(n_dk), 1 if n_dk.dtype == torch.int16 else 0, _native.ptr(commons),
+                          _native.ptr(desc), _native.ptr(panel_of_step), steps, S, workers, cs, n_dk.shape[1],
+                          float(alpha), float(beta), int(seed) & 0xFFFFFFFFFFFFFFFF, ticket_epoch & 0xFFFFFFFF, deadline,
+                          _native.ptr(trained), *ring.ring_args(steps, src_dev), _native.stream_ptr())
+    _native.check(rc, "hb_lda_epoch")
+    _native.count_launch()
 
 
 def build_token_panel(docs: torch.Tensor, words: torch.Tensor, z: torch.Tensor, B: int, max_run: int = 64) -> TokenPanel:

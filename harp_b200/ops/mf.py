@@ -25,6 +25,9 @@ def _declare(lib) -> None:
     lib.hb_sgd_pass_dynamic.argtypes = [P, P, P, P, P, P, P, I, I, I, F, F, P, ctypes.c_ulonglong, P, P]
     lib.hb_mf_sq_err.argtypes = [P, P, P, P, P, LL, I, P, P]
     lib.hb_ccd_update.argtypes = [P, P, P, P, P, P, I, F, P]
+    lib.hb_sgd_epoch_max_workers.argtypes = [I, I]
+    lib.hb_sgd_epoch.argtypes = [P, P, P, I, I, I, I, I, F, F, U, ULL, P,
+                                 P, I, I, ULL, P, P, P, U, P, ULL, P]
     lib._hb_mf_declared = True
 
 
@@ -54,6 +57,54 @@ def max_blocks(rank: int) -> int:
     lib = _native.lib()
     _declare(lib)
     return int(lib.hb_sgd_max_blocks(rank))
+
+
+def epoch_max_workers(rank: int, cs: int) -> int:
+    """Workers (clusters of ``cs`` CTAs) the whole-epoch kernel keeps resident on this GPU."""
+    lib = _native.lib()
+    _declare(lib)
+    return int(lib.hb_sgd_epoch_max_workers(rank, cs))
+
+
+def pick_cluster(nnz_per_panel: float) -> int:
+    """CTAs per worker for the whole-epoch kernels: a pass costs B hand-overs plus nnz / (B x warps per worker)
+    updates, so small panels want few, fat workers (``HB_EPOCH_CS`` overrides)."""
+    import os
+    if os.environ.get("HB_EPOCH_CS"):
+        return int(os.environ["HB_EPOCH_CS"])
+    if nnz_per_panel >= 16e6:
+        return 1
+    if nnz_per_panel >= 6e6:
+        return 2
+    if nnz_per_panel >= 1.5e6:
+        return 4
+    return 8
+
+
+def pick_max_run(nnz_per_panel: float, workers: int, cs: int, warps_per_cta: int = 31) -> int:
+    """Longest column run one warp trains sequentially: short enough that a cell has ~2 runs per warp."""
+    cell = nnz_per_panel / float(workers * workers)
+    return int(max(4, min(32, cell / (2.0 * cs * warps_per_cta))))
+
+
+def panel_descriptors(panels) -> torch.Tensor:
+    """Device array of the 6-pointer descriptors the epoch kernel reads (``SgdPanelDesc``)."""
+    rows = [[t.data_ptr() for t in (p.blk_seg_ptr, p.seg_col, p.seg_ptr, p.r_row, p.r_val, p.col_ticket)] for p in panels]
+    return torch.tensor(rows, dtype=torch.int64, device=panels[0].r_row.device)
+
+
+def sgd_epoch(W: torch.Tensor, desc: torch.Tensor, panel_of_step: torch.Tensor, steps: int, S: int, workers: int,
+              cs: int, eps: float, lam: float, ticket_epoch: int, deadline_ms: Optional[float],
+              trained: torch.Tensor, ring, src_dev: Optional[torch.Tensor]) -> None:
+    """One launch = ``steps`` panel passes with the rotation done in-kernel (``hb_sgd_epoch``)."""
+    lib = _native.lib()
+    _declare(lib)
+    deadline = int(deadline_ms * 1e6) if deadline_ms is not None else 0
+    rc = lib.hb_sgd_epoch(_native.ptr(W), _native.ptr(desc), _native.ptr(panel_of_step), steps, S, workers, cs,
+                          W.shape[1], float(eps), float(lam), ticket_epoch & 0xFFFFFFFF, deadline,
+                          _native.ptr(trained), *ring.ring_args(steps, src_dev), _native.stream_ptr())
+    _native.check(rc, "hb_sgd_epoch")
+    _native.count_launch()
 
 
 def auto_blocks(nnz_per_panel: float, limit: int, per_block: int = 500) -> int:
@@ -171,6 +222,30 @@ def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: i
     return SgdPanel(B, blk_seg_ptr.contiguous(), seg_col.contiguous(), seg_ptr.to(torch.int32).contiguous(),
                     rows[order].to(torch.int32).contiguous(), vals[order].to(torch.float32).contiguous(),
                     torch.zeros(C, dtype=torch.int32, device=dev), 0, C)
+
+
+def row_collision_bound(panel: SgdPanel) -> float:
+    """Upper bound on the fraction of a panel's ratings whose W row another warp of the same worker could be
+    updating at the same moment: ratings whose row occurs in more than one column run of their cell.  (Different
+    cells of a row-block never run concurrently, and different row-blocks never share a row: that is the
+    reference's Scheduler exclusivity, ``dymoro/Scheduler.java:95-237``; only runs INSIDE one cell overlap.)"""
+    n = panel.nnz
+    if n == 0:
+        return 0.0
+    seg_len = (panel.seg_ptr[1:] - panel.seg_ptr[:-1]).long()
+    nseg = seg_len.numel()
+    seg_of = torch.repeat_interleave(torch.arange(nseg, device=panel.r_row.device), seg_len)
+    cell_of_seg = torch.searchsorted(panel.blk_seg_ptr.long(), torch.arange(nseg, device=seg_of.device), right=True) - 1
+    cell = cell_of_seg[seg_of]
+    nrow = int(panel.r_row.max().item()) + 1
+    key = cell * nrow + panel.r_row.long()
+    # a (cell, row) pair is exposed when it shows up in two different runs
+    pair = torch.unique(torch.stack([key, seg_of], 1), dim=0)
+    uk, inv = torch.unique(key, return_inverse=True)
+    exposed_keys = torch.zeros(uk.numel(), dtype=torch.bool, device=key.device)
+    k2, c2 = torch.unique(pair[:, 0], return_counts=True)
+    exposed_keys[torch.searchsorted(uk, k2)] = c2 > 1
+    return float(exposed_keys[inv].float().mean().item())
 
 
 def _cpu_sgd_pass(panel: SgdPanel, W, H, eps, lam) -> int:
