@@ -536,8 +536,8 @@ struct LdaPanelDesc {
 struct LdaEpochArgs {
   void* n_dk;
   const float* commons;
-  const LdaPanelDesc* panels;
-  const int* panel_of_step;
+  LdaPanelDesc panels[rot::MAX_STEPS];   // kernel-parameter space: every field stays warp-uniform
+  int panel_of_step[rot::MAX_STEPS];
   unsigned long long* trained;
   unsigned long long deadline_ns;
   unsigned long long seed;
@@ -582,6 +582,17 @@ __device__ __forceinline__ void lmbar_wait_acq_cluster(uint32_t bar, uint32_t pa
   }
 }
 
+__device__ __forceinline__ uint32_t latom_add_remote_u32(uint32_t addr, uint32_t cta, uint32_t v) {
+  uint32_t old;
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %1, %2;\n"
+      "atom.shared::cluster.add.u32 %0, [ra], %3;\n"
+      "}\n" : "=r"(old) : "r"(addr), "r"(cta), "r"(v) : "memory");
+  return old;
+}
+
 template <int KJ, bool DK16>
 __global__ void __launch_bounds__(32 * (lda_smem_warps<KJ, DK16>() + 1), 1)
 lda_epoch_kernel(const __grid_constant__ LdaEpochArgs a) {
@@ -594,6 +605,8 @@ lda_epoch_kernel(const __grid_constant__ LdaEpochArgs a) {
   uint8_t* s_row_all = reinterpret_cast<uint8_t*>(s_phi_all + NW * KS);
   __shared__ __align__(8) unsigned long long s_bar[2];
   __shared__ unsigned int s_flags;
+  __shared__ int s_end;
+  __shared__ unsigned int s_next;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cs = (uint32_t)a.cs;
   const uint32_t crank = cs > 1 ? cluster_ctarank() : 0u;
@@ -615,33 +628,35 @@ lda_epoch_kernel(const __grid_constant__ LdaEpochArgs a) {
   } else {
     float* phi = s_phi_all + warp * KS;
     uint8_t* rowbuf = s_row_all + (size_t)warp * 2 * ROWB;
-    const int wid = (int)crank * NW + warp, nw = (int)cs * NW;
     const bool leader = (crank == 0u && threadIdx.x == 0);
-    rot::RingCtl* ctl = ring_on ? rot::ctl_of(a.ring, a.ring.rank) : nullptr;
     unsigned long long local_trained = 0;
     uint32_t ph_go = 0, ph_done = 0;
     bool dead = false;
     const unsigned int tbase = a.ticket_epoch * (unsigned)B;
     for (int g = 0; g < a.ring.steps && !dead; ++g) {
-      const LdaPanelDesc pd = a.panels[a.panel_of_step[g]];
+      const LdaPanelDesc* pdp = &a.panels[a.panel_of_step[g]];
       LdaCore core;
       core.n_dk = reinterpret_cast<int*>(a.n_dk);
       core.n_wk = ring_on ? reinterpret_cast<int*>(rot::slice_ptr(a.ring, g))
                           : reinterpret_cast<int*>(a.ring.peer[0] + a.ring.off_buf[g % a.ring.S][0]);
-      core.seg_word = pd.seg_word; core.seg_ptr = pd.seg_ptr; core.tok_doc = pd.tok_doc; core.tok_z = pd.tok_z;
+      core.seg_word = pdp->seg_word; core.seg_ptr = pdp->seg_ptr; core.tok_doc = pdp->tok_doc; core.tok_z = pdp->tok_z;
       core.seed = a.seed + (unsigned long long)g * 0x9E3779B97F4A7C15ULL; core.alpha = a.alpha; core.beta = a.beta;
       const unsigned long long t_end = a.deadline_ns ? globaltimer_ns() + a.deadline_ns : 0ULL;
       for (int t = 0; t < B; ++t) {
         const int c = (worker + t) % B;
         if (leader) {
+          rot::RingCtl* ctl = ring_on ? rot::ctl_of(a.ring, a.ring.rank) : nullptr;
+          unsigned int* tick = pdp->col_ticket + c;
+          const int* bsp = pdp->blk_seg_ptr + (size_t)worker * B + c;
+          const int s0 = bsp[0], s1 = bsp[1];
           unsigned int fl = 0u;
           if (t == 0 && ring_on && !rot::wait_slice(a.ring, g)) fl = 2u;
           if (fl == 0u) {
             const unsigned int want = tbase + (unsigned)t;
-            if (ld_acquire_gpu(pd.col_ticket + c) != want) {
+            if (ld_acquire_gpu(tick) != want) {
               const unsigned long long t0 = rot::now_ns();
               unsigned spins = 0;
-              while (ld_acquire_gpu(pd.col_ticket + c) != want) {
+              while (ld_acquire_gpu(tick) != want) {
                 __nanosleep(32);
                 if ((++spins & 255u) == 0u && ring_on) {
                   if (rot::aborted(ctl)) { fl = 2u; break; }
@@ -654,18 +669,30 @@ lda_epoch_kernel(const __grid_constant__ LdaEpochArgs a) {
             }
           }
           if (fl == 0u && t_end != 0ULL && globaltimer_ns() > t_end) fl = 1u;
-          for (uint32_t q = 0; q < cs; ++q) {
-            if (cs > 1) { lst_remote_u32(smem_u32(&s_flags), q, fl); lmbar_arrive_remote(bar_go, q); }
-            else { s_flags = fl; mbar_arrive(bar_go); }
+          s_next = (unsigned)s0;
+          if (cs > 1) {
+            for (uint32_t q = 0; q < cs; ++q) {
+              lst_remote_u32(smem_u32(&s_flags), q, fl);
+              lst_remote_u32(smem_u32(&s_end), q, (unsigned)s1);
+              lmbar_arrive_remote(bar_go, q);
+            }
+          } else {
+            s_flags = fl; s_end = s1;
+            mbar_arrive(bar_go);
           }
         }
         lmbar_wait_acq_cluster(bar_go, ph_go);
         ph_go ^= 1u;
         const unsigned int fl = *reinterpret_cast<volatile unsigned int*>(&s_flags);
         if (!(fl & 3u)) {
-          const int s0 = pd.blk_seg_ptr[(size_t)worker * B + c], s1 = pd.blk_seg_ptr[(size_t)worker * B + c + 1];
-          for (int seg = s0 + wid; seg < s1; seg += nw)
+          const int s1 = *reinterpret_cast<volatile int*>(&s_end);
+          for (;;) {
+            int seg = 0;
+            if (lane == 0) seg = cs > 1 ? (int)latom_add_remote_u32(smem_u32(&s_next), 0, 1u) : (int)atomicAdd(&s_next, 1u);
+            seg = __shfl_sync(0xffffffffu, seg, 0);
+            if (seg >= s1) break;
             local_trained += lda_run_segment_smem<KJ, DK16>(core, seg, lane, K, worker, phi, rowbuf, s_cm);
+          }
         }
         asm volatile("bar.sync 1, %0;" ::"n"(32 * NW) : "memory");
         if (threadIdx.x == 0) {
@@ -675,7 +702,7 @@ lda_epoch_kernel(const __grid_constant__ LdaEpochArgs a) {
         if (leader) {
           lmbar_wait_acq_cluster(bar_done, ph_done);
           ph_done ^= 1u;
-          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(pd.col_ticket + c), "r"(tbase + (unsigned)t + 1u) : "memory");
+          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(pdp->col_ticket + c), "r"(tbase + (unsigned)t + 1u) : "memory");
         }
         if (fl & 2u) { dead = true; break; }
       }
@@ -821,11 +848,11 @@ int hb_lda_epoch_max_workers(int K, int dk16, int cs) {
   return n;
 }
 
-int hb_lda_epoch(void* n_dk, int dk16, const float* commons, const void* panels_dev, const int* panel_of_step_dev,
+int hb_lda_epoch(void* n_dk, int dk16, const float* commons, const void* panels_host, int npanels, const int* panel_of_step_host,
                  int steps, int S, int workers, int cs, int K, float alpha, float beta, unsigned long long seed,
                  unsigned ticket_epoch, unsigned long long deadline_ns, unsigned long long* trained,
                  void* const* peer_state, int my_rank, int world, unsigned long long off_ctl,
-                 const unsigned long long* off_buf4, const unsigned long long* bytes2, const int* src_rank_dev,
+                 const unsigned long long* off_buf4, const unsigned long long* bytes2, const int* src_rank_host,
                  unsigned cnt_base, const unsigned* par_base2, unsigned long long timeout_ns, void* stream) {
   HB_REQUIRE(hb_lda_epoch_supported(K, dk16), "hb_lda_epoch: K=%d (dk16=%d) not supported (need K <= 1024, rows of whole 16-byte chunks)", K, dk16);
   HB_REQUIRE(workers >= 1 && workers <= hb_lda_epoch_max_workers(K, dk16, cs),
@@ -833,10 +860,16 @@ int hb_lda_epoch(void* n_dk, int dk16, const float* commons, const void* panels_
   HB_REQUIRE((reinterpret_cast<uintptr_t>(n_dk) & 15) == 0, "hb_lda_epoch: the document-topic table must be 16-byte aligned");
   LdaEpochArgs a;
   memset(&a, 0, sizeof(a));
-  if (rot::fill_ring(a.ring, peer_state, my_rank, world, S, steps, off_ctl, off_buf4, bytes2, src_rank_dev, cnt_base,
+  if (rot::fill_ring(a.ring, peer_state, my_rank, world, S, steps, off_ctl, off_buf4, bytes2, src_rank_host, cnt_base,
                      par_base2, timeout_ns) != 0) return -2;
-  a.n_dk = n_dk; a.commons = commons; a.panels = reinterpret_cast<const LdaPanelDesc*>(panels_dev);
-  a.panel_of_step = panel_of_step_dev; a.trained = trained; a.deadline_ns = deadline_ns; a.seed = seed;
+  HB_REQUIRE(npanels >= 1 && npanels <= rot::MAX_STEPS && panels_host != nullptr && panel_of_step_host != nullptr,
+             "hb_lda_epoch: need 1..%d panel descriptors (got %d)", rot::MAX_STEPS, npanels);
+  memcpy(a.panels, panels_host, (size_t)npanels * sizeof(LdaPanelDesc));
+  for (int g = 0; g < steps; ++g) {
+    HB_REQUIRE(panel_of_step_host[g] >= 0 && panel_of_step_host[g] < npanels, "hb_lda_epoch: step %d names panel %d of %d", g, panel_of_step_host[g], npanels);
+    a.panel_of_step[g] = panel_of_step_host[g];
+  }
+  a.n_dk = n_dk; a.commons = commons; a.trained = trained; a.deadline_ns = deadline_ns; a.seed = seed;
   a.ticket_epoch = ticket_epoch; a.cs = cs; a.K = K; a.alpha = alpha; a.beta = beta;
   size_t smem = 0; int threads = 0;
   const void* fn = lda_epoch_fn(K, dk16 != 0, &smem, &threads);

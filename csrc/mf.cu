@@ -287,8 +287,8 @@ struct SgdPanelDesc {
 
 struct SgdEpochArgs {
   float* W;
-  const SgdPanelDesc* panels;      // device array
-  const int* panel_of_step;        // [steps] index into panels
+  SgdPanelDesc panels[rot::MAX_STEPS];   // kernel-parameter space: every field stays warp-uniform
+  int panel_of_step[rot::MAX_STEPS];     // [steps] index into panels
   unsigned long long* trained;
   unsigned long long deadline_ns;  // per step, 0 = none
   unsigned int ticket_epoch;       // launches of this kernel so far (every panel is visited once per launch)
@@ -339,10 +339,23 @@ __device__ __forceinline__ void mbar_wait_acq_cluster(uint32_t bar, uint32_t par
   }
 }
 
+__device__ __forceinline__ uint32_t atom_add_remote_u32(uint32_t addr, uint32_t cta, uint32_t v) {
+  uint32_t old;
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %1, %2;\n"
+      "atom.shared::cluster.add.u32 %0, [ra], %3;\n"
+      "}\n" : "=r"(old) : "r"(addr), "r"(cta), "r"(v) : "memory");
+  return old;
+}
+
 template <int RV>
 __global__ void __launch_bounds__(EPOCH_THREADS, 1) sgd_epoch_kernel(const __grid_constant__ SgdEpochArgs a) {
   __shared__ __align__(8) unsigned long long s_bar[2];    // [0] go (1 arrival), [1] done (cs arrivals; used in the leader)
   __shared__ unsigned int s_flags;                        // bit 0: stop (deadline), bit 1: abort
+  __shared__ int s_end;                                   // one past the cell's last column run
+  __shared__ unsigned int s_next;                         // next unclaimed run of the cell (the leader CTA's copy is used)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cs = (uint32_t)a.cs;
   const uint32_t crank = cs > 1 ? cluster_ctarank() : 0u;
@@ -350,6 +363,8 @@ __global__ void __launch_bounds__(EPOCH_THREADS, 1) sgd_epoch_kernel(const __gri
   const uint32_t bar_go = smem_u32(&s_bar[0]), bar_done = smem_u32(&s_bar[1]);
   const int nl4 = a.rank >> 2;
   const bool ring_on = a.ring.world > 0;
+  // without a ring there is nothing to communicate: the last warp trains too
+  const int ntrain = ring_on ? EPOCH_TRAIN_THREADS : EPOCH_THREADS;
   if (threadIdx.x == 0) {
     mbar_init(bar_go, 1);
     mbar_init(bar_done, cs);
@@ -358,11 +373,9 @@ __global__ void __launch_bounds__(EPOCH_THREADS, 1) sgd_epoch_kernel(const __gri
   }
   if (cs > 1) cluster_sync_all(); else __syncthreads();
 
-  if (warp == EPOCH_COMM_WARP) {
-    if (ring_on) rot::comm_warp_loop(a.ring);
+  if (ring_on && warp == EPOCH_COMM_WARP) {
+    rot::comm_warp_loop(a.ring);
   } else {
-    const int wid = (int)crank * (EPOCH_TRAIN_THREADS / 32) + warp;      // training warp id inside the worker
-    const int nw = (int)cs * (EPOCH_TRAIN_THREADS / 32);
     const bool leader = (crank == 0u && threadIdx.x == 0);
     rot::RingCtl* ctl = ring_on ? rot::ctl_of(a.ring, a.ring.rank) : nullptr;
     unsigned long long local_trained = 0;
@@ -370,26 +383,29 @@ __global__ void __launch_bounds__(EPOCH_THREADS, 1) sgd_epoch_kernel(const __gri
     bool dead = false;
     const unsigned int tbase = a.ticket_epoch * (unsigned)B;
     for (int g = 0; g < a.ring.steps && !dead; ++g) {
-      const SgdPanelDesc pd = a.panels[a.panel_of_step[g]];
+      const SgdPanelDesc* pdp = &a.panels[a.panel_of_step[g]];
       SgdCore core;
       core.W = a.W;
       core.H = ring_on ? reinterpret_cast<float*>(rot::slice_ptr(a.ring, g))
                        : reinterpret_cast<float*>(a.ring.peer[0] + a.ring.off_buf[g % a.ring.S][0]);
-      core.seg_col = pd.seg_col; core.seg_ptr = pd.seg_ptr; core.r_row = pd.r_row; core.r_val = pd.r_val;
+      core.seg_col = pdp->seg_col; core.seg_ptr = pdp->seg_ptr; core.r_row = pdp->r_row; core.r_val = pdp->r_val;
       core.rank = a.rank; core.eps = a.eps; core.lambda = a.lambda;
       const unsigned long long t_end = a.deadline_ns ? globaltimer_ns() + a.deadline_ns : 0ULL;
       for (int t = 0; t < B; ++t) {
         const int c = (worker + t) % B;
         if (leader) {
+          unsigned int* tick = pdp->col_ticket + c;
+          const int* bsp = pdp->blk_seg_ptr + (size_t)worker * B + c;
+          const int s0 = bsp[0], s1 = bsp[1];                 // independent of the ticket: issued before the spin
           unsigned int fl = 0u;
           if (t == 0 && ring_on && !rot::wait_slice(a.ring, g)) fl = 2u;
           if (fl == 0u) {
             // column-block c is ours once its previous holder has released it
             const unsigned int want = tbase + (unsigned)t;
-            if (ld_acquire_gpu(pd.col_ticket + c) != want) {
+            if (ld_acquire_gpu(tick) != want) {
               const unsigned long long t0 = rot::now_ns();
               unsigned spins = 0;
-              while (ld_acquire_gpu(pd.col_ticket + c) != want) {
+              while (ld_acquire_gpu(tick) != want) {
                 __nanosleep(32);
                 if ((++spins & 255u) == 0u && ring_on) {
                   if (rot::aborted(ctl)) { fl = 2u; break; }
@@ -402,20 +418,33 @@ __global__ void __launch_bounds__(EPOCH_THREADS, 1) sgd_epoch_kernel(const __gri
             }
           }
           if (fl == 0u && t_end != 0ULL && globaltimer_ns() > t_end) fl = 1u;
-          for (uint32_t q = 0; q < cs; ++q) {
-            if (cs > 1) { st_remote_u32(smem_u32(&s_flags), q, fl); mbar_arrive_remote(bar_go, q); }
-            else { s_flags = fl; mbar_arrive(bar_go); }
+          s_next = (unsigned)s0;
+          if (cs > 1) {
+            for (uint32_t q = 0; q < cs; ++q) {
+              st_remote_u32(smem_u32(&s_flags), q, fl);
+              st_remote_u32(smem_u32(&s_end), q, (unsigned)s1);
+              mbar_arrive_remote(bar_go, q);
+            }
+          } else {
+            s_flags = fl; s_end = s1;
+            mbar_arrive(bar_go);
           }
         }
         mbar_wait_acq_cluster(bar_go, ph_go);      // unbounded: the leader may be waiting for a peer GPU
         ph_go ^= 1u;
         const unsigned int fl = *reinterpret_cast<volatile unsigned int*>(&s_flags);
         if (!(fl & 3u)) {
-          const int s0 = pd.blk_seg_ptr[(size_t)worker * B + c], s1 = pd.blk_seg_ptr[(size_t)worker * B + c + 1];
-          for (int seg = s0 + wid; seg < s1; seg += nw) local_trained += sgd_run_segment<RV>(core, seg, lane, nl4);
+          const int s1 = *reinterpret_cast<volatile int*>(&s_end);
+          for (;;) {
+            int seg = 0;
+            if (lane == 0) seg = cs > 1 ? (int)atom_add_remote_u32(smem_u32(&s_next), 0, 1u) : (int)atomicAdd(&s_next, 1u);
+            seg = __shfl_sync(0xffffffffu, seg, 0);
+            if (seg >= s1) break;
+            local_trained += sgd_run_segment<RV>(core, seg, lane, nl4);
+          }
         }
         // ---- hand the column-block on ----
-        asm volatile("bar.sync 1, %0;" ::"n"(EPOCH_TRAIN_THREADS) : "memory");
+        asm volatile("bar.sync 1, %0;" ::"r"(ntrain) : "memory");
         if (threadIdx.x == 0) {
           __threadfence();
           if (cs > 1) mbar_arrive_remote(bar_done, 0); else mbar_arrive(bar_done);
@@ -424,7 +453,7 @@ __global__ void __launch_bounds__(EPOCH_THREADS, 1) sgd_epoch_kernel(const __gri
           mbar_wait_acq_cluster(bar_done, ph_done);
           ph_done ^= 1u;
           // tickets keep moving even when the step was cut short (deadline / abort) so nobody waits for ever
-          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(pd.col_ticket + c), "r"(tbase + (unsigned)t + 1u) : "memory");
+          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(pdp->col_ticket + c), "r"(tbase + (unsigned)t + 1u) : "memory");
         }
         if (fl & 2u) { dead = true; break; }
       }
@@ -579,25 +608,32 @@ int hb_sgd_epoch_max_workers(int rank, int cs) {
 int hb_ring_ctl_bytes(void) { return (int)sizeof(rot::RingCtl); }
 
 // One epoch = `steps` panel passes (step g trains panel panel_of_step[g] against slice g % S) in ONE launch.
-//   panels: device array of 6-pointer descriptors {blk_seg_ptr, seg_col, seg_ptr, r_row, r_val, col_ticket};
+//   panels: HOST array of `npanels` 6-pointer descriptors {blk_seg_ptr, seg_col, seg_ptr, r_row, r_val, col_ticket};
 //   every panel must be bucketed with B = `workers` blocks per side and is visited exactly once per launch
 //   (its tickets advance by B), ticket_epoch = number of earlier launches on these panels.
 //   world == 0: no ring, peer_state[0] + off_buf4[2k] is slice k.  world >= 1: symmetric ring state of every
 //   rank (world == 1 is a loop-back ring onto this rank's own buffers).
-int hb_sgd_epoch(float* W, const void* panels_dev, const int* panel_of_step_dev, int steps, int S, int workers,
+int hb_sgd_epoch(float* W, const void* panels_host, int npanels, const int* panel_of_step_host, int steps, int S, int workers,
                  int cs, int rank, float eps, float lambda, unsigned ticket_epoch, unsigned long long deadline_ns,
                  unsigned long long* trained, void* const* peer_state, int my_rank, int world,
                  unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
-                 const int* src_rank_dev, unsigned cnt_base, const unsigned* par_base2,
+                 const int* src_rank_host, unsigned cnt_base, const unsigned* par_base2,
                  unsigned long long timeout_ns, void* stream) {
   HB_REQUIRE(rank >= 4 && rank % 4 == 0 && rank <= 512, "hb_sgd_epoch: need rank %% 4 == 0 and rank <= 512 (got %d)", rank);
   HB_REQUIRE(workers >= 1 && workers <= hb_sgd_epoch_max_workers(rank, cs),
              "hb_sgd_epoch: %d workers of %d CTAs cannot be co-resident (max %d)", workers, cs, hb_sgd_epoch_max_workers(rank, cs));
   SgdEpochArgs a;
   memset(&a, 0, sizeof(a));
-  if (rot::fill_ring(a.ring, peer_state, my_rank, world, S, steps, off_ctl, off_buf4, bytes2, src_rank_dev, cnt_base,
+  if (rot::fill_ring(a.ring, peer_state, my_rank, world, S, steps, off_ctl, off_buf4, bytes2, src_rank_host, cnt_base,
                 par_base2, timeout_ns) != 0) return -2;
-  a.W = W; a.panels = reinterpret_cast<const SgdPanelDesc*>(panels_dev); a.panel_of_step = panel_of_step_dev;
+  HB_REQUIRE(npanels >= 1 && npanels <= rot::MAX_STEPS && panels_host != nullptr && panel_of_step_host != nullptr,
+             "hb_sgd_epoch: need 1..%d panel descriptors (got %d)", rot::MAX_STEPS, npanels);
+  memcpy(a.panels, panels_host, (size_t)npanels * sizeof(SgdPanelDesc));
+  for (int g = 0; g < steps; ++g) {
+    HB_REQUIRE(panel_of_step_host[g] >= 0 && panel_of_step_host[g] < npanels, "hb_sgd_epoch: step %d names panel %d of %d", g, panel_of_step_host[g], npanels);
+    a.panel_of_step[g] = panel_of_step_host[g];
+  }
+  a.W = W;
   a.trained = trained; a.deadline_ns = deadline_ns; a.ticket_epoch = ticket_epoch; a.cs = cs; a.rank = rank;
   a.eps = eps; a.lambda = lambda;
   return rot::launch_epoch(sgd_epoch_fn(rank), EPOCH_THREADS, 0, workers, cs, a, stream);

@@ -36,6 +36,7 @@ namespace hb {
 namespace rot {
 
 constexpr int MAX_SLICES = 2;
+constexpr int MAX_STEPS = HB_MAX_RANKS * MAX_SLICES;    // steps of one launch: N rotations x S slices
 
 struct RingCtl {                      // one per rank, in the symmetric slab, zeroed once at creation
   uint32_t done[MAX_SLICES];
@@ -62,7 +63,7 @@ struct RingArgs {
   unsigned long long off_ctl;              // RingCtl
   unsigned long long off_buf[MAX_SLICES][2];
   unsigned long long bytes[MAX_SLICES];    // bytes of a slice (multiple of 16)
-  const int* src_rank;                     // [steps] source rank of the pull issued at step g; null = ring
+  int src_rank[MAX_STEPS];                 // source rank of the pull issued at step g
   int rank, world, S, steps;
   uint32_t cnt_base;                       // uses of each slice completed by earlier launches
   uint32_t par_base[MAX_SLICES];           // parity of the buffer holding the first use of this launch
@@ -113,7 +114,7 @@ __device__ __forceinline__ void comm_warp_loop(const RingArgs& r) {
   for (int g = 0; g < r.steps; ++g) {
     const int k = g % r.S, j = g / r.S;
     const uint32_t u = r.cnt_base + (uint32_t)j;
-    const int src = r.src_rank ? r.src_rank[g] : (r.rank + r.world - 1) % r.world;
+    const int src = r.src_rank[g];
     int ok = 1;
     if (lane == 0) {
       // 1. the buffer we are about to overwrite held use u-1; its consumer must have copied it (which also
@@ -195,10 +196,10 @@ __device__ __forceinline__ void* slice_ptr(const RingArgs& r, int g) {
 // ---- host side: argument marshalling and the cooperative (+ cluster) launch shared by the epoch kernels ----
 inline int fill_ring(RingArgs& r, void* const* peer_state, int my_rank, int world, int S, int steps,
                      unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
-                     const int* src_rank_dev, unsigned cnt_base, const unsigned* par_base2,
+                     const int* src_rank_host, unsigned cnt_base, const unsigned* par_base2,
                      unsigned long long timeout_ns) {
   memset(&r, 0, sizeof(r));
-  HB_REQUIRE(S >= 1 && S <= MAX_SLICES && steps >= 0 && steps % S == 0, "ring: bad slice count %d / steps %d", S, steps);
+  HB_REQUIRE(S >= 1 && S <= MAX_SLICES && steps >= 0 && steps % S == 0 && steps <= MAX_STEPS, "ring: bad slice count %d / steps %d", S, steps);
   HB_REQUIRE(world >= 0 && world <= HB_MAX_RANKS, "ring: bad world %d", world);
   HB_REQUIRE(world == 0 || (my_rank >= 0 && my_rank < world), "ring: bad rank %d of %d", my_rank, world);
   const int np = world > 0 ? world : 1;
@@ -214,7 +215,11 @@ inline int fill_ring(RingArgs& r, void* const* peer_state, int my_rank, int worl
     HB_REQUIRE((r.off_buf[k][0] & 15) == 0 && (r.off_buf[k][1] & 15) == 0 && (r.bytes[k] & 15) == 0,
                "ring: slice buffers must be 16-byte aligned and a multiple of 16 bytes long");
   }
-  r.src_rank = src_rank_dev; r.rank = world > 0 ? my_rank : 0; r.world = world; r.S = S; r.steps = steps;
+  for (int g = 0; g < steps; ++g) {
+    r.src_rank[g] = (world > 0) ? (src_rank_host ? src_rank_host[g] : (my_rank + world - 1) % world) : 0;
+    HB_REQUIRE(world == 0 || (r.src_rank[g] >= 0 && r.src_rank[g] < world), "ring: bad source rank %d at step %d", r.src_rank[g], g);
+  }
+  r.rank = world > 0 ? my_rank : 0; r.world = world; r.S = S; r.steps = steps;
   r.cnt_base = cnt_base; r.timeout_ns = timeout_ns;
   return 0;
 }

@@ -120,7 +120,6 @@ class LDAEngine:
         self.commons = torch.zeros(self.K, dtype=torch.float32, device=self.dev)
         self.trained = torch.zeros(1, dtype=torch.int64, device=self.dev)
         self.epochs_fused = 0
-        self._tables = {}
         if cuda:
             self.desc = L.panel_descriptors([self.panels[s][k] for s in range(N) for k in range(S)])
         self._refresh_topic_sums()
@@ -183,15 +182,9 @@ class LDAEngine:
                     src_l.append(self.sched[k].rotate()[self.me])
             for k in range(S):
                 self._wait_slice(k)
-            key = tuple(pos_l + src_l)
-            pos = self._tables.get(key)
-            if pos is None:
-                pos = torch.tensor(key, dtype=torch.int32).to(self.dev)
-                self._tables[key] = pos
-            steps = N * S
-            L.lda_epoch(self.n_dk, self.commons, self.desc, pos[:steps], steps, S, self.B, self.cs, self.alpha, self.beta,
+            L.lda_epoch(self.n_dk, self.commons, self.desc, pos_l, S, self.B, self.cs, self.alpha, self.beta,
                         self.seed * 1000003 + self.iteration * 7919 + 104729 * self.me, self.epochs_fused, deadline_ms,
-                        self.trained, self.ring, pos[steps:])
+                        self.trained, self.ring, src_l)
             self.epochs_fused += 1
             self.ring.advance(N)
             tb = (self.epochs_fused * self.B) & 0x7FFFFFFF

@@ -111,7 +111,6 @@ class MFSGDEngine:
             self.panels.append(per)
         self.trained = torch.zeros(1, dtype=torch.int64, device=self.dev)
         self.epochs_fused = 0
-        self._tables: Dict[tuple, torch.Tensor] = {}
         if cuda:
             self.desc = mf.panel_descriptors([self.panels[s][k] for s in range(N) for k in range(S)])
             self.comm_stream = torch.cuda.Stream(device=self.dev)
@@ -176,14 +175,8 @@ class MFSGDEngine:
                 src_of_step.append(self.sched[k].rotate()[self.me])
         for k in range(S):
             self._wait_slice(k)
-        key = tuple(panel_of_step + src_of_step)
-        pos = self._tables.get(key)
-        if pos is None:                        # the plain ring repeats the same tables every epoch
-            pos = torch.tensor(key, dtype=torch.int32).to(self.dev)
-            self._tables[key] = pos
-        steps = N * S
-        mf.sgd_epoch(self.W, self.desc, pos[:steps], steps, S, self.B, self.cs, self.eps, self.lam, self.epochs_fused,
-                     deadline_ms, self.trained, self.ring, pos[steps:])
+        mf.sgd_epoch(self.W, self.desc, panel_of_step, S, self.B, self.cs, self.eps, self.lam, self.epochs_fused,
+                     deadline_ms, self.trained, self.ring, src_of_step)
         self.epochs_fused += 1
         self.ring.advance(N)
         tb = (self.epochs_fused * self.B) & 0x7FFFFFFF

@@ -25,7 +25,7 @@ def _declare(lib) -> None:
     lib.hb_lda_count.argtypes = [P, P, LL, I, P, P]
     lib.hb_lda_epoch_supported.argtypes = [I, I]
     lib.hb_lda_epoch_max_workers.argtypes = [I, I, I]
-    lib.hb_lda_epoch.argtypes = [P, I, P, P, P, I, I, I, I, I, F, F, ULL, U, ULL, P,
+    lib.hb_lda_epoch.argtypes = [P, I, P, P, I, P, I, I, I, I, I, F, F, ULL, U, ULL, P,
                                  P, I, I, ULL, P, P, P, U, P, ULL, P]
     lib._hb_lda_declared = True
 
@@ -66,23 +66,25 @@ def epoch_max_workers(K: int, dk16: bool, cs: int) -> int:
     return int(lib.hb_lda_epoch_max_workers(int(K), 1 if dk16 else 0, int(cs)))
 
 
-def panel_descriptors(panels) -> torch.Tensor:
-    """Device array of the 6-pointer descriptors of ``lda_epoch_kernel`` (``LdaPanelDesc``)."""
-    rows = [[t.data_ptr() for t in (p.blk_seg_ptr, p.seg_word, p.seg_ptr, p.tok_doc, p.tok_z, p.col_ticket)] for p in panels]
-    return torch.tensor(rows, dtype=torch.int64, device=panels[0].tok_doc.device)
+def panel_descriptors(panels):
+    """Host array of the 6-pointer descriptors of ``lda_epoch_kernel`` (``LdaPanelDesc``)."""
+    flat = [t.data_ptr() for p in panels for t in (p.blk_seg_ptr, p.seg_word, p.seg_ptr, p.tok_doc, p.tok_z, p.col_ticket)]
+    return (ctypes.c_uint64 * len(flat))(*flat)
 
 
-def lda_epoch(n_dk: torch.Tensor, commons: torch.Tensor, desc: torch.Tensor, panel_of_step: torch.Tensor, steps: int,
+def lda_epoch(n_dk: torch.Tensor, commons: torch.Tensor, desc, panel_of_step,
               S: int, workers: int, cs: int, alpha: float, beta: float, seed: int, ticket_epoch: int,
-              deadline_ms: Optional[float], trained: torch.Tensor, ring, src_dev: Optional[torch.Tensor]) -> None:
+              deadline_ms: Optional[float], trained: torch.Tensor, ring, src_of_step) -> None:
     """One launch = a whole iteration's ``steps`` panel passes with the rotation done in-kernel (``hb_lda_epoch``)."""
     lib = _native.lib()
     _declare(lib)
     deadline = int(deadline_ms * 1e6) if deadline_ms is not None else 0
+    steps = len(panel_of_step)
+    pos = (ctypes.c_int * steps)(*panel_of_step)
     rc = lib.hb_lda_epoch(_native.ptr(n_dk), 1 if n_dk.dtype == torch.int16 else 0, _native.ptr(commons),
-                          _native.ptr(desc), _native.ptr(panel_of_step), steps, S, workers, cs, n_dk.shape[1],
+                          desc, len(desc) // 6, pos, steps, S, workers, cs, n_dk.shape[1],
                           float(alpha), float(beta), int(seed) & 0xFFFFFFFFFFFFFFFF, ticket_epoch & 0xFFFFFFFF, deadline,
-                          _native.ptr(trained), *ring.ring_args(steps, src_dev), _native.stream_ptr())
+                          _native.ptr(trained), *ring.ring_args(src_of_step), _native.stream_ptr())
     _native.check(rc, "hb_lda_epoch")
     _native.count_launch()
 

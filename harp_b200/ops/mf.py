@@ -26,7 +26,7 @@ def _declare(lib) -> None:
     lib.hb_mf_sq_err.argtypes = [P, P, P, P, P, LL, I, P, P]
     lib.hb_ccd_update.argtypes = [P, P, P, P, P, P, I, F, P]
     lib.hb_sgd_epoch_max_workers.argtypes = [I, I]
-    lib.hb_sgd_epoch.argtypes = [P, P, P, I, I, I, I, I, F, F, U, ULL, P,
+    lib.hb_sgd_epoch.argtypes = [P, P, I, P, I, I, I, I, I, F, F, U, ULL, P,
                                  P, I, I, ULL, P, P, P, U, P, ULL, P]
     lib._hb_mf_declared = True
 
@@ -87,22 +87,25 @@ def pick_max_run(nnz_per_panel: float, workers: int, cs: int, warps_per_cta: int
     return int(max(4, min(32, cell / (2.0 * cs * warps_per_cta))))
 
 
-def panel_descriptors(panels) -> torch.Tensor:
-    """Device array of the 6-pointer descriptors the epoch kernel reads (``SgdPanelDesc``)."""
-    rows = [[t.data_ptr() for t in (p.blk_seg_ptr, p.seg_col, p.seg_ptr, p.r_row, p.r_val, p.col_ticket)] for p in panels]
-    return torch.tensor(rows, dtype=torch.int64, device=panels[0].r_row.device)
+def panel_descriptors(panels):
+    """Host array of the 6-pointer descriptors (``SgdPanelDesc``) that ``hb_sgd_epoch`` copies into the kernel's
+    parameter block."""
+    flat = [t.data_ptr() for p in panels for t in (p.blk_seg_ptr, p.seg_col, p.seg_ptr, p.r_row, p.r_val, p.col_ticket)]
+    return (ctypes.c_uint64 * len(flat))(*flat)
 
 
-def sgd_epoch(W: torch.Tensor, desc: torch.Tensor, panel_of_step: torch.Tensor, steps: int, S: int, workers: int,
+def sgd_epoch(W: torch.Tensor, desc, panel_of_step, S: int, workers: int,
               cs: int, eps: float, lam: float, ticket_epoch: int, deadline_ms: Optional[float],
-              trained: torch.Tensor, ring, src_dev: Optional[torch.Tensor]) -> None:
+              trained: torch.Tensor, ring, src_of_step) -> None:
     """One launch = ``steps`` panel passes with the rotation done in-kernel (``hb_sgd_epoch``)."""
     lib = _native.lib()
     _declare(lib)
     deadline = int(deadline_ms * 1e6) if deadline_ms is not None else 0
-    rc = lib.hb_sgd_epoch(_native.ptr(W), _native.ptr(desc), _native.ptr(panel_of_step), steps, S, workers, cs,
+    steps = len(panel_of_step)
+    pos = (ctypes.c_int * steps)(*panel_of_step)
+    rc = lib.hb_sgd_epoch(_native.ptr(W), desc, len(desc) // 6, pos, steps, S, workers, cs,
                           W.shape[1], float(eps), float(lam), ticket_epoch & 0xFFFFFFFF, deadline,
-                          _native.ptr(trained), *ring.ring_args(steps, src_dev), _native.stream_ptr())
+                          _native.ptr(trained), *ring.ring_args(src_of_step), _native.stream_ptr())
     _native.check(rc, "hb_sgd_epoch")
     _native.count_launch()
 

@@ -112,13 +112,15 @@ class RingState:
     def other(self, k: int) -> torch.Tensor:
         return self.buf[k][1 - self.cur[k]]
 
-    def ring_args(self, steps: int, src_dev: Optional[torch.Tensor]):
+    def ring_args(self, src_of_step: Optional[Sequence[int]]):
         """Positional tail shared by the epoch entry points: (peer_state, rank, world, off_ctl, off_buf4, bytes2,
         src_rank, cnt_base, par_base2, timeout_ns)."""
         par = (ctypes.c_uint32 * 2)(*(self.cur + [0] * (2 - self.S)))
+        src = None
+        if src_of_step is not None and self.ring_world > 0:
+            src = (ctypes.c_int * len(src_of_step))(*[int(x) % self.ring_world for x in src_of_step])
         return (self._peer_arr, self.rank if self.ring_world > 0 else 0, self.ring_world, 0, self._off_arr,
-                self._bytes_arr, _native.ptr(src_dev) if (src_dev is not None and self.ring_world > 0) else None,
-                self.cnt & 0xFFFFFFFF, par, wait_timeout_ns())
+                self._bytes_arr, src, self.cnt & 0xFFFFFFFF, par, wait_timeout_ns())
 
     def advance(self, uses: int) -> None:
         """Book-keeping after an epoch launch that trained ``uses`` times on every slice."""

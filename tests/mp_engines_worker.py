@@ -25,11 +25,15 @@ def main():
     r = torch.randint(0, nr, (nnz,), device=dev, generator=g); c = torch.randint(0, nc, (nnz,), device=dev, generator=g)
     v = (Wt[r] * Ht[c]).sum(1) * 2 + 3
     eng = MFSGDEngine(r, c, v, nr, nc, rk, 0.01, 0.02, symm=ws, seed=5)
+    assert eng.fused and eng.S == 2, "the default path must be the whole-epoch kernel with two slices in flight"
     e0 = eng.rmse(r, c, v)
+    from harp_b200 import _native
+    l0 = _native.launches()
     for it in range(12):
         n = eng.epoch()
         assert int(n.item()) == nnz, (int(n.item()), nnz)
     eng.synchronize()
+    assert _native.launches() - l0 == 12, "one launch per epoch expected"
     e1 = eng.rmse(r, c, v)
     assert e1 < 0.5 * e0, (e0, e1)
     assert all(r % world == 0 for r in eng.rot)
@@ -54,20 +58,29 @@ def main():
         tot += lda.Wbuf[k][lda.cur[k]].sum()
     dist.all_reduce(tot)
     assert int(tot.item()) == D * L * world
-    # both slice layouts of the rotation (the default picks by panel size)
-    other = 3 - eng.S
-    eng2 = MFSGDEngine(r, c, v, nr, nc, rk, 0.01, 0.02, symm=ws, seed=5, num_slices=other)
-    f0 = eng2.rmse(r, c, v)
-    for it in range(6):
-        assert int(eng2.epoch().item()) == nnz
-    eng2.synchronize()
-    assert eng2.rmse(r, c, v) < 0.7 * f0
-    lda2 = LDAEngine(docs, words, D, V, K, 0.1, 0.01, symm=ws, seed=2, num_slices=3 - lda.S)
-    m0 = lda2.log_likelihood()
-    for it in range(4):
-        assert int(lda2.iterate().item()) == D * L
-    lda2.synchronize()
-    assert lda2.log_likelihood() > m0 and int(lda2.topic_sums.sum()) == D * L * world
+    # randomised rotation orders (RotationUtil.createRotationOrder), a single slice, other cluster sizes,
+    # and the per-panel launch path as the A/B arm
+    import random
+    from harp_b200.dymoro import create_rotation_order
+    orders = create_rotation_order(random.Random(7), 8, world)          # identical on every rank
+    for kw in (dict(orders=orders), dict(num_slices=1, cluster=2), dict(fused=False), dict(orders=orders, fused=False)):
+        eng2 = MFSGDEngine(r, c, v, nr, nc, rk, 0.01, 0.02, symm=ws, seed=5, **kw)
+        f0 = eng2.rmse(r, c, v)
+        for it in range(6):
+            assert int(eng2.epoch().item()) == nnz
+        eng2.synchronize()
+        f1 = eng2.rmse(r, c, v)
+        assert f1 < 0.7 * f0, (kw, f0, f1)
+        ids = torch.cat([x[0] for x in eng2.home_H().values()])
+        home = eng2.sched[0].shard_at[rank]
+        assert bool((ids % world == home).all()), kw
+    for kw in (dict(num_slices=1), dict(fused=False), dict(cluster=2)):
+        lda2 = LDAEngine(docs, words, D, V, K, 0.1, 0.01, symm=ws, seed=2, **kw)
+        m0 = lda2.log_likelihood()
+        for it in range(4):
+            assert int(lda2.iterate().item()) == D * L
+        lda2.synchronize()
+        assert lda2.log_likelihood() > m0 and int(lda2.topic_sums.sum()) == D * L * world, kw
     dist.barrier()
     if rank == 0:
         print(f"ENGINES_OK world={world} sgd_rmse {e0:.4f}->{e1:.4f} lda_ll {ll0:.4e}->{ll1:.4e}", flush=True)
