@@ -345,6 +345,8 @@ template <int KJ, bool DK16> constexpr int lda_smem_warps() {
 template <int KJ, bool DK16, typename Core>
 __device__ __forceinline__ unsigned long long lda_run_segment_smem(const Core& a, int seg, int lane, int K, int salt,
                                                                     float* phi, uint8_t* rowbuf, const float* s_cm) {
+  __builtin_assume(__isGlobal(a.seg_word)); __builtin_assume(__isGlobal(a.seg_ptr)); __builtin_assume(__isGlobal(a.tok_doc));
+  __builtin_assume(__isGlobal(a.tok_z)); __builtin_assume(__isGlobal(a.n_dk)); __builtin_assume(__isGlobal(a.n_wk));
   constexpr int KS = 32 * KJ;
   constexpr int KP = KJ / 2;
   constexpr int ROWB = DK16 ? KS * 2 : KS * 4;
@@ -561,6 +563,14 @@ __device__ __forceinline__ void lmbar_arrive_remote(uint32_t bar, uint32_t cta) 
       "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
       "}\n" ::"r"(bar), "r"(cta) : "memory");
 }
+__device__ __forceinline__ void lmbar_arrive_remote_relaxed(uint32_t bar, uint32_t cta) {     // after ONE fence by the caller
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n"
+      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n"
+      "}\n" ::"r"(bar), "r"(cta) : "memory");
+}
 __device__ __forceinline__ void lst_remote_u32(uint32_t addr, uint32_t cta, uint32_t v) {
   asm volatile(
       "{\n"
@@ -656,8 +666,8 @@ lda_epoch_kernel(const __grid_constant__ LdaEpochArgs a) {
             if (ld_acquire_gpu(tick) != want) {
               const unsigned long long t0 = rot::now_ns();
               unsigned spins = 0;
-              while (ld_acquire_gpu(tick) != want) {
-                __nanosleep(32);
+              while (ld_relaxed_gpu(tick) != want) {       // relaxed polls: an acquire load per poll would keep invalidating L1
+                __nanosleep(100);
                 if ((++spins & 255u) == 0u && ring_on) {
                   if (rot::aborted(ctl)) { fl = 2u; break; }
                   if (a.ring.timeout_ns != 0ULL && rot::now_ns() - t0 > a.ring.timeout_ns) {
@@ -666,6 +676,7 @@ lda_epoch_kernel(const __grid_constant__ LdaEpochArgs a) {
                   }
                 }
               }
+              (void)ld_acquire_gpu(tick);
             }
           }
           if (fl == 0u && t_end != 0ULL && globaltimer_ns() > t_end) fl = 1u;
@@ -674,15 +685,17 @@ lda_epoch_kernel(const __grid_constant__ LdaEpochArgs a) {
             for (uint32_t q = 0; q < cs; ++q) {
               lst_remote_u32(smem_u32(&s_flags), q, fl);
               lst_remote_u32(smem_u32(&s_end), q, (unsigned)s1);
-              lmbar_arrive_remote(bar_go, q);
             }
+            asm volatile("fence.acq_rel.cluster;" ::: "memory");      // one fence, then relaxed arrivals (see csrc/mf.cu)
+            for (uint32_t q = 0; q < cs; ++q) lmbar_arrive_remote_relaxed(bar_go, q);
           } else {
             s_flags = fl; s_end = s1;
             mbar_arrive(bar_go);
           }
         }
-        lmbar_wait_acq_cluster(bar_go, ph_go);
+        if (threadIdx.x == 0) { if (cs > 1) lmbar_wait_acq_cluster(bar_go, ph_go); else { while (!mbar_try_wait(bar_go, ph_go)) {} } }
         ph_go ^= 1u;
+        asm volatile("bar.sync 2, %0;" ::"n"(32 * NW) : "memory");     // the others park here instead of spinning
         const unsigned int fl = *reinterpret_cast<volatile unsigned int*>(&s_flags);
         if (!(fl & 3u)) {
           const int s1 = *reinterpret_cast<volatile int*>(&s_end);
@@ -695,12 +708,11 @@ lda_epoch_kernel(const __grid_constant__ LdaEpochArgs a) {
           }
         }
         asm volatile("bar.sync 1, %0;" ::"n"(32 * NW) : "memory");
-        if (threadIdx.x == 0) {
-          __threadfence();
-          if (cs > 1) lmbar_arrive_remote(bar_done, 0); else mbar_arrive(bar_done);
+        if (cs > 1) {
+          if (threadIdx.x == 0) { __threadfence(); lmbar_arrive_remote_relaxed(bar_done, 0); }
+          if (leader) lmbar_wait_acq_cluster(bar_done, ph_done);
         }
         if (leader) {
-          lmbar_wait_acq_cluster(bar_done, ph_done);
           ph_done ^= 1u;
           asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(pdp->col_ticket + c), "r"(tbase + (unsigned)t + 1u) : "memory");
         }

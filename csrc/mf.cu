@@ -24,6 +24,7 @@
 #include "../include/harp_b200.h"
 
 #include <cooperative_groups.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace hb {
@@ -80,28 +81,26 @@ struct SgdArgs {
 #endif
 // One column run (segment) of a block: h stays in registers, the run's ratings are trained in order.
 // Returns the number of ratings of the run (same value in every lane).
+// The run's ratings trained in order with h in registers.  `h` (the column's vector) and the first 32 row ids /
+// values (`rows0`, `vals0`: lane j holds rating k0 + j) are passed in, so a caller can fetch them for the NEXT run
+// while the current one is being trained.
 template <int RV, typename Core>
-__device__ __forceinline__ unsigned long long sgd_run_segment(const Core& a, int seg, int lane, int nl4) {
+__device__ __forceinline__ unsigned long long sgd_process_run(const Core& a, int col_raw, int k0, int k1, float4 (&h)[RV],
+                                                              int rows0, float vals0, int lane, int nl4) {
   constexpr int PF = RV == 1 ? HB_SGD_PF : (RV == 2 ? 2 : 1);     // w rows in flight per warp
     // bit 31 of seg_col marks a sub-run of a long column run that was split so that several warps
     // can work on a popular column at once; such sub-runs merge their h deltas additively
-    const int col_raw = a.seg_col[seg];
     const bool shared_col = col_raw < 0;
     const int col = col_raw & 0x7FFFFFFF;
-    const int k0 = a.seg_ptr[seg], k1 = a.seg_ptr[seg + 1];
-    float4 h[RV], h0[RV];
+    float4 h0[RV];
 #pragma unroll
-    for (int u = 0; u < RV; ++u) {
-      h[u] = (lane + 32 * u < nl4) ? ldcg4(a.H + (size_t)col * a.rank + (lane + 32 * u) * 4)
-                                   : make_float4(0.f, 0.f, 0.f, 0.f);
-      h0[u] = h[u];
-    }
+    for (int u = 0; u < RV; ++u) h0[u] = h[u];
     // Row ids and values of the run come in with one coalesced load (lane j holds rating k0 + j); the w rows
     // of the next PF ratings are kept in flight, so a rating costs 1/PF of a memory round trip, not a whole one.
     for (int kb = k0; kb < k1; kb += 32) {
       const int nb = min(32, k1 - kb);
-      const int rows_l = (lane < nb) ? a.r_row[kb + lane] : 0;
-      const float vals_l = (lane < nb) ? a.r_val[kb + lane] : 0.f;
+      const int rows_l = (kb == k0) ? rows0 : ((lane < nb) ? a.r_row[kb + lane] : 0);
+      const float vals_l = (kb == k0) ? vals0 : ((lane < nb) ? a.r_val[kb + lane] : 0.f);
       // a w row fetched early is stale if one of the PF ratings before it hits the same row (duplicate
       // (row, col) ratings only): those are flagged in bit 31 and re-read at their turn
       unsigned dup = 0;
@@ -174,6 +173,22 @@ __device__ __forceinline__ unsigned long long sgd_run_segment(const Core& a, int
       }
     }
     return (unsigned long long)(k1 - k0);
+}
+
+// One column run (segment) of a block, fetched and trained.  Returns the number of ratings of the run (same value
+// in every lane).
+template <int RV, typename Core>
+__device__ __forceinline__ unsigned long long sgd_run_segment(const Core& a, int seg, int lane, int nl4) {
+  const int col_raw = a.seg_col[seg];
+  const int col = col_raw & 0x7FFFFFFF;
+  const int k0 = a.seg_ptr[seg], k1 = a.seg_ptr[seg + 1];
+  float4 h[RV];
+#pragma unroll
+  for (int u = 0; u < RV; ++u)
+    h[u] = (lane + 32 * u < nl4) ? ldcg4(a.H + (size_t)col * a.rank + (lane + 32 * u) * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const int rows0 = (k0 + lane < k1) ? a.r_row[k0 + lane] : 0;
+  const float vals0 = (k0 + lane < k1) ? a.r_val[k0 + lane] : 0.f;
+  return sgd_process_run<RV>(a, col_raw, k0, k1, h, rows0, vals0, lane, nl4);
 }
 
 template <int RV>   // float4s per lane: rank <= 128 * RV
@@ -293,6 +308,7 @@ struct SgdEpochArgs {
   unsigned long long deadline_ns;  // per step, 0 = none
   unsigned int ticket_epoch;       // launches of this kernel so far (every panel is visited once per launch)
   int cs;                          // CTAs per worker (cluster size)
+  unsigned long long* trace;       // optional [steps][B][workers][3] %globaltimer stamps: wait start, go, done (tuning aid)
   int rank;
   float eps, lambda;
   rot::RingArgs ring;
@@ -304,9 +320,9 @@ struct SgdCore {
   int rank; float eps, lambda;
 };
 
-constexpr int EPOCH_THREADS = 1024;
-constexpr int EPOCH_COMM_WARP = EPOCH_THREADS / 32 - 1;      // last warp = communication warp
-constexpr int EPOCH_TRAIN_THREADS = EPOCH_THREADS - 32;
+// CTA sizes: 31 training warps + the communication warp for the one-run-per-warp cell, 16 + 1 for the quad-run cell
+// (it needs ~100 registers per thread).  The last warp is the communication warp.
+__host__ __device__ constexpr int epoch_threads(bool quad) { return quad ? 544 : 1024; }
 
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t cta) {
   // release at cluster scope: the arriving thread's prior writes (and, through the CTA barrier before it,
@@ -318,6 +334,17 @@ __device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t cta) {
       "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
       "}\n" ::"r"(bar), "r"(cta) : "memory");
 }
+// Relaxed form: the caller has already issued ONE fence for all the arrivals it is about to make (a release
+// arrive per destination CTA costs a MEMBAR.ALL.GPU each, and the leader makes `cs` of them per hand-over).
+__device__ __forceinline__ void mbar_arrive_remote_relaxed(uint32_t bar, uint32_t cta) {
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n"
+      "mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [ra];\n"
+      "}\n" ::"r"(bar), "r"(cta) : "memory");
+}
+__device__ __forceinline__ void fence_acq_rel_cluster() { asm volatile("fence.acq_rel.cluster;" ::: "memory"); }
 __device__ __forceinline__ void st_remote_u32(uint32_t addr, uint32_t cta, uint32_t v) {
   asm volatile(
       "{\n"
@@ -350,8 +377,157 @@ __device__ __forceinline__ uint32_t atom_add_remote_u32(uint32_t addr, uint32_t 
   return old;
 }
 
+// All runs of one cell, claimed one at a time from the worker's shared counter.  Kept out of line so that its
+// register allocation is that of the per-panel kernel's hot loop, independent of the epoch loop's live state.
 template <int RV>
-__global__ void __launch_bounds__(EPOCH_THREADS, 1) sgd_epoch_kernel(const __grid_constant__ SgdEpochArgs a) {
+__device__ __noinline__ unsigned long long sgd_run_cell(const SgdCore core, int s1, bool clustered, uint32_t next_addr,
+                                                        int lane, int nl4) {
+  // the descriptors travel through the parameter block as plain 64-bit words: tell the compiler they are global
+  // addresses, or every rating costs four generic loads
+  __builtin_assume(__isGlobal(core.seg_col)); __builtin_assume(__isGlobal(core.seg_ptr));
+  __builtin_assume(__isGlobal(core.r_row)); __builtin_assume(__isGlobal(core.r_val));
+  __builtin_assume(__isGlobal(core.W)); __builtin_assume(__isGlobal(core.H));
+  unsigned long long n = 0;
+  for (;;) {
+    int seg = 0;
+    if (lane == 0) {
+      if (clustered) seg = (int)atom_add_remote_u32(next_addr, 0, 1u);
+      else asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(seg) : "r"(next_addr) : "memory");
+    }
+    seg = __shfl_sync(0xffffffffu, seg, 0);
+    if (seg >= s1) break;
+    n += sgd_run_segment<RV>(core, seg, lane, nl4);
+  }
+  return n;
+}
+
+// ----------------------------------------------------------------------------
+// Quad-run cell (rank <= 128): a warp trains FOUR column runs at once, eight lanes per run, sixteen floats of w
+// and h per lane.  The one-run-per-warp form above spends 86 issued instructions per rating (ncu: the pass is
+// instruction-issue bound, a 5-step shuffle reduction and the address arithmetic for four floats of real work per
+// lane); here every issued instruction serves four ratings, the dot product needs three shuffle steps, and a warp
+// keeps four w rows in flight instead of one.  Runs are stored longest first, so the four runs a warp claims
+// together have nearly the same length.  Semantics per run are unchanged: ratings in order, h in registers,
+// split runs merge their h deltas with red.add.
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ float4 ld_w4(const float* p, bool on) {
+  return on ? ldcg4(p) : make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+__device__ __noinline__ unsigned long long sgd_run_cell_quad(const SgdCore core, int s1, bool clustered, uint32_t next_addr,
+                                                             int lane) {
+  __builtin_assume(__isGlobal(core.seg_col)); __builtin_assume(__isGlobal(core.seg_ptr));
+  __builtin_assume(__isGlobal(core.r_row)); __builtin_assume(__isGlobal(core.r_val));
+  __builtin_assume(__isGlobal(core.W)); __builtin_assume(__isGlobal(core.H));
+  const int grp = lane >> 3, sub = lane & 7;
+  const int nl4 = core.rank >> 2;
+  bool on[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) on[q] = (q * 8 + sub) < nl4;
+  const float ee_scale = core.eps, el = core.eps * core.lambda;
+  unsigned long long n = 0;
+  for (;;) {
+    int base = 0;
+    if (lane == 0) {
+      if (clustered) base = (int)atom_add_remote_u32(next_addr, 0, 4u);
+      else asm volatile("atom.shared.add.u32 %0, [%1], 4;" : "=r"(base) : "r"(next_addr) : "memory");
+    }
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= s1) break;
+    const int seg = base + grp;
+    const bool valid = seg < s1;
+    int col_raw = 0, k0 = 0, k1 = 0;
+    if (valid) { col_raw = core.seg_col[seg]; k0 = core.seg_ptr[seg]; k1 = core.seg_ptr[seg + 1]; }
+    const bool shared_col = col_raw < 0;
+    const int col = col_raw & 0x7FFFFFFF;
+    const int len = k1 - k0;
+    float4 h[4], h0[4];
+    float* hrow = core.H + (size_t)col * core.rank + sub * 4;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { h[q] = ld_w4(hrow + q * 32, valid && on[q]); h0[q] = h[q]; }
+    int maxlen = len;
+    maxlen = max(maxlen, __shfl_xor_sync(0xffffffffu, maxlen, 8));
+    maxlen = max(maxlen, __shfl_xor_sync(0xffffffffu, maxlen, 16));
+    for (int kb = 0; kb < maxlen; kb += 8) {
+      const int nb = min(8, len - kb);                    // ratings of MY run in this batch (<= 0: run is over)
+      const int nbmax = min(8, maxlen - kb);
+      const int rows_l = (sub < nb) ? core.r_row[k0 + kb + sub] : 0;
+      const float vals_l = (sub < nb) ? core.r_val[k0 + kb + sub] : 0.f;
+      int row = __shfl_sync(0xffffffffu, rows_l, 0, 8);
+      float4 wq[4];
+      {
+        const float* wrow = core.W + (size_t)row * core.rank + sub * 4;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) wq[q] = ld_w4(wrow + q * 32, nb > 0 && on[q]);
+      }
+      bool reload = false;
+      for (int j = 0; j < nbmax; ++j) {
+        const bool act = j < nb;
+        const float v = __shfl_sync(0xffffffffu, vals_l, j, 8);
+        float* wrow = core.W + (size_t)row * core.rank + sub * 4;
+        float4 w[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) w[q] = wq[q];
+        if (reload) {             // the same row twice in a row (duplicate rating): the copy fetched ahead is stale
+#pragma unroll
+          for (int q = 0; q < 4; ++q) w[q] = ld_w4(wrow + q * 32, on[q]);
+        }
+        // fetch the next rating's row while this one is trained
+        const int rown = __shfl_sync(0xffffffffu, rows_l, (j + 1) & 7, 8);
+        const bool more = (j + 1 < nb);
+        reload = more && (rown == row);
+        if (more && !reload) {
+          const float* wn = core.W + (size_t)rown * core.rank + sub * 4;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) wq[q] = ld_w4(wn + q * 32, on[q]);
+        }
+        float dot = 0.f;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) dot += w[q].x * h[q].x + w[q].y * h[q].y + w[q].z * h[q].z + w[q].w * h[q].w;
+        dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+        const float ee = ee_scale * (dot - v);
+        if (act) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            // w -= eps (e h + lambda w);  h -= eps (e w_old + lambda h)     (SGDMPTask.java:60-72)
+            float4 wn, hn;
+            wn.x = w[q].x - (ee * h[q].x + el * w[q].x); hn.x = h[q].x - (ee * w[q].x + el * h[q].x);
+            wn.y = w[q].y - (ee * h[q].y + el * w[q].y); hn.y = h[q].y - (ee * w[q].y + el * h[q].y);
+            wn.z = w[q].z - (ee * h[q].z + el * w[q].z); hn.z = h[q].z - (ee * w[q].z + el * h[q].z);
+            wn.w = w[q].w - (ee * h[q].w + el * w[q].w); hn.w = h[q].w - (ee * w[q].w + el * h[q].w);
+            h[q] = hn;
+            if (on[q]) stcg4(wrow + q * 32, wn);
+          }
+        }
+        row = rown;
+      }
+    }
+    if (valid) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (on[q]) {
+          if (shared_col)
+            red_add_v4(hrow + q * 32, make_float4(h[q].x - h0[q].x, h[q].y - h0[q].y, h[q].z - h0[q].z, h[q].w - h0[q].w));
+          else
+            stcg4(hrow + q * 32, h[q]);
+        }
+      }
+    }
+    int tot = (sub == 0) ? len : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    n += (unsigned long long)tot;
+  }
+  return n;
+}
+
+template <int RV, bool QUAD>
+__global__ void __launch_bounds__(epoch_threads(QUAD), 1) sgd_epoch_kernel(const __grid_constant__ SgdEpochArgs a) {
+  constexpr int EPOCH_THREADS = epoch_threads(QUAD);
+  constexpr int EPOCH_COMM_WARP = EPOCH_THREADS / 32 - 1;
+  constexpr int EPOCH_TRAIN_THREADS = EPOCH_THREADS - 32;
   __shared__ __align__(8) unsigned long long s_bar[2];    // [0] go (1 arrival), [1] done (cs arrivals; used in the leader)
   __shared__ unsigned int s_flags;                        // bit 0: stop (deadline), bit 1: abort
   __shared__ int s_end;                                   // one past the cell's last column run
@@ -398,6 +574,8 @@ __global__ void __launch_bounds__(EPOCH_THREADS, 1) sgd_epoch_kernel(const __gri
           const int* bsp = pdp->blk_seg_ptr + (size_t)worker * B + c;
           const int s0 = bsp[0], s1 = bsp[1];                 // independent of the ticket: issued before the spin
           unsigned int fl = 0u;
+          unsigned long long* tr = a.trace ? a.trace + (((size_t)g * B + t) * B + worker) * 27 : nullptr;
+          if (tr) tr[0] = rot::now_ns();
           if (t == 0 && ring_on && !rot::wait_slice(a.ring, g)) fl = 2u;
           if (fl == 0u) {
             // column-block c is ours once its previous holder has released it
@@ -405,8 +583,8 @@ __global__ void __launch_bounds__(EPOCH_THREADS, 1) sgd_epoch_kernel(const __gri
             if (ld_acquire_gpu(tick) != want) {
               const unsigned long long t0 = rot::now_ns();
               unsigned spins = 0;
-              while (ld_acquire_gpu(tick) != want) {
-                __nanosleep(32);
+              while (ld_relaxed_gpu(tick) != want) {       // relaxed polls: an acquire load per poll would keep invalidating L1
+                __nanosleep(100);
                 if ((++spins & 255u) == 0u && ring_on) {
                   if (rot::aborted(ctl)) { fl = 2u; break; }
                   if (a.ring.timeout_ns != 0ULL && rot::now_ns() - t0 > a.ring.timeout_ns) {
@@ -415,44 +593,52 @@ __global__ void __launch_bounds__(EPOCH_THREADS, 1) sgd_epoch_kernel(const __gri
                   }
                 }
               }
+              (void)ld_acquire_gpu(tick);
             }
           }
           if (fl == 0u && t_end != 0ULL && globaltimer_ns() > t_end) fl = 1u;
+          if (tr) tr[1] = rot::now_ns();
           s_next = (unsigned)s0;
           if (cs > 1) {
             for (uint32_t q = 0; q < cs; ++q) {
               st_remote_u32(smem_u32(&s_flags), q, fl);
               st_remote_u32(smem_u32(&s_end), q, (unsigned)s1);
-              mbar_arrive_remote(bar_go, q);
             }
+            fence_acq_rel_cluster();         // one fence, then relaxed arrivals: publishes the stores above and what the
+            for (uint32_t q = 0; q < cs; ++q) mbar_arrive_remote_relaxed(bar_go, q);      // ticket acquire made visible
           } else {
             s_flags = fl; s_end = s1;
             mbar_arrive(bar_go);
           }
         }
-        mbar_wait_acq_cluster(bar_go, ph_go);      // unbounded: the leader may be waiting for a peer GPU
+        // One thread per CTA waits for the worker's leader (unbounded: the leader may be waiting for a peer GPU and
+        // broadcasts an abort flag if it gives up); everybody else parks at a hardware barrier instead of spinning
+        // on the mbarrier, which cost a quarter more issued instructions.
+        if (threadIdx.x == 0) { if (cs > 1) mbar_wait_acq_cluster(bar_go, ph_go); else { while (!mbar_try_wait(bar_go, ph_go)) {} } }
         ph_go ^= 1u;
+        asm volatile("bar.sync 2, %0;" ::"r"(ntrain) : "memory");
+        unsigned long long* trc = (a.trace && threadIdx.x == 0) ? a.trace + (((size_t)g * B + t) * B + worker) * 27 + 3 + crank * 3 : nullptr;
+        if (trc) trc[0] = rot::now_ns();
         const unsigned int fl = *reinterpret_cast<volatile unsigned int*>(&s_flags);
         if (!(fl & 3u)) {
           const int s1 = *reinterpret_cast<volatile int*>(&s_end);
-          for (;;) {
-            int seg = 0;
-            if (lane == 0) seg = cs > 1 ? (int)atom_add_remote_u32(smem_u32(&s_next), 0, 1u) : (int)atomicAdd(&s_next, 1u);
-            seg = __shfl_sync(0xffffffffu, seg, 0);
-            if (seg >= s1) break;
-            local_trained += sgd_run_segment<RV>(core, seg, lane, nl4);
-          }
+          if (QUAD) local_trained += sgd_run_cell_quad(core, s1, cs > 1, smem_u32(&s_next), lane);
+          else local_trained += sgd_run_cell<RV>(core, s1, cs > 1, smem_u32(&s_next), lane, nl4);
         }
         // ---- hand the column-block on ----
         asm volatile("bar.sync 1, %0;" ::"r"(ntrain) : "memory");
-        if (threadIdx.x == 0) {
-          __threadfence();
-          if (cs > 1) mbar_arrive_remote(bar_done, 0); else mbar_arrive(bar_done);
+        if (trc) trc[1] = rot::now_ns();
+        // One fence per CTA (its writes, ordered before thread 0 by the barrier above), then a relaxed arrival at the
+        // leader; the leader's ticket store below is the gpu-scope release that hands everything to the next worker.
+        // With a single CTA per worker the release store alone does it.
+        if (cs > 1) {
+          if (threadIdx.x == 0) { __threadfence(); if (trc) trc[2] = rot::now_ns(); mbar_arrive_remote_relaxed(bar_done, 0); }
+          if (leader) mbar_wait_acq_cluster(bar_done, ph_done);
         }
         if (leader) {
-          mbar_wait_acq_cluster(bar_done, ph_done);
           ph_done ^= 1u;
           // tickets keep moving even when the step was cut short (deadline / abort) so nobody waits for ever
+          if (a.trace) a.trace[(((size_t)g * B + t) * B + worker) * 27 + 2] = rot::now_ns();
           asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(pdp->col_ticket + c), "r"(tbase + (unsigned)t + 1u) : "memory");
         }
         if (fl & 2u) { dead = true; break; }
@@ -579,17 +765,27 @@ static int sgd_launch(SgdArgs& a, void* stream) {
 }
 
 // ---- whole-epoch launch (rotation fused) ----
-static const void* sgd_epoch_fn(int rank) {
-  return rank <= 128 ? (const void*)sgd_epoch_kernel<1> : rank <= 256 ? (const void*)sgd_epoch_kernel<2>
-                                                                         : (const void*)sgd_epoch_kernel<4>;
+static unsigned long long* g_epoch_trace = nullptr;
+// Tuning aid: when set, the next hb_sgd_epoch launches write three %globaltimer stamps per (step, hand-over, worker)
+// — wait start, go, done — into this device buffer of steps * B * B * 27 uint64 (3 leader stamps + 3 per CTA of the worker: work start, work end, fenced) (NULL switches it off).
+int hb_sgd_epoch_trace(unsigned long long* buf) { g_epoch_trace = buf; return 0; }
+static bool sgd_use_quad(int rank) {
+  static const bool off = getenv("HB_SGD_QUAD") != nullptr && atoi(getenv("HB_SGD_QUAD")) == 0;     // A/B knob
+  return rank <= 128 && !off;
 }
+static const void* sgd_epoch_fn(int rank) {
+  if (sgd_use_quad(rank)) return (const void*)sgd_epoch_kernel<1, true>;
+  return rank <= 128 ? (const void*)sgd_epoch_kernel<1, false> : rank <= 256 ? (const void*)sgd_epoch_kernel<2, false>
+                                                                                : (const void*)sgd_epoch_kernel<4, false>;
+}
+static int sgd_epoch_threads(int rank) { return epoch_threads(sgd_use_quad(rank)); }
 
 // How many workers (clusters of `cs` CTAs, one CTA per SM) one cooperative launch keeps resident.
 int hb_sgd_epoch_max_workers(int rank, int cs) {
   if (cs < 1 || cs > 8 || (cs & (cs - 1)) != 0) return 0;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(sm_count() / cs * cs));
-  cfg.blockDim = dim3(EPOCH_THREADS);
+  cfg.blockDim = dim3((unsigned)sgd_epoch_threads(rank));
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = (unsigned)cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
@@ -598,7 +794,7 @@ int hb_sgd_epoch_max_workers(int rank, int cs) {
   int n = 0;
   if (cs == 1) {
     int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sgd_epoch_fn(rank), EPOCH_THREADS, 0) != cudaSuccess) return 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sgd_epoch_fn(rank), sgd_epoch_threads(rank), 0) != cudaSuccess) return 0;
     return per_sm > 0 ? sm_count() : 0;
   }
   if (cudaOccupancyMaxActiveClusters(&n, sgd_epoch_fn(rank), &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -614,11 +810,12 @@ int hb_ring_ctl_bytes(void) { return (int)sizeof(rot::RingCtl); }
 //   world == 0: no ring, peer_state[0] + off_buf4[2k] is slice k.  world >= 1: symmetric ring state of every
 //   rank (world == 1 is a loop-back ring onto this rank's own buffers).
 int hb_sgd_epoch(float* W, const void* panels_host, int npanels, const int* panel_of_step_host, int steps, int S, int workers,
-                 int cs, int rank, float eps, float lambda, unsigned ticket_epoch, unsigned long long deadline_ns,
+                 int cs_and_flags /* CTAs per worker */, int rank, float eps, float lambda, unsigned ticket_epoch, unsigned long long deadline_ns,
                  unsigned long long* trained, void* const* peer_state, int my_rank, int world,
                  unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
                  const int* src_rank_host, unsigned cnt_base, const unsigned* par_base2,
                  unsigned long long timeout_ns, void* stream) {
+  const int cs = cs_and_flags;
   HB_REQUIRE(rank >= 4 && rank % 4 == 0 && rank <= 512, "hb_sgd_epoch: need rank %% 4 == 0 and rank <= 512 (got %d)", rank);
   HB_REQUIRE(workers >= 1 && workers <= hb_sgd_epoch_max_workers(rank, cs),
              "hb_sgd_epoch: %d workers of %d CTAs cannot be co-resident (max %d)", workers, cs, hb_sgd_epoch_max_workers(rank, cs));
@@ -634,9 +831,9 @@ int hb_sgd_epoch(float* W, const void* panels_host, int npanels, const int* pane
     a.panel_of_step[g] = panel_of_step_host[g];
   }
   a.W = W;
-  a.trained = trained; a.deadline_ns = deadline_ns; a.ticket_epoch = ticket_epoch; a.cs = cs; a.rank = rank;
+  a.trained = trained; a.deadline_ns = deadline_ns; a.ticket_epoch = ticket_epoch; a.cs = cs; a.trace = g_epoch_trace; a.rank = rank;
   a.eps = eps; a.lambda = lambda;
-  return rot::launch_epoch(sgd_epoch_fn(rank), EPOCH_THREADS, 0, workers, cs, a, stream);
+  return rot::launch_epoch(sgd_epoch_fn(rank), sgd_epoch_threads(rank), 0, workers, cs, a, stream);
 }
 
 // Device wall clock (ns) usable as a deadline base for hb_sgd_pass.

@@ -89,10 +89,14 @@ __device__ __forceinline__ bool wait_ge(const uint32_t* p, uint32_t target, Ring
   const unsigned long long t0 = now_ns();
   unsigned spins = 0;
   for (;;) {
-    if ((int32_t)((SYS ? ld_acquire_sys(p) : ld_acquire_gpu(p)) - target) >= 0) return true;
-    __nanosleep(SYS ? 200 : 64);
+    // relaxed polls (an acquire load invalidates the SM's L1 each time), one acquire when the value is there
+    if ((int32_t)((SYS ? ld_relaxed_sys(p) : ld_relaxed_gpu(p)) - target) >= 0) {
+      (void)(SYS ? ld_acquire_sys(p) : ld_acquire_gpu(p));
+      return true;
+    }
+    __nanosleep(SYS ? 200 : 100);
     if ((++spins & 63u) == 0u) {
-      if (ld_acquire_gpu(&ctl->error) != 0u) return false;
+      if (ld_relaxed_gpu(&ctl->error) != 0u) return false;
       if (timeout_ns != 0ULL && now_ns() - t0 > timeout_ns) {
         if (atomicCAS(&ctl->error, 0u, code) == 0u) ctl->error_detail = detail;
         __threadfence();
@@ -102,7 +106,7 @@ __device__ __forceinline__ bool wait_ge(const uint32_t* p, uint32_t target, Ring
   }
 }
 
-__device__ __forceinline__ bool aborted(const RingCtl* ctl) { return ld_acquire_gpu(&ctl->error) != 0u; }
+__device__ __forceinline__ bool aborted(const RingCtl* ctl) { return ld_relaxed_gpu(&ctl->error) != 0u; }
 
 // Body of the communication warp of CTA blockIdx.x (all 32 lanes call it).  Walks the launch's steps and, for
 // each, pulls this CTA's stripe of the slice's NEXT use from the step's source rank.

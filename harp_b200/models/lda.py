@@ -24,7 +24,8 @@ class LDAEngine:
     def __init__(self, docs: torch.Tensor, words: torch.Tensor, num_docs_local: int, vocab: int, K: int,
                  alpha: float, beta: float, *, symm=None, blocks: Optional[int] = None, seed: int = 0, group=None,
                  num_slices: Optional[int] = None, dk_dtype: str = "auto", fused: Optional[bool] = None,
-                 cluster: Optional[int] = None, loopback: bool = False, max_run: Optional[int] = None):
+                 cluster: Optional[int] = None, loopback: bool = False, max_run: Optional[int] = None,
+                 virtual_world: int = 0):
         self.dev = docs.device
         self.K, self.V = int(K), int(vocab)
         self.alpha, self.beta = float(alpha), float(beta)
@@ -34,6 +35,11 @@ class LDAEngine:
         self.symm = symm if self.N > 1 else None
         N = self.N
         import os
+        # tuning aid, one GPU only: the per-rank layout of a `virtual_world`-rank job (see MFSGDEngine)
+        self.Nv = int(virtual_world) if (virtual_world and N == 1) else 0
+        if self.Nv:
+            N = self.Nv
+            loopback = True
         cuda = self.dev.type == "cuda"
         self.S = S = int(num_slices) if num_slices else 2          # two slices in flight, like the reference
         assert S in (1, 2)
@@ -52,7 +58,7 @@ class LDAEngine:
             dk_dtype = "int16" if (cuda and longest < 32768) else "int32"
         self.dk16 = dk_dtype == "int16"
         if fused is None:
-            fused = (cuda and (N == 1 or self.symm is not None) and os.environ.get("HB_LDA_FUSED", "1") != "0"
+            fused = (cuda and (self.N == 1 or self.symm is not None) and os.environ.get("HB_LDA_FUSED", "1") != "0"
                      and L.epoch_supported(self.K, self.dk16))
         self.fused = bool(fused)
         self.cs = 1
@@ -64,7 +70,8 @@ class LDAEngine:
                 mx = L.epoch_max_workers(self.K, self.dk16, self.cs)
             self.B = max(1, min(int(blocks) if blocks else mx, mx))
             if max_run is None:
-                max_run = max(8, min(64, int(per_panel / (self.B * self.B) / (2.0 * self.cs * 24))))
+                x = per_panel / (self.B * self.B) / (2.0 * self.cs * 24)        # ~2 runs per sampling warp of a worker
+                max_run = 16 if x < 24 else (32 if x < 48 else 64)
         elif cuda:
             sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
             self.B = int(blocks) if blocks else _mf.auto_blocks(per_panel, min(L.max_blocks(self.K), sms), per_block=32)
@@ -95,9 +102,9 @@ class LDAEngine:
             self.n_dk = self.n_dk.to(torch.int16)
         self.ring = None
         self._cur = [0] * S
-        self.sched = [RingSchedule(N, None) for _ in range(S)]     # plain ring (LDAMPCollectiveMapper.java:255-259)
+        self.sched = [RingSchedule(self.N, None) for _ in range(S)]     # plain ring (LDAMPCollectiveMapper.java:255-259)
         if cuda:
-            self.ring = RingState(self.dev, self.cap * self.K, cdt, S, symm=self.symm, rank=self.me, world=N,
+            self.ring = RingState(self.dev, self.cap * self.K, cdt, S, symm=self.symm, rank=self.me, world=self.N,
                                   loopback=loopback)
             self.Wbuf = [[b_.view(self.cap, self.K) for b_ in pair] for pair in self.ring.buf]
         else:
@@ -110,12 +117,13 @@ class LDAEngine:
             for e in self.ev_comm:
                 e.record()
         # word-topic table: one full rotation in which every worker adds its tokens to the visiting shard
-        for _ in range(N):
+        for j in range(N):
             for k in range(self.S):
                 self._wait_slice(k)
-                p = self.panels[self._visiting(k)][k]
+                p = self.panels[j if self.Nv else self._visiting(k)][k]
                 L.count_into(p.tok_word, p.tok_z, self.K, self.Wbuf[k][self.cur[k]])
-                self._rotate(k)
+                if not self.Nv:
+                    self._rotate(k)
         self.topic_sums = torch.zeros(self.K, dtype=torch.int64, device=self.dev)
         self.commons = torch.zeros(self.K, dtype=torch.float32, device=self.dev)
         self.trained = torch.zeros(1, dtype=torch.int64, device=self.dev)
@@ -176,10 +184,15 @@ class LDAEngine:
         if self.fused and self.dev.type == "cuda":
             N, S = self.N, self.S
             pos_l, src_l = [], []
-            for _ in range(N):
-                for k in range(S):
-                    pos_l.append(self.sched[k].shard_at[self.me] * S + k)
-                    src_l.append(self.sched[k].rotate()[self.me])
+            if self.Nv:
+                N = self.Nv
+                pos_l = [j * S + k for j in range(N) for k in range(S)]
+                src_l = [0] * (N * S)
+            else:
+                for _ in range(N):
+                    for k in range(S):
+                        pos_l.append(self.sched[k].shard_at[self.me] * S + k)
+                        src_l.append(self.sched[k].rotate()[self.me])
             for k in range(S):
                 self._wait_slice(k)
             L.lda_epoch(self.n_dk, self.commons, self.desc, pos_l, S, self.B, self.cs, self.alpha, self.beta,

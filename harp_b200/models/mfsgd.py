@@ -33,7 +33,7 @@ class MFSGDEngine:
                  num_cols: int, rank: int, eps: float, lam: float, *, symm=None, blocks: Optional[int] = None,
                  seed: int = 0, group=None, num_slices: Optional[int] = None, fused: Optional[bool] = None,
                  cluster: Optional[int] = None, orders: Optional[Sequence[int]] = None, loopback: bool = False,
-                 max_run: Optional[int] = None):
+                 max_run: Optional[int] = None, virtual_world: int = 0):
         self.dev = rows.device
         self.rank_k = int(rank)
         self.eps, self.lam = float(eps), float(lam)
@@ -44,11 +44,23 @@ class MFSGDEngine:
         self.num_cols = int(num_cols)
         self.num_rows_local = int(num_rows_local)
         N = self.N
+        # Tuning aid (single GPU only): lay the problem out as ONE rank of a `virtual_world`-rank job would see it
+        # (N_v x S panels, N_v x S steps per epoch, loop-back ring) so that the per-rank kernel time of a large
+        # job can be measured on one GPU.  The slices' contents are not meaningful in this mode.
+        self.Nv = int(virtual_world) if (virtual_world and N == 1) else 0
+        if self.Nv:
+            N = self.Nv
+            loopback = True
         cuda = self.dev.type == "cuda"
         self.S = S = int(num_slices) if num_slices else 2        # two slices in flight, like the reference
         assert S in (1, 2)
         if fused is None:
-            fused = cuda and (N == 1 or self.symm is not None) and os.environ.get("HB_SGD_FUSED", "1") != "0"
+            # one rank has nothing to rotate: two per-panel launches per epoch measured faster there (15.4 vs 19.5 ms
+            # on BASELINE config 3) than the epoch kernel, whose cells end with a fence that drains their stores
+            env = os.environ.get("HB_SGD_FUSED")
+            fused = cuda and ((self.N > 1 and self.symm is not None) or loopback or bool(self.Nv))
+            if env is not None:
+                fused = cuda and env != "0" and (self.N == 1 or self.symm is not None)
         self.fused = bool(fused)
         self.cap = max(1, (self.num_cols + S * N - 1) // (S * N))          # columns per (shard, slice)
         nnz_max = float(rows.numel())
@@ -68,7 +80,7 @@ class MFSGDEngine:
             self.B = int(blocks) if blocks else mx
             self.B = max(1, min(self.B, mx))
             if max_run is None:
-                max_run = mf.pick_max_run(per_panel, self.B, self.cs)
+                max_run = mf.pick_max_run(per_panel, self.B, self.cs, mf.epoch_run_slots(self.rank_k))
         elif cuda:
             mx = mf.max_blocks(self.rank_k)
             sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
@@ -84,14 +96,14 @@ class MFSGDEngine:
         # H slices: control block + ping-pong buffers, one allocation (symmetric memory when there are peers)
         self.ring = None
         if cuda:
-            self.ring = RingState(self.dev, self.cap * self.rank_k, dt, S, symm=self.symm, rank=self.me, world=N,
+            self.ring = RingState(self.dev, self.cap * self.rank_k, dt, S, symm=self.symm, rank=self.me, world=self.N,
                                   loopback=loopback)
             self.Hbuf = [[b.view(self.cap, self.rank_k) for b in pair] for pair in self.ring.buf]
         else:
             self.Hbuf = [[torch.empty(self.cap, self.rank_k, dtype=dt, device=self.dev) for _ in range(2 if N > 1 else 1)]
                          for _ in range(S)]
         self._cur = [0] * S
-        self.sched = [RingSchedule(N, orders) for _ in range(S)]        # every slice walks the same order array
+        self.sched = [RingSchedule(self.N, orders) for _ in range(S)]   # every slice walks the same order array
         gh = torch.Generator(device=self.dev).manual_seed(seed + 104729)      # same H init on every rank, then
         for k in range(S):                                                    # each keeps its own shard
             full = torch.rand(N, self.cap, self.rank_k, device=self.dev, generator=gh, dtype=dt) * scale
@@ -169,10 +181,15 @@ class MFSGDEngine:
         """The whole epoch as one launch; the per-step panel / source-rank tables come from the schedules."""
         N, S = self.N, self.S
         panel_of_step, src_of_step = [], []
-        for _ in range(N):
-            for k in range(S):
-                panel_of_step.append(self.sched[k].shard_at[self.me] * S + k)
-                src_of_step.append(self.sched[k].rotate()[self.me])
+        if self.Nv:
+            N = self.Nv
+            panel_of_step = [j * S + k for j in range(N) for k in range(S)]
+            src_of_step = [0] * (N * S)
+        else:
+            for _ in range(N):
+                for k in range(S):
+                    panel_of_step.append(self.sched[k].shard_at[self.me] * S + k)
+                    src_of_step.append(self.sched[k].rotate()[self.me])
         for k in range(S):
             self._wait_slice(k)
         mf.sgd_epoch(self.W, self.desc, panel_of_step, S, self.B, self.cs, self.eps, self.lam, self.epochs_fused,

@@ -67,24 +67,30 @@ def epoch_max_workers(rank: int, cs: int) -> int:
 
 
 def pick_cluster(nnz_per_panel: float) -> int:
-    """CTAs per worker for the whole-epoch kernels: a pass costs B hand-overs plus nnz / (B x warps per worker)
-    updates, so small panels want few, fat workers (``HB_EPOCH_CS`` overrides)."""
+    """CTAs per worker for the whole-epoch kernels.  A pass costs B hand-overs (each ends with a gpu-scope fence that
+    has to drain the cell's stores: ~5 us measured) plus nnz / (B x warps per worker) updates, so few, fat workers
+    win at every size tried: clusters of 8 (15 workers on a B200: two 8-SM clusters fit per GPC) beat 4, 2 and 1 at
+    781 K, 3 M and 12 M ratings per panel (``scripts/tune_sgd_virtual.py``).  ``HB_EPOCH_CS`` overrides."""
     import os
     if os.environ.get("HB_EPOCH_CS"):
         return int(os.environ["HB_EPOCH_CS"])
-    if nnz_per_panel >= 16e6:
-        return 1
-    if nnz_per_panel >= 6e6:
-        return 2
-    if nnz_per_panel >= 1.5e6:
-        return 4
     return 8
 
 
-def pick_max_run(nnz_per_panel: float, workers: int, cs: int, warps_per_cta: int = 31) -> int:
-    """Longest column run one warp trains sequentially: short enough that a cell has ~2 runs per warp."""
+def epoch_run_slots(rank: int) -> int:
+    """Column runs one CTA of the whole-epoch kernel trains at the same time: 16 warps x 4 runs with the quad-run
+    cell (rank <= 128), 31 warps x 1 run otherwise (``csrc/mf.cu``; ``HB_SGD_QUAD=0`` switches the quad cell off)."""
+    import os
+    return 64 if (rank <= 128 and os.environ.get("HB_SGD_QUAD", "1") != "0") else 31
+
+
+def pick_max_run(nnz_per_panel: float, workers: int, cs: int, slots_per_cta: int = 31) -> int:
+    """Longest column run trained sequentially: short enough that a cell has ~2 runs per run slot of its worker."""
     cell = nnz_per_panel / float(workers * workers)
-    return int(max(4, min(32, cell / (2.0 * cs * warps_per_cta))))
+    x = cell / (2.0 * cs * slots_per_cta)
+    if slots_per_cta == 64:          # quad-run cell: eight ratings per batch, so whole multiples of 8 (measured)
+        return 8 if x < 12 else (16 if x < 24 else 32)
+    return int(max(4, min(32, x)))
 
 
 def panel_descriptors(panels):

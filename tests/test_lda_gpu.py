@@ -65,7 +65,7 @@ def test_lda_epoch_kernel_single_gpu(native_built, cluster, loopback):
     g = torch.Generator(device="cuda").manual_seed(3)
     docs = torch.arange(D, device="cuda").repeat_interleave(Ld)
     words = (torch.rand(D * Ld, device="cuda", generator=g) ** 2 * V).long() % V
-    eng = LDAEngine(docs, words, D, V, K, 0.1, 0.01, seed=2, cluster=cluster, loopback=loopback)
+    eng = LDAEngine(docs, words, D, V, K, 0.1, 0.01, seed=2, cluster=cluster, loopback=loopback, fused=True)
     ref = LDAEngine(docs, words, D, V, K, 0.1, 0.01, seed=2, fused=False)
     assert eng.fused and eng.cs == cluster
     ll0 = eng.log_likelihood()

@@ -135,7 +135,8 @@ def test_sgd_epoch_kernel_single_gpu(native_built, cluster, loopback, slices):
     from harp_b200.models.mfsgd import MFSGDEngine
     r, c, v = _problem(nr=20000, nc=3000, nnz=600000, rank=64, seed=2)
     r, c, v = r.cuda(), c.cuda(), v.cuda()
-    eng = MFSGDEngine(r, c, v, 20000, 3000, 64, 0.01, 0.02, seed=5, cluster=cluster, loopback=loopback, num_slices=slices)
+    eng = MFSGDEngine(r, c, v, 20000, 3000, 64, 0.01, 0.02, seed=5, cluster=cluster, loopback=loopback, num_slices=slices,
+                      fused=True)
     assert eng.fused and eng.cs == cluster
     ref = MFSGDEngine(r, c, v, 20000, 3000, 64, 0.01, 0.02, seed=5, fused=False, num_slices=slices)
     e0 = eng.rmse(r, c, v)
