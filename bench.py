@@ -45,6 +45,9 @@ def parse_args():
     ap.add_argument("--dim", type=int, default=DIM)
     ap.add_argument("--k", type=int, default=K)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the MF-SGD / LDA / Gram block of the default run")
+    ap.add_argument("--no-library-arm", action="store_true", help="skip the cuBLAS + NCCL arm of the default run")
+    ap.add_argument("--secondary-steps", type=int, default=20)
     return ap.parse_args()
 
 
@@ -108,7 +111,30 @@ class ClockSampler:
         }
 
 
-def roofline(flops_per_gpu: float, reduce_bytes: int, world: int, ms_per_step: float) -> dict:
+def measure_nvlink_gbs(symm, dev) -> float:
+    """Peer pull bandwidth per direction per GPU over the symmetric slab (every rank pulls 256 MB from its ring
+    predecessor at the same time): the NVLink denominator of the roofline, measured on the box the bench runs on."""
+    import torch
+    import torch.distributed as dist
+    n = 64 << 20
+    src = symm.alloc(n, torch.float32)
+    dst = symm.alloc(n, torch.float32)
+    src.fill_(1.0)
+    pred = (symm.rank - 1) % symm.world
+    for _ in range(2):
+        symm.rotate_(dst, src, pred)
+    torch.cuda.synchronize(); dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        symm.rotate_(dst, src, pred)
+    e1.record(); torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / 5], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return (n * 4) / (float(t.item()) * 1e-3) / 1e9
+
+
+def roofline(flops_per_gpu: float, reduce_bytes: int, world: int, ms_per_step: float, nvlink_gbs=None) -> dict:
     """Achieved / target for a fused compute+collective step: target = slower of FLOPs / measured GEMM peak and
     NVLink bytes / measured link rate.  Denominators: MEASURED_PEAKS.json (cuBLAS bf16, sustained figure because the
     step runs for seconds under the power cap), else the profiling recipe's fallback.  The kernel's products are
@@ -119,12 +145,14 @@ def roofline(flops_per_gpu: float, reduce_bytes: int, world: int, ms_per_step: f
         bf16, src = float(mp.get("bf16_tflops_sustained") or mp["bf16_tflops"]), "measured"
     except Exception:  # noqa: BLE001
         pass
-    nvlink_gbs = 770.0                                   # measured peer copy per direction per GPU (recipe)
+    nvlink_src = "measured in this run (peer pull of 256 MB by every rank at once)"
+    if not nvlink_gbs:
+        nvlink_gbs, nvlink_src = 770.0, "profiling recipe's measured peer copy (single GPU run: nothing to measure)"
     link_bytes = 2.0 * reduce_bytes * (world - 1) / max(world, 1)      # reduce-scatter in + all-gather out
     t_compute = flops_per_gpu / (bf16 * 1e12) * 1e3
     t_link = link_bytes / (nvlink_gbs * 1e9) * 1e3
     target = max(t_compute, t_link)
-    return {"denominator": f"cuBLAS bf16 {bf16:.0f} TFLOP/s sustained, of {src}; NVLink {nvlink_gbs:.0f} GB/s per direction",
+    return {"denominator": f"cuBLAS bf16 {bf16:.0f} TFLOP/s sustained, of {src}; NVLink {nvlink_gbs:.0f} GB/s per direction, {nvlink_src}",
             "target_ms": target, "compute_ms_at_bf16_peak": t_compute, "nvlink_ms": t_link,
             "fraction_of_bf16_peak": target / ms_per_step,
             "fraction_of_tf32_rate": min(2.0 * target, max(2.0 * t_compute, t_link)) / ms_per_step}
@@ -174,7 +202,7 @@ def main():
 
     if args.workload != "kmeans":
         from harp_b200.bench_workloads import run_workload
-        return run_workload(args, rank, world, dev)
+        return run_workload(args, rank, world, dev, ClockSampler)
 
     from harp_b200.models.kmeans import KMeansEngine
     from harp_b200.parallel.symm import SymmetricWorkspace
@@ -189,7 +217,7 @@ def main():
     comm = args.comm
     if world > 1 and comm in ("auto", "p2p", "fused"):
         try:
-            symm = SymmetricWorkspace(dev, bytes_=64 << 20)
+            symm = SymmetricWorkspace(dev, bytes_=5 << 29)      # K-means state + NVLink probe + the secondary engines
         except Exception as e:  # noqa: BLE001
             if comm in ("p2p", "fused"):
                 raise
@@ -230,6 +258,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_per_step = float(t.item()) / args.steps
     final_mse = eng.mse()
+    comm_used = eng.comm
 
     # ---------------- end-to-end through the public API ----------------
     e2e = None
@@ -269,9 +298,36 @@ def main():
                        "worker memory); each step copies the centroid model H2D from pinned memory and "
                        "reads new centroids + objective back D2H"}
 
+    nvlink_gbs = measure_nvlink_gbs(symm, dev) if (world > 1 and symm is not None) else None
+
+    # ---------------- library arm (cuBLAS + stock torch ops + NCCL) on the same box, in the same clocks window --------
+    import gc
+    del eng, X
+    gc.collect(); torch.cuda.empty_cache()
+    library = None
+    if not args.no_library_arm:
+        from harp_b200.baseline_arm import measure as measure_library
+        library = measure_library(args, rank, world, dev, ClockSampler, "kmeans", max(10, args.steps), max(3, args.warmup))
+        gc.collect(); torch.cuda.empty_cache()
+
+    # ---------------- the other BASELINE.json metrics, same contract, their own clocks records ----------------
+    secondary = None
+    if not args.no_secondary:
+        from harp_b200.bench_workloads import measure_workload
+        secondary = {}
+        for wl in ("sgd", "lda", "gram"):
+            try:
+                res = measure_workload(wl, max(20, args.secondary_steps), 3, rank, world, dev, symm, ClockSampler)
+            except Exception as e:  # noqa: BLE001  (one workload must not take the headline line down)
+                res = {"error": repr(e)[:300]}
+            if rank == 0:
+                secondary[res.get("metric", wl) if isinstance(res, dict) else wl] = res
+            gc.collect(); torch.cuda.empty_cache()
+
     if rank == 0:
         total_points = n * world
         flops = 2.0 * total_points * k * d
+        lib_value = library.get("value") if isinstance(library, dict) else None
         out = {
             "metric": "kmeans_allreduce_s_per_iter",
             "value": ms_per_step / 1e3,
@@ -282,7 +338,14 @@ def main():
             "ms_per_step": ms_per_step,
             "higher_is_better": False,
             "scaling": "weak",
-            "vs_baseline": None,
+            # BASELINE.md publishes no s/iter figure (time-to-quality on CPU clusters only); the baseline this line is
+            # held against is the cuBLAS + NCCL arm measured above on this box: value / baseline, < 1 means faster
+            "vs_baseline": (ms_per_step / 1e3) / lib_value if lib_value else None,
+            "baseline": {"what": "bench.py's nccl_cublas arm (cuBLAS TF32 GEMM, torch arg-min / index_add, NCCL all_reduce), "
+                                 "same box, same process, same data shape", "value": lib_value,
+                         "speedup": lib_value / (ms_per_step / 1e3) if lib_value else None,
+                         "steps": library.get("steps") if isinstance(library, dict) else None,
+                         "clocks": library.get("clocks") if isinstance(library, dict) else None},
             "dtype": "tf32 (fp32 storage, TF32 tensor-core products, fp32 accumulate)",
             "data": "synthetic uniform[0,1) points, random-init centroids",
             "impl": "harp_b200",
@@ -294,7 +357,7 @@ def main():
                 "dim": d,
                 "centroids": k,
                 "parallelism": f"dp{world}",
-                "comm": eng.comm,
+                "comm": comm_used,
                 "l2": "inputs larger than L2 (6.4 GB of points per GPU re-streamed every step)",
             },
             "points_per_s": total_points / (ms_per_step / 1e3),
@@ -302,8 +365,10 @@ def main():
             "final_mse": final_mse,
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": roofline(flops / world, k * (d + 1) * 4, world, ms_per_step),
+            "roofline": roofline(flops / world, k * (d + 1) * 4, world, ms_per_step, nvlink_gbs),
+            "nvlink_gbs_measured": nvlink_gbs,
             "e2e": e2e,
+            "secondary": secondary,
         }
         print(json.dumps(out))
     if world > 1:

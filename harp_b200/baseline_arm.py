@@ -15,6 +15,17 @@ import torch.distributed as dist
 
 
 def run(args, rank: int, world: int, dev: torch.device, sampler_cls) -> int:
+    out = measure(args, rank, world, dev, sampler_cls, args.workload, args.steps, args.warmup)
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def measure(args, rank: int, world: int, dev: torch.device, sampler_cls, workload: str, steps: int, warmup: int):
+    """Times ``steps`` iterations of the library-only arm; returns the result dict on rank 0 (None elsewhere)."""
     torch.backends.cuda.matmul.allow_tf32 = True
 
     def barrier():
@@ -22,7 +33,7 @@ def run(args, rank: int, world: int, dev: torch.device, sampler_cls) -> int:
             dist.barrier()
         torch.cuda.synchronize()
 
-    if args.workload == "kmeans":
+    if workload == "kmeans":
         n, d, k = args.points_per_gpu, args.dim, args.k
         g = torch.Generator(device=dev).manual_seed(1234 + rank)
         X = torch.rand(n, d, device=dev, generator=g)
@@ -31,12 +42,15 @@ def run(args, rank: int, world: int, dev: torch.device, sampler_cls) -> int:
         sums, counts = acc[: k * d].view(k, d), acc[k * d:]
         ones = torch.ones(n, device=dev)
         best = torch.empty(n, dtype=torch.int64, device=dev)
-        chunk = 262144
+        # 8192 x 10 000 fp32 distances per GEMM: small enough that arg-min reads them back out of L2-sized traffic
+        # instead of streaming a 10 GB block through HBM (the first version of this arm used 262 144 rows)
+        chunk = 8192
 
         def step():
             cn = (C * C).sum(1)
+            Ct = C.t().contiguous()
             for s in range(0, n, chunk):
-                dist2 = torch.addmm(cn[None, :], X[s:s + chunk], C.t(), alpha=-2.0)
+                dist2 = torch.addmm(cn, X[s:s + chunk], Ct, alpha=-2.0)       # 1-D bias: the cuBLASLt epilogue path
                 best[s:s + chunk] = dist2.argmin(1)
             acc.zero_()
             sums.index_add_(0, best, X)
@@ -50,7 +64,7 @@ def run(args, rank: int, world: int, dev: torch.device, sampler_cls) -> int:
                   "global_batch": n * world, "points_per_gpu": n, "dim": d, "centroids": k, "parallelism": f"dp{world}",
                   "comm": "nccl", "l2": "inputs larger than L2"}}
         flops = 2.0 * n * world * k * d
-    elif args.workload == "gram":
+    elif workload == "gram":
         d = 1024
         n = min(50_000_000 // world, 6_250_000)
         X = torch.randn(n, d, device=dev)
@@ -67,11 +81,9 @@ def run(args, rank: int, world: int, dev: torch.device, sampler_cls) -> int:
                              "rows_per_gpu": n, "dim": d, "parallelism": f"dp{world}", "l2": "X exceeds L2"}}
         flops = 2.0 * n * world * d * d
     else:
-        if rank == 0:
-            print(json.dumps({"impl": "nccl_cublas", "unavailable": f"no library-only formulation of workload {args.workload!r}"}))
-        return 0
+        return {"impl": "nccl_cublas", "unavailable": f"no library-only formulation of workload {workload!r}"} if rank == 0 else None
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step()
     barrier()
     sampler = sampler_cls(dev.index) if rank == 0 else None
@@ -80,22 +92,19 @@ def run(args, rank: int, world: int, dev: torch.device, sampler_cls) -> int:
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
-    for _ in range(args.steps):
+    for _ in range(steps):
         step()
     e1.record()
     barrier()
     t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item()) / args.steps
+    ms = float(t.item()) / steps
     clocks = sampler.stop() if sampler else None
     if rank == 0:
-        out = {"impl": "nccl_cublas", "value": ms / 1e3, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        out = {"impl": "nccl_cublas", "value": ms / 1e3, "n_gpus": world, "steps": steps, "warmup": warmup,
                "ms_per_step": ms, "vs_baseline": None, "data": "synthetic", "gpu_launches": 0, "clocks": clocks,
                "tflops_tf32_aggregate": flops / (ms / 1e3) / 1e12}
         out.update(metric)
-        print(json.dumps(out))
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    return 0
+        return out
+    return None

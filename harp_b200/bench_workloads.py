@@ -16,24 +16,53 @@ import torch.distributed as dist
 from . import _native
 
 
-def _finish(args, rank, world, dev, ms_local, out):
+class _Steps:
+    def __init__(self, steps, warmup):
+        self.steps, self.warmup = int(steps), int(warmup)
+
+
+def _finish(args, rank, world, dev, ms_local, out, sampler=None):
     t = torch.tensor([ms_local], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item()) / args.steps
     out.update({"n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "impl": "harp_b200",
-                "data": "synthetic", "vs_baseline": None, "gpu_launches": _native.launches()})
+                "data": "synthetic", "vs_baseline": None, "gpu_launches": _native.launches(),
+                "clocks": sampler.stop() if sampler is not None else None})
     return ms, out
 
 
-def run_workload(args, rank, world, dev):
+def run_workload(args, rank, world, dev, sampler_cls=None):
+    """``bench.py --workload sgd|lda|gram``: measures one workload and prints its JSON line on rank 0."""
     symm = None
     if world > 1:
         from .parallel.symm import SymmetricWorkspace
         try:
-            symm = SymmetricWorkspace(dev, bytes_=1 << 30)
+            symm = SymmetricWorkspace(dev, bytes_=3 << 29)
         except Exception:  # noqa: BLE001
             symm = None
+    out = measure_workload(args.workload, args.steps, args.warmup, rank, world, dev, symm, sampler_cls)
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def measure_workload(workload, steps, warmup, rank, world, dev, symm, sampler_cls=None):
+    """W warm-up steps, then ``steps`` timed steps between barriers + synchronises, CUDA-event time, max over ranks,
+    clocks sampled during the timed region.  Returns the result dict on rank 0 (None elsewhere)."""
+    args = _Steps(steps, warmup)
+    args.workload = workload
+    result = None
+
+    def start_sampler():
+        if sampler_cls is None or rank != 0:
+            return None
+        smp = sampler_cls(dev.index if dev.index is not None else 0)
+        smp.start()
+        return smp
 
     def barrier():
         if world > 1:
@@ -55,19 +84,20 @@ def run_workload(args, rank, world, dev):
             eng.epoch()
         eng.synchronize(); barrier()
         _native.reset_launches()
+        smp = start_sampler()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier(); e0.record()
         for _ in range(args.steps):
             eng.epoch()
-        eng.synchronize(); e1.record(); barrier()
-        ms, out = _finish(args, rank, world, dev, e0.elapsed_time(e1), {})
+        e1.record(); eng.synchronize(); barrier()
+        ms, out = _finish(args, rank, world, dev, e0.elapsed_time(e1), {}, smp)
         if rank == 0:
             out.update({"metric": "mfsgd_updates_per_s", "value": nnz / (ms / 1e3), "unit": "updates/s",
                         "higher_is_better": True, "scaling": "strong", "dtype": "fp32",
                         "config": {"model": "MF-SGD model rotation (BASELINE config 3)", "rows": rows, "cols": cols,
                                    "ratings": nnz, "rank": rk, "parallelism": f"rows dp{world} + H rotation",
                                    "l2": "W (245 MB) + ratings (1.2 GB) exceed L2"}})
-            print(json.dumps(out))
+            result = out
     elif args.workload == "lda":
         from .models.lda import LDAEngine
         D, V, K, L = 1_000_000, 100_000, 1000, 100
@@ -80,19 +110,20 @@ def run_workload(args, rank, world, dev):
             eng.iterate()
         eng.synchronize(); barrier()
         _native.reset_launches()
+        smp = start_sampler()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier(); e0.record()
         for _ in range(args.steps):
             eng.iterate()
-        eng.synchronize(); e1.record(); barrier()
-        ms, out = _finish(args, rank, world, dev, e0.elapsed_time(e1), {})
+        e1.record(); eng.synchronize(); barrier()
+        ms, out = _finish(args, rank, world, dev, e0.elapsed_time(e1), {}, smp)
         if rank == 0:
             out.update({"metric": "lda_cgs_tokens_per_s", "value": D * L / (ms / 1e3), "unit": "tokens/s",
                         "higher_is_better": True, "scaling": "strong", "dtype": "int32 counts / fp32 probabilities",
                         "config": {"model": "LDA-CGS model rotation (BASELINE config 4)", "docs": D, "vocab": V,
                                    "topics": K, "tokens": D * L, "parallelism": f"docs dp{world} + word-topic rotation",
                                    "l2": "doc-topic table (4 GB) exceeds L2"}})
-            print(json.dumps(out))
+            result = out
     else:  # gram
         from .ops.gram import gram, moments
         n, d = 50_000_000 // world, 1024
@@ -127,12 +158,13 @@ def run_workload(args, rank, world, dev):
             step()
         barrier()
         _native.reset_launches()
+        smp = start_sampler()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier(); e0.record()
         for _ in range(args.steps):
             step()
         e1.record(); barrier()
-        ms, out = _finish(args, rank, world, dev, e0.elapsed_time(e1), {})
+        ms, out = _finish(args, rank, world, dev, e0.elapsed_time(e1), {}, smp)
         if rank == 0:
             out.update({"metric": "gram_s_per_pass", "value": ms / 1e3, "unit": "s/pass", "higher_is_better": False,
                         "scaling": "weak", "dtype": "tf32",
@@ -140,8 +172,5 @@ def run_workload(args, rank, world, dev):
                                    "rows_per_gpu": n, "dim": d, "parallelism": f"dp{world}",
                                    "l2": "X (25.6 GB per GPU) exceeds L2"},
                         "tflops_tf32_aggregate": 2.0 * n * world * d * d / (ms / 1e3) / 1e12})
-            print(json.dumps(out))
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    return 0
+            result = out
+    return result
