@@ -42,6 +42,11 @@ int make_tmap_2d_f32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t
                      uint64_t row_stride_bytes, uint32_t box_rows, uint32_t box_cols,
                      CUtensorMapSwizzle swizzle);
 
+// Same for a 2-D row-major tensor of 16-bit elements (fp16 / bf16 bit patterns).
+int make_tmap_2d_u16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+                     uint64_t row_stride_bytes, uint32_t box_rows, uint32_t box_cols,
+                     CUtensorMapSwizzle swizzle);
+
 int sm_count();
 
 #ifdef __CUDACC__
@@ -287,6 +292,21 @@ __device__ __forceinline__ void umma_tf32_2sm(uint32_t tmem_d, uint64_t desc_a, 
       ".reg .pred p;\n"
       "setp.ne.b32 p, %4, 0;\n"
       "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// kind::f16 (fp16 or bf16 inputs, fp32 accumulate): K = 16 per instruction.  fmt: 0 = fp16, 1 = bf16.
+__host__ __device__ constexpr uint32_t umma_idesc_16(uint32_t M, uint32_t N, uint32_t fmt) {
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_f16_2sm(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                             uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
       "}\n" ::"r"(tmem_d),
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");

@@ -22,6 +22,8 @@
 #include "common.cuh"
 #include "../include/harp_b200.h"
 
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <math_constants.h>
 
 #include <mutex>
@@ -127,6 +129,96 @@ __global__ void prep_kernel(const float* __restrict__ C, int k, int d, int kpad,
     for (size_t i = tid; i < (size_t)k; i += nth) counts[i] = 0.f;
     if (tid == 0 && obj != nullptr) *obj = 0.0;
   }
+}
+
+// ----------------------------------------------------------------------------
+// Split-precision operands (PREC = 1 kernels).  tcgen05 has no fp32-input MMA; TF32 keeps 10 mantissa bits of
+// each input, so near-ties between centroids can resolve differently from fp32 arithmetic.  Here every fp32 value
+// v (times a power-of-two `scale` in fp16 mode) is stored as TWO 16-bit numbers hi = rn16(v), lo = rn16(v - hi)
+// and the distance GEMM is evaluated as hi·hi + lo·hi + hi·lo with kind::f16 MMAs (fp32 accumulate): with fp16
+// halves (11 + 11 mantissa bits, values scaled into fp16's range) the dropped lo·lo term is ~2^-22 relative, i.e.
+// fp32-faithful products at 1.5x the tensor time of TF32 (kind::f16 runs at twice the kind::tf32 rate); bf16
+// halves (8 + 8 bits, no scaling needed) give ~2^-16.
+// Row layout: [hi_0 .. hi_{dp-1} | lo_0 .. lo_{dp-1}] 16-bit, dp = d rounded up to 64 — for d = 128 a row is 512
+// bytes, the same as the fp32 row, and the hi / lo halves are 128-byte K-chunks for TMA + SWIZZLE_128B.
+// ----------------------------------------------------------------------------
+__host__ __device__ constexpr int split_dp(int d) { return (d + 63) / 64 * 64; }
+
+__device__ __forceinline__ unsigned short cvt16(float v, int fmt16) {
+  if (fmt16 == 0) return __half_as_ushort(__float2half_rn(v));
+  return __bfloat16_as_ushort(__float2bfloat16_rn(v));
+}
+__device__ __forceinline__ float back16(unsigned short h, int fmt16) {
+  if (fmt16 == 0) return __half2float(__ushort_as_half(h));
+  return __bfloat162float(__ushort_as_bfloat16(h));
+}
+__device__ __forceinline__ void split16(float v, int fmt16, unsigned short& hi, unsigned short& lo) {
+  hi = cvt16(v, fmt16);
+  lo = cvt16(v - back16(hi, fmt16), fmt16);
+}
+
+// rows of X (or C) -> split rows; one thread per 4 consecutive elements
+__global__ void split_rows_kernel(const float* __restrict__ X, long long n, int d, float scale, int fmt16,
+                                  unsigned short* __restrict__ Xs) {
+  const int dp = split_dp(d), q4 = dp >> 2;
+  const long long total = n * q4;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / q4;
+    const int c = (int)(i % q4) * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < d) v = *reinterpret_cast<const float4*>(X + (size_t)row * d + c);      // d % 4 == 0
+    unsigned short h[4], l[4];
+    split16(v.x * scale, fmt16, h[0], l[0]); split16(v.y * scale, fmt16, h[1], l[1]);
+    split16(v.z * scale, fmt16, h[2], l[2]); split16(v.w * scale, fmt16, h[3], l[3]);
+    unsigned short* dst = Xs + (size_t)row * 2 * dp + c;
+    *reinterpret_cast<uint2*>(dst) = make_uint2(h[0] | ((uint32_t)h[1] << 16), h[2] | ((uint32_t)h[3] << 16));
+    *reinterpret_cast<uint2*>(dst + dp) = make_uint2(l[0] | ((uint32_t)l[1] << 16), l[2] | ((uint32_t)l[3] << 16));
+  }
+}
+
+// -(scale^2)‖c‖²/2 as three bf16 terms in a 32-byte operand row (one K = 16 step of kind::f16 with bf16 inputs)
+__device__ __forceinline__ void bias_row_bf16(float t0, uint32_t (&w)[2]) {
+  const __nv_bfloat16 hi = __float2bfloat16_rn(t0);
+  const float r1 = t0 - __bfloat162float(hi);
+  const __nv_bfloat16 mid = __float2bfloat16_rn(r1);
+  const __nv_bfloat16 lo = __float2bfloat16_rn(r1 - __bfloat162float(mid));
+  w[0] = (uint32_t)__bfloat16_as_ushort(hi) | ((uint32_t)__bfloat16_as_ushort(mid) << 16);
+  w[1] = (uint32_t)__bfloat16_as_ushort(lo);
+}
+
+// split-mode counterpart of prep_kernel's operand part: Cs rows, bias rows (kpad x 8 words), the ones tile
+__global__ void prep_split_kernel(const float* __restrict__ C, int k, int d, int kpad, float scale, int fmt16,
+                                  unsigned short* __restrict__ Cs, uint32_t* __restrict__ ext, uint32_t* __restrict__ ones) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  const int dp = split_dp(d);
+  for (int j = warp; j < kpad; j += nwarps) {
+    float s = 0.f;
+    if (j < k) {
+      const float4* row4 = reinterpret_cast<const float4*>(C + (size_t)j * d);
+      for (int c4 = lane; c4 < (dp >> 2); c4 += 32) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c4 < (d >> 2)) v = row4[c4];
+        s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
+        unsigned short h[4], l[4];
+        split16(v.x * scale, fmt16, h[0], l[0]); split16(v.y * scale, fmt16, h[1], l[1]);
+        split16(v.z * scale, fmt16, h[2], l[2]); split16(v.w * scale, fmt16, h[3], l[3]);
+        unsigned short* dst = Cs + (size_t)j * 2 * dp + c4 * 4;
+        *reinterpret_cast<uint2*>(dst) = make_uint2(h[0] | ((uint32_t)h[1] << 16), h[2] | ((uint32_t)h[3] << 16));
+        *reinterpret_cast<uint2*>(dst + dp) = make_uint2(l[0] | ((uint32_t)l[1] << 16), l[2] | ((uint32_t)l[3] << 16));
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    }
+    if (lane < 8) {
+      uint32_t w[2];
+      bias_row_bf16(j < k ? -0.5f * s * scale * scale : -3.0e38f, w);
+      ext[(size_t)j * 8 + lane] = lane < 2 ? w[lane] : 0u;
+    }
+  }
+  const int tid0 = blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid0 < 128 * 8) ones[tid0] = (tid0 & 7) == 0 ? 0x3F803F80u : ((tid0 & 7) == 1 ? 0x00003F80u : 0u);   // bf16 [1,1,1,0..]
 }
 
 // Running arg-min over 32 accumulator columns held in registers.  d = ‖c‖² - 2·x·c.
@@ -462,6 +554,29 @@ __device__ __forceinline__ float packed_max32(const uint32_t (&v)[32]) {
   return key[0];
 }
 
+// Exact arg-max over 32 accumulator columns for the split-precision kernels: the packed form above overwrites the
+// low mantissa byte (a 2^-15 relative perturbation, more than the split products' own error), so here the maximum
+// is taken on the untouched values and the column is looked up only when a lane's running best improves — about
+// ln(k) times per point, so the branch is cold.
+__device__ __forceinline__ void exact_max32(const uint32_t (&v)[32], int cbase, float& bestx, int& bi) {
+  float t[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) t[j] = fmaxf(__uint_as_float(v[j]), __uint_as_float(v[j + 16]));
+#pragma unroll
+  for (int w = 8; w > 0; w >>= 1) {
+#pragma unroll
+    for (int j = 0; j < w; ++j) t[j] = fmaxf(t[j], t[j + w]);
+  }
+  const float m = t[0];
+  if (m > bestx) {
+    bestx = m;
+    int idx = 31;
+#pragma unroll
+    for (int j = 30; j >= 0; --j) idx = (__uint_as_float(v[j]) == m) ? j : idx;      // lowest column wins ties
+    bi = cbase + idx;
+  }
+}
+
 // ----------------------------------------------------------------------------
 // Fused iteration (FUSED = 1): the same launch that computes distances / arg-min /
 // partial sums also performs Harp's regroup -> centroid update -> allgather
@@ -498,6 +613,9 @@ struct FusedArgs {
   uint32_t epoch;
   int keep_empty;
   unsigned long long off_ext[2], off_c[2], off_acc[2];
+  unsigned long long off_cs[2];  // split-precision centroid rows (PREC = 1)
+  float scale;                   // power of two applied to X and C before the 16-bit split (1 for bf16)
+  int fmt16;                     // 0 = fp16 halves, 1 = bf16 halves
 };
 
 __device__ __forceinline__ void spin_until(const uint32_t* p, uint32_t target, bool sys, const char* what) {
@@ -510,6 +628,7 @@ __device__ __forceinline__ void spin_until(const uint32_t* p, uint32_t target, b
   }
 }
 
+template <int PREC>
 __device__ __noinline__ void fused_tail(const FusedArgs& fa, int k, int d, uint32_t* smem_flag) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nwarps_cta = blockDim.x >> 5;
@@ -596,6 +715,20 @@ __device__ __noinline__ void fused_tail(const FusedArgs& fa, int k, int d, uint3
         else c = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int p = 0; p < world; ++p)
           *reinterpret_cast<float4*>(fa.peer[(fa.rank + p) % world] + fa.off_c[nxt] + eoff) = c;
+        if (PREC == 1) {       // the next iteration's GEMM operand: the row split into 16-bit halves
+          const int dp = split_dp(d);
+          unsigned short h[4], l[4];
+          split16(c.x * fa.scale, fa.fmt16, h[0], l[0]); split16(c.y * fa.scale, fa.fmt16, h[1], l[1]);
+          split16(c.z * fa.scale, fa.fmt16, h[2], l[2]); split16(c.w * fa.scale, fa.fmt16, h[3], l[3]);
+          const uint2 hv = make_uint2(h[0] | ((uint32_t)h[1] << 16), h[2] | ((uint32_t)h[3] << 16));
+          const uint2 lv = make_uint2(l[0] | ((uint32_t)l[1] << 16), l[2] | ((uint32_t)l[3] << 16));
+          const size_t soff = ((size_t)(rowb + u) * 2 * dp + c4 * 4) * sizeof(unsigned short);
+          for (int p = 0; p < world; ++p) {
+            uint8_t* dst = fa.peer[(fa.rank + p) % world] + fa.off_cs[nxt] + soff;
+            *reinterpret_cast<uint2*>(dst) = hv;
+            *reinterpret_cast<uint2*>(dst + dp * sizeof(unsigned short)) = lv;
+          }
+        }
         sq[u] = fmaf(c.x, c.x, sq[u]); sq[u] = fmaf(c.y, c.y, sq[u]); sq[u] = fmaf(c.z, c.z, sq[u]); sq[u] = fmaf(c.w, c.w, sq[u]);
       }
     }
@@ -605,11 +738,18 @@ __device__ __noinline__ void fused_tail(const FusedArgs& fa, int k, int d, uint3
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) sv += __shfl_xor_sync(0xffffffffu, sv, o);
       if (lane < 8 && rowb + u < r1) {
-        const float t0 = -0.5f * sv;
-        const float hi = tf32_trunc(t0);
-        const float mid = tf32_trunc(t0 - hi);
-        const float lo = tf32_trunc(t0 - hi - mid);
-        const float v = lane == 0 ? hi : (lane == 1 ? mid : (lane == 2 ? lo : 0.f));
+        float v;
+        if (PREC == 1) {
+          uint32_t w[2];
+          bias_row_bf16(-0.5f * sv * fa.scale * fa.scale, w);
+          v = __uint_as_float(lane < 2 ? w[lane] : 0u);
+        } else {
+          const float t0 = -0.5f * sv;
+          const float hi = tf32_trunc(t0);
+          const float mid = tf32_trunc(t0 - hi);
+          const float lo = tf32_trunc(t0 - hi - mid);
+          v = lane == 0 ? hi : (lane == 1 ? mid : (lane == 2 ? lo : 0.f));
+        }
         for (int p = 0; p < world; ++p)
           *reinterpret_cast<float*>(fa.peer[(fa.rank + p) % world] + fa.off_ext[nxt] + ((size_t)(rowb + u) * 8 + lane) * sizeof(float)) = v;
       }
@@ -657,7 +797,7 @@ __device__ __noinline__ void fused_tail(const FusedArgs& fa, int k, int d, uint3
   }
 }
 
-template <int DBG, int EXT, int FUSED = 0>
+template <int DBG, int EXT, int FUSED = 0, int PREC = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(pair::NTHREADS2, 1)
 assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_c,
                       const __grid_constant__ CUtensorMap tmap_ones, const __grid_constant__ CUtensorMap tmap_cext,
@@ -681,7 +821,11 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
   const int lane = threadIdx.x & 31;
   const uint32_t cta = cluster_ctarank();           // 0 = leader
   const bool leader = (cta == 0);
-  const int kch = (d + BK - 1) / BK;
+  // K-chunks (one 128-byte swizzle row each) of a point tile / per centroid tile: fp32 -> d / 32 chunks of 32
+  // floats; split precision -> hi chunks then lo chunks of 64 halves
+  const int dh = (d + 63) / 64;
+  const int kch = PREC == 1 ? 2 * dh : (d + BK - 1) / BK;
+  const int bke = PREC == 1 ? 64 : BK;                      // elements per chunk (TMA coordinate step)
   const int nct = kpad / BN;
   const long long npairs = (n + 2 * BM - 1) / (2 * BM);   // pair-tiles of 256 points
   const long long cluster_id = blockIdx.x >> 1;
@@ -736,7 +880,7 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
         const int32_t row0 = (int32_t)(tp * 2 * BM + cta * BM);
         for (int kc = 0; kc < kch; ++kc)
           tma_load_2d_2sm(base + Smem::x + xb * X_TILE_BYTES + kc * X_CHUNK_BYTES, &tmap_x,
-                          bar(X_FULL + xb) & kPeerBitMask, kc * BK, row0, pol_stream);
+                          bar(X_FULL + xb) & kPeerBitMask, kc * bke, row0, pol_stream);
         for (int ct = 0; ct < nct; ++ct, ++ga) {
           // ‖c‖² tile -> its own 8-deep ring: with only as many slots as accumulators this
           // prefetch would be gated on the epilogue of tile ct-2 and epilogue + TMA latency
@@ -760,7 +904,7 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
             mbar_wait(bar(B_EMPTY + s), ph ^ 1);
             if (leader) mbar_expect_tx(bar(B_FULL + s), 2 * B_HALF_BYTES);
             tma_load_2d_2sm(base + Smem::b + s * B_HALF_BYTES, &tmap_c, bar(B_FULL + s) & kPeerBitMask,
-                            kc * BK, ct * BN + (int)cta * BH, pol_keep);
+                            kc * bke, ct * BN + (int)cta * BH, pol_keep);
           }
         }
       }
@@ -773,6 +917,8 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
     // on the epilogue -> issuer -> tensor pipe -> epilogue chain, so every instruction counts.
     if (leader) {
       const uint32_t idesc = umma_idesc_tf32(2 * BM, BN);
+      const uint32_t idesc16 = umma_idesc_16(2 * BM, BN, (uint32_t)fa.fmt16);      // split halves: fp16 or bf16
+      const uint32_t idesc_b16 = umma_idesc_16(2 * BM, BN, 1u);                    // bias step: always bf16
       const uint64_t dhi = umma_desc_kmajor_sw128(0);          // address-free part of the descriptor
       uint32_t it = 0, ga = 0, gp = 0;
       long long prof_issue = 0, prof_n = 0;
@@ -791,8 +937,30 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
             const uint32_t s = it % NSTAGE2, ph = (it / NSTAGE2) & 1;
             mbar_wait(bar(B_FULL + s), ph);
             tc_fence_after();
-            const uint64_t da0 = dhi | (((base + Smem::x + xb * X_TILE_BYTES + kc * X_CHUNK_BYTES) & 0x3FFFFu) >> 4);
             const uint64_t db0 = dhi | (((base + Smem::b + s * B_HALF_BYTES) & 0x3FFFFu) >> 4);
+            if (PREC == 1) {
+              // stage kc holds B chunk kc: hi half (kc < dh) meets A hi AND A lo, lo half meets A hi only:
+              // x·c ~ hi·hi + lo·hi + hi·lo, 4 K=16 steps per 64-element chunk
+              const int hb = kc < dh ? kc : kc - dh;
+              const uint64_t da_hi = dhi | (((base + Smem::x + xb * X_TILE_BYTES + hb * X_CHUNK_BYTES) & 0x3FFFFu) >> 4);
+              const uint64_t da_lo = dhi | (((base + Smem::x + xb * X_TILE_BYTES + (dh + hb) * X_CHUNK_BYTES) & 0x3FFFFu) >> 4);
+              int ksteps = (d - hb * 64 + 15) / 16;
+              if (ksteps > 4) ksteps = 4;
+              if (elect_one()) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  if (j < ksteps) umma_f16_2sm(tmem_d, da_hi + (uint64_t)(2 * j), db0 + (uint64_t)(2 * j), idesc16, (kc | j) != 0 ? 1u : 0u);
+                if (kc < dh) {
+#pragma unroll
+                  for (int j = 0; j < 4; ++j)
+                    if (j < ksteps) umma_f16_2sm(tmem_d, da_lo + (uint64_t)(2 * j), db0 + (uint64_t)(2 * j), idesc16, 1u);
+                }
+                umma_commit_2sm_mc(bar(B_EMPTY + s), 0x3);
+              }
+              __syncwarp();
+              continue;
+            }
+            const uint64_t da0 = dhi | (((base + Smem::x + xb * X_TILE_BYTES + kc * X_CHUNK_BYTES) & 0x3FFFFu) >> 4);
             int ksteps = (d - kc * BK + UK - 1) / UK;
             if (ksteps > BK / UK) ksteps = BK / UK;
             if (elect_one()) {
@@ -810,6 +978,10 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
             mbar_wait(bar(CN_FULL + es), eph);
             tc_fence_after();
             if (elect_one()) {
+              if (PREC == 1)
+                umma_f16_2sm(tmem_d, umma_desc_kmajor_sw32(base + Smem::aext),
+                             umma_desc_kmajor_sw32(base + Smem::bext + es * EXT_BYTES), idesc_b16, 1u);
+              else
               umma_tf32_2sm(tmem_d, umma_desc_kmajor_sw32(base + Smem::aext),
                             umma_desc_kmajor_sw32(base + Smem::bext + es * EXT_BYTES), idesc, 1u);
               umma_commit_2sm_mc(bar(CN_EMPTY + es), 0x3);
@@ -886,7 +1058,9 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
             tmem_ld_wait_regs(va);
             tmem_ld_32x32(taddr + (c + 1) * 32, vb);
             if (dbg & 2) { best = fminf(best, __uint_as_float(va[0]) + __uint_as_float(va[31])); } else
-            if (EXT) {
+            if (PREC == 1) {
+              exact_max32(va, tbase + c * 32, bestx, bi);
+            } else if (EXT) {
               const float m = packed_max32(va);
               const bool gt = m > bestx;
               bestx = gt ? m : bestx;
@@ -906,7 +1080,9 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
               if (lane == 0) mbar_arrive_cluster(bar(T_EMPTY + a), 0);
             }
             if (dbg & 2) { best = fminf(best, __uint_as_float(vb[0]) + __uint_as_float(vb[31])); } else
-            if (EXT) {
+            if (PREC == 1) {
+              exact_max32(vb, tbase + (c + 1) * 32, bestx, bi);
+            } else if (EXT) {
               const float m = packed_max32(vb);
               const bool gt = m > bestx;
               bestx = gt ? m : bestx;
@@ -931,7 +1107,8 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
         if (dbg & 16) { prof_work += clock64() - tw0; ++prof_n; }
       }
       // unpack the in-chunk column, then merge the two column halves of each row through smem
-      if (EXT) { bi += (int)(__float_as_uint(bestx) & 255u); best = -bestx; }
+      if (PREC == 1) best = -bestx;       // exact arg-max: bi is already the full index
+      else if (EXT) { bi += (int)(__float_as_uint(bestx) & 255u); best = -bestx; }
       else bi += (int)(__float_as_uint(best) & 255u);
       // (512 B of smem: best goes over first, then the index, then the verdict comes back)
       const int slot = q * 32 + lane;
@@ -969,7 +1146,7 @@ assign_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_c
   tc_fence_before();
   cluster_sync_all();            // nobody leaves while the peer may still touch its smem / TMEM / barriers
   if (warp == MMA_WARP) tmem_dealloc_2sm(tmem_base, TMEM_COLS);
-  if (FUSED) fused_tail(fa, k, d, reinterpret_cast<uint32_t*>(smem_raw + Smem::merge));
+  if (FUSED) fused_tail<PREC>(fa, k, d, reinterpret_cast<uint32_t*>(smem_raw + Smem::merge));
 }
 
 // ----------------------------------------------------------------------------
@@ -1129,6 +1306,7 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
         if (make_tmap_2d_f32(&tcext, cn_ext, (uint64_t)kpad, 8, 32, BN / 2, 8, CU_TENSOR_MAP_SWIZZLE_32B) != 0) return -3;
       }
       auto kern = ext128 ? assign_tc_pair_kernel<0, 2> : (ext ? assign_tc_pair_kernel<0, 1> : assign_tc_pair_kernel<0, 0>);
+#ifdef HB_DEBUG_KERNELS       // triage variants (masked epilogues, per-role cycle counters): not in the product build
       if (dbg == 1) kern = assign_tc_pair_kernel<1, 0>;
       else if (dbg == 2) kern = assign_tc_pair_kernel<2, 0>;
       else if (dbg == 4) kern = ext ? assign_tc_pair_kernel<4, 1> : assign_tc_pair_kernel<4, 0>;
@@ -1136,6 +1314,9 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
       else if (dbg == 36) kern = assign_tc_pair_kernel<36, 1>;
       else if (dbg == 68) kern = assign_tc_pair_kernel<68, 1>;
       else if (dbg == 16) kern = ext128 ? assign_tc_pair_kernel<16, 2> : (ext ? assign_tc_pair_kernel<16, 1> : assign_tc_pair_kernel<16, 0>);
+#else
+      HB_REQUIRE(dbg == 0, "hb_kmeans_step: debug kernel variant %d needs a build with -DHB_DEBUG_KERNELS", dbg);
+#endif
       HB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::Smem::total));
       const long long npairs = (n + 2 * BM - 1) / (2 * BM);
       long long nclusters = sm_count() / 2;
@@ -1150,12 +1331,8 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
           tx, tch, tones, tcext, X, C, cn, n, d, k, kpad, sums, counts, assign, obj, nofuse);
       HB_CUDA_OK(cudaGetLastError());
     } else {
-      static bool attr_set[64] = {false};
-      if (dev < 64 && !attr_set[dev]) {
-        HB_CUDA_OK(cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        SMEM_BYTES));
-        attr_set[dev] = true;
-      }
+      // (cheap and idempotent: set on every call rather than cached in an unsynchronised host static)
+      HB_CUDA_OK(cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
       int grid = sm_count();
       if ((long long)grid > ntiles) grid = (int)ntiles;
       assign_tc_kernel<<<grid, NTHREADS, SMEM_BYTES, stream>>>(tx, tc, X, C, cn, n, d, k, kpad, sums,
@@ -1191,7 +1368,7 @@ int hb_kmeans_step(const float* X, long long n, int d, const float* C, int k, fl
 
 // ---- fused iteration: distance GEMM + arg-min + partial sums + regroup/update/allgather in one launch ----
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-struct FusedLayout { size_t ones, ext[2], c[2], acc[2], total; };
+struct FusedLayout { size_t ones, ext[2], c[2], acc[2], cs[2], total; };
 static FusedLayout fused_layout(int k, int d) {
   const size_t kpad = ((size_t)k + BN - 1) / BN * BN;
   FusedLayout L;
@@ -1200,6 +1377,7 @@ static FusedLayout fused_layout(int k, int d) {
   for (int i = 0; i < 2; ++i) { L.ext[i] = o; o = align_up(o + kpad * 8 * sizeof(float), 256); }
   for (int i = 0; i < 2; ++i) { L.c[i] = o; o = align_up(o + (size_t)k * d * sizeof(float), 256); }
   for (int i = 0; i < 2; ++i) { L.acc[i] = o; o = align_up(o + ((size_t)k * d + k + 3) / 4 * 16, 256); }
+  for (int i = 0; i < 2; ++i) { L.cs[i] = o; o = align_up(o + (size_t)k * 2 * split_dp(d) * sizeof(unsigned short), 256); }
   L.total = o;
   return L;
 }
@@ -1210,6 +1388,46 @@ int hb_kmeans_fused_offsets(int k, int d, unsigned long long* out8) {
   const FusedLayout L = fused_layout(k, d);
   out8[0] = L.c[0]; out8[1] = L.c[1]; out8[2] = L.acc[0]; out8[3] = L.acc[1];
   out8[4] = offsetof(FusedCtl, obj); out8[5] = offsetof(FusedCtl, obj_total); out8[6] = L.ext[0]; out8[7] = L.ext[1];
+  return 0;
+}
+
+// Split-precision helpers.  prec: 0 = TF32 products (default), 1 = fp16 halves (values scaled by `scale`, a power of
+// two that brings max |x| near 2^14), 2 = bf16 halves (scale 1).
+size_t hb_kmeans_split_row_bytes(int d) { return (size_t)2 * split_dp(d) * sizeof(unsigned short); }
+
+int hb_kmeans_split_rows(const float* X, long long n, int d, float scale, int prec, void* Xs, void* stream_) {
+  HB_REQUIRE(prec == 1 || prec == 2, "hb_kmeans_split_rows: prec must be 1 (fp16 halves) or 2 (bf16 halves)");
+  HB_REQUIRE(d >= 4 && d % 4 == 0 && d <= BK * MAX_KCH, "hb_kmeans_split_rows: need d %% 4 == 0 and d <= 128 (got %d)", d);
+  HB_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0 && (reinterpret_cast<uintptr_t>(Xs) & 15) == 0, "hb_kmeans_split_rows: pointers must be 16-byte aligned");
+  if (n == 0) return 0;
+  long long blocks = (n * (split_dp(d) / 4) + 255) / 256;
+  const long long cap = (long long)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  split_rows_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream_>>>(X, n, d, scale, prec == 1 ? 0 : 1,
+                                                                         reinterpret_cast<unsigned short*>(Xs));
+  HB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int hb_kmeans_fused_prep(void* state, int k, int d, int parity, void* stream_);
+
+// (Re)computes the operands of centroid buffer `parity` for precision mode `prec`.
+int hb_kmeans_fused_prep2(void* state, int k, int d, int parity, int prec, float scale, void* stream_) {
+  if (prec == 0) return hb_kmeans_fused_prep(state, k, d, parity, stream_);
+  cudaStream_t stream = (cudaStream_t)stream_;
+  HB_REQUIRE(state != nullptr && (parity == 0 || parity == 1) && (prec == 1 || prec == 2), "hb_kmeans_fused_prep2: bad arguments");
+  const FusedLayout L = fused_layout(k, d);
+  const int kpad = (k + BN - 1) / BN * BN;
+  uint8_t* st = reinterpret_cast<uint8_t*>(state);
+  const int threads = 256;
+  int blocks = (kpad * 32 + threads - 1) / threads;
+  const int cap = sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  prep_split_kernel<<<blocks, threads, 0, stream>>>(reinterpret_cast<const float*>(st + L.c[parity]), k, d, kpad, scale,
+                                                    prec == 1 ? 0 : 1, reinterpret_cast<unsigned short*>(st + L.cs[parity]),
+                                                    reinterpret_cast<uint32_t*>(st + L.ext[parity]),
+                                                    reinterpret_cast<uint32_t*>(st + L.ones));
+  HB_CUDA_OK(cudaGetLastError());
   return 0;
 }
 
@@ -1247,9 +1465,21 @@ int hb_kmeans_fused_init(void* state, int k, int d, const float* C0, void* strea
   return hb_kmeans_fused_prep(state, k, d, 0, stream_);
 }
 
+int hb_kmeans_fused_step2(const float* X, const void* Xs, long long n, int d, int k, void* const* peer_state, int rank,
+                          int world, unsigned epoch, int keep_empty, int* assign, int prec, float scale, void* stream_);
+
 int hb_kmeans_fused_step(const float* X, long long n, int d, int k, void* const* peer_state, int rank, int world,
                          unsigned epoch, int keep_empty, int* assign, void* stream_) {
+  return hb_kmeans_fused_step2(X, nullptr, n, d, k, peer_state, rank, world, epoch, keep_empty, assign, 0, 1.0f, stream_);
+}
+
+// Xs: the points as split rows (hb_kmeans_split_rows) when prec != 0; X (fp32) is always needed: the partial sums and
+// the objective are accumulated from the exact values.
+int hb_kmeans_fused_step2(const float* X, const void* Xs, long long n, int d, int k, void* const* peer_state, int rank,
+                          int world, unsigned epoch, int keep_empty, int* assign, int prec, float scale, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
+  HB_REQUIRE(prec >= 0 && prec <= 2, "hb_kmeans_fused_step2: prec must be 0 (tf32), 1 (fp16 halves) or 2 (bf16 halves)");
+  HB_REQUIRE(prec == 0 || n == 0 || (Xs != nullptr && (reinterpret_cast<uintptr_t>(Xs) & 15) == 0), "hb_kmeans_fused_step2: split rows missing or misaligned");
   HB_REQUIRE(world >= 1 && world <= HB_MAX_RANKS && rank >= 0 && rank < world, "hb_kmeans_fused_step: bad rank %d / world %d", rank, world);
   HB_REQUIRE(n >= 0 && k >= 1 && hb_kmeans_tc_supported(d, k), "hb_kmeans_fused_step: shape (n=%lld, k=%d, d=%d) not supported", n, k, d);
   HB_REQUIRE(n == 0 || (X != nullptr && (reinterpret_cast<uintptr_t>(X) & 15) == 0), "hb_kmeans_fused_step: X must be 16-byte aligned");
@@ -1263,7 +1493,8 @@ int hb_kmeans_fused_step(const float* X, long long n, int d, int k, void* const*
     fa.peer[i] = reinterpret_cast<uint8_t*>(peer_state[i]);
   }
   fa.rank = rank; fa.world = world; fa.epoch = epoch; fa.keep_empty = keep_empty;
-  for (int i = 0; i < 2; ++i) { fa.off_ext[i] = L.ext[i]; fa.off_c[i] = L.c[i]; fa.off_acc[i] = L.acc[i]; }
+  fa.scale = prec == 1 ? scale : 1.0f; fa.fmt16 = prec == 2 ? 1 : 0;
+  for (int i = 0; i < 2; ++i) { fa.off_ext[i] = L.ext[i]; fa.off_c[i] = L.c[i]; fa.off_acc[i] = L.acc[i]; fa.off_cs[i] = L.cs[i]; }
   uint8_t* me = fa.peer[rank];
   const float* C = reinterpret_cast<const float*>(me + L.c[cur]);
   float* sums = reinterpret_cast<float*>(me + L.acc[cur]);
@@ -1273,12 +1504,22 @@ int hb_kmeans_fused_step(const float* X, long long n, int d, int k, void* const*
   // a rank without points still takes part in the collective tail; its X map is never dereferenced
   const float* Xm = n > 0 ? X : C;
   const uint64_t nm = n > 0 ? (uint64_t)n : (uint64_t)k;
-  if (make_tmap_2d_f32(&tx, Xm, nm, (uint64_t)d, (uint64_t)d * 4, BM, BK, CU_TENSOR_MAP_SWIZZLE_128B) != 0) return -3;
-  if (make_tmap_2d_f32(&tch, C, (uint64_t)k, (uint64_t)d, (uint64_t)d * 4, BN / 2, BK, CU_TENSOR_MAP_SWIZZLE_128B) != 0) return -3;
+  if (prec == 0) {
+    if (make_tmap_2d_f32(&tx, Xm, nm, (uint64_t)d, (uint64_t)d * 4, BM, BK, CU_TENSOR_MAP_SWIZZLE_128B) != 0) return -3;
+    if (make_tmap_2d_f32(&tch, C, (uint64_t)k, (uint64_t)d, (uint64_t)d * 4, BN / 2, BK, CU_TENSOR_MAP_SWIZZLE_128B) != 0) return -3;
+  } else {
+    // split rows: 2 * dp 16-bit columns, boxes of 64 columns (128 bytes) x 128 rows
+    const uint64_t cols = (uint64_t)2 * split_dp(d);
+    const void* Xsm = n > 0 ? Xs : (const void*)(me + L.cs[cur]);
+    if (make_tmap_2d_u16(&tx, Xsm, nm, cols, cols * 2, BM, 64, CU_TENSOR_MAP_SWIZZLE_128B) != 0) return -3;
+    if (make_tmap_2d_u16(&tch, me + L.cs[cur], (uint64_t)k, cols, cols * 2, BN / 2, 64, CU_TENSOR_MAP_SWIZZLE_128B) != 0) return -3;
+  }
   if (make_tmap_2d_f32(&tones, me + L.ones, 128, 8, 32, 128, 8, CU_TENSOR_MAP_SWIZZLE_32B) != 0) return -3;
   if (make_tmap_2d_f32(&tcext, me + L.ext[cur], (uint64_t)kpad, 8, 32, BN / 2, 8, CU_TENSOR_MAP_SWIZZLE_32B) != 0) return -3;
-  auto kern = assign_tc_pair_kernel<0, 1, 1>;
+  auto kern = prec == 0 ? assign_tc_pair_kernel<0, 1, 1, 0> : assign_tc_pair_kernel<0, 1, 1, 1>;
+#ifdef HB_DEBUG_KERNELS
   if (const char* e = getenv("HB_FUSED_DBG")) { if (atoi(e) == 16) kern = assign_tc_pair_kernel<16, 1, 1>; else if (atoi(e) == 4) kern = assign_tc_pair_kernel<4, 1, 1>; }   // triage knob
+#endif
   HB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::Smem::total));
   const long long npairs = (n + 2 * BM - 1) / (2 * BM);
   long long nclusters = sm_count() / 2;
@@ -1295,7 +1536,7 @@ int hb_kmeans_fused_step(const float* X, long long n, int d, int k, void* const*
   attr[0].id = cudaLaunchAttributeCooperative;
   attr[0].val.cooperative = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = getenv("HB_FUSED_NO_COOP") ? 0 : 1;      // triage knob
+  cfg.numAttrs = 1;
   HB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tx, tch, tones, tcext, Xm, C, (const float*)nullptr, n, d, k, kpad, sums, counts,
                                 assign, obj, fa));
   return 0;
@@ -1394,6 +1635,12 @@ extern "C" int hb_kmeans_step_static(const float* X, long long n, int d, const f
              "hb_kmeans_step_static: d=%d is not handled without caller scratch "
              "(needs d %% 4 == 0 and d <= 128); use hb_kmeans_step",
              d);
+  // hb_kmeans_step would quietly take its SIMT branch for misaligned pointers and then complain about a workspace this
+  // caller never supplied: say what is actually wrong, before anything is queued
+  HB_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
+                 (reinterpret_cast<uintptr_t>(sums) & 15) == 0,
+             "hb_kmeans_step_static: X, C and sums must be 16-byte aligned (the tensor-core path is the only one "
+             "that runs without caller scratch)");
   const size_t bytes = hb::kmeans::STATIC_SCRATCH_FLOATS * sizeof(float);
   HB_REQUIRE(hb_kmeans_min_workspace_bytes(k, d) <= bytes,
              "hb_kmeans_step_static: internal scratch too small for k=%d", k);

@@ -57,6 +57,25 @@ int make_tmap_2d_f32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t
   return 0;
 }
 
+int make_tmap_2d_u16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+                     uint64_t row_stride_bytes, uint32_t box_rows, uint32_t box_cols,
+                     CUtensorMapSwizzle swizzle) {
+  EncodeTiledFn fn = encode_fn();
+  HB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  HB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
+  HB_REQUIRE((row_stride_bytes & 15) == 0, "TMA row stride must be a multiple of 16 bytes (got %llu)",
+             (unsigned long long)row_stride_bytes);
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {row_stride_bytes};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(base), gdim, gstride,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  HB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (16-bit) failed with CUresult %d", (int)r);
+  return 0;
+}
+
 int sm_count() {
   static int cached[64] = {0};
   int dev = 0;

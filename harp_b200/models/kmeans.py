@@ -19,6 +19,7 @@ Reference semantics kept: an empty cluster collapses to the zero vector
 """
 from __future__ import annotations
 
+import math
 import os
 from typing import Optional
 
@@ -30,7 +31,7 @@ from ..ops import kmeans as kops
 
 class KMeansEngine:
     def __init__(self, X: torch.Tensor, k: int, *, comm: str = "auto", group=None,
-                 keep_empty: bool = False, symm=None):
+                 keep_empty: bool = False, symm=None, precision: Optional[str] = None):
         assert X.dim() == 2
         self.X = X.contiguous() if X.device.type == "cuda" else X
         self.n, self.d = X.shape
@@ -49,6 +50,13 @@ class KMeansEngine:
             comm = "fused" if fused_ok else ("p2p" if (symm is not None and self.world > 1) else "nccl")
         self.comm = comm
         self.fused = None
+        # Products of the distance GEMM (fused kernel only): "tf32" = fp32 inputs truncated to 10 mantissa bits by the
+        # tensor core; "fp16x3" / "bf16x3" = every value split into two 16-bit halves and three MMAs per product
+        # (fp32-faithful with fp16 halves, see csrc/kmeans.cu).  HB_KMEANS_PRECISION overrides the default.
+        self.precision = precision or os.environ.get("HB_KMEANS_PRECISION", "tf32")
+        if self.comm != "fused":
+            self.precision = "tf32" if self.dev.type == "cuda" else "exact"
+        self.Xs = None
         if self.comm == "fused":
             nbytes = kops.FusedKMeans.state_bytes(k, d)
             if self.world > 1:
@@ -59,8 +67,19 @@ class KMeansEngine:
             else:
                 st = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
                 peers = [st.data_ptr()]
-            self.fused = kops.FusedKMeans(st, peers, self.rank, k, d, keep_empty)
+            scale = 1.0
+            if self.precision == "fp16x3":
+                # power of two that brings the largest |x| of the whole data set to [2^13, 2^14): halves stay inside
+                # fp16's range, and centroids (means of points) can never exceed it
+                mx = self.X.abs().max().to(torch.float64) if self.n else torch.zeros((), dtype=torch.float64, device=self.dev)
+                if self.world > 1:
+                    dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=group)
+                mxv = float(mx.item())
+                scale = 2.0 ** (13 - math.floor(math.log2(mxv))) if mxv > 0 else 1.0
+            self.fused = kops.FusedKMeans(st, peers, self.rank, k, d, keep_empty, precision=self.precision, scale=scale)
             self.fused.init(None)
+            if self.fused.prec:
+                self.Xs = self.fused.split_rows(self.X)
             if self.world > 1:
                 torch.cuda.synchronize(self.dev)
                 dist.barrier(group=group)          # nobody signals a peer whose flags are not zeroed yet
@@ -125,7 +144,7 @@ class KMeansEngine:
     def step(self, want_obj: bool = True) -> Optional[torch.Tensor]:
         """One Lloyd iteration; returns the (device) Σ min-distance² of the *input* centroids."""
         if self.fused is not None:
-            self.fused.step(self.X)
+            self.fused.step(self.X, Xs=self.Xs)
             return self.obj if want_obj else None
         kops.kmeans_step(self.X, self.C, self.sums, self.counts, None,
                          self.obj if want_obj else None, self.workspace, variant=self.variant)

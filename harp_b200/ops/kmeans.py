@@ -147,8 +147,15 @@ class FusedKMeans:
     ``peer_ptrs`` are the device addresses of that block on every rank (for one GPU: just its own).
     """
 
-    def __init__(self, state: torch.Tensor, peer_ptrs, rank: int, k: int, d: int, keep_empty: bool = False):
+    PREC = {"tf32": 0, "fp16x3": 1, "bf16x3": 2}
+
+    def __init__(self, state: torch.Tensor, peer_ptrs, rank: int, k: int, d: int, keep_empty: bool = False,
+                 precision: str = "tf32", scale: float = 1.0):
         import ctypes
+
+        self.prec = self.PREC[precision]
+        self.precision = precision
+        self.scale = float(scale) if self.prec == 1 else 1.0
 
         lib = _native.lib()
         lib.hb_kmeans_fused_state_bytes.restype = ctypes.c_size_t
@@ -159,6 +166,15 @@ class FusedKMeans:
         lib.hb_kmeans_fused_step.argtypes = [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
                                              ctypes.c_int, ctypes.c_int, ctypes.c_uint, ctypes.c_int, ctypes.c_void_p,
                                              ctypes.c_void_p]
+        lib.hb_kmeans_fused_prep2.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                              ctypes.c_float, ctypes.c_void_p]
+        lib.hb_kmeans_fused_step2.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_int,
+                                              ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_uint, ctypes.c_int,
+                                              ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_void_p]
+        lib.hb_kmeans_split_row_bytes.restype = ctypes.c_size_t
+        lib.hb_kmeans_split_row_bytes.argtypes = [ctypes.c_int]
+        lib.hb_kmeans_split_rows.argtypes = [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_float, ctypes.c_int,
+                                             ctypes.c_void_p, ctypes.c_void_p]
         self.lib = lib
         self.k, self.d = int(k), int(d)
         self.rank, self.world = int(rank), len(peer_ptrs)
@@ -200,21 +216,39 @@ class FusedKMeans:
                                                     _native.stream_ptr()), "hb_kmeans_fused_init")
         _native.count_launch(2)
         self.epoch = 0
+        if self.prec:
+            for par in (1, 0):
+                _native.check(self.lib.hb_kmeans_fused_prep2(_native.ptr(self.state), self.k, self.d, par, self.prec,
+                                                             self.scale, _native.stream_ptr()), "hb_kmeans_fused_prep2")
+            _native.count_launch(2)
 
     def set_centroids(self, C: torch.Tensor, non_blocking: bool = True) -> None:
         """Overwrite the current centroids (every rank must do the same) and rebuild the GEMM operands."""
         self.centroids.copy_(C.view(self.k, self.d), non_blocking=non_blocking)
-        _native.check(self.lib.hb_kmeans_fused_prep(_native.ptr(self.state), self.k, self.d, self.epoch & 1,
-                                                    _native.stream_ptr()), "hb_kmeans_fused_prep")
+        _native.check(self.lib.hb_kmeans_fused_prep2(_native.ptr(self.state), self.k, self.d, self.epoch & 1, self.prec,
+                                                     self.scale, _native.stream_ptr()), "hb_kmeans_fused_prep2")
         _native.count_launch(1)
 
-    def step(self, X: torch.Tensor, assign: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def split_rows(self, X: torch.Tensor) -> torch.Tensor:
+        """The points as 16-bit hi/lo rows for the split-precision GEMM (``hb_kmeans_split_rows``); done once per
+        data set, the rows never change."""
+        assert self.prec and X.dtype == torch.float32 and X.is_contiguous() and X.shape[1] == self.d
+        rb = int(self.lib.hb_kmeans_split_row_bytes(self.d))
+        Xs = torch.empty(X.shape[0], rb // 2, dtype=torch.int16, device=X.device)
+        _native.check(self.lib.hb_kmeans_split_rows(_native.ptr(X), X.shape[0], self.d, self.scale, self.prec,
+                                                    _native.ptr(Xs), _native.stream_ptr()), "hb_kmeans_split_rows")
+        _native.count_launch(1)
+        return Xs
+
+    def step(self, X: torch.Tensor, assign: Optional[torch.Tensor] = None, Xs: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One full Lloyd iteration in one launch; returns the new centroids (a view of the state)."""
         assert X.dtype == torch.float32 and X.is_contiguous() and X.shape[1] == self.d
-        rc = self.lib.hb_kmeans_fused_step(_native.ptr(X), X.shape[0], self.d, self.k,
-                                           ctypes_cast_void(self._peers), self.rank, self.world, self.epoch,
-                                           1 if self.keep_empty else 0, _native.ptr(assign), _native.stream_ptr())
-        _native.check(rc, "hb_kmeans_fused_step")
+        assert (Xs is not None) == bool(self.prec) or X.shape[0] == 0, "split-precision steps need the split rows"
+        rc = self.lib.hb_kmeans_fused_step2(_native.ptr(X), _native.ptr(Xs), X.shape[0], self.d, self.k,
+                                            ctypes_cast_void(self._peers), self.rank, self.world, self.epoch,
+                                            1 if self.keep_empty else 0, _native.ptr(assign), self.prec, self.scale,
+                                            _native.stream_ptr())
+        _native.check(rc, "hb_kmeans_fused_step2")
         _native.count_launch(1)
         self.epoch += 1
         return self.centroids

@@ -79,3 +79,24 @@ def test_static_scratch_rejects_what_it_cannot_hold(native_built):
                                    None, None, nat.stream_ptr())
     assert rc != 0 and b"hb_kmeans_step" in lib.hb_last_error()
     torch.cuda.synchronize()
+
+
+def test_static_scratch_alignment_and_largest_k(native_built):
+    """A misaligned input is refused with a message about alignment (not about a workspace this caller never gave),
+    before anything is queued; k = 16384, the documented limit, still runs."""
+    lib, nat = _lib()
+    n, d, k = 4096, 64, 16384
+    X = torch.rand(n, d, device="cuda"); C = torch.rand(k, d, device="cuda")
+    sums = torch.full((k, d), -1.0, device="cuda"); counts = torch.full((k,), -1.0, device="cuda")
+    flat = torch.rand(n * d + 1, device="cuda")
+    Xmis = flat[1:]                                         # 4 bytes past a 16-byte boundary
+    rc = lib.hb_kmeans_step_static(c_void_p(Xmis.data_ptr()), n, d, nat.ptr(C), k, nat.ptr(sums), nat.ptr(counts),
+                                   None, None, nat.stream_ptr())
+    assert rc != 0 and b"16-byte aligned" in lib.hb_last_error()
+    torch.cuda.synchronize()
+    assert float(sums.min()) == -1.0 and float(counts.min()) == -1.0        # nothing was touched
+    rc = lib.hb_kmeans_step_static(nat.ptr(X), n, d, nat.ptr(C), k, nat.ptr(sums), nat.ptr(counts), None, None,
+                                   nat.stream_ptr())
+    assert rc == 0, lib.hb_last_error().decode()
+    torch.cuda.synchronize()
+    assert float(counts.sum()) == n
