@@ -45,6 +45,9 @@ def parse_args():
     ap.add_argument("--dim", type=int, default=DIM)
     ap.add_argument("--k", type=int, default=K)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--precision", default="fp16x3", choices=["fp16x3", "bf16x3", "tf32"],
+                    help="products of the distance GEMM for the headline value (BASELINE config 2 is fp32 data: the default "
+                         "is the fp32-faithful split mode; the TF32 figure is reported next to it)")
     ap.add_argument("--no-secondary", action="store_true", help="skip the MF-SGD / LDA / Gram block of the default run")
     ap.add_argument("--no-library-arm", action="store_true", help="skip the cuBLAS + NCCL arm of the default run")
     ap.add_argument("--secondary-steps", type=int, default=20)
@@ -226,7 +229,7 @@ def main():
             symm = None
     if comm == "auto":
         comm = "fused" if (world == 1 or symm is not None) else "nccl"
-    eng = KMeansEngine(X, k, comm=comm, symm=symm)
+    eng = KMeansEngine(X, k, comm=comm, symm=symm, precision=args.precision if comm == "fused" else None)
     eng.set_centroids(C0)
 
     def barrier():
@@ -259,6 +262,50 @@ def main():
     ms_per_step = float(t.item()) / args.steps
     final_mse = eng.mse()
     comm_used = eng.comm
+    precision_used = eng.precision
+
+    # ---------------- the other precision arm + how often each arm's arg-min differs from exact fp32 ----------------
+    def timed_steps(e, steps):
+        for _ in range(3):
+            e.step()
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(steps):
+            e.step()
+        a1.record(); barrier()
+        tt = torch.tensor([a0.elapsed_time(a1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item()) / steps
+
+    precision_report = None
+    if comm_used == "fused":
+        from harp_b200.ops.kmeans import kmeans_step
+        other = "tf32" if precision_used != "tf32" else "fp16x3"
+        eng_o = KMeansEngine(X, k, comm=comm, symm=symm, precision=other)
+        eng_o.set_centroids(C0)
+        other_ms = timed_steps(eng_o, args.steps)
+        del eng_o
+        # assignment disagreement on a 1 M-point sample of the bench data against the exact fp32 SIMT kernel
+        # ((x - c)^2 accumulated in fp32, no tensor cores), with the centroids the timed run ended on
+        ns = min(n, 1_000_000)
+        Xsmp = X[:ns].contiguous()
+        Cnow = eng.C.clone()
+        exact = kmeans_step(Xsmp, Cnow, want_assign=True, want_obj=True, force_simt=True)
+        torch.cuda.synchronize()
+        ea, eobj = exact.assign.long(), float(exact.obj)
+        precision_report = {"sample_points": ns, "oracle": "exact fp32 SIMT kernel (assign_simt_kernel)"}
+        for prec in ("fp16x3", "bf16x3", "tf32"):
+            es = KMeansEngine(Xsmp, k, precision=prec)           # single-GPU engine on the sample
+            es.set_centroids(Cnow)
+            a = torch.full((ns,), -1, dtype=torch.int32, device=dev)
+            es.fused.step(Xsmp, assign=a, Xs=es.Xs)
+            torch.cuda.synchronize()
+            precision_report[prec] = {"assignment_disagreement": float((a.long() != ea).double().mean()),
+                                      "objective_gap": (float(es.obj) - eobj) / eobj}
+            del es
+        precision_report[other + "_s_per_iter"] = other_ms / 1e3
 
     # ---------------- end-to-end through the public API ----------------
     e2e = None
@@ -346,7 +393,12 @@ def main():
                          "speedup": lib_value / (ms_per_step / 1e3) if lib_value else None,
                          "steps": library.get("steps") if isinstance(library, dict) else None,
                          "clocks": library.get("clocks") if isinstance(library, dict) else None},
-            "dtype": "tf32 (fp32 storage, TF32 tensor-core products, fp32 accumulate)",
+            "dtype": {"fp16x3": "fp32 data; products as fp16 hi/lo halves, 3 kind::f16 MMAs per product, fp32 accumulate "
+                                "(fp32-faithful: see precision.assignment_disagreement)",
+                      "bf16x3": "fp32 data; products as bf16 hi/lo halves, 3 kind::f16 MMAs per product, fp32 accumulate",
+                      "tf32": "tf32 (fp32 storage, TF32 tensor-core products, fp32 accumulate)"}.get(precision_used, "fp32"),
+            "tf32_value": (precision_report or {}).get("tf32_s_per_iter") if precision_used != "tf32" else ms_per_step / 1e3,
+            "precision": precision_report,
             "data": "synthetic uniform[0,1) points, random-init centroids",
             "impl": "harp_b200",
             "config": {
@@ -361,11 +413,15 @@ def main():
                 "l2": "inputs larger than L2 (6.4 GB of points per GPU re-streamed every step)",
             },
             "points_per_s": total_points / (ms_per_step / 1e3),
-            "tflops_tf32_aggregate": flops / (ms_per_step / 1e3) / 1e12,
+            "tflops_algorithmic_aggregate": flops / (ms_per_step / 1e3) / 1e12,
+            "tflops_issued_aggregate": flops * (1.5 if precision_used != "tf32" else 1.0) / (ms_per_step / 1e3) / 1e12,
             "final_mse": final_mse,
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": roofline(flops / world, k * (d + 1) * 4, world, ms_per_step, nvlink_gbs),
+            # split precision issues 3 half-precision MMAs per product, at twice the TF32 MMA rate: 1.5x the algorithmic
+            # FLOPs go through the pipe at the bf16/fp16 rate, and that is what the compute target counts
+            "roofline": dict(roofline(flops / world * (1.5 if precision_used != "tf32" else 1.0), k * (d + 1) * 4, world,
+                                      ms_per_step, nvlink_gbs), issued_over_algorithmic_flops=1.5 if precision_used != "tf32" else 1.0),
             "nvlink_gbs_measured": nvlink_gbs,
             "e2e": e2e,
             "secondary": secondary,
