@@ -33,6 +33,7 @@ constexpr int MAX_CTAS = HB_COLL_MAX_CTAS;
 
 struct Peers {
   uint8_t* base[MAX_RANKS];  // peer-mapped slab base of every rank (index = rank)
+  unsigned long long timeout_ns;
 };
 
 __device__ __forceinline__ uint32_t* flag_ptr(uint8_t* slab, size_t flags_off, int cta, int src) {
@@ -41,24 +42,43 @@ __device__ __forceinline__ uint32_t* flag_ptr(uint8_t* slab, size_t flags_off, i
 
 // All-to-all handshake of CTA blockIdx.x across ranks.  `ticket` must increase
 // with every use.  Called by all threads of the CTA.
-__device__ __forceinline__ void cta_barrier_all(const Peers& P, int rank, int world, size_t flags_off,
+// The wait is bounded by `Peers::timeout_ns` of %globaltimer (0 = unbounded; the host default is the reference's
+// DATA_MAX_WAIT_TIME, 1800 s, HB_WAIT_TIMEOUT_S overrides).  When it expires the CTA records (ticket, peer) in the
+// error words behind the flags, returns false and the kernel skips its data phase: the context stays usable and
+// the host raises from SymmetricWorkspace.check().
+__device__ __forceinline__ uint32_t* error_words(uint8_t* slab, size_t flags_off) {
+  return reinterpret_cast<uint32_t*>(slab + flags_off) + (size_t)MAX_CTAS * MAX_RANKS;
+}
+__device__ __forceinline__ bool cta_barrier_all(const Peers& P, int rank, int world, size_t flags_off,
                                                 uint32_t ticket) {
   __syncthreads();
+  int bad = 0;
   if (threadIdx.x < world) {
     const int p = threadIdx.x;
     fence_sys();  // make this CTA's prior (peer) writes visible before the flag
     st_release_sys(flag_ptr(P.base[p], flags_off, blockIdx.x, rank), ticket);
     const uint32_t* mine = flag_ptr(P.base[rank], flags_off, blockIdx.x, p);
-    long long t0 = clock64();
-    while ((int32_t)(ld_acquire_sys(mine) - ticket) < 0) {
-      if (clock64() - t0 > 20000000000LL) {  // ~10 s: a peer died or the call order diverged
-        printf("harp_b200: NVLink barrier timeout rank %d cta %d waiting for rank %d ticket %u\n",
-               rank, blockIdx.x, p, ticket);
-        __trap();
+    if ((int32_t)(ld_acquire_sys(mine) - ticket) < 0) {
+      unsigned long long t0;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+      unsigned spins = 0;
+      while ((int32_t)(ld_relaxed_sys(mine) - ticket) < 0) {
+        __nanosleep(100);
+        if ((++spins & 255u) == 0u && P.timeout_ns != 0ULL) {
+          unsigned long long t1;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+          if (t1 - t0 > P.timeout_ns) {
+            uint32_t* err = error_words(P.base[rank], flags_off);
+            if (atomicCAS(err, 0u, ticket | 0x80000000u) == 0u) err[1] = (uint32_t)p;
+            bad = 1;
+            break;
+          }
+        }
       }
+      (void)ld_acquire_sys(mine);
     }
   }
-  __syncthreads();
+  return __syncthreads_or(bad) == 0;
 }
 
 template <typename T> struct Vec16 { static constexpr int N = 16 / sizeof(T); T v[16 / sizeof(T)]; };
@@ -86,7 +106,7 @@ template <int OP, typename T>
 __global__ void __launch_bounds__(512)
 reduce_kernel(Peers P, int rank, int world, size_t off, size_t count, size_t flags_off,
               uint32_t ticket, int mode, int root) {
-  cta_barrier_all(P, rank, world, flags_off, ticket);
+  if (!cta_barrier_all(P, rank, world, flags_off, ticket)) return;
   constexpr int VN = Vec16<T>::N;
   size_t lo, hi;  // element range this rank reduces
   if (mode == 2) {
@@ -126,7 +146,7 @@ reduce_kernel(Peers P, int rank, int world, size_t off, size_t count, size_t fla
       *reinterpret_cast<T*>(P.base[rank] + byte) = acc;
     }
   }
-  cta_barrier_all(P, rank, world, flags_off, ticket + 1);
+  (void)cta_barrier_all(P, rank, world, flags_off, ticket + 1);
 }
 
 // Byte mover used by allgather / broadcast / rotate.
@@ -136,7 +156,7 @@ reduce_kernel(Peers P, int rank, int world, size_t off, size_t count, size_t fla
 __global__ void __launch_bounds__(512)
 move_kernel(Peers P, int rank, int world, size_t off, size_t src_off, size_t bytes,
             size_t flags_off, uint32_t ticket, int mode, int root) {
-  cta_barrier_all(P, rank, world, flags_off, ticket);
+  if (!cta_barrier_all(P, rank, world, flags_off, ticket)) return;
   const size_t tid = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const size_t nth = (size_t)gridDim.x * blockDim.x;
   const size_t nvec = bytes / 16;
@@ -163,11 +183,11 @@ move_kernel(Peers P, int rank, int world, size_t off, size_t src_off, size_t byt
       for (size_t b = nvec * 16 + tid; b < bytes; b += nth) dst[b] = src[b];
     }
   }
-  cta_barrier_all(P, rank, world, flags_off, ticket + 1);
+  (void)cta_barrier_all(P, rank, world, flags_off, ticket + 1);
 }
 
 __global__ void barrier_kernel(Peers P, int rank, int world, size_t flags_off, uint32_t ticket) {
-  cta_barrier_all(P, rank, world, flags_off, ticket);
+  if (!cta_barrier_all(P, rank, world, flags_off, ticket)) return;
 }
 
 // ----------------------------------------------------------------------------
@@ -180,7 +200,7 @@ __global__ void barrier_kernel(Peers P, int rank, int world, size_t flags_off, u
 __global__ void __launch_bounds__(512)
 kmeans_regroup_allgather_kernel(Peers P, int rank, int world, size_t acc_off, size_t c_off, int k,
                                 int d, size_t flags_off, uint32_t ticket, int keep_empty) {
-  cta_barrier_all(P, rank, world, flags_off, ticket);
+  if (!cta_barrier_all(P, rank, world, flags_off, ticket)) return;
   const int rows_per = (k + world - 1) / world;
   const int r0 = min(k, rank * rows_per), r1 = min(k, r0 + rows_per);
   const int d4 = d >> 2;  // d % 4 == 0 guaranteed by the host
@@ -209,7 +229,72 @@ kmeans_regroup_allgather_kernel(Peers P, int rank, int world, size_t acc_off, si
       for (int p = 0; p < world; ++p) *reinterpret_cast<float4*>(P.base[(rank + p) % world] + cbyte) = z;
     }
   }
-  cta_barrier_all(P, rank, world, flags_off, ticket + 1);
+  (void)cta_barrier_all(P, rank, world, flags_off, ticket + 1);
+}
+
+
+// ----------------------------------------------------------------------------
+// Row collectives over a dense table [rows x row_elems] that sits at the same offset of every rank's slab.
+// Ownership is Harp's default Partitioner: row (= partition id) p belongs to rank p % world
+// (partition/Partitioner.java:36-43).
+//   mode 0  regroup      owner sums its rows over all ranks, in rank order, in place        (K2, RegroupCollective
+//                        .java:154-226 with a SUM combiner = reduce-scatter by ownership)
+//   mode 1  allgather    owner stores its rows into every peer                              (AllgatherCollective.java:
+//                        147-213 after a regroup: the second half of `aggregate`)
+//   mode 2  push         every rank adds ALL rows of its local table into the owners' global tables with
+//                        red.global.add over the peer pointer (K18, LocalGlobalSyncCollective.java:456-549); the
+//                        owner's global table holds its rows densely: row p at index p / world
+//   mode 3  pull         every rank adds the owners' global rows into its local table (gather over peer
+//                        pointers; `pull` combines, callers zero first: :564-698)
+//   mode 4  pull, bcast  same result, but the owner PUSHES each of its rows into every peer's local table — the
+//                        useBcast branch for rows that all workers want (:654-659)
+// ----------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ void red_add_t(T* p, T v);
+template <> __device__ __forceinline__ void red_add_t<float>(float* p, float v) { red_add_f32(p, v); }
+template <> __device__ __forceinline__ void red_add_t<double>(double* p, double v) { red_add_f64(p, v); }
+
+template <typename T>
+__global__ void __launch_bounds__(512)
+rows_kernel(Peers P, int rank, int world, size_t loc_off, size_t glob_off, long long rows, long long row_elems,
+            size_t flags_off, uint32_t ticket, int mode) {
+  if (!cta_barrier_all(P, rank, world, flags_off, ticket)) return;
+  const size_t tid = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const size_t nth = (size_t)gridDim.x * blockDim.x;
+  if (mode == 0 || mode == 1 || mode == 4) {
+    // iterate over the rows this rank owns
+    const long long nown = rows > rank ? (rows - rank + world - 1) / world : 0;
+    const size_t total = (size_t)nown * row_elems;
+    for (size_t i = tid; i < total; i += nth) {
+      const long long p = rank + (long long)(i / row_elems) * world;
+      const size_t e = i % row_elems;
+      if (mode == 0) {
+        const size_t byte = loc_off + ((size_t)p * row_elems + e) * sizeof(T);
+        T acc = *reinterpret_cast<const volatile T*>(P.base[0] + byte);
+        for (int q = 1; q < world; ++q) acc += *reinterpret_cast<const volatile T*>(P.base[q] + byte);
+        *reinterpret_cast<T*>(P.base[rank] + byte) = acc;
+      } else if (mode == 1) {
+        const size_t byte = loc_off + ((size_t)p * row_elems + e) * sizeof(T);
+        const T v = *reinterpret_cast<const T*>(P.base[rank] + byte);
+        for (int q = 1; q < world; ++q) *reinterpret_cast<T*>(P.base[(rank + q) % world] + byte) = v;
+      } else {
+        const T v = *reinterpret_cast<const T*>(P.base[rank] + glob_off + ((size_t)(p / world) * row_elems + e) * sizeof(T));
+        const size_t byte = loc_off + ((size_t)p * row_elems + e) * sizeof(T);
+        for (int q = 0; q < world; ++q) red_add_t<T>(reinterpret_cast<T*>(P.base[(rank + q) % world] + byte), v);
+      }
+    }
+  } else {
+    const size_t total = (size_t)rows * row_elems;
+    for (size_t i = tid; i < total; i += nth) {
+      const long long p = (long long)(i / row_elems);
+      const size_t e = i % row_elems;
+      const int owner = (int)(p % world);
+      T* loc = reinterpret_cast<T*>(P.base[rank] + loc_off + ((size_t)p * row_elems + e) * sizeof(T));
+      uint8_t* glob = P.base[owner] + glob_off + ((size_t)(p / world) * row_elems + e) * sizeof(T);
+      if (mode == 2) red_add_t<T>(reinterpret_cast<T*>(glob), *loc);
+      else *loc += *reinterpret_cast<const volatile T*>(glob);
+    }
+  }
+  (void)cta_barrier_all(P, rank, world, flags_off, ticket + 1);
 }
 
 }  // namespace coll
@@ -218,7 +303,10 @@ kmeans_regroup_allgather_kernel(Peers P, int rank, int world, size_t acc_off, si
 using namespace hb;
 using namespace hb::coll;
 
+static unsigned long long g_timeout_ns = 1800ULL * 1000000000ULL;      // DATA_MAX_WAIT_TIME of the reference
+
 static int fill_peers(Peers& P, const void* const* peer_ptrs, int rank, int world) {
+  P.timeout_ns = g_timeout_ns;
   HB_REQUIRE(world >= 1 && world <= MAX_RANKS, "world=%d exceeds HB_MAX_RANKS=%d", world, MAX_RANKS);
   HB_REQUIRE(rank >= 0 && rank < world, "bad rank %d of %d", rank, world);
   for (int i = 0; i < MAX_RANKS; ++i)
@@ -259,7 +347,30 @@ static int dispatch_op(int op, const Peers& P, int rank, int world, size_t off, 
 
 extern "C" {
 
-size_t hb_coll_flags_bytes(void) { return (size_t)MAX_CTAS * MAX_RANKS * sizeof(uint32_t); }
+// flags + 256 bytes whose first two words report an expired wait: (0x80000000 | ticket, peer rank waited for)
+size_t hb_coll_flags_bytes(void) { return (size_t)MAX_CTAS * MAX_RANKS * sizeof(uint32_t) + 256; }
+
+// Bound (ns) on every in-kernel wait for a peer; 0 = wait for ever.
+int hb_coll_set_timeout_ns(unsigned long long ns) { g_timeout_ns = ns; return 0; }
+
+int hb_coll_rows(const void* const* peer_ptrs, int rank, int world, size_t local_offset_bytes, size_t global_offset_bytes,
+                 long long rows, long long row_elems, int dtype, int mode, size_t flags_offset, uint32_t ticket,
+                 void* stream) {
+  Peers P;
+  if (fill_peers(P, peer_ptrs, rank, world) != 0) return -2;
+  HB_REQUIRE(mode >= 0 && mode <= 4, "hb_coll_rows: bad mode %d", mode);
+  HB_REQUIRE(dtype == HB_F32 || dtype == HB_F64, "hb_coll_rows: float32 / float64 tables only (dtype %d)", dtype);
+  HB_REQUIRE(rows >= 0 && row_elems >= 1, "hb_coll_rows: bad shape");
+  const int grid = pick_grid((size_t)rows * (size_t)row_elems / (mode == 2 || mode == 3 ? 1 : world) + 1, 512);
+  if (dtype == HB_F32)
+    rows_kernel<float><<<grid, 512, 0, (cudaStream_t)stream>>>(P, rank, world, local_offset_bytes, global_offset_bytes,
+                                                               rows, row_elems, flags_offset, ticket, mode);
+  else
+    rows_kernel<double><<<grid, 512, 0, (cudaStream_t)stream>>>(P, rank, world, local_offset_bytes, global_offset_bytes,
+                                                                rows, row_elems, flags_offset, ticket, mode);
+  HB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
 
 int hb_coll_reduce(const void* const* peer_ptrs, int rank, int world, size_t offset_bytes,
                    size_t count, int dtype, int op, int mode, int root, size_t flags_offset,

@@ -173,6 +173,29 @@ class Comm:
         return all(s is not None and s == sigs[0] for s in sigs)
 
 
+def _symm_slab(comm: Comm, table: Table, need_range_ids: bool = True) -> Optional[torch.Tensor]:
+    """The table's slab when the NVLink row / buffer kernels may run on it: slab-backed (``Table.dense``), inside the
+    symmetric workspace, float32/float64, an ArrayCombiner with SUM, ids 0..P-1 in slab order, and the same layout
+    on every rank.  The cross-rank check costs one ``all_gather_object`` the FIRST time a table is seen; the verdict
+    is cached on the table (a dense table loses its slab, and with it the cache, as soon as a partition is added,
+    removed or re-pointed), so the steady state of an iterative app does no host round trip at all."""
+    if comm.symm is None or not table.is_dense():
+        return None
+    slab = table.slab
+    cached = getattr(table, "_symm_ok", None)
+    key = (slab.data_ptr(), tuple(slab.shape), str(slab.dtype))
+    if cached is not None and cached[0] == key:
+        return slab if cached[1] else None
+    comb = table.get_combiner()
+    ok = (isinstance(comb, ArrayCombiner) and comb.op is Operation.SUM and slab.is_contiguous()
+          and slab.dtype in (torch.float32, torch.float64) and comm.symm.contains(slab)
+          and (not need_range_ids or table.get_partition_ids() == list(range(slab.shape[0]))))
+    sig = (tuple(slab.shape), str(slab.dtype), comm.symm.offset_of(slab) if ok else -1) if ok else None
+    ok = comm.all_same(sig)
+    table._symm_ok = (key, ok)
+    return slab if ok else None
+
+
 def _tensor_of(payload) -> Optional[torch.Tensor]:
     if isinstance(payload, Array):
         return payload.get()
@@ -246,6 +269,18 @@ def barrier(comm: Comm, context_name: str = "", operation_name: str = "") -> boo
 def broadcast(comm: Comm, table: Table, root: int, use_mst_bcast: bool = False) -> bool:
     if comm.is_the_only_worker():
         return True
+    slab = _symm_slab(comm, table)
+    if slab is not None:
+        # dense table in the symmetric slab: non-roots pull the root's rows over NVLink and combine them into their own
+        # ("broadcast onto a table that already holds the id combines") — one kernel, no host metadata
+        tmp = comm.symm.alloc(slab.numel(), slab.dtype)
+        if comm.rank == root:
+            tmp.copy_(slab.view(-1))
+        comm.symm.broadcast_(tmp, root)
+        if comm.rank != root:
+            slab.view(-1).add_(tmp)
+        comm.symm.free(tmp)
+        return True
     send: Dict[int, List[Tuple[int, Any]]] = {}
     if comm.rank == root:
         items = [(p.id(), p.get()) for p in table.get_partitions()]
@@ -256,6 +291,12 @@ def broadcast(comm: Comm, table: Table, root: int, use_mst_bcast: bool = False) 
 
 def reduce(comm: Comm, table: Table, root: int) -> bool:
     if comm.is_the_only_worker():
+        return True
+    slab = _symm_slab(comm, table)
+    if slab is not None:
+        comm.symm.reduce_(slab.view(-1), root, "sum")       # the root sums every rank's rows over NVLink
+        if comm.rank != root:
+            table.release()                                  # ReduceCollective.java:234-238
         return True
     send = {}
     if comm.rank != root:
@@ -269,6 +310,10 @@ def reduce(comm: Comm, table: Table, root: int) -> bool:
 
 def allreduce(comm: Comm, table: Table, assume_uniform: Optional[bool] = None) -> bool:
     if comm.is_the_only_worker():
+        return True
+    slab = _symm_slab(comm, table, need_range_ids=False)
+    if slab is not None:
+        comm.symm.allreduce_(slab.view(-1), "sum")          # in-kernel NVLink allreduce, layout check cached on the table
         return True
     sig = comm.uniform_signature(table)
     comb = table.get_combiner()
@@ -295,6 +340,21 @@ def allreduce(comm: Comm, table: Table, assume_uniform: Optional[bool] = None) -
 def allgather(comm: Comm, table: Table) -> bool:
     if comm.is_the_only_worker():
         return True
+    # second half of `aggregate` on a dense symmetric table: every rank holds exactly the rows it owns
+    # (id % world == rank) as views of the slab it regrouped in place -> owners store their rows into every peer
+    st = getattr(table, "_regrouped", None)
+    if st is not None and comm.symm is not None and st[1] == sorted(table.get_partition_ids()) and all(
+            _tensor_of(table.get_partition(pid).get()).data_ptr() == st[0][pid].data_ptr() for pid in st[1][:4]):
+        slab = st[0]
+        comm.symm.allgather_rows_(slab)
+        dense = Table.dense(table.get_table_id(), table.get_combiner(), slab)
+        table._partitions = dense._partitions
+        for part in table._partitions.values():
+            part._owner = table
+        table.slab = slab
+        table._regrouped = None
+        table._symm_ok = st[2]
+        return True
     items = [(p.id(), p.get()) for p in table.get_partitions()]
     send = {d: items for d in range(comm.world) if d != comm.rank}
     received = comm.exchange(send)
@@ -304,6 +364,21 @@ def allgather(comm: Comm, table: Table) -> bool:
 def regroup(comm: Comm, table: Table, partitioner: Optional[Partitioner] = None) -> bool:
     if comm.is_the_only_worker():
         return True
+    if partitioner is None or (type(partitioner) is Partitioner and partitioner.num_workers == comm.world):
+        slab = _symm_slab(comm, table)
+        if slab is not None:
+            # K2: the owner (id % world) sums its rows over all ranks in place; the rows this rank does not own
+            # leave the table, like every partition a regroup sends away (RegroupCollective.java:200-216)
+            ok_cache = table._symm_ok
+            comm.symm.regroup_rows_(slab)
+            keep = [pid for pid in range(slab.shape[0]) if pid % comm.world == comm.rank]
+            parts = {pid: table._partitions[pid] for pid in keep}
+            for part in parts.values():
+                part._owner = None
+            table._partitions = parts
+            table.slab = None
+            table._regrouped = (slab, keep, ok_cache)
+            return True
     partitioner = partitioner or Partitioner(comm.world)
     send: Dict[int, List[Tuple[int, Any]]] = {}
     for p in table.get_partitions():
@@ -337,6 +412,32 @@ def rotate(comm: Comm, table: Table, rotate_map: Optional[Dict[int, int]] = None
     if comm.is_the_only_worker():
         return True
     dest = (comm.rank + 1) % comm.world if rotate_map is None else int(rotate_map[comm.rank])
+    slab = _symm_slab(comm, table, need_range_ids=False)
+    if slab is not None and (rotate_map is None or sorted(int(v) for v in rotate_map.values()) == list(range(comm.world))):
+        # Dense model shard in the symmetric slab: pull the source rank's rows into the twin buffer over NVLink and
+        # swap.  The partition ids travel with the data: every rank knows every rank's id list (gathered once per
+        # table) and applies the same map to it.
+        ids_by_rank = getattr(table, "_rot_ids", None)
+        if ids_by_rank is None:
+            ids_by_rank = comm.all_gather_object(table.get_partition_ids())
+        src = (comm.rank - 1) % comm.world if rotate_map is None else [r for r, d in rotate_map.items() if int(d) == comm.rank][0]
+        twin = getattr(table, "_rot_twin", None)
+        if twin is None or twin.shape != slab.shape or twin.dtype != slab.dtype:
+            twin = comm.symm.alloc(slab.numel(), slab.dtype).view(slab.shape)
+        comm.symm.rotate_(twin, slab, int(src))
+        new_ids = [None] * comm.world
+        for r in range(comm.world):
+            d = (r + 1) % comm.world if rotate_map is None else int(rotate_map[r])
+            new_ids[d] = ids_by_rank[r]
+        ok_cache = table._symm_ok
+        dense = Table.dense(table.get_table_id(), table.get_combiner(), twin, new_ids[comm.rank])
+        table._partitions = dense._partitions
+        for part in table._partitions.values():
+            part._owner = table
+        table.slab = twin
+        table._rot_twin, table._rot_ids = slab, new_ids
+        table._symm_ok = ((twin.data_ptr(), tuple(twin.shape), str(twin.dtype)), ok_cache[1])
+        return True
     parts = table.get_partitions()
     send = {dest: [(p.id(), p.get()) for p in parts]} if dest != comm.rank else {}
     received = comm.exchange(send)
@@ -365,8 +466,39 @@ def _ownership(comm: Comm, global_table: Table, partitioner: Optional[Partitione
     return owner
 
 
+def _symm_pushpull(comm: Comm, local_table: Table, global_table: Table, partitioner: Optional[Partitioner]):
+    """(local slab, global slab) when push / pull can run as one NVLink kernel: the local table is dense over ids
+    0..P-1 on every rank, the global table is dense over exactly the ids this rank owns under the default
+    partitioner (id % world == rank, ascending), both live in the symmetric workspace.  Verified across ranks once
+    per table pair, then cached."""
+    if comm.symm is None or comm.is_the_only_worker():
+        return None
+    if partitioner is not None and not (type(partitioner) is Partitioner and partitioner.num_workers == comm.world):
+        return None
+    loc = _symm_slab(comm, local_table)
+    if loc is None or not global_table.is_dense():
+        return None
+    g = global_table.slab
+    cached = getattr(global_table, "_pp_ok", None)
+    key = (g.data_ptr(), tuple(g.shape), loc.data_ptr())
+    if cached is not None and cached[0] == key:
+        return (loc, g) if cached[1] else None
+    P = loc.shape[0]
+    owned = [pid for pid in range(P) if pid % comm.world == comm.rank]
+    comb = global_table.get_combiner()
+    ok = (isinstance(comb, ArrayCombiner) and comb.op is Operation.SUM and g.is_contiguous() and g.dtype == loc.dtype
+          and comm.symm.contains(g) and global_table.get_partition_ids() == owned and tuple(g.shape[1:]) == tuple(loc.shape[1:]))
+    ok = comm.all_same((P, str(loc.dtype), comm.symm.offset_of(g) if ok else -1) if ok else None)
+    global_table._pp_ok = (key, ok)
+    return (loc, g) if ok else None
+
+
 def push(comm: Comm, local_table: Table, global_table: Table, partitioner: Optional[Partitioner] = None) -> bool:
     """local → global; ``local_table`` is left untouched (``LocalGlobalSyncCollective.java:456-549``)."""
+    pair = _symm_pushpull(comm, local_table, global_table, partitioner)
+    if pair is not None:
+        comm.symm.push_rows_(pair[0], pair[1])           # K18: red.add of every local row into its owner's global table
+        return True
     all_wanted = comm.all_gather_object(sorted(local_table.get_partition_ids()))
     wanted = sorted({pid for ids in all_wanted for pid in ids})
     owner = _ownership(comm, global_table, partitioner, wanted)
@@ -394,6 +526,12 @@ def push(comm: Comm, local_table: Table, global_table: Table, partitioner: Optio
 def pull(comm: Comm, local_table: Table, global_table: Table, use_bcast: bool = False) -> bool:
     """global → local; received partitions are *combined* into ``local_table`` — callers zero it first
     (``LocalGlobalSyncCollective.java:564-698``)."""
+    pair = _symm_pushpull(comm, local_table, global_table, None)
+    if pair is not None:
+        # gather over peer pointers; every worker wants every row here, which is exactly the reference's useBcast
+        # case (LocalGlobalSyncCollective.java:654-659): then the owners push their rows into all peers instead
+        comm.symm.pull_rows_(pair[0], pair[1], use_bcast=use_bcast)
+        return True
     wanted_all = comm.all_gather_object(sorted(local_table.get_partition_ids()))
     owned = comm.all_gather_object(sorted(global_table.get_partition_ids()))
     owner: Dict[int, int] = {}

@@ -156,11 +156,9 @@ class LDAEngine:
         src, dst = self.Wbuf[k][self.cur[k]], self.Wbuf[k][1 - self.cur[k]]
         pred, succ = srcs[self.me], srcs.index(self.me)
         if self.symm is not None and self.dev.type == "cuda":
-            self.ev_compute[k].record()
-            with torch.cuda.stream(self.comm_stream):
-                self.comm_stream.wait_event(self.ev_compute[k])
-                self.symm.rotate_(dst, src, pred)
-                self.ev_comm[k].record()
+            # on the stream of every other collective of this workspace (its flags / tickets are per workspace);
+            # the per-panel path is the A/B arm, the whole-epoch kernel is what overlaps the transfer
+            self.symm.rotate_(dst, src, pred)
         else:
             ops = [dist.P2POp(dist.isend, src.contiguous(), succ, group=self.group),
                    dist.P2POp(dist.irecv, dst, pred, group=self.group)]

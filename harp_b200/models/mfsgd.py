@@ -159,11 +159,9 @@ class MFSGDEngine:
         pred = srcs[self.me]
         succ = srcs.index(self.me)
         if self.symm is not None and self.dev.type == "cuda":
-            self.ev_compute[k].record()
-            with torch.cuda.stream(self.comm_stream):
-                self.comm_stream.wait_event(self.ev_compute[k])
-                self.symm.rotate_(dst, src, pred)
-                self.ev_comm[k].record()
+            # on the stream of every other collective of this workspace (its flags / tickets are per workspace);
+            # the per-panel path is the A/B arm, the whole-epoch kernel is what overlaps the transfer
+            self.symm.rotate_(dst, src, pred)
         else:
             # gloo / NCCL send-recv ring (baseline path and CPU tests)
             send = src.contiguous()

@@ -12,14 +12,23 @@ Slab sources, in order of preference:
 1. ``torch.distributed._symmetric_memory`` (CUDA VMM + fabric/fd handle exchange);
 2. legacy CUDA IPC on a ``cudaMalloc`` slab owned by ``libharp_b200.so``.
 
-All ranks must create workspaces, allocate from them and call collectives in the
-same order (allocation is a deterministic bump pointer, so offsets are identical
-everywhere — "symmetric addressing").
+All ranks must create workspaces, allocate / free from them and call collectives in the
+same order: the allocator (first-fit free list with coalescing, 256-byte granules) is
+deterministic, so offsets are identical everywhere — "symmetric addressing".
+
+Rules the caller must keep (also in INTEGRATION.md):
+
+* ONE stream per workspace: all collectives of a workspace share one flag array and one ticket counter, so they
+  must be issued on the same CUDA stream (the first one used is remembered and later calls assert it).
+* Waits for a peer inside the kernels are bounded by ``HB_WAIT_TIMEOUT_S`` (default 1800 s, the reference's
+  ``DATA_MAX_WAIT_TIME``; 0 = for ever).  An expired wait does not trap: the kernel records it and skips its data
+  phase; ``check()`` raises.  Construct engines / tables behind a ``dist.barrier`` so that a slow rank's set-up is
+  not charged to the first collective.
 """
 from __future__ import annotations
 
 import ctypes
-from typing import List
+from typing import List, Optional
 
 import torch
 import torch.distributed as dist
@@ -38,6 +47,8 @@ def _declare(lib) -> None:
     lib.hb_coll_reduce.argtypes = [P, I, I, S, S, I, I, I, I, S, U, P]
     lib.hb_coll_move.argtypes = [P, I, I, S, S, S, I, I, S, U, P]
     lib.hb_coll_barrier.argtypes = [P, I, I, S, U, P]
+    lib.hb_coll_rows.argtypes = [P, I, I, S, S, ctypes.c_longlong, ctypes.c_longlong, I, I, S, U, P]
+    lib.hb_coll_set_timeout_ns.argtypes = [ctypes.c_ulonglong]
     lib.hb_kmeans_regroup_allgather.argtypes = [P, I, I, S, S, I, I, I, S, U, P]
     lib.hb_ipc_export.argtypes = [P, P]
     lib.hb_ipc_open.argtypes = [P, ctypes.POINTER(P)]
@@ -64,8 +75,12 @@ class SymmetricWorkspace:
         self.data_bytes = (int(bytes_) + 255) // 256 * 256
         self.total_bytes = self.data_bytes + self.flags_bytes
         self.flags_offset = self.data_bytes
-        self._bump = 0
+        self._free = [(0, self.data_bytes)]     # sorted (offset, size) holes
+        self._live = {}                         # offset -> size of live allocations
         self._ticket = 2
+        self._stream = None
+        import os
+        self.lib.hb_coll_set_timeout_ns(int(float(os.environ.get("HB_WAIT_TIMEOUT_S", "1800")) * 1e9))
         self._ipc_opened: List[int] = []
         self._owned_slab = None
         self.multicast_ptr = 0
@@ -134,17 +149,45 @@ class SymmetricWorkspace:
 
     # ------------------------------------------------------------------ allocation
     def alloc(self, numel: int, dtype: torch.dtype = torch.float32) -> torch.Tensor:
-        """Symmetric allocation: same offset on every rank (call in the same order everywhere)."""
+        """Symmetric allocation: same offset on every rank (call alloc / free in the same order everywhere).
+        First fit over the free list, 256-byte granules."""
         esz = torch.empty((), dtype=dtype).element_size()
         nbytes = numel * esz
-        start = (self._bump + 255) // 256 * 256
-        if start + nbytes > self.data_bytes:
-            raise MemoryError(f"symmetric workspace exhausted ({start + nbytes} > {self.data_bytes})")
-        self._bump = start + nbytes
-        return self.slab[start:start + nbytes].view(dtype)
+        need = max(256, (nbytes + 255) // 256 * 256)
+        for i, (off, size) in enumerate(self._free):
+            if size >= need:
+                if size == need:
+                    self._free.pop(i)
+                else:
+                    self._free[i] = (off + need, size - need)
+                self._live[off] = need
+                return self.slab[off:off + nbytes].view(dtype)
+        raise MemoryError(f"symmetric workspace exhausted: {need} bytes wanted, largest hole "
+                          f"{max([sz for _, sz in self._free], default=0)} of {self.data_bytes}")
+
+    def free(self, t: torch.Tensor) -> None:
+        """Returns an allocation (the tensor ``alloc`` returned, or any view starting at its first byte) to the
+        free list; neighbouring holes are merged.  Every rank must free in the same order it would allocate."""
+        off = t.data_ptr() - self.slab.data_ptr()
+        size = self._live.pop(off, None)
+        if size is None:
+            raise ValueError("not a live allocation of this symmetric workspace")
+        import bisect
+        i = bisect.bisect_left(self._free, (off, 0))
+        self._free.insert(i, (off, size))
+        if i + 1 < len(self._free) and self._free[i][0] + self._free[i][1] == self._free[i + 1][0]:
+            self._free[i] = (self._free[i][0], self._free[i][1] + self._free[i + 1][1])
+            self._free.pop(i + 1)
+        if i > 0 and self._free[i - 1][0] + self._free[i - 1][1] == self._free[i][0]:
+            self._free[i - 1] = (self._free[i - 1][0], self._free[i - 1][1] + self._free[i][1])
+            self._free.pop(i)
 
     def reset(self) -> None:
-        self._bump = 0
+        self._free = [(0, self.data_bytes)]
+        self._live = {}
+
+    def bytes_in_use(self) -> int:
+        return sum(self._live.values())
 
     def offset_of(self, t: torch.Tensor) -> int:
         off = t.data_ptr() - self.slab.data_ptr()
@@ -157,9 +200,29 @@ class SymmetricWorkspace:
         return 0 <= off and off + t.numel() * t.element_size() <= self.data_bytes
 
     def _next_ticket(self) -> int:
+        # natural 32-bit wrap: the kernels compare with a signed difference, which is wrap-safe only that way
         t = self._ticket
         self._ticket += 2
-        return t & 0x7FFFFFFF
+        cur = torch.cuda.current_stream(self.device).cuda_stream
+        if self._stream is None:
+            self._stream = cur
+        elif self._stream != cur:
+            raise RuntimeError("SymmetricWorkspace collectives must all be issued on one CUDA stream (flags and "
+                               "tickets are shared); this call is on a different stream than the first one")
+        return t & 0xFFFFFFFF
+
+    def rebind_stream(self) -> None:
+        """Forget the remembered stream (after a synchronize, when the owner moves its collectives elsewhere)."""
+        self._stream = None
+
+    def check(self) -> None:
+        """Raises if an in-kernel wait for a peer expired since the last check (call after a synchronize)."""
+        w = self.slab[self.flags_offset + self.flags_bytes - 256: self.flags_offset + self.flags_bytes - 248].view(torch.int32).cpu()
+        if int(w[0]) != 0:
+            tick, peer = int(w[0]) & 0x7FFFFFFF, int(w[1])
+            self.slab[self.flags_offset + self.flags_bytes - 256: self.flags_offset + self.flags_bytes - 248].zero_()
+            raise _native.NativeError(f"NVLink collective (ticket {tick}) gave up waiting for rank {peer} after "
+                                      f"HB_WAIT_TIMEOUT_S; the ranks' collective call order diverged or a rank died")
 
     # ------------------------------------------------------------------ collectives
     def barrier(self) -> None:
@@ -226,6 +289,35 @@ class SymmetricWorkspace:
         _native.check(rc, "hb_coll_move(rotate)")
         _native.count_launch()
         return dst
+
+    def _rows(self, local: torch.Tensor, glob: Optional[torch.Tensor], mode: int) -> None:
+        assert local.is_contiguous() and local.dim() >= 1 and local.dtype in (torch.float32, torch.float64)
+        rows = local.shape[0]
+        row_elems = local.numel() // max(rows, 1)
+        rc = self.lib.hb_coll_rows(self._ptr_array, self.rank, self.world, self.offset_of(local),
+                                   self.offset_of(glob) if glob is not None else 0, rows, row_elems, _DT[local.dtype], mode,
+                                   self.flags_offset, self._next_ticket(), _native.stream_ptr())
+        _native.check(rc, "hb_coll_rows")
+        _native.count_launch()
+
+    def regroup_rows_(self, t: torch.Tensor) -> torch.Tensor:
+        """Dense regroup with a SUM combiner: afterwards rank r holds the sum over ranks of the rows it owns
+        (``row % world == r``), in place; the other rows keep this rank's stale partials."""
+        self._rows(t, None, 0)
+        return t
+
+    def allgather_rows_(self, t: torch.Tensor) -> torch.Tensor:
+        """Every owner's rows are stored into every peer's copy of ``t`` (same offset)."""
+        self._rows(t, None, 1)
+        return t
+
+    def push_rows_(self, local: torch.Tensor, glob: torch.Tensor) -> None:
+        """``glob`` (this rank's rows of the global table, id p at index p // world) += every rank's ``local[p]``."""
+        self._rows(local, glob, 2)
+
+    def pull_rows_(self, local: torch.Tensor, glob: torch.Tensor, use_bcast: bool = False) -> None:
+        """``local[p]`` += the owner's global row of p, for every p (gather; with ``use_bcast`` the owners push)."""
+        self._rows(local, glob, 4 if use_bcast else 3)
 
     def kmeans_regroup_allgather_(self, acc: torch.Tensor, C: torch.Tensor, k: int, d: int,
                                   keep_empty: bool = False) -> torch.Tensor:

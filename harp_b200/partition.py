@@ -44,11 +44,12 @@ class Operation(enum.Enum):
 class Partition(Generic[P]):
     """``(id, payload)`` — ``partition/Partition.java:32-58``."""
 
-    __slots__ = ("_id", "_data")
+    __slots__ = ("_id", "_data", "_owner")
 
     def __init__(self, partition_id: int, data: P):
         self._id = int(partition_id)
         self._data = data
+        self._owner = None          # the slab-backed Table this partition is a row view of (Table.dense)
 
     def id(self) -> int:
         return self._id
@@ -58,6 +59,10 @@ class Partition(Generic[P]):
 
     def set(self, data: P) -> None:
         self._data = data
+        if self._owner is not None:
+            # the payload no longer is the slab row: the table must not take the flat-buffer collective paths
+            self._owner.slab = None
+            self._owner = None
 
     def num_bytes(self) -> int:
         d = self._data
@@ -270,7 +275,9 @@ class Table(Generic[P]):
         ids = list(range(slab.shape[0])) if partition_ids is None else list(partition_ids)
         assert len(ids) == slab.shape[0]
         for i, pid in enumerate(ids):
-            t._partitions[int(pid)] = Partition(pid, slab[i])
+            part = Partition(pid, slab[i])
+            part._owner = t
+            t._partitions[int(pid)] = part
         t.slab = slab
         return t
 

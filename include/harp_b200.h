@@ -194,13 +194,26 @@ int hb_smo_binary(const double* K, const double* y, int n, double C, double tol,
  * flags area (each call consumes `ticket` and `ticket + 1`).  The flags area
  * (hb_coll_flags_bytes() bytes at `flags_offset` inside every slab) must be
  * zeroed once before first use.  All ranks must issue the calls in the same
- * order; a peer that never arrives trips a ~10 s in-kernel watchdog. */
+ * order; waits for a peer are bounded by hb_coll_set_timeout_ns. */
 #define HB_MAX_RANKS 16
 #define HB_COLL_MAX_CTAS 256
 enum { HB_F32 = 0, HB_F64 = 1, HB_I32 = 2, HB_I64 = 3 };
 enum { HB_OP_SUM = 0, HB_OP_MINUS = 1, HB_OP_PROD = 2, HB_OP_MAX = 3, HB_OP_MIN = 4 };
 
 size_t hb_coll_flags_bytes(void);
+/* Bound, in ns of %globaltimer, on every in-kernel wait for a peer (default 1800 s like the reference's
+ * DATA_MAX_WAIT_TIME, HC/io/Constant.java:35; 0 = unbounded).  An expired wait does not trap: the kernel records
+ * (0x80000000 | ticket, peer) in the two words at flags_offset + MAX_CTAS * MAX_RANKS * 4 and skips its data phase. */
+int hb_coll_set_timeout_ns(unsigned long long ns);
+/* Row collectives on a dense [rows, row_elems] table at the same offset of every slab; row p is owned by rank
+ * p % world (HC/partition/Partitioner.java:36-43).  mode 0: regroup = owner sums its rows over all ranks
+ * (HC/collective/RegroupCollective.java:154-226); 1: owner stores its rows into every peer (allgather half of
+ * aggregate, :252-297); 2: push = red.add of every local row into the owner's global table, whose row for id p is at
+ * index p / world (HC/collective/LocalGlobalSyncCollective.java:456-549); 3: pull = local row += owner's global row
+ * (:564-698); 4: pull with useBcast = owners add their rows into every peer's local table (:654-659). */
+int hb_coll_rows(const void* const* peer_ptrs, int rank, int world, size_t local_offset_bytes,
+                 size_t global_offset_bytes, long long rows, long long row_elems, int dtype, int mode,
+                 size_t flags_offset, uint32_t ticket, void* stream);
 /* mode 0: allreduce in place (HC/collective/AllreduceCollective.java:150-292)
  * mode 1: reduce-scatter — rank r ends with the reduced r-th slice in place
  *         (dense regroup, HC/collective/RegroupCollective.java:154-226)

@@ -108,6 +108,127 @@ def main():
     if rank == 0:
         print("fused gram ok", flush=True)
 
+    # ---- Table collectives routed to the NVLink kernels: dense tables in the slab vs the generic path on copies ----
+    from harp_b200 import _native
+    from harp_b200 import collective as C
+    from harp_b200.partition import DoubleArrPlus, Partitioner, Table
+    ws.reset()
+    comm_s = C.Comm(device=dev, symm=ws)        # NVLink kernels
+    comm_g = C.Comm(device=dev, symm=None)      # generic path: metadata + all_to_all
+    calls = {"n": 0}
+    orig_ago = C.Comm.all_gather_object
+
+    def counting(self, obj):
+        calls["n"] += 1
+        return orig_ago(self, obj)
+    C.Comm.all_gather_object = counting
+    P, W = 37, 24                                # 37 partitions (not a multiple of the world size) of 24 doubles
+
+    def make(dtype=torch.float64, seed=0, rows=P, ids=None):
+        slab = ws.alloc(rows * W, dtype).view(rows, W)
+        slab.copy_(torch.rand(rows, W, device=dev, dtype=dtype, generator=torch.Generator(device=dev).manual_seed(seed + 31 * rank)))
+        return Table.dense(0, DoubleArrPlus(), slab, ids), slab
+
+    def twin(table):                             # same contents, ordinary tensors -> generic path
+        t2 = Table(0, DoubleArrPlus())
+        from harp_b200.partition import Partition
+        for p in table.get_partitions():
+            t2.add_partition(Partition(p.id(), p.get().clone()))
+        return t2
+
+    def same(a, b):
+        assert sorted(a.get_partition_ids()) == sorted(b.get_partition_ids()), (a.get_partition_ids(), b.get_partition_ids())
+        for pid in a.get_partition_ids():
+            torch.testing.assert_close(a.get_partition(pid).get(), b.get_partition(pid).get(), rtol=1e-12, atol=1e-12)
+
+    for dt in (torch.float64, torch.float32):
+        # allreduce / broadcast / reduce
+        for op in ("allreduce", "broadcast", "reduce"):
+            t, _ = make(dt, seed=1); g_ = twin(t)
+            for rep_ in range(3):
+                l0, c0 = _native.launches(), calls["n"]
+                if op == "allreduce":
+                    assert C.allreduce(comm_s, t); C.allreduce(comm_g, g_)
+                elif op == "broadcast":
+                    assert C.broadcast(comm_s, t, world - 1); C.broadcast(comm_g, g_, world - 1)
+                else:
+                    break
+                torch.cuda.synchronize()
+                assert _native.launches() > l0, op
+                same(t, g_) if dt == torch.float64 else None
+                if rep_ > 0:
+                    # steady state: the dense route did no metadata exchange at all (the generic twin does its own)
+                    pass
+            if op == "reduce":
+                assert C.reduce(comm_s, t, 1 % world); C.reduce(comm_g, g_, 1 % world); torch.cuda.synchronize()
+                if dt == torch.float64:
+                    same(t, g_)
+        # regroup -> (divide) -> allgather = aggregate, three rounds on the same table: K2 + allgather rows
+        t, slab = make(dt, seed=2); g_ = twin(t)
+        for rep_ in range(3):
+            c_before = calls["n"]
+            assert C.regroup(comm_s, t, Partitioner(world)); C.regroup(comm_g, g_, Partitioner(world)); torch.cuda.synchronize()
+            assert sorted(t.get_partition_ids()) == [p_ for p_ in range(P) if p_ % world == rank]
+            if dt == torch.float64:
+                same(t, g_)
+            for tt in (t, g_):
+                for p_ in tt.get_partitions():
+                    p_.get().mul_(0.5)
+            assert C.allgather(comm_s, t); C.allgather(comm_g, g_); torch.cuda.synchronize()
+            assert t.is_dense() and t.get_num_partitions() == P
+            if dt == torch.float64:
+                same(t, g_)
+        # rotate: ids travel with the rows; ring and an arbitrary permutation
+        ids = [1000 * rank + i for i in range(5)]
+        t, _ = make(dt, seed=3, rows=5, ids=ids); g_ = twin(t)
+        perm = {r: (r + 1) % world for r in range(world)} if world < 3 else {r: (r * 3 + 1) % world if (world % 3) else (r + 2) % world for r in range(world)}
+        if sorted(perm.values()) != list(range(world)):
+            perm = {r: (r + 1) % world for r in range(world)}
+        for rmap in (None, perm, None):
+            l0 = _native.launches()
+            assert C.rotate(comm_s, t, rmap); C.rotate(comm_g, g_, rmap); torch.cuda.synchronize()
+            assert _native.launches() > l0
+            same(t, g_)
+        # push / pull (K18): local = all P rows on every rank, global = the rows this rank owns
+        nown = (P + world - 1) // world
+        for use_bcast in (False, True):
+            lt, lslab = make(dt, seed=4)
+            gs = ws.alloc(nown * W, dt).view(nown, W); gs.zero_()
+            owned = [p_ for p_ in range(P) if p_ % world == rank]
+            gt = Table.dense(1, DoubleArrPlus(), gs[:len(owned)], owned)
+            lt2, gt2 = twin(lt), twin(gt)
+            l0 = _native.launches()
+            assert C.push(comm_s, lt, gt, Partitioner(world)); C.push(comm_g, lt2, gt2, Partitioner(world)); torch.cuda.synchronize()
+            assert _native.launches() > l0
+            if dt == torch.float64:
+                same(gt, gt2)
+            lslab.zero_()
+            for p_ in lt2.get_partitions():
+                p_.get().zero_()
+            assert C.pull(comm_s, lt, gt, use_bcast); C.pull(comm_g, lt2, gt2, use_bcast); torch.cuda.synchronize()
+            if dt == torch.float64:
+                same(lt, lt2)
+            ref = gs[:len(owned)].clone()
+    # steady state of the dense routes does no host metadata exchange: repeat every op once more and count
+    t, _ = make(torch.float64, seed=9)
+    C.allreduce(comm_s, t); C.broadcast(comm_s, t, 0)
+    n0 = calls["n"]
+    for _ in range(3):
+        C.allreduce(comm_s, t); C.broadcast(comm_s, t, 0)
+        C.regroup(comm_s, t, Partitioner(world)); C.allgather(comm_s, t)
+    torch.cuda.synchronize()
+    assert calls["n"] == n0, (calls["n"], n0)
+    C.Comm.all_gather_object = orig_ago
+    # the allocator really frees: allocate / free in a loop far beyond the slab size
+    ws.reset()
+    for i in range(200):
+        a_ = ws.alloc(4 << 20, torch.float32); b_ = ws.alloc(1 << 20, torch.float32)
+        ws.free(a_); ws.free(b_)
+    assert ws.bytes_in_use() == 0
+    ws.check()
+    if rank == 0:
+        print("table collectives on NVLink kernels ok", flush=True)
+
     # timing of the 5 MB allreduce vs NCCL
     ws.reset()
     n = 10000 * 129
