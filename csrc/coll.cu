@@ -297,6 +297,55 @@ rows_kernel(Peers P, int rank, int world, size_t loc_off, size_t glob_off, long 
   (void)cta_barrier_all(P, rank, world, flags_off, ticket + 1);
 }
 
+
+// ----------------------------------------------------------------------------
+// NVLS collectives: the slab is also bound to an NVSwitch multicast object; `mc` is this rank's mapping of it.
+// A multimem.ld_reduce on an mc address returns the SUM of that address over every rank's slab, computed in the
+// switch; a multimem.st writes every rank's slab at once.  One-shot allreduce: rank r reduces its 1/world slice
+// with ld_reduce and multicasts the result with st — two NVSwitch traversals, no N-way peer loads
+// (AllreduceCollective.java:150-292).  Synchronisation stays on the peer-to-peer flag barrier above.
+//   mode 0 allreduce (f32 sum, in place)   mode 1 broadcast from `root`   mode 2 allgather of `world` equal shards
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ float4 multimem_ld_reduce_add_v4(const void* mc) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc) : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st_v4(void* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(512)
+nvls_kernel(Peers P, uint8_t* mc, int rank, int world, size_t off, size_t bytes, size_t flags_off, uint32_t ticket,
+            int mode, int root) {
+  if (!cta_barrier_all(P, rank, world, flags_off, ticket)) return;
+  const size_t tid = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const size_t nth = (size_t)gridDim.x * blockDim.x;
+  const size_t nvec = bytes >> 4;
+  if (mode == 0) {
+    const size_t per = (nvec + world - 1) / world;
+    const size_t v0 = min(nvec, (size_t)rank * per), v1 = min(nvec, v0 + per);
+    for (size_t i = v0 + tid; i < v1; i += nth) {
+      const float4 v = multimem_ld_reduce_add_v4(mc + off + i * 16);
+      multimem_st_v4(mc + off + i * 16, v);
+    }
+  } else if (mode == 1) {
+    if (rank == root)
+      for (size_t i = tid; i < nvec; i += nth)
+        multimem_st_v4(mc + off + i * 16, *reinterpret_cast<const float4*>(P.base[rank] + off + i * 16));
+  } else {
+    const size_t shard = nvec / world;
+    for (size_t i = tid; i < shard; i += nth) {
+      const size_t b = off + ((size_t)rank * shard + i) * 16;
+      multimem_st_v4(mc + b, *reinterpret_cast<const float4*>(P.base[rank] + b));
+    }
+  }
+  __threadfence_system();      // multimem stores are ordered before the flags of the closing barrier
+  (void)cta_barrier_all(P, rank, world, flags_off, ticket + 1);
+}
+
 }  // namespace coll
 }  // namespace hb
 
@@ -352,6 +401,25 @@ size_t hb_coll_flags_bytes(void) { return (size_t)MAX_CTAS * MAX_RANKS * sizeof(
 
 // Bound (ns) on every in-kernel wait for a peer; 0 = wait for ever.
 int hb_coll_set_timeout_ns(unsigned long long ns) { g_timeout_ns = ns; return 0; }
+
+// NVLS data path (multimem.ld_reduce / multimem.st through `mc_ptr`, this rank's mapping of the multicast object the
+// slabs are bound to).  mode 0: in-place f32 sum allreduce of [offset, +bytes); 1: broadcast from root; 2: allgather
+// of `world` equal shards.  bytes must be a multiple of 16 (x world for mode 2).
+int hb_coll_nvls(const void* const* peer_ptrs, void* mc_ptr, int rank, int world, size_t offset_bytes, size_t bytes, int mode,
+                 int root, size_t flags_offset, uint32_t ticket, void* stream) {
+  Peers P;
+  if (fill_peers(P, peer_ptrs, rank, world) != 0) return -2;
+  HB_REQUIRE(mc_ptr != nullptr, "hb_coll_nvls: no multicast mapping");
+  HB_REQUIRE(mode >= 0 && mode <= 2 && root >= 0 && root < world, "hb_coll_nvls: bad mode %d / root %d", mode, root);
+  HB_REQUIRE((offset_bytes & 15) == 0 && (bytes & 15) == 0 && (mode != 2 || (bytes / 16) % world == 0),
+             "hb_coll_nvls: offset and size must be multiples of 16 bytes (and of 16 x world for allgather)");
+  const size_t work = mode == 1 ? bytes / 16 : bytes / 16 / world;
+  const int grid = pick_grid(work + 1, 512);
+  nvls_kernel<<<grid, 512, 0, (cudaStream_t)stream>>>(P, (uint8_t*)mc_ptr, rank, world, offset_bytes, bytes, flags_offset,
+                                                      ticket, mode, root);
+  HB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
 
 int hb_coll_rows(const void* const* peer_ptrs, int rank, int world, size_t local_offset_bytes, size_t global_offset_bytes,
                  long long rows, long long row_elems, int dtype, int mode, size_t flags_offset, uint32_t ticket,

@@ -49,6 +49,17 @@ def _declare(lib) -> None:
     lib.hb_coll_barrier.argtypes = [P, I, I, S, U, P]
     lib.hb_coll_rows.argtypes = [P, I, I, S, S, ctypes.c_longlong, ctypes.c_longlong, I, I, S, U, P]
     lib.hb_coll_set_timeout_ns.argtypes = [ctypes.c_ulonglong]
+    lib.hb_coll_nvls.argtypes = [P, P, I, I, S, S, I, I, S, U, P]
+    ULLP, IP = ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_int)
+    lib.hb_vmm_granularity.argtypes = [I, ctypes.POINTER(S)]
+    lib.hb_vmm_create.argtypes = [S, ULLP, IP]
+    lib.hb_vmm_import.argtypes = [I, ULLP]
+    lib.hb_vmm_map.argtypes = [ctypes.c_ulonglong, S, S, ctypes.POINTER(P)]
+    lib.hb_vmm_unmap.argtypes = [P, S]
+    lib.hb_vmm_release.argtypes = [ctypes.c_ulonglong]
+    lib.hb_mc_create.argtypes = [I, S, ULLP, IP]
+    lib.hb_mc_add_device.argtypes = [ctypes.c_ulonglong]
+    lib.hb_mc_bind.argtypes = [ctypes.c_ulonglong, ctypes.c_ulonglong, S]
     lib.hb_kmeans_regroup_allgather.argtypes = [P, I, I, S, S, I, I, I, S, U, P]
     lib.hb_ipc_export.argtypes = [P, P]
     lib.hb_ipc_open.argtypes = [P, ctypes.POINTER(P)]
@@ -86,9 +97,13 @@ class SymmetricWorkspace:
         self.multicast_ptr = 0
         self.backend = None
         errors = []
-        for be in (["torch", "ipc"] if backend == "auto" else [backend]):
+        import os
+        order = ["vmm", "torch", "ipc"] if os.environ.get("HB_SYMM_VMM", "1") != "0" else ["torch", "ipc"]
+        for be in (order if backend == "auto" else [backend]):
             try:
-                if be == "torch":
+                if be == "vmm":
+                    self._init_vmm()
+                elif be == "torch":
                     self._init_torch()
                 else:
                     self._init_ipc()
@@ -124,6 +139,84 @@ class SymmetricWorkspace:
                 self.device.type, self.device.index) else 0
         except Exception:  # noqa: BLE001
             self.multicast_ptr = 0
+
+    def _init_vmm(self) -> None:
+        """Own slab: cuMemCreate physical memory on every rank, POSIX-fd handles passed between the processes over a
+        unix socket (SCM_RIGHTS), every peer's memory mapped locally, and the whole slab bound to ONE NVSwitch
+        multicast object whose mapping (``multicast_ptr``) the NVLS kernels use (``csrc/nvls.cu``)."""
+        import array
+        import os
+        import socket
+
+        lib, world, rank = self.lib, self.world, self.rank
+        gran = ctypes.c_size_t(0)
+        _native.check(lib.hb_vmm_granularity(world, ctypes.byref(gran)), "hb_vmm_granularity")
+        g = int(gran.value)
+        size = (self.total_bytes + g - 1) // g * g
+        handle, fd = ctypes.c_ulonglong(0), ctypes.c_int(-1)
+        _native.check(lib.hb_vmm_create(size, ctypes.byref(handle), ctypes.byref(fd)), "hb_vmm_create")
+        mc_handle, mc_fd = ctypes.c_ulonglong(0), ctypes.c_int(-1)
+        if rank == 0 and world > 1:
+            _native.check(lib.hb_mc_create(world, size, ctypes.byref(mc_handle), ctypes.byref(mc_fd)), "hb_mc_create")
+        # ---- fd exchange: every rank listens on an abstract unix socket, sends its fd(s) to every peer
+        SymmetricWorkspace._vmm_seq = getattr(SymmetricWorkspace, "_vmm_seq", 0) + 1       # same count on every rank
+        tag = f"{os.environ.get('MASTER_PORT', '0')}_{os.getppid()}_{SymmetricWorkspace._vmm_seq}"
+        names = [f"\0hb_vmm_{tag}_{r}" for r in range(world)]
+        srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        srv.bind(names[rank]); srv.listen(world)
+        dist.barrier(group=self.group)
+        for r in range(world):
+            if r == rank:
+                continue
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            c.connect(names[r])
+            fds = [fd.value] + ([mc_fd.value] if rank == 0 else [])
+            socket.send_fds(c, [rank.to_bytes(4, "little")], fds)
+            c.close()
+        peer_fd, got_mc = {}, None
+        for _ in range(world - 1):
+            conn, _a = srv.accept()
+            msg, fds, _f, _ad = socket.recv_fds(conn, 4, 2)
+            src = int.from_bytes(msg, "little")
+            peer_fd[src] = fds[0]
+            if src == 0 and len(fds) > 1:
+                got_mc = fds[1]
+            conn.close()
+        srv.close()
+        # ---- map everybody's memory; bind ours to the multicast object; map the multicast object
+        ptrs, self._vmm = [], {"size": size, "handles": [], "maps": []}
+        for r in range(world):
+            h = handle if r == rank else ctypes.c_ulonglong(0)
+            if r != rank:
+                _native.check(lib.hb_vmm_import(peer_fd[r], ctypes.byref(h)), "hb_vmm_import")
+                os.close(peer_fd[r])
+            out = ctypes.c_void_p(0)
+            _native.check(lib.hb_vmm_map(h.value, size, g, ctypes.byref(out)), "hb_vmm_map")
+            ptrs.append(int(out.value))
+            self._vmm["handles"].append(h.value); self._vmm["maps"].append(int(out.value))
+        os.close(fd.value)
+        self.multicast_ptr = 0
+        if world > 1:
+            if rank != 0:
+                _native.check(lib.hb_vmm_import(got_mc, ctypes.byref(mc_handle)), "hb_vmm_import(multicast)")
+                os.close(got_mc)
+            else:
+                os.close(mc_fd.value)
+            _native.check(lib.hb_mc_add_device(mc_handle.value), "hb_mc_add_device")
+            dist.barrier(group=self.group)                      # every device added before anybody binds
+            _native.check(lib.hb_mc_bind(mc_handle.value, handle.value, size), "hb_mc_bind")
+            dist.barrier(group=self.group)
+            out = ctypes.c_void_p(0)
+            _native.check(lib.hb_vmm_map(mc_handle.value, size, g, ctypes.byref(out)), "hb_vmm_map(multicast)")
+            self.multicast_ptr = int(out.value)
+            self._vmm["mc_handle"] = mc_handle.value
+
+        class _Raw:                # torch tensor over the mapping (kept alive by this workspace)
+            def __init__(self, ptr, nbytes):
+                self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+        self.slab = torch.as_tensor(_Raw(ptrs[rank], self.total_bytes), device=self.device)
+        self.slab.zero_()
+        self.peer_ptrs = ptrs
 
     def _init_ipc(self) -> None:
         # a plain torch allocation (cudaMalloc-backed block); export handle + offset of the block
@@ -240,12 +333,42 @@ class SymmetricWorkspace:
         _native.count_launch()
         return t
 
-    def allreduce_(self, t: torch.Tensor, op: str = "sum") -> torch.Tensor:
-        """In-place allreduce of a tensor living at the same offset on every rank."""
+    def allreduce_(self, t: torch.Tensor, op: str = "sum", deterministic: bool = False) -> torch.Tensor:
+        """In-place allreduce of a tensor living at the same offset on every rank.  float32 sums take the NVLS path
+        (in-switch reduction) when the slab is multicast-bound; ``deterministic=True`` keeps the rank-ordered peer-load
+        kernel, whose result is bit-identical on every rank and from run to run."""
+        if (op == "sum" and t.dtype == torch.float32 and self.has_nvls and not deterministic
+                and (t.numel() * 4) % 16 == 0 and self.offset_of(t) % 16 == 0):
+            return self._nvls(t, 0)
         return self._reduce(t, op, 0)
 
     def allreduce_sum_(self, t: torch.Tensor) -> torch.Tensor:
         return self._reduce(t, "sum", 0)
+
+    # ---- NVLS data path (needs backend "vmm": the slab is bound to a multicast object) ----
+    @property
+    def has_nvls(self) -> bool:
+        return bool(self.multicast_ptr) and self.world > 1
+
+    def _nvls(self, t: torch.Tensor, mode: int, root: int = 0) -> torch.Tensor:
+        nbytes = t.numel() * t.element_size()
+        rc = self.lib.hb_coll_nvls(self._ptr_array, ctypes.c_void_p(self.multicast_ptr), self.rank, self.world,
+                                   self.offset_of(t), nbytes, mode, int(root), self.flags_offset, self._next_ticket(),
+                                   _native.stream_ptr())
+        _native.check(rc, "hb_coll_nvls")
+        _native.count_launch()
+        return t
+
+    def nvls_allreduce_(self, t: torch.Tensor) -> torch.Tensor:
+        """In-place float32 sum allreduce with ``multimem.ld_reduce`` + ``multimem.st`` (size a multiple of 16 bytes)."""
+        assert t.dtype == torch.float32 and t.is_contiguous()
+        return self._nvls(t, 0)
+
+    def nvls_broadcast_(self, t: torch.Tensor, root: int) -> torch.Tensor:
+        return self._nvls(t, 1, root)
+
+    def nvls_allgather_(self, t: torch.Tensor) -> torch.Tensor:
+        return self._nvls(t, 2)
 
     def reduce_scatter_(self, t: torch.Tensor, op: str = "sum") -> torch.Tensor:
         """Rank r ends up with the reduced r-th 1/world slice (in place); returns that slice view."""

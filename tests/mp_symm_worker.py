@@ -229,11 +229,32 @@ def main():
     if rank == 0:
         print("table collectives on NVLink kernels ok", flush=True)
 
+    # ---- NVLS (multimem) data path, when the slab is multicast-bound (backend "vmm") ----
+    if ws.has_nvls:
+        ws.reset()
+        for n in (4, 1000 * 4, (1 << 20) + 4, 1290000):
+            t = ws.alloc(n, torch.float32)
+            src = torch.rand(n, device=dev, generator=g)
+            ref = src.clone(); dist.all_reduce(ref)
+            t.copy_(src); ws.nvls_allreduce_(t); torch.cuda.synchronize()
+            torch.testing.assert_close(t, ref, rtol=1e-5, atol=1e-5)
+            t.fill_(float(rank)); ws.nvls_broadcast_(t, world - 1); torch.cuda.synchronize()
+            assert torch.equal(t, torch.full_like(t, float(world - 1)))
+        per = 4096
+        t = ws.alloc(per * world, torch.float32); t.zero_(); t[rank * per:(rank + 1) * per] = float(rank + 1)
+        ws.nvls_allgather_(t); torch.cuda.synchronize()
+        assert torch.equal(t, torch.arange(1, world + 1, device=dev, dtype=torch.float32).repeat_interleave(per))
+        if rank == 0:
+            print("nvls multimem allreduce / broadcast / allgather ok", flush=True)
+
     # timing of the 5 MB allreduce vs NCCL
     ws.reset()
     n = 10000 * 129
     t = ws.alloc(n, torch.float32); u = torch.rand(n, device=dev)
-    for fn, name in ((lambda: ws.allreduce_sum_(t), "p2p"), (lambda: dist.all_reduce(u), "nccl")):
+    arms = [(lambda: ws.allreduce_sum_(t), "p2p"), (lambda: dist.all_reduce(u), "nccl")]
+    if ws.has_nvls:
+        arms.insert(0, (lambda: ws.nvls_allreduce_(t), "nvls"))
+    for fn, name in arms:
         for _ in range(5):
             fn()
         torch.cuda.synchronize(); dist.barrier()
