@@ -479,6 +479,58 @@ __global__ void moments_init_kernel(int d, double* sum, double* sumsq, float* mn
 }  // namespace gram
 }  // namespace hb
 
+namespace hb {
+namespace gram {
+
+// K14: [Σx ; Yᵀ X] in ONE streaming pass over X (DAAL linear_regression / ridge partials: Xᵀy and the column sums,
+// ml/daal/.../daal_linreg/normaleq/LinRegDaalCollectiveMapper.java:162-167).  Thread t of a CTA owns four
+// consecutive columns; a CTA walks a slab of rows with coalesced 16-byte loads, the row's few y values come in
+// as one broadcast load; accumulation is fp64 per thread (the pass is HBM bound: 8 B of X per 2 (m + 1) flops).
+template <int M>
+__global__ void __launch_bounds__(256) xty_kernel(const float* __restrict__ X, long long n, int d,
+                                                  const float* __restrict__ Y, double* __restrict__ out) {
+  const int c4 = blockIdx.x * blockDim.x + threadIdx.x;          // float4 column group
+  if (c4 * 4 >= d) return;
+  const long long rows_per = (n + gridDim.y - 1) / gridDim.y;
+  const long long r0 = blockIdx.y * rows_per, r1 = min(n, r0 + rows_per);
+  double acc[M + 1][4];
+#pragma unroll
+  for (int j = 0; j <= M; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0;
+  for (long long r = r0; r < r1; ++r) {
+    const float4 x = ld_nc_v4(X + (size_t)r * d + c4 * 4);
+    acc[0][0] += x.x; acc[0][1] += x.y; acc[0][2] += x.z; acc[0][3] += x.w;
+#pragma unroll
+    for (int j = 0; j < M; ++j) {
+      const double y = (double)__ldg(Y + (size_t)r * M + j);
+      acc[j + 1][0] += y * x.x; acc[j + 1][1] += y * x.y; acc[j + 1][2] += y * x.z; acc[j + 1][3] += y * x.w;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j <= M; ++j)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) red_add_f64(out + (size_t)j * d + c4 * 4 + e, acc[j][e]);
+}
+
+// rows of X minus a per-column shift (fp32): the centring step of the two-pass covariance for data whose mean is
+// large against its spread, where TF32 products of the raw values would keep almost nothing of the spread.
+__global__ void center_rows_kernel(const float* __restrict__ X, long long n, int d, const float* __restrict__ shift,
+                                   float* __restrict__ out) {
+  const int d4 = d >> 2;
+  const long long total = n * d4;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c4 = (int)(i % d4);
+    const float4 x = ld_nc_v4(X + i * 4);
+    const float4 m = __ldg(reinterpret_cast<const float4*>(shift) + c4);
+    // rounded to the nearest TF32 value here: the tensor core would otherwise TRUNCATE the low 13 bits, a one-sided error
+    // that biases every sum of squares by ~ -5e-4 relative; round-to-nearest errors are unbiased and average out
+    auto rna = [](float v) { uint32_t u; asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v)); return __uint_as_float(u); };
+    *reinterpret_cast<float4*>(out + i * 4) = make_float4(rna(x.x - m.x), rna(x.y - m.y), rna(x.z - m.z), rna(x.w - m.w));
+  }
+}
+
+}  // namespace gram
+}  // namespace hb
+
 using namespace hb;
 using namespace hb::gram;
 
@@ -625,6 +677,48 @@ int hb_moments(const float* X, long long n, int d, double* sum, double* sumsq, f
   if (gy > 65535) gy = 65535;
   if (vec4) moments_vec4_kernel<<<dim3(gx, (unsigned)gy), 256, 0, stream>>>(X, n, d, sum, sumsq, mn, mx);
   else moments_kernel<<<dim3(gx, (unsigned)gy), 256, 0, stream>>>(X, n, d, sum, sumsq, mn, mx);
+  HB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// out[(m + 1), d] (double, accumulated into: zero it first) : row 0 += column sums of X, row 1 + j += Σ_r Y[r, j] X[r, :].
+// X [n, d] and Y [n, m] row-major fp32, d % 4 == 0, 0 <= m <= 8.
+int hb_xty(const float* X, long long n, int d, const float* Y, int m, double* out, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  HB_REQUIRE(n >= 0 && d >= 4 && d % 4 == 0 && m >= 0 && m <= 8, "hb_xty: need d %% 4 == 0 and at most 8 dependent variables (d=%d, m=%d)", d, m);
+  HB_REQUIRE((reinterpret_cast<uintptr_t>(X) & 15) == 0, "hb_xty: X must be 16-byte aligned");
+  if (n == 0) return 0;
+  const int gx = (d / 4 + 255) / 256;
+  long long gy = (long long)sm_count() * 8 / gx;
+  if (gy > n) gy = n;
+  if (gy < 1) gy = 1;
+  const dim3 grid((unsigned)gx, (unsigned)gy);
+  using namespace hb::gram;
+  switch (m) {
+    case 0: xty_kernel<0><<<grid, 256, 0, stream>>>(X, n, d, Y, out); break;
+    case 1: xty_kernel<1><<<grid, 256, 0, stream>>>(X, n, d, Y, out); break;
+    case 2: xty_kernel<2><<<grid, 256, 0, stream>>>(X, n, d, Y, out); break;
+    case 3: xty_kernel<3><<<grid, 256, 0, stream>>>(X, n, d, Y, out); break;
+    case 4: xty_kernel<4><<<grid, 256, 0, stream>>>(X, n, d, Y, out); break;
+    case 5: xty_kernel<5><<<grid, 256, 0, stream>>>(X, n, d, Y, out); break;
+    case 6: xty_kernel<6><<<grid, 256, 0, stream>>>(X, n, d, Y, out); break;
+    case 7: xty_kernel<7><<<grid, 256, 0, stream>>>(X, n, d, Y, out); break;
+    default: xty_kernel<8><<<grid, 256, 0, stream>>>(X, n, d, Y, out); break;
+  }
+  HB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// out[r, :] = X[r, :] - shift[:]   (fp32, d % 4 == 0)
+int hb_center_rows(const float* X, long long n, int d, const float* shift, float* out, void* stream_) {
+  HB_REQUIRE(n >= 0 && d >= 4 && d % 4 == 0, "hb_center_rows: need d %% 4 == 0 (d=%d)", d);
+  HB_REQUIRE(((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(shift) | reinterpret_cast<uintptr_t>(out)) & 15) == 0,
+             "hb_center_rows: pointers must be 16-byte aligned");
+  if (n == 0) return 0;
+  long long blocks = (n * (d / 4) + 255) / 256;
+  const long long cap = (long long)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  hb::gram::center_rows_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream_>>>(X, n, d, shift, out);
   HB_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -12,7 +12,7 @@ Every function takes ``comm`` (a :class:`harp_b200.collective.Comm` or None for 
 from __future__ import annotations
 
 import math
-from typing import Dict, NamedTuple, Tuple
+from typing import Dict, NamedTuple, Optional, Tuple
 
 import torch
 import torch.distributed as dist
@@ -107,8 +107,35 @@ def _cross_product_partials(X: torch.Tensor, comm) -> Tuple[torch.Tensor, torch.
     return G, s, float(n.item())
 
 
-def covariance(X: torch.Tensor, comm=None) -> CovResult:
-    """``daal_cov/densedistri`` and ``csrdistri`` (``COVDaalCollectiveMapper.java:143-176``)."""
+def covariance(X: torch.Tensor, comm=None, center: Optional[bool] = None) -> CovResult:
+    """``daal_cov/densedistri`` and ``csrdistri`` (``COVDaalCollectiveMapper.java:143-176``).
+
+    ``G - N mean meanᵀ`` loses everything to cancellation once the mean is large against the spread (and TF32
+    products of the raw values have already dropped most of the spread by then), so such data takes a two-pass
+    route: exact float64 column sums first (one streaming kernel), then the tensor-core Gram of the CENTRED rows,
+    whose partial results are allreduced like the plain ones.  ``center=None`` decides from the first pass
+    (any column with |mean| > 4 sd); True / False force either route."""
+    if X.layout != torch.strided:
+        X = X.to_dense()
+    if center is not False and X.is_floating_point():
+        from ..ops.gram import centered_gram, xty
+        mom = moments(X)
+        st = torch.stack([mom.sum.double(), mom.sumsq.double(),
+                          torch.full_like(mom.sum.double(), float(X.shape[0]))])
+        _allreduce_(st, comm)
+        N = float(st[2, 0].item())
+        mean = st[0] / N
+        var = (st[1] / N - mean * mean).clamp(min=0)
+        if center is None:
+            center = bool((mean.abs() > 4.0 * var.sqrt()).any().item())
+        if center:
+            m32 = mean.to(torch.float32)
+            Gc = _f64(centered_gram(X if X.dtype == torch.float32 or X.device.type != "cuda" else X.float(), m32))
+            _allreduce_(Gc, comm)
+            delta = mean - m32.double()                      # the shift was the float32-rounded mean
+            cov = (Gc - N * torch.outer(delta, delta)) / max(N - 1.0, 1.0)
+            sd = cov.diag().clamp(min=1e-300).sqrt()
+            return CovResult(cov, mean, int(N), cov / torch.outer(sd, sd))
     G, s, N = _cross_product_partials(X, comm)
     mean = s / N
     cov = (G - N * torch.outer(mean, mean)) / max(N - 1.0, 1.0)
@@ -229,10 +256,42 @@ class LinearModel(NamedTuple):
 
 
 def _normal_eq_partials(X: torch.Tensor, Y: torch.Tensor, comm):
-    """Partial (ZᵀZ) of Z = [1 | X | Y] — one Gram call gives XᵀX, Xᵀy, Σx, Σy, n."""
+    """ZᵀZ of Z = [1 | X | Y] assembled from its blocks WITHOUT building Z: XᵀX from the (fused, allreduced) Gram of X
+    itself, [Σx ; YᵀX] from one streaming pass (K14, ``ops.gram.xty``, float64 accumulation — no TF32 in the intercept
+    and Xᵀy terms), and the tiny Y blocks in float64."""
     n, d = X.shape
     k = Y.shape[1]
     width = 1 + d + k
+    if X.device.type == "cuda" and X.dtype == torch.float32 and d % 32 == 0 and k <= 8:
+        from ..ops.gram import centered_gram, xty
+        small = torch.zeros(k + 2, max(d, k + 1), dtype=torch.float64, device=X.device)
+        small[:k + 1, :d] = xty(X, Y)
+        Yd = Y.double()
+        small[k + 1, 0] = float(n)
+        small[k + 1, 1:1 + k] = Yd.sum(0)
+        yty = Yd.t() @ Yd
+        _allreduce_(small, comm); _allreduce_(yty, comm)
+        G = _gram_allreduced(X, comm)                                   # [d, d] float64, already global
+        # The tensor core truncates its inputs to TF32; on columns with a non-zero mean that one-sided error is a
+        # rank-one bias ~ -7e-4 N m mᵀ whose norm grows with d |m|² and soon rivals the covariance the solve depends on.
+        # Such data gets XᵀX rebuilt, in float64, from the Gram of the CENTRED rows and the exact column sums.
+        N = float(small[k + 1, 0].item())
+        mean = small[0, :d] / N
+        var = (G.diag() / N - mean * mean).clamp(min=0)
+        if bool((mean.abs() > 0.05 * var.sqrt()).any().item()):
+            m32 = mean.to(torch.float32)
+            Gc = _f64(centered_gram(X, m32))
+            _allreduce_(Gc, comm)
+            sx, m = small[0, :d], m32.double()
+            G = Gc + torch.outer(sx, m) + torch.outer(m, sx) - N * torch.outer(m, m)
+        Z = torch.zeros(width, width, dtype=torch.float64, device=X.device)
+        Z[0, 0] = small[k + 1, 0]
+        Z[0, 1:1 + d] = small[0, :d]; Z[1:1 + d, 0] = small[0, :d]
+        Z[1:1 + d, 1:1 + d] = G
+        Z[1 + d:, 1:1 + d] = small[1:k + 1, :d]; Z[1:1 + d, 1 + d:] = small[1:k + 1, :d].t()
+        Z[0, 1 + d:] = small[k + 1, 1:1 + k]; Z[1 + d:, 0] = small[k + 1, 1:1 + k]
+        Z[1 + d:, 1 + d:] = yty
+        return Z
     pad = (-width) % 32 if X.device.type == "cuda" else 0          # tensor-core path wants d % 32 == 0
     Z = torch.zeros(n, width + pad, dtype=X.dtype, device=X.device)
     Z[:, 0] = 1

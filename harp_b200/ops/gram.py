@@ -21,6 +21,8 @@ def _declare(lib) -> None:
     lib.hb_gram_tc_supported.argtypes = [I]
     lib.hb_gram.argtypes = [P, LL, I, P, I, P]
     lib.hb_moments.argtypes = [P, LL, I, P, P, P, P, I, P]
+    lib.hb_xty.argtypes = [P, LL, I, P, I, P, P]
+    lib.hb_center_rows.argtypes = [P, LL, I, P, P, P]
     lib._hb_gram_declared = True
 
 
@@ -45,6 +47,50 @@ def gram(X: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool =
     _native.check(lib.hb_gram(_native.ptr(X), n, d, _native.ptr(out), flags, _native.stream_ptr()), "hb_gram")
     _native.count_launch(2)
     return out
+
+
+def xty(X: torch.Tensor, Y: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``[Σx ; Yᵀ X]`` as ``[(m + 1), d]`` float64 in one streaming pass over ``X`` (K14, ``hb_xty``): row 0 holds the
+    column sums, row ``1 + j`` the cross products with dependent variable ``j``.  The normal-equation partials of
+    linear / ridge regression without ever building ``[1 | X | Y]``."""
+    n, d = X.shape
+    m = 0 if Y is None else Y.shape[1]
+    if X.device.type != "cuda" or d % 4 != 0 or m > 8 or X.dtype != torch.float32:
+        Xd = X.double()
+        rows = [Xd.sum(0)] + ([Y.double().t() @ Xd] if m else [])
+        return torch.cat([rows[0][None, :]] + rows[1:], 0)
+    lib = _native.lib()
+    _declare(lib)
+    X = X.contiguous()
+    Yc = Y.to(torch.float32).contiguous() if m else None
+    out = torch.zeros(m + 1, d, dtype=torch.float64, device=X.device)
+    _native.check(lib.hb_xty(_native.ptr(X), n, d, _native.ptr(Yc), m, _native.ptr(out), _native.stream_ptr()), "hb_xty")
+    _native.count_launch()
+    return out
+
+
+def centered_gram(X: torch.Tensor, shift: torch.Tensor, chunk_rows: int = 1 << 20) -> torch.Tensor:
+    """``Σ (x - shift)(x - shift)ᵀ`` (float32 result, tensor-core Gram of centred rows).  X is centred chunk by chunk
+    into one scratch buffer of ``chunk_rows`` rows (``hb_center_rows``) and the chunks' Grams are accumulated, so the
+    extra memory is bounded; used when the mean of the data is large against its spread, where TF32 products of the raw
+    values keep almost nothing of the spread."""
+    n, d = X.shape
+    if X.device.type != "cuda" or d % 4 != 0:
+        Xc = X - shift.to(X.dtype)
+        return Xc.t() @ Xc
+    lib = _native.lib()
+    _declare(lib)
+    X = X.contiguous()
+    sh = shift.to(torch.float32).contiguous()
+    G = torch.zeros(d, d, dtype=torch.float32, device=X.device)
+    buf = torch.empty(min(n, chunk_rows), d, dtype=torch.float32, device=X.device)
+    for r0 in range(0, n, chunk_rows):
+        rows = min(chunk_rows, n - r0)
+        _native.check(lib.hb_center_rows(_native.ptr(X[r0:]), rows, d, _native.ptr(sh), _native.ptr(buf),
+                                         _native.stream_ptr()), "hb_center_rows")
+        _native.count_launch()
+        gram(buf[:rows], out=G, accumulate=True)
+    return G
 
 
 class Moments(NamedTuple):

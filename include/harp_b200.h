@@ -120,6 +120,11 @@ int hb_gram(const float* X, long long n, int d, float* G, int flags, void* strea
 size_t hb_gram_fused_state_bytes(int d);
 int hb_gram_allreduce_fused(const float* X, long long n, int d, void* const* peer_state, int rank, int world,
                             unsigned epoch, void* stream);
+/* K14: out[(m+1), d] (double, accumulated: zero first): row 0 += column sums of X, row 1+j += sum_r Y[r,j] X[r,:]; one
+ * streaming pass (MD/daal_linreg/normaleq/LinRegDaalCollectiveMapper.java:162-167).  d % 4 == 0, m <= 8. */
+int hb_xty(const float* X, long long n, int d, const float* Y, int m, double* out, void* stream);
+/* out[r,:] = X[r,:] - shift[:] (centring step of the two-pass covariance; d % 4 == 0). */
+int hb_center_rows(const float* X, long long n, int d, const float* shift, float* out, void* stream);
 /* Per-column sum / sum of squares (double) and min / max (float) of X[n,d]. */
 int hb_moments(const float* X, long long n, int d, double* sum, double* sumsq, float* mn, float* mx,
                int flags, void* stream);

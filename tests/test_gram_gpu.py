@@ -60,3 +60,41 @@ def test_gram_fused_single_gpu(native_built, n, d):
             G2 = gram(X)
             torch.cuda.synchronize()
             torch.testing.assert_close(G, G2, rtol=1e-5, atol=1e-4 * scale)   # split-K reductions land in any order
+
+
+def test_covariance_of_data_with_a_large_mean(native_built):
+    """mean 100, spread 1: the two-pass route (exact float64 column sums, then the tensor-core Gram of the centred
+    rows) must reproduce the float64 covariance to rtol 1e-4 in the diagonal and 1e-3 of sd_i sd_j off it; the
+    one-pass G - N m mᵀ route, forced, is shown NOT to (that is why the default switches)."""
+    from harp_b200.daal.linalg import covariance
+    g = torch.Generator(device="cuda").manual_seed(0)
+    n, d = 200_000, 256
+    A = torch.randn(d, d, device="cuda", generator=g) * 0.2 + torch.eye(d, device="cuda")
+    X = (torch.randn(n, d, device="cuda", generator=g) @ A + 100.0).contiguous()
+    ref = torch.cov(X.double().t())
+    c = covariance(X)
+    torch.testing.assert_close(c.mean, X.double().mean(0), rtol=1e-10, atol=1e-9)
+    sd = ref.diag().sqrt()
+    torch.testing.assert_close(c.covariance.diag(), ref.diag(), rtol=1e-4, atol=0)
+    assert float(((c.covariance - ref).abs() / torch.outer(sd, sd)).max()) < 1e-3
+    bad = covariance(X, center=False)
+    assert float(((bad.covariance - ref).abs() / torch.outer(sd, sd)).max()) > 1e-2
+
+
+def test_xty_and_linear_regression_without_copy(native_built):
+    from harp_b200.daal.linalg import linear_regression_normeq
+    from harp_b200.ops.gram import xty
+    g = torch.Generator(device="cuda").manual_seed(1)
+    n, d, k = 100_000, 128, 2
+    X = (torch.randn(n, d, device="cuda", generator=g) + 3.0).contiguous()
+    beta = torch.randn(k, d + 1, device="cuda", generator=g, dtype=torch.float64)
+    Y = (X.double() @ beta[:, 1:].t() + beta[:, 0] + 0.01 * torch.randn(n, k, device="cuda", generator=g, dtype=torch.float64)).float()
+    out = xty(X, Y)
+    torch.testing.assert_close(out[0], X.double().sum(0), rtol=1e-12, atol=1e-6)
+    torch.testing.assert_close(out[1:], Y.double().t() @ X.double(), rtol=1e-10, atol=1e-4)
+    peak0 = torch.cuda.max_memory_allocated()
+    model = linear_regression_normeq(X, Y)
+    assert torch.cuda.max_memory_allocated() - peak0 < X.numel() * 2          # no [1 | X | Y] copy of X
+    torch.testing.assert_close(model.beta, beta, rtol=5e-2, atol=5e-2)
+    pred = model.predict(X)
+    assert float((pred - Y.double()).pow(2).mean().sqrt()) < 0.05
