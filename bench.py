@@ -297,7 +297,7 @@ def main():
         ea, eobj = exact.assign.long(), float(exact.obj)
         precision_report = {"sample_points": ns, "oracle": "exact fp32 SIMT kernel (assign_simt_kernel)"}
         for prec in ("fp16x3", "bf16x3", "tf32"):
-            es = KMeansEngine(Xsmp, k, precision=prec)           # single-GPU engine on the sample
+            es = KMeansEngine(Xsmp, k, precision=prec, local=True)           # single-GPU engine on the sample
             es.set_centroids(Cnow)
             a = torch.full((ns,), -1, dtype=torch.int32, device=dev)
             es.fused.step(Xsmp, assign=a, Xs=es.Xs)

@@ -31,7 +31,7 @@ from ..ops import kmeans as kops
 
 class KMeansEngine:
     def __init__(self, X: torch.Tensor, k: int, *, comm: str = "auto", group=None,
-                 keep_empty: bool = False, symm=None, precision: Optional[str] = None):
+                 keep_empty: bool = False, symm=None, precision: Optional[str] = None, local: bool = False):
         assert X.dim() == 2
         self.X = X.contiguous() if X.device.type == "cuda" else X
         self.n, self.d = X.shape
@@ -39,7 +39,8 @@ class KMeansEngine:
         self.dev = X.device
         self.group = group
         self.keep_empty = keep_empty
-        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        # local=True: a single-GPU engine even inside a multi-rank job (no collective, e.g. to score a sample)
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized() and not local) else 1
         self.rank = dist.get_rank(group) if self.world > 1 else 0
         self.symm = symm
         self.variant = os.environ.get("HB_KMEANS_VARIANT", "auto")
