@@ -25,7 +25,7 @@ class LDAEngine:
                  alpha: float, beta: float, *, symm=None, blocks: Optional[int] = None, seed: int = 0, group=None,
                  num_slices: Optional[int] = None, dk_dtype: str = "auto", fused: Optional[bool] = None,
                  cluster: Optional[int] = None, loopback: bool = False, max_run: Optional[int] = None,
-                 virtual_world: int = 0):
+                 virtual_world: int = 0, sampler: Optional[str] = None):
         self.dev = docs.device
         self.K, self.V = int(K), int(vocab)
         self.alpha, self.beta = float(alpha), float(beta)
@@ -57,17 +57,33 @@ class LDAEngine:
             longest = int(torch.bincount(docs.long(), minlength=1).max().item()) if docs.numel() else 0
             dk_dtype = "int16" if (cuda and longest < 32768) else "int32"
         self.dk16 = dk_dtype == "int16"
+        # Sampler: "dense" forms p_k for all K topics per token (csrc/lda.cu, K <= 2048); "tokenlist" is the
+        # SparseLDA-style sampler of csrc/lda_tl.cu (document bucket = sum over the document's token list, word and
+        # smoothing buckets through block sums; any K <= 16384, no document-topic table).  Default: tokenlist on GPUs.
+        sampler = sampler or os.environ.get("HB_LDA_SAMPLER")
+        can_fuse = cuda and (self.N == 1 or self.symm is not None)
+        if sampler is None:
+            # measured on BASELINE config 4 (K = 1000, 100-token documents): dense 1.42 G tokens/s, token list 0.61 G on
+            # one B200 — the dense kernel prefetches the next document row while it samples, the token-list kernel
+            # pays two dependent gathers per token; so dense wherever it exists, token list beyond
+            dense_ok = L.epoch_supported(self.K, self.dk16) if cuda else True
+            sampler = "dense" if (dense_ok or not can_fuse or fused is False) else "tokenlist"
+        self.sampler = sampler
+        self.tl = sampler == "tokenlist"
+        if self.tl:
+            assert can_fuse, "the token-list sampler runs in the whole-iteration kernel (CUDA; symmetric workspace when N > 1)"
+            fused = True
         if fused is None:
-            fused = (cuda and (self.N == 1 or self.symm is not None) and os.environ.get("HB_LDA_FUSED", "1") != "0"
-                     and L.epoch_supported(self.K, self.dk16))
+            fused = (can_fuse and os.environ.get("HB_LDA_FUSED", "1") != "0" and L.epoch_supported(self.K, self.dk16))
         self.fused = bool(fused)
         self.cs = 1
         if cuda and self.fused:
             self.cs = int(cluster) if cluster else _mf.pick_cluster(per_panel * 8)    # a token costs ~8x a rating
-            mx = L.epoch_max_workers(self.K, self.dk16, self.cs)
+            maxw = (lambda c: L.tl_max_workers(self.K, c)) if self.tl else (lambda c: L.epoch_max_workers(self.K, self.dk16, c))
+            mx = maxw(self.cs)
             while mx < 1 and self.cs > 1:
                 self.cs //= 2
-                mx = L.epoch_max_workers(self.K, self.dk16, self.cs)
+                mx = maxw(self.cs)
             self.B = max(1, min(int(blocks) if blocks else mx, mx))
             if max_run is None:
                 x = per_panel / (self.B * self.B) / (2.0 * self.cs * 24)        # ~2 runs per sampling warp of a worker
@@ -84,22 +100,36 @@ class LDAEngine:
         self.ntok = int(docs.numel())
         z = torch.randint(0, self.K, (self.ntok,), device=self.dev, generator=g)
         words = words.to(torch.int64)
+        pos = None
+        if self.tl:
+            # the rank's tokens in document order: doc_z[d_ptr[d] .. d_ptr[d+1]) are the current topics of document d
+            order = torch.argsort(docs.to(torch.int64), stable=True)
+            pos = torch.empty(self.ntok, dtype=torch.int64, device=self.dev)
+            pos[order] = torch.arange(self.ntok, device=self.dev)
+            self.doc_z = z[order].to(torch.int32).contiguous()
+            self.d_ptr = torch.zeros(num_docs_local + 1, dtype=torch.int32, device=self.dev)
+            self.d_ptr[1:] = torch.cumsum(torch.bincount(docs.to(torch.int64), minlength=num_docs_local), 0).to(torch.int32)
+            self.doc_of_pos = docs.to(torch.int64)[order]
         shard, slc, local = words % N, (words // N) % S, words // (S * N)
         self.panels: List[List[L.TokenPanel]] = []
         for s in range(N):
             per = []
             for k in range(self.S):
                 m = (shard == s) & (slc == k)
-                per.append(L.build_token_panel(docs[m], local[m], z[m], self.B, max_run=self.max_run))
+                per.append(L.build_token_panel(docs[m], local[m], z[m], self.B, max_run=self.max_run,
+                                               pos=pos[m] if pos is not None else None))
             self.panels.append(per)
         cdt = torch.int32
-        self.n_dk = torch.zeros(num_docs_local, self.K, dtype=cdt, device=self.dev)
-        for s in range(N):
-            for k in range(self.S):
-                p = self.panels[s][k]
-                L.count_into(p.tok_doc, p.tok_z, self.K, self.n_dk)
-        if self.dk16:
-            self.n_dk = self.n_dk.to(torch.int16)
+        self.num_docs_local = int(num_docs_local)
+        self._n_dk = None
+        if not self.tl:
+            self._n_dk = torch.zeros(num_docs_local, self.K, dtype=cdt, device=self.dev)
+            for s in range(N):
+                for k in range(self.S):
+                    p = self.panels[s][k]
+                    L.count_into(p.tok_doc, p.tok_z, self.K, self._n_dk)
+            if self.dk16:
+                self._n_dk = self._n_dk.to(torch.int16)
         self.ring = None
         self._cur = [0] * S
         self.sched = [RingSchedule(self.N, None) for _ in range(S)]     # plain ring (LDAMPCollectiveMapper.java:255-259)
@@ -129,10 +159,21 @@ class LDAEngine:
         self.trained = torch.zeros(1, dtype=torch.int64, device=self.dev)
         self.epochs_fused = 0
         if cuda:
-            self.desc = L.panel_descriptors([self.panels[s][k] for s in range(N) for k in range(S)])
+            flat = [self.panels[s][k] for s in range(N) for k in range(S)]
+            self.desc = L.tl_panel_descriptors(flat) if self.tl else L.panel_descriptors(flat)
         self._refresh_topic_sums()
         if dist.is_initialized() and N > 1:
             dist.barrier(group=group)
+
+    @property
+    def n_dk(self) -> torch.Tensor:
+        """Document-topic counts.  The token-list sampler keeps no such table: it is rebuilt from the documents' token
+        lists on demand (tests, model dumps)."""
+        if self._n_dk is not None:
+            return self._n_dk
+        t = torch.zeros(self.num_docs_local, self.K, dtype=torch.int32, device=self.dev)
+        t.view(-1).index_add_(0, self.doc_of_pos * self.K + self.doc_z.long(), torch.ones(self.ntok, dtype=torch.int32, device=self.dev))
+        return t
 
     @property
     def cur(self) -> List[int]:
@@ -193,9 +234,13 @@ class LDAEngine:
                         src_l.append(self.sched[k].rotate()[self.me])
             for k in range(S):
                 self._wait_slice(k)
-            L.lda_epoch(self.n_dk, self.commons, self.desc, pos_l, S, self.B, self.cs, self.alpha, self.beta,
-                        self.seed * 1000003 + self.iteration * 7919 + 104729 * self.me, self.epochs_fused, deadline_ms,
-                        self.trained, self.ring, src_l)
+            seed_it = self.seed * 1000003 + self.iteration * 7919 + 104729 * self.me
+            if self.tl:
+                L.lda_tl_epoch(self.doc_z, self.d_ptr, self.commons, self.K, self.desc, pos_l, S, self.B, self.cs, self.alpha,
+                               self.beta, seed_it, self.epochs_fused, deadline_ms, self.trained, self.ring, src_l)
+            else:
+                L.lda_epoch(self._n_dk, self.commons, self.desc, pos_l, S, self.B, self.cs, self.alpha, self.beta,
+                            seed_it, self.epochs_fused, deadline_ms, self.trained, self.ring, src_l)
             self.epochs_fused += 1
             self.ring.advance(N)
             tb = (self.epochs_fused * self.B) & 0x7FFFFFFF
@@ -222,15 +267,20 @@ class LDAEngine:
         acc = torch.zeros(1, dtype=torch.float64, device=self.dev)
         for k in range(self.S):
             self._wait_slice(k)
-            tab = self.Wbuf[k][self.cur[k]].double()
-            # only rows that are real words of this shard/slice
-            s = self._visiting(k)
-            gid = torch.arange(self.cap, device=self.dev) * (self.S * self.N) + k * self.N + s
-            tab = tab[gid < V]
-            acc += torch.lgamma(tab + b).sum() - tab.shape[0] * K * math.lgamma(b)
-        nd = self.n_dk.double()
-        doc = (torch.lgamma(nd + a).sum() - torch.lgamma(nd.sum(1) + K * a).sum()
-               + nd.shape[0] * (math.lgamma(K * a) - K * math.lgamma(a)))
+            # K11: one fused pass over the int32 table (rows beyond the vocabulary are all zero and add nothing);
+            # Σ lgamma(n + β) − (rows K) lgamma(β) = Σ_{n>0} [lgamma(n + β) − lgamma(β)]
+            sm, nz = L.lgamma_sum(self.Wbuf[k][self.cur[k]], b)
+            acc += sm - nz * math.lgamma(b)
+        if self.tl:
+            # sparse document side from the token lists: counts of the distinct (document, topic) pairs
+            _, cnt = torch.unique(self.doc_of_pos * K + self.doc_z.long(), return_counts=True)
+            lens = (self.d_ptr[1:] - self.d_ptr[:-1]).double()
+            doc = ((torch.lgamma(cnt.double() + a) - math.lgamma(a)).sum() - torch.lgamma(lens + K * a).sum()
+                   + lens.numel() * math.lgamma(K * a))
+        else:
+            nd = self._n_dk.double()
+            doc = (torch.lgamma(nd + a).sum() - torch.lgamma(nd.sum(1) + K * a).sum()
+                   + nd.shape[0] * (math.lgamma(K * a) - K * math.lgamma(a)))
         acc += doc
         if self.N > 1:
             dist.all_reduce(acc, group=self.group)

@@ -27,6 +27,11 @@ def _declare(lib) -> None:
     lib.hb_lda_epoch_max_workers.argtypes = [I, I, I]
     lib.hb_lda_epoch.argtypes = [P, I, P, P, I, P, I, I, I, I, I, F, F, ULL, U, ULL, P,
                                  P, I, I, ULL, P, P, P, U, P, ULL, P]
+    lib.hb_lda_tl_supported.argtypes = [I]
+    lib.hb_lda_tl_max_workers.argtypes = [I, I]
+    lib.hb_lda_tl_epoch.argtypes = [P, P, P, P, I, P, I, I, I, I, I, F, F, ULL, U, ULL, P,
+                                    P, I, I, ULL, P, P, P, U, P, ULL, P]
+    lib.hb_lgamma_sum.argtypes = [P, LL, ctypes.c_double, P, P, P]
     lib._hb_lda_declared = True
 
 
@@ -42,6 +47,7 @@ class TokenPanel:
     tok_word: torch.Tensor    # int32 [ntok] slice-local word id (for table initialisation / checks)
     col_ticket: torch.Tensor
     ticket_base: int = 0
+    tok_pos: Optional[torch.Tensor] = None   # token -> index into the rank's document-ordered topic list (token-list sampler)
 
     @property
     def ntok(self) -> int:
@@ -89,13 +95,62 @@ def lda_epoch(n_dk: torch.Tensor, commons: torch.Tensor, desc, panel_of_step,
     _native.count_launch()
 
 
-def build_token_panel(docs: torch.Tensor, words: torch.Tensor, z: torch.Tensor, B: int, max_run: int = 64) -> TokenPanel:
-    sp = mf.build_panel(docs, words, z.to(torch.float32), B, max_run=max_run)
+def tl_max_workers(K: int, cs: int) -> int:
+    lib = _native.lib()
+    _declare(lib)
+    return int(lib.hb_lda_tl_max_workers(int(K), int(cs)))
+
+
+def tl_panel_descriptors(panels):
+    """Host array of the 7-pointer descriptors of the token-list kernel (``csrc/lda_tl.cu::PanelDesc``)."""
+    flat = [t.data_ptr() for p in panels for t in (p.blk_seg_ptr, p.seg_word, p.seg_ptr, p.tok_doc, p.tok_z, p.col_ticket,
+                                                    p.tok_pos)]
+    return (ctypes.c_uint64 * len(flat))(*flat)
+
+
+def lda_tl_epoch(doc_z: torch.Tensor, d_ptr: torch.Tensor, commons: torch.Tensor, K: int, desc, panel_of_step, S: int,
+                 workers: int, cs: int, alpha: float, beta: float, seed: int, ticket_epoch: int,
+                 deadline_ms: Optional[float], trained: torch.Tensor, ring, src_of_step) -> None:
+    """One iteration with the SparseLDA-style token-list sampler (``hb_lda_tl_epoch``), any K <= 16384."""
+    lib = _native.lib()
+    _declare(lib)
+    deadline = int(deadline_ms * 1e6) if deadline_ms is not None else 0
+    steps = len(panel_of_step)
+    pos = (ctypes.c_int * steps)(*panel_of_step)
+    rc = lib.hb_lda_tl_epoch(_native.ptr(doc_z), _native.ptr(d_ptr), _native.ptr(commons), desc, len(desc) // 7, pos, steps,
+                             S, workers, cs, int(K), float(alpha), float(beta), int(seed) & 0xFFFFFFFFFFFFFFFF,
+                             ticket_epoch & 0xFFFFFFFF, deadline, _native.ptr(trained), *ring.ring_args(src_of_step),
+                             _native.stream_ptr())
+    _native.check(rc, "hb_lda_tl_epoch")
+    _native.count_launch()
+
+
+def lgamma_sum(counts: torch.Tensor, add: float):
+    """``(Σ_{c>0} lgamma(c + add), #non-zeros)`` of an int32 count table in one fused pass (K11, ``hb_lgamma_sum``)."""
+    if counts.device.type != "cuda" or counts.dtype != torch.int32:
+        c = counts[counts > 0].double()
+        return float(torch.lgamma(c + add).sum()), int(c.numel())
+    lib = _native.lib()
+    _declare(lib)
+    out = torch.zeros(1, dtype=torch.float64, device=counts.device)
+    nnz = torch.zeros(1, dtype=torch.int64, device=counts.device)
+    c = counts.contiguous()
+    _native.check(lib.hb_lgamma_sum(_native.ptr(c), c.numel(), float(add), _native.ptr(out), _native.ptr(nnz),
+                                    _native.stream_ptr()), "hb_lgamma_sum")
+    _native.count_launch()
+    return float(out.item()), int(nnz.item())
+
+
+def build_token_panel(docs: torch.Tensor, words: torch.Tensor, z: torch.Tensor, B: int, max_run: int = 64,
+                      pos: Optional[torch.Tensor] = None) -> TokenPanel:
+    assert int(z.max().item()) < (1 << 24) if z.numel() else True      # topics travel through a float32 column
+    sp = mf.build_panel(docs, words, z.to(torch.float32), B, max_run=max_run, payload=pos)
     # recover each token's word from the run structure
     seg_len = (sp.seg_ptr[1:] - sp.seg_ptr[:-1]).long()
     tok_word = torch.repeat_interleave((sp.seg_col & 0x7FFFFFFF).to(torch.int32), seg_len)
     return TokenPanel(B, sp.blk_seg_ptr, sp.seg_col, sp.seg_ptr, sp.r_row, sp.r_val.to(torch.int32).contiguous(),
-                      tok_word.contiguous(), sp.col_ticket)
+                      tok_word.contiguous(), sp.col_ticket, 0,
+                      sp.extra.to(torch.int32).contiguous() if sp.extra is not None else None)
 
 
 def count_into(idx0: torch.Tensor, z: torch.Tensor, K: int, counts: torch.Tensor) -> None:

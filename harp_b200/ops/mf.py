@@ -43,6 +43,7 @@ class SgdPanel:
     col_ticket: torch.Tensor    # uint32-as-int32 [C]: ring tickets, or (dynamic schedule) locks that rest at 0
     ticket_base: int = 0
     C: int = 0                  # column-blocks; 0 / == B -> Latin-square ticket ring, > B -> dynamic schedule
+    extra: Optional[torch.Tensor] = None   # caller's per-rating payload, permuted like the ratings
 
     @property
     def ncolblocks(self) -> int:
@@ -153,7 +154,8 @@ def _serpentine_blocks(weight: torch.Tensor, B: int, greedy_rounds: int = 64) ->
 
 
 def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: int, max_run: int = 32,
-                hot_spread: bool = True, balance: bool = True, C: Optional[int] = None, lpt: bool = True) -> SgdPanel:
+                hot_spread: bool = True, balance: bool = True, C: Optional[int] = None, lpt: bool = True,
+                payload: Optional[torch.Tensor] = None) -> SgdPanel:
     """Buckets a COO rating list (worker-local row ids, slice-local column ids).  Rows and columns are dealt
     to the B row-blocks / column-blocks by weight (``balance=False``: row % B, col % B); inside a block
     ratings are ordered by column (then by original order).
@@ -230,7 +232,8 @@ def build_panel(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, B: i
     blk_seg_ptr = torch.searchsorted(seg_blk, torch.arange(B * C + 1, device=dev, dtype=torch.int64)).to(torch.int32)
     return SgdPanel(B, blk_seg_ptr.contiguous(), seg_col.contiguous(), seg_ptr.to(torch.int32).contiguous(),
                     rows[order].to(torch.int32).contiguous(), vals[order].to(torch.float32).contiguous(),
-                    torch.zeros(C, dtype=torch.int32, device=dev), 0, C)
+                    torch.zeros(C, dtype=torch.int32, device=dev), 0, C,
+                    payload[order].contiguous() if payload is not None else None)
 
 
 def row_collision_bound(panel: SgdPanel) -> float:
