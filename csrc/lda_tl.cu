@@ -125,7 +125,30 @@ __device__ __forceinline__ unsigned long long run_segment(const Core& a, int seg
     // ---- document bucket: sum over the document's other tokens of (n_w,z + beta) c_z ----
     const int p0 = a.d_ptr[d], p1 = a.d_ptr[d + 1];
     float dsum = 0.f;
-    for (int j0 = p0; j0 < p1; j0 += 32) {
+    // the first KEEP rounds (documents up to 128 tokens) stay in registers so that a draw from this bucket does not
+    // gather the word counts a second time
+    constexpr int KEEP = 4;
+    float vr[KEEP], tr[KEEP];
+    int zr[KEEP];
+#pragma unroll
+    for (int r = 0; r < KEEP; ++r) { vr[r] = 0.f; tr[r] = 0.f; zr[r] = zold; }
+#pragma unroll
+    for (int r = 0; r < KEEP; ++r) {
+      const int j = p0 + r * 32 + lane;
+      if (p0 + r * 32 < p1) {
+        if (j < p1 && j != pos) {
+          zr[r] = a.doc_z[j];
+          const int nw = ldcg_i32(wrow + zr[r]) - (zr[r] == zold ? 1 : 0);
+          vr[r] = ((float)max(nw, 0) + a.beta) * s_cm[zr[r]];
+        }
+        float t = vr[r];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        tr[r] = t;
+        dsum += t;
+      }
+    }
+    for (int j0 = p0 + KEEP * 32; j0 < p1; j0 += 32) {
       const int j = j0 + lane;
       float v = 0.f;
       if (j < p1 && j != pos) {
@@ -141,8 +164,25 @@ __device__ __forceinline__ unsigned long long run_segment(const Core& a, int seg
     float u = uniform01(a.seed, (unsigned long long)tk * 2654435761ULL + (unsigned long long)salt) * (dsum + amass);
     int znew = zold;
     if (u < dsum) {
-      // walk the token list again (it is in L1 / L2 now) and stop in the round that contains u
-      for (int j0 = p0; j0 < p1; j0 += 32) {
+      bool found = false;
+#pragma unroll
+      for (int r = 0; r < KEEP; ++r) {
+        if (!found && p0 + r * 32 < p1) {
+          const bool last = (p0 + (r + 1) * 32 >= p1);
+          if (u < tr[r] || last) {
+            const float inc = warp_incl_scan(vr[r], lane);
+            const unsigned m = __ballot_sync(0xffffffffu, inc > u && vr[r] > 0.f);
+            const unsigned any = __ballot_sync(0xffffffffu, vr[r] > 0.f);
+            const int l = m ? (__ffs(m) - 1) : (any ? (31 - __clz(any)) : 0);
+            znew = __shfl_sync(0xffffffffu, zr[r], l);
+            found = true;
+          } else {
+            u -= tr[r];
+          }
+        }
+      }
+      // longer documents: walk the rest of the list again and stop in the round that contains u
+      for (int j0 = p0 + KEEP * 32; j0 < p1 && !found; j0 += 32) {
         const int j = j0 + lane;
         float v = 0.f;
         int z = zold;
@@ -158,7 +198,7 @@ __device__ __forceinline__ unsigned long long run_segment(const Core& a, int seg
           const unsigned any = __ballot_sync(0xffffffffu, v > 0.f);
           const int l = m ? (__ffs(m) - 1) : (any ? (31 - __clz(any)) : 0);
           znew = __shfl_sync(0xffffffffu, z, l);
-          break;
+          found = true;
         }
         u -= tot;
       }

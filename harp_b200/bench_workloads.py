@@ -38,7 +38,7 @@ def run_workload(args, rank, world, dev, sampler_cls=None):
     if world > 1:
         from .parallel.symm import SymmetricWorkspace
         try:
-            symm = SymmetricWorkspace(dev, bytes_=3 << 29)
+            symm = SymmetricWorkspace(dev, bytes_=(3 << 29) if args.workload != "lda10k" else (12 << 30))
         except Exception:  # noqa: BLE001
             symm = None
     out = measure_workload(args.workload, args.steps, args.warmup, rank, world, dev, symm, sampler_cls)
@@ -98,9 +98,11 @@ def measure_workload(workload, steps, warmup, rank, world, dev, symm, sampler_cl
                                    "ratings": nnz, "rank": rk, "parallelism": f"rows dp{world} + H rotation",
                                    "l2": "W (245 MB) + ratings (1.2 GB) exceed L2"}})
             result = out
-    elif args.workload == "lda":
+    elif args.workload in ("lda", "lda10k"):
         from .models.lda import LDAEngine
         D, V, K, L = 1_000_000, 100_000, 1000, 100
+        if args.workload == "lda10k":        # the shape of the reference's published LDA runs: K = 10 000, V = 1 M
+            V, K = 1_000_000, 10_000
         d_local = D // world
         g = torch.Generator(device=dev).manual_seed(5 + rank)
         docs = torch.arange(d_local, device=dev).repeat_interleave(L)
@@ -120,7 +122,10 @@ def measure_workload(workload, steps, warmup, rank, world, dev, symm, sampler_cl
         if rank == 0:
             out.update({"metric": "lda_cgs_tokens_per_s", "value": D * L / (ms / 1e3), "unit": "tokens/s",
                         "higher_is_better": True, "scaling": "strong", "dtype": "int32 counts / fp32 probabilities",
-                        "config": {"model": "LDA-CGS model rotation (BASELINE config 4)", "docs": D, "vocab": V,
+                        "sampler": eng.sampler,
+                        "config": {"model": "LDA-CGS model rotation (BASELINE config 4)" if K == 1000 else
+                                   "LDA-CGS model rotation, K = 10 000 topics, 1 M vocabulary (clueweb-shaped, lda-cgs.md:36-40)",
+                                   "docs": D, "vocab": V,
                                    "topics": K, "tokens": D * L, "parallelism": f"docs dp{world} + word-topic rotation",
                                    "l2": "doc-topic table (4 GB) exceeds L2"}})
             result = out
