@@ -200,16 +200,34 @@ class CCDCollectiveMapper(CollectiveMapper):
         Cc, ptr_c, idx_c = csr(by_col, 1, 0, nloc_c)
         g = torch.Generator(device=dev).manual_seed(self.seed + 11)
         scale = 1.0 / math.sqrt(self.r)
-        W = torch.rand(self.r, nrows, device=dev, generator=g, dtype=wdt) * scale      # feature-major (rank-1 rows)
-        H = torch.zeros(self.r, ncols, device=dev, dtype=wdt)                           # CCD++ starts from H = 0
+        # W and H are SHARDED: rank r keeps the rank-one rows of its own ids (i % N == r) only, like the reference's
+        # rotating W / H tables (CCDMPCollectiveMapper.java:546-547, :635-636); the full vectors u, v of the feature
+        # being updated exist only transiently, gathered over NVLink when the mapper has a symmetric workspace.
+        W_full0 = torch.rand(self.r, nrows, device=dev, generator=g, dtype=wdt) * scale      # same stream on every rank
+        own_r = torch.arange(me, nrows, N, device=dev)
+        own_c = torch.arange(me, ncols, N, device=dev)
+        W_loc = W_full0[:, own_r].contiguous()                                               # feature-major (rank-1 rows)
+        H_loc = torch.zeros(self.r, own_c.numel(), device=dev, dtype=wdt)                    # CCD++ starts from H = 0
+        del W_full0
+        symm = self.symm if (dev.type == "cuda" and N > 1 and wdt == torch.float32) else None
+        if symm is not None:
+            u_buf = symm.alloc(nrows, torch.float32)
+            v_buf = symm.alloc(ncols, torch.float32)
+        else:
+            u_buf = torch.zeros(nrows, device=dev, dtype=wdt)
+            v_buf = torch.zeros(ncols, device=dev, dtype=wdt)
         res_r = R[:, 2].to(wdt).clone()                                                  # residual = v (since H = 0)
         res_c = Cc[:, 2].to(wdt).clone()
         rows_r, cols_r = R[:, 0].long(), R[:, 1].long()
         rows_c, cols_c = Cc[:, 0].long(), Cc[:, 1].long()
-        own_r = torch.arange(me, nrows, N, device=dev)
-        own_c = torch.arange(me, ncols, N, device=dev)
 
         def gather_vec(vec_full, own_idx, new_local, op):
+            if symm is not None:
+                # owners store their entries into every peer's copy (row p is owned by rank p % N): one NVLink kernel,
+                # no metadata — the W / H shard exchange of the reference's two rotators
+                vec_full[own_idx] = new_local.to(vec_full.dtype)
+                symm.allgather_rows_(vec_full.view(-1, 1))
+                return
             tab = Table(0, FnCombiner(lambda a, b: a))            # disjoint ids: nothing ever combines
             tab.add_partition(Partition(me, torch.stack([own_idx.to(new_local.dtype), new_local])))
             self.allgather("ccd", op, tab)
@@ -220,7 +238,9 @@ class CCDCollectiveMapper(CollectiveMapper):
         step = 0
         for it in range(self.num_iterations):
             for f in range(self.r):
-                u, v = W[f].clone(), H[f].clone()
+                u, v = u_buf, v_buf
+                gather_vec(u, own_r, W_loc[f], f"allgather-w0-{it}-{f}")
+                gather_vec(v, own_c, H_loc[f], f"allgather-h0-{it}-{f}")
                 # put feature f back into the residuals
                 res_r += u[rows_r] * v[cols_r]
                 res_c += u[rows_c] * v[cols_c]
@@ -235,7 +255,7 @@ class CCDCollectiveMapper(CollectiveMapper):
                     r_tmp = res_r - u[rows_r] * v[cols_r]
                     mf.ccd_update(ptr_r, idx_r, r_tmp, None, u_loc, v.contiguous(), self.lam)
                     gather_vec(u, own_r, u_loc, f"allgather-w-{step}"); step += 1
-                W[f], H[f] = u, v
+                W_loc[f], H_loc[f] = u[own_r], v[own_c]
                 res_r -= u[rows_r] * v[cols_r]
                 res_c -= u[rows_c] * v[cols_c]
             obj = Table(0, DoubleArrPlus())
@@ -244,7 +264,14 @@ class CCDCollectiveMapper(CollectiveMapper):
             se, cnt = obj.get_partition(0).get().tolist()
             self.objective_history.append(math.sqrt(se / max(cnt, 1.0)))
             context.progress()
-        self.W, self.H = W, H
+        # whole factors for the model files / test RMSE: gathered once, at the end
+        W = torch.zeros(self.r, nrows, device=dev, dtype=wdt)
+        H = torch.zeros(self.r, ncols, device=dev, dtype=wdt)
+        for f in range(self.r):
+            gather_vec(u_buf, own_r, W_loc[f], f"allgather-wend-{f}")
+            gather_vec(v_buf, own_c, H_loc[f], f"allgather-hend-{f}")
+            W[f], H[f] = u_buf, v_buf
+        self.W, self.H, self.W_loc, self.H_loc = W, H, W_loc, H_loc
         # test RMSE
         test_files = [f for i, f in enumerate(sorted(self.test_files)) if i % N == me]
         traw = _load_ratings(test_files, dev)
