@@ -184,8 +184,11 @@ class MLRMapper(CollectiveMapper):
 
 # ---------------------------------------------------------------------------------------
 class LDACVBMapper(CollectiveMapper):
-    """conf: ``num_topics``, ``num_terms``, ``num_iterations``, ``alpha``, ``beta``, ``dynamic`` (push/pull variant);
-    input = ``docName term:count term:count ...`` (``contrib/.../lda/README.md``)."""
+    """conf: ``num_topics``, ``num_terms``, ``num_iterations``, ``alpha``, ``beta``, ``dynamic`` (push/pull variant),
+    ``update_alpha`` (default on); input = ``docName term:count term:count ...`` (``contrib/.../lda/README.md``).
+
+    The topic prior is an asymmetric Dirichlet whose vector is re-estimated after every pass from the all-reduced
+    statistics sum_d [psi(gamma_dk) - psi(sum_k gamma_dk)] (``contrib/.../lda/LDAMapper.java:345-360,428-447``)."""
 
     def setup(self, context: Context) -> None:
         c = context.get_configuration()
@@ -193,6 +196,41 @@ class LDACVBMapper(CollectiveMapper):
         self.iters = int(c.get("num_iterations", 10))
         self.alpha, self.beta = float(c.get("alpha", 0.1)), float(c.get("beta", 0.01))
         self.dynamic = bool(c.get("dynamic", False))
+        self.update_alpha = bool(c.get("update_alpha", True))
+
+    @staticmethod
+    def update_vector_alpha(alpha: torch.Tensor, num_docs: int, suff: torch.Tensor, *, decay_factor: float = 0.8,
+                            max_decay: int = 10, max_iter: int = 1000, tol: float = 1e-6) -> torch.Tensor:
+        """Newton iteration on the Dirichlet prior with the diagonal-plus-rank-one Hessian inverted in closed form
+        (``LDAMapper.java:476-600``; constants from ``lda/Constants.java:24-31``).  gradient_k = D (psi(sum a) -
+        psi(a_k)) + s_k, h_k = -D psi'(a_k), z = D psi'(sum a), c = sum(g/h) / (1/z + sum(1/h)); the step
+        (g_k - c) / h_k is shrunk by ``decay_factor`` until every component stays positive."""
+        a = alpha.clone().double()
+        D = float(num_docs)
+        decay = 0
+        for _ in range(max_iter + 1):
+            asum = a.sum()
+            grad = D * (torch.digamma(asum) - torch.digamma(a)) + suff
+            if not bool(torch.isfinite(grad).all()):
+                raise ArithmeticError("alpha gradient is not finite")
+            hess = -D * torch.polygamma(1, a)
+            z = D * torch.polygamma(1, asum)
+            cc = (grad / hess).sum() / (1.0 / z + (1.0 / hess).sum())
+            new = None
+            while decay <= max_decay:
+                step = (decay_factor ** decay) * (grad - cc) / hess
+                if bool((a <= step).any()):
+                    decay += 1                                  # would leave the positive orthant: shrink the step
+                    continue
+                new = a - step
+                break
+            if new is None:
+                break
+            done = bool((((new - a) / a).abs() < tol).all())
+            a = new
+            if done:
+                break
+        return a
 
     def map_collective(self, reader: KeyValReader, context: Context) -> None:
         docs = []
@@ -210,16 +248,19 @@ class LDACVBMapper(CollectiveMapper):
         log_phi -= torch.logsumexp(log_phi, 0, keepdim=True)           # each topic is a distribution over terms
         self.likelihood_history = []
         N = self.get_num_workers()
+        alpha = torch.full((K,), self.alpha, dtype=torch.float64)
+        num_docs = int(sum(self.comm.all_gather_object(len(docs))))
         for it in range(self.iters):
             new = torch.full((V, K), -float("inf"), dtype=torch.float64)
             ll = 0.0
+            suff = torch.zeros(K, dtype=torch.float64)
             for ids, cnt in docs:
-                gamma = torch.full((K,), self.alpha + float(cnt.sum()) / K, dtype=torch.float64)
+                gamma = alpha + float(cnt.sum()) / K
                 lp = log_phi[ids]                                       # [terms, K]
                 for _ in range(20):                                      # per-document fixed point (digamma updates)
                     log_r = lp + torch.digamma(gamma)
                     log_r = log_r - torch.logsumexp(log_r, 1, keepdim=True)
-                    g_new = self.alpha + (cnt[:, None] * torch.exp(log_r)).sum(0)
+                    g_new = alpha + (cnt[:, None] * torch.exp(log_r)).sum(0)
                     if float((g_new - gamma).abs().max()) < 1e-4:
                         gamma = g_new
                         break
@@ -228,6 +269,7 @@ class LDACVBMapper(CollectiveMapper):
                 new[ids] = torch.logaddexp(new[ids], contrib)
                 theta = gamma / gamma.sum()
                 ll += float((cnt * torch.logsumexp(lp + torch.log(theta), 1)).sum())
+                suff += torch.digamma(gamma) - torch.digamma(gamma.sum())
             table = Table(0, LogSumExpCombiner())
             if self.dynamic:
                 # LDAMapperDyn: log-phi sharded by term block with push / pull
@@ -248,11 +290,16 @@ class LDACVBMapper(CollectiveMapper):
                 new = table.get_partition(0).get()
             log_phi = torch.logaddexp(new, torch.full_like(new, math.log(self.beta)))
             log_phi = log_phi - torch.logsumexp(log_phi, 0, keepdim=True)
+            if self.update_alpha:
+                st = Table(4, DoubleArrPlus()); st.add_partition(Partition(0, suff))
+                self.allreduce("lda", f"allreduce-alpha-suff-{it}", st)
+                alpha = self.update_vector_alpha(alpha, num_docs, st.get_partition(0).get())
             lt = Table(3, DoubleArrPlus()); lt.add_partition(Partition(0, torch.tensor([ll], dtype=torch.float64)))
             self.allreduce("lda", f"allreduce-ll-{it}", lt)
             self.likelihood_history.append(float(lt.get_partition(0).get().item()))
             context.progress()
         self.log_phi = log_phi
+        self.alpha_vector = alpha
 
 
 # ---------------------------------------------------------------------------------------

@@ -85,6 +85,8 @@ def main():
     for dyn in (False, True):
         m = AC.LDACVBMapper(); run(m, [f"{base}/cvb/p{k}" for k in range(4)], {"num_topics": 3, "num_terms": 30, "num_iterations": 8, "dynamic": dyn})
         assert m.likelihood_history[-1] > m.likelihood_history[0], m.likelihood_history
+        assert m.alpha_vector.shape == (3,) and bool((m.alpha_vector > 0).all())
+        assert float((m.alpha_vector - 0.1).abs().max()) > 1e-3          # the prior was re-estimated
         lls.append(m.likelihood_history)
     np.testing.assert_allclose(lls[0], lls[1], rtol=1e-9)            # push/pull variant == allreduce variant
 

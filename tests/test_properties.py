@@ -81,3 +81,23 @@ def test_data_heads_round_trip_any_names(ctx, op, wid):
     head, body = d.encode()
     e = S.Data.decode(head, body)
     assert (e.context_name, e.operation_name, e.worker_id) == (ctx, op, wid)
+
+
+def test_cvb_alpha_newton_recovers_the_dirichlet_mle():
+    """The update of the asymmetric topic prior (contrib LDAMapper.java:476-600) is the MLE of a Dirichlet from
+    the statistics sum_d log(theta_dk): with the psi(gamma)-psi(sum gamma) terms replaced by log-samples of a
+    known Dirichlet it must land on that Dirichlet, from a far-away start, and stay positive on the way."""
+    import torch
+    from harp_b200.apps.contrib import LDACVBMapper
+    g = torch.Generator().manual_seed(3)
+    true = torch.tensor([0.3, 1.5, 4.0, 0.8], dtype=torch.float64)
+    D = 20000
+    theta = \
+        torch._sample_dirichlet(true.expand(D, 4).contiguous(), generator=g)
+    suff = torch.log(theta.clamp_min(1e-300)).sum(0)
+    est = LDACVBMapper.update_vector_alpha(torch.full((4,), 0.1, dtype=torch.float64), D, suff)
+    assert bool((est > 0).all())
+    assert float(((est - true) / true).abs().max()) < 0.05, est
+    # a fixed point: the gradient D (psi(sum a) - psi(a)) + s vanishes there
+    grad = D * (torch.digamma(est.sum()) - torch.digamma(est)) + suff
+    assert float(grad.abs().max()) / D < 1e-4
