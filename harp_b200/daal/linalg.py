@@ -165,7 +165,11 @@ def tsqr_r(X: torch.Tensor, comm=None) -> torch.Tensor:
     """R factor of the row-distributed matrix by communication-avoiding TSQR: local QR, gather the small
     R blocks, QR of the stack (DAAL qr/svd step1Local → step2Master)."""
     Xd = X.to_dense() if X.layout != torch.strided else X
-    R = torch.linalg.qr(Xd.double(), mode="r").R
+    from ..ops import linalg as KL
+    if KL.tsqr_supported(Xd):
+        R = KL.tsqr_r(Xd).double()           # K21: one streaming Householder pass over the local rows
+    else:
+        R = torch.linalg.qr(Xd.double(), mode="r").R
     if comm is None or comm.world == 1:
         return _fix_r_sign(R)
     blocks = [torch.zeros_like(R) for _ in range(comm.world)]
@@ -186,7 +190,10 @@ def pca_svd(X: torch.Tensor, comm=None) -> PCAResult:
     """``daal_pca/svddensedistr`` (``…/svddensedistr/PCADaalCollectiveMapper.java:116-164``): SVD of the
     z-scored data through TSQR."""
     mom = low_order_moments(X, comm)
-    Z = (X.double() - mom.mean) / mom.standard_deviation.clamp(min=1e-300)
+    if X.device.type == "cuda" and X.dtype == torch.float32:
+        Z = (X - mom.mean.to(X)) / mom.standard_deviation.clamp(min=1e-300).to(X)     # stays fp32 for the K21 kernel
+    else:
+        Z = (X.double() - mom.mean) / mom.standard_deviation.clamp(min=1e-300)
     R = tsqr_r(Z, comm)
     _, S, Vh = torch.linalg.svd(R)
     ev = S * S / max(mom.n - 1, 1)
@@ -200,6 +207,10 @@ def pca_svd(X: torch.Tensor, comm=None) -> PCAResult:
 def qr_distributed(X: torch.Tensor, comm=None) -> Tuple[torch.Tensor, torch.Tensor]:
     """Returns (local rows of Q, R) — ``SVDDaalCollectiveMapper.java:136-219`` 3-step protocol."""
     R = tsqr_r(X, comm)
+    if X.device.type == "cuda" and X.dtype == torch.float32:
+        # keep the n x d product in fp32 on the device: Q = X R^-1 as one library GEMM against the small inverse
+        Rinv = torch.linalg.inv(R).to(torch.float32)
+        return X @ Rinv, R
     Q = torch.linalg.solve_triangular(R, X.double(), upper=True, left=False)
     return Q, R
 
@@ -208,7 +219,7 @@ def svd_distributed(X: torch.Tensor, comm=None) -> Tuple[torch.Tensor, torch.Ten
     """Returns (local rows of U, singular values, Vᵀ)."""
     Q, R = qr_distributed(X, comm)
     Ur, S, Vh = torch.linalg.svd(R)
-    return Q @ Ur, S, Vh
+    return Q @ Ur.to(Q.dtype), S, Vh
 
 
 def cholesky(A: torch.Tensor) -> torch.Tensor:

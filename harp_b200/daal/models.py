@@ -178,6 +178,32 @@ def als_implicit(rows: torch.Tensor, cols: torch.Tensor, vals: torch.Tensor, n_u
         part[own] = M[own]
         _allreduce_(part, comm)
         return part
+    from ..ops import linalg as KL
+    if dev.type == "cuda" and KL.als_pad(n_factors):
+        # K22: steps 1-2 = cross-product of the owned factor rows, summed over ranks; step 3 = the factor rows
+        # travel; step 4 = one warp per owned row builds, factors and solves its normal matrix (fp32)
+        F = KL.als_pad(n_factors)
+        Xf = torch.zeros(n_users, F, dtype=torch.float32, device=dev); Xf[:, :n_factors] = X.float()
+        Yf = torch.zeros(n_items, F, dtype=torch.float32, device=dev); Yf[:, :n_factors] = Y.float()
+        su = KL.ALSSide(up, ui, uv, own_u if N > 1 else None)
+        si = KL.ALSSide(ip, ii, iv, own_i if N > 1 else None)
+
+        def half(side, other, own_other, out):
+            blk = other[own_other] if N > 1 else other
+            G = blk.t() @ blk
+            if N > 1:
+                _allreduce_(G, comm)
+                out.zero_()
+            KL.als_solve(side, other, out, n_factors, lam, alpha, G)
+            if N > 1:
+                _allreduce_(out, comm)
+        for _ in range(n_iter):
+            half(su, Yf, own_i, Xf)
+            half(si, Xf, own_u, Yf)
+        bad = int(su.info.item()) + int(si.info.item())
+        if bad:
+            raise RuntimeError(f"als_implicit: {bad} normal matrices were not positive definite")
+        return Xf[:, :n_factors].double(), Yf[:, :n_factors].double()
     for _ in range(n_iter):
         Xn = _als_solve_side(up, ui, uv, Y, n_users, lam, alpha)
         X = share(Xn, own_u) if N > 1 else Xn

@@ -1,16 +1,19 @@
 #!/bin/bash
-# compute-sanitizer pass over CI-sized kernel tests.  One tool per gpurun call, and only after the same
-# command has passed without it:   gpurun --timeout 900 -- 'bash scripts/sanitize.sh memcheck'
+# compute-sanitizer pass over CI-sized launches of every kernel family.  One tool per gpurun call, and
+# only after the same program has passed without it:   gpurun --timeout 1500 -- 'bash scripts/sanitize.sh memcheck'
 # tools: memcheck | racecheck | synccheck | initcheck.  Single GPU only.  Output: gpurun_out/sanitize_<tool>.log
 tool=${1:-memcheck}
-sel=${2:-"tests/test_kmeans_gpu.py tests/test_gram_gpu.py tests/test_mf_gpu.py tests/test_lda_gpu.py tests/test_svm_native.py"}
+shift
+sections="$@"
 mkdir -p gpurun_out
-export HB_SANITIZE=1          # tests may shrink their shapes when this is set
-timeout 600 python -m pytest $sel -x -q -m gpu > gpurun_out/sanitize_plain.log 2>&1 && \
-timeout 1500 compute-sanitizer --tool $tool --error-exitcode 99 --launch-timeout 120 \
-  python -m pytest $sel -x -q -m gpu > gpurun_out/sanitize_$tool.log 2>&1
+export PYTHONPATH=.
+timeout 600 python scripts/sanitize_targets.py $sections > gpurun_out/sanitize_plain.log 2>&1
+rc=$?
+tail -3 gpurun_out/sanitize_plain.log
+if [ $rc -ne 0 ]; then echo "plain run failed rc=$rc"; exit $rc; fi
+timeout 2400 compute-sanitizer --tool $tool --error-exitcode 99 --launch-timeout 300 \
+  python scripts/sanitize_targets.py $sections > gpurun_out/sanitize_$tool.log 2>&1
 rc=$?
 echo "sanitize $tool rc=$rc"
-tail -5 gpurun_out/sanitize_plain.log
-grep -E "ERROR SUMMARY|Invalid|Race|hazard|passed|failed" gpurun_out/sanitize_$tool.log 2>/dev/null | tail -12
+grep -E "ERROR SUMMARY|Invalid|Race|hazard|section|Uninitialized|SANITIZE_TARGETS_OK" gpurun_out/sanitize_$tool.log 2>/dev/null | tail -30
 exit $rc
