@@ -5,214 +5,188 @@
 //                           ml/daal/.../daal_svd/SVDDaalCollectiveMapper.java:136-219).
 //   K16  potrs_batched      batched f x f Cholesky factor + solve, one warp per system.
 //   K22  als_solve_kernel   implicit-ALS step 4: per row, the normal matrix Y'Y + Y_u'(C_u - I)Y_u + lambda I is built
-//                           in registers, factored and solved in shared memory by one warp
+//                           in registers, factored and solved by one warp
 //                           (ml/daal/.../daal_als/ALSDaalCollectiveMapper.java:354-492).
 //
 // TSQR design.  A CTA owns a contiguous range of rows and keeps ONE running upper-triangular R (D x D) in shared
-// memory.  It streams tiles of 128*RPT rows: every thread holds RPT whole rows of the tile in registers, and the
-// stacked matrix [R ; tile] is reduced column by column with the structured reflector v = [R_kk - alpha ; tile[:,k]]
-// (rows k+1.. of R are already zero in column k, so the reflector only touches row k of R and the tile).  The dot
-// products of column k with columns k..D-1 do not depend on the norm, so the norm and all the projections come out of
-// ONE block-wide reduction per column: a transposing butterfly inside the warp (31 shuffles for 32 sums), four
-// partials through shared memory, two barriers per column.  While a tile is being reduced the next one is already in
-// flight: the rows are fetched with cp.async.bulk into a padded shared buffer (pitch D+4 floats keeps the 128-bit
-// row reads conflict-free) that is free as soon as the previous tile sits in registers.  X is read exactly once; the
-// per-CTA triangles are stacked and reduced by the same kernel until one is left.
+// memory.  It streams tiles; the stacked matrix [R ; tile] is reduced column by column with the structured reflector
+// v = [R_kk - alpha ; tile[:,k]] (rows k+1.. of R are already zero in column k, so the reflector only touches row k
+// of R and the tile).  The tile lives in registers, laid out so that NO cross-lane reduction is needed: a group of
+// D/4 lanes holds 32 rows, lane c of the group owning columns c, c + D/4, c + 2D/4, c + 3D/4 of every one of them.
+// Column k is broadcast from its owner lane with one shuffle per row; every lane then forms the dot products of that
+// column with its own four columns and applies the update to them.  Per column the CTA exchanges one row of partial
+// dot products through shared memory (one barrier); the scalar part of the reflector is recomputed by every lane.
+// The dot products do not depend on the norm, so the norm comes out of the same exchange.  Because ownership is
+// cyclic, after D/4 columns every lane's first register column is dead and the code moves on to a body that no
+// longer touches it: four bodies, each a rolled loop over D/4 columns, ~1000 instructions in total.  (A first
+// version kept whole rows per thread with all D columns unrolled; its 370 KB of straight-line code ran at 30 % issue
+// utilisation waiting for instruction fetch.)  While a tile is being reduced the next one is in flight: every warp
+// fetches its own 16 KB strip with cp.async.bulk into shared memory and signals its own mbarrier.  X is read exactly
+// once; the per-CTA triangles are stacked and reduced by the same kernel until one is left.
 #include "common.cuh"
 #include "harp_b200.h"
 
 namespace hb {
 namespace tsqr {
 
-constexpr int THREADS = 128;          // two CTAs per SM: one CTA's barrier and reduction latency hides behind the other
-constexpr int NW = THREADS / 32;
+constexpr int WARPS = 4;                     // two CTAs per SM: one CTA's barrier + reflector latency hides behind the other
+constexpr int THREADS = WARPS * 32;
+constexpr int CPL = 4;                       // columns per lane
+constexpr int RW = 32;                       // rows per lane group
 
 template <int D>
 struct Cfg {
-  static constexpr int RPT = D <= 16 ? 8 : (D <= 32 ? 4 : 2);   // rows per thread
-  static constexpr int TILE = THREADS * RPT;
-  static constexpr int PITCH = D + 4;
-  static constexpr int CW = D < 32 ? D : 32;                    // sums per butterfly
+  static constexpr int LPG = D / CPL;        // lanes per group
+  static constexpr int G = 32 / LPG;         // groups per warp
+  static constexpr int STRIP = RW * G;       // rows per warp and tile
+  static constexpr int TILE = WARPS * STRIP;
   static constexpr size_t smem_bytes() {
-    return (size_t)TILE * PITCH * 4 + (size_t)D * D * 4 + (size_t)NW * D * 4 + (size_t)D * 4 + 64;
+    return (size_t)TILE * D * 4 + (size_t)2 * D * D * 4 + (size_t)2 * WARPS * D * 4 + WARPS * 8 + 64;
   }
 };
 
-// One column of the reduction.  K is a template parameter so that every register-array index is static.
-template <int D, int RPT, int K>
-__device__ __forceinline__ void column_step(float (&b)[RPT][D], float* __restrict__ Rm, float* __restrict__ part,
-                                            float* __restrict__ wv, const int warp, const int lane, const int tid) {
-  constexpr int CW = Cfg<D>::CW;
-  constexpr int C_FIRST = (K / CW) * CW;
-  // ---- stage 1: per-warp sums of tile[:,K] * tile[:,j] for j >= K ----
+// Columns [Q*D/4, (Q+1)*D/4): register column Q of the owner lanes is eliminated, columns Q..3 are updated.
+template <int D, int Q>
+__device__ __forceinline__ void phase(float (&b)[RW][CPL], const float* __restrict__ Rcur, float* __restrict__ Rnext,
+                                      float* __restrict__ part, int& pbuf, const int warp, const int lane) {
+  constexpr int LPG = Cfg<D>::LPG;
+  const int grp = lane / LPG, cl = lane - grp * LPG;
+#pragma unroll 1
+  for (int kk = 0; kk < LPG; ++kk) {
+    const int k = Q * LPG + kk;
+    const int src = grp * LPG + kk;
+    float bk[RW];
 #pragma unroll
-  for (int c0 = C_FIRST; c0 < D; c0 += CW) {
-    float p[CW];
+    for (int i = 0; i < RW; ++i) bk[i] = __shfl_sync(0xffffffffu, b[i][Q], src);
+    float s[CPL][2];
 #pragma unroll
-    for (int i = 0; i < CW; ++i) {
-      const int j = c0 + i;
-      float s = 0.f;
-      if (j >= K) {
+    for (int q = 0; q < CPL; ++q) s[q][0] = s[q][1] = 0.f;
 #pragma unroll
-        for (int r = 0; r < RPT; ++r) s = fmaf(b[r][K], b[r][j], s);
-      }
-      p[i] = s;
+    for (int i = 0; i < RW; ++i)
+#pragma unroll
+      for (int q = Q; q < CPL; ++q) s[q][i & 1] = fmaf(bk[i], b[i][q], s[q][i & 1]);
+    float t[CPL];
+#pragma unroll
+    for (int q = 0; q < CPL; ++q) t[q] = s[q][0] + s[q][1];
+#pragma unroll
+    for (int off = LPG; off < 32; off <<= 1)
+#pragma unroll
+      for (int q = Q; q < CPL; ++q) t[q] += __shfl_xor_sync(0xffffffffu, t[q], off);
+    float* mine = part + (size_t)(pbuf * WARPS + warp) * D;
+    if (grp == 0) *reinterpret_cast<float4*>(mine + cl * 4) = make_float4(t[0], t[1], t[2], t[3]);
+    __syncthreads();
+    float g[CPL] = {0.f, 0.f, 0.f, 0.f}, gk = 0.f;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) {
+      const float* pw = part + (size_t)(pbuf * WARPS + w) * D;
+      const float4 v = *reinterpret_cast<const float4*>(pw + cl * 4);
+      g[0] += v.x; g[1] += v.y; g[2] += v.z; g[3] += v.w;
+      gk += pw[kk * 4 + Q];
     }
-    int lo = K - c0 > 0 ? K - c0 : 0;              // slots below `lo` are identically zero in every lane
-#pragma unroll
-    for (int h = CW / 2; h >= 1; h >>= 1) {
-      const bool up = (lane & h) != 0;
-#pragma unroll
-      for (int i = 0; i < h; ++i) {
-        if (i + h >= lo) {
-          const float keep = up ? p[i + h] : p[i];
-          const float send = up ? p[i] : p[i + h];
-          p[i] = keep + __shfl_xor_sync(0xffffffffu, send, h);
-        }
-      }
-      lo = lo - h > 0 ? lo - h : 0;
-    }
-    if (CW < 32) p[0] += __shfl_xor_sync(0xffffffffu, p[0], 16);
-    const int j = c0 + (lane & (CW - 1));
-    if (lane < CW && j >= K) part[warp * D + j] = p[0];
-  }
-  __syncthreads();
-  // ---- stage 2: thread j finishes column j: new R[K][j] and the coefficient of the row update ----
-  if (tid >= K && tid < D) {
-    float gk = 0.f, gj = 0.f;
-#pragma unroll
-    for (int w = 0; w < NW; ++w) {
-      gk += part[w * D + K];
-      gj += part[w * D + tid];
-    }
-    const float rkk = Rm[K * D + K];
-    float coef = 0.f;
+    pbuf ^= 1;
+    const float rkk = Rcur[k * D + k];
     const float normsq = fmaf(rkk, rkk, gk);
-    if (gk > 0.f && normsq > 1e-34f) {             // below that alpha * v0 would leave the normal range
-      const float alpha = -copysignf(normsq * rsqrtf(normsq), rkk);
-      const float v0 = rkk - alpha;
-      const float tau = __frcp_rn(0.5f * fmaf(v0, v0, gk));   // 2 / (v'v): exactly orthogonal for the alpha in use
-      if (tid == K) {
-        Rm[K * D + K] = alpha;
-      } else {
-        const float rkj = Rm[K * D + tid];
-        const float w = fmaf(v0, rkj, gj);
-        Rm[K * D + tid] = rkj - tau * v0 * w;
-        coef = tau * w;
-      }
+    const bool valid = gk > 0.f && normsq > 1e-34f;   // below that alpha * v0 would leave the normal range
+    const float alpha = -copysignf(normsq * rsqrtf(fmaxf(normsq, 1e-34f)), rkk);
+    const float v0 = rkk - alpha;
+    const float tau = valid ? __frcp_rn(0.5f * fmaf(v0, v0, gk)) : 0.f;   // 2 / (v'v)
+    float coef[CPL];
+#pragma unroll
+    for (int q = Q; q < CPL; ++q) {
+      const int j = cl + q * LPG;
+      const float rkj = Rcur[k * D + j];
+      const float w = fmaf(v0, rkj, g[q]);
+      coef[q] = j > k ? tau * w : 0.f;
+      if (warp == 0 && grp == 0 && j >= k) Rnext[k * D + j] = !valid ? rkj : (j == k ? alpha : rkj - tau * v0 * w);
     }
-    wv[tid] = coef;
-  }
-  __syncthreads();
-  // ---- stage 3: tile[:, j] -= tile[:, K] * coef_j ----
-  if (K + 1 < D) {
 #pragma unroll
-    for (int j4 = ((K + 1) / 4) * 4; j4 < D; j4 += 4) {
-      const float4 c = *reinterpret_cast<const float4*>(wv + j4);
-      const float cc[4] = {c.x, c.y, c.z, c.w};
+    for (int i = 0; i < RW; ++i)
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int j = j4 + q;
-        if (j > K) {
-#pragma unroll
-          for (int r = 0; r < RPT; ++r) b[r][j] = fmaf(-b[r][K], cc[q], b[r][j]);
-        }
-      }
-    }
+      for (int q = Q; q < CPL; ++q) b[i][q] = fmaf(-bk[i], coef[q], b[i][q]);
   }
 }
 
-template <int D, int RPT, int K>
-struct Columns {
-  static __device__ __forceinline__ void run(float (&b)[RPT][D], float* Rm, float* part, float* wv, int warp, int lane,
-                                             int tid) {
-    column_step<D, RPT, K>(b, Rm, part, wv, warp, lane, tid);
-    Columns<D, RPT, K + 1>::run(b, Rm, part, wv, warp, lane, tid);
-  }
-};
-template <int D, int RPT>
-struct Columns<D, RPT, D> {
-  static __device__ __forceinline__ void run(float (&)[RPT][D], float*, float*, float*, int, int, int) {}
-};
-
 // X: [n, d] fp32, row pitch `ld` floats.  Every CTA reduces rows [cta*rows_per_cta, ...) and writes its triangle to
 // out[cta][D][D] (row-major, zeros below the diagonal, columns >= d zero).  BULK: rows are fetched with cp.async.bulk
-// (needs d == D, ld % 4 == 0, 16-byte aligned base); otherwise the tile is staged with plain coalesced loads.
+// (needs d == D, ld % 4 == 0, 16-byte aligned base); otherwise the strip is staged with plain loads.
 template <int D, bool BULK>
 __global__ void __launch_bounds__(THREADS, 2)
 tsqr_kernel(const float* __restrict__ X, const long long n, const int d, const long long ld,
             const long long rows_per_cta, float* __restrict__ out) {
   using C = Cfg<D>;
-  constexpr int RPT = C::RPT, TILE = C::TILE, PITCH = C::PITCH;
+  constexpr int LPG = C::LPG, STRIP = C::STRIP, TILE = C::TILE;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  float* tile = reinterpret_cast<float*>(smem_raw);
-  float* Rm = tile + (size_t)TILE * PITCH;
-  float* part = Rm + D * D;
-  float* wv = part + NW * D;
-  uint64_t* bar = reinterpret_cast<uint64_t*>(wv + D);
+  float* stage = reinterpret_cast<float*>(smem_raw);
+  float* Rm = stage + (size_t)TILE * D;            // two triangles: read one, write the other, swap per tile
+  float* part = Rm + 2 * D * D;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(part + 2 * WARPS * D);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int grp = lane / LPG, cl = lane - grp * LPG;
   const long long r_begin = (long long)blockIdx.x * rows_per_cta;
   long long r_end = r_begin + rows_per_cta;
   if (r_end > n) r_end = n;
-  for (int i = tid; i < D * D; i += THREADS) Rm[i] = 0.f;
-  if (BULK && tid == 0) {
-    mbar_init(smem_u32(bar), 1);
+  for (int i = tid; i < 2 * D * D; i += THREADS) Rm[i] = 0.f;
+  if (BULK && lane == 0) {
+    mbar_init(smem_u32(bars + warp), 1);
     fence_barrier_init();
   }
   __syncthreads();
+  float* my_stage = stage + (size_t)warp * STRIP * D;
+  const uint32_t my_bar = smem_u32(bars + warp);
 
-  auto issue = [&](long long row0) {                       // fetch rows [row0, row0 + TILE) ∩ [.., r_end)
-    if (BULK) {
-      long long left = r_end - row0;
-      const int rows = left > TILE ? TILE : (int)left;
-      if (tid == 0) mbar_expect_tx(smem_u32(bar), (uint32_t)rows * D * 4u);
-#pragma unroll
-      for (int r = 0; r < RPT; ++r) {
-        const int lr = tid + r * THREADS;
-        if (lr < rows) bulk_load_1d(smem_u32(tile + (size_t)lr * PITCH), X + (row0 + lr) * ld, D * 4, smem_u32(bar));
-      }
-    }
+  auto strip_rows = [&](long long row0) -> int {            // rows of this warp's strip in the tile at row0
+    const long long left = r_end - (row0 + (long long)warp * STRIP);
+    return left <= 0 ? 0 : (left > STRIP ? STRIP : (int)left);
+  };
+  auto issue = [&](long long row0) {
+    const int rows = strip_rows(row0);
+    if (!BULK || rows == 0) return;
+    if (lane == 0) mbar_expect_tx(my_bar, (uint32_t)rows * D * 4u);
+    const float* src = X + (row0 + (long long)warp * STRIP) * ld;
+    for (int r = lane; r < rows; r += 32) bulk_load_1d(smem_u32(my_stage + (size_t)r * D), src + (long long)r * ld, D * 4, my_bar);
   };
 
-  uint32_t phase = 0;
+  uint32_t phase_bit = 0;
+  int cur = 0, pbuf = 0;
   if (r_begin < r_end) issue(r_begin);
   for (long long row0 = r_begin; row0 < r_end; row0 += TILE) {
-    long long left = r_end - row0;
-    const int rows = left > TILE ? TILE : (int)left;
+    const int rows = strip_rows(row0);
     if (BULK) {
-      mbar_wait(smem_u32(bar), phase);
-      phase ^= 1;
+      if (rows > 0) {
+        mbar_wait(my_bar, phase_bit);
+        phase_bit ^= 1;
+      }
     } else {
-      for (int i = tid; i < rows * D; i += THREADS) {
-        const int lr = i / D, c = i - lr * D;
-        tile[(size_t)lr * PITCH + c] = c < d ? X[(row0 + lr) * ld + c] : 0.f;
+      const float* src = X + (row0 + (long long)warp * STRIP) * ld;
+      for (int i = lane; i < rows * D; i += 32) {
+        const int r = i / D, c = i - r * D;
+        my_stage[i] = c < d ? src[(long long)r * ld + c] : 0.f;
       }
-      __syncthreads();
+      __syncwarp();
     }
-    float b[RPT][D];
+    float b[RW][CPL];
 #pragma unroll
-    for (int r = 0; r < RPT; ++r) {
-      const int lr = tid + r * THREADS;
-      if (lr < rows) {
+    for (int i = 0; i < RW; ++i) {
+      const int r = grp * RW + i;
 #pragma unroll
-        for (int c = 0; c < D; c += 4) {
-          const float4 v = *reinterpret_cast<const float4*>(tile + (size_t)lr * PITCH + c);
-          b[r][c] = v.x; b[r][c + 1] = v.y; b[r][c + 2] = v.z; b[r][c + 3] = v.w;
-        }
-      } else {
-#pragma unroll
-        for (int c = 0; c < D; ++c) b[r][c] = 0.f;
-      }
+      for (int q = 0; q < CPL; ++q) b[i][q] = r < rows ? my_stage[(size_t)r * D + cl + q * LPG] : 0.f;
     }
-    __syncthreads();                                       // the staging buffer is free again
+    __syncwarp();                                          // the strip buffer is free again
     if (row0 + TILE < r_end) issue(row0 + TILE);
-    Columns<D, RPT, 0>::run(b, Rm, part, wv, warp, lane, tid);
+    const float* Rc = Rm + cur * D * D;
+    float* Rn = Rm + (cur ^ 1) * D * D;
+    phase<D, 0>(b, Rc, Rn, part, pbuf, warp, lane);
+    phase<D, 1>(b, Rc, Rn, part, pbuf, warp, lane);
+    phase<D, 2>(b, Rc, Rn, part, pbuf, warp, lane);
+    phase<D, 3>(b, Rc, Rn, part, pbuf, warp, lane);
+    cur ^= 1;
   }
   __syncthreads();
+  const float* Rc = Rm + cur * D * D;
   float* o = out + (size_t)blockIdx.x * D * D;
   for (int i = tid; i < D * D; i += THREADS) {
     const int r = i / D, c = i - r * D;
-    o[i] = c >= r ? Rm[i] : 0.f;
+    o[i] = c >= r ? Rc[i] : 0.f;
   }
 }
 
@@ -243,7 +217,7 @@ int run(const float* X, long long n, int d, long long ld, float* work, float* R_
   int which = 0;
   for (;;) {
     long long tiles = (rows + TILE - 1) / TILE;
-    int grid = src == X ? 2 * sm_count() : (int)((tiles + 3) / 4);
+    int grid = src == X ? 2 * sm_count() : (int)((tiles + 1) / 2);
     if (grid > tiles) grid = (int)tiles;
     if (grid < 1) grid = 1;
     long long per = ((tiles + grid - 1) / grid) * TILE;
@@ -263,86 +237,148 @@ int run(const float* X, long long n, int d, long long ld, float* work, float* R_
 }  // namespace tsqr
 
 // ------------------------------------------------------------------------------------------------------------
-// Cholesky factor + solve of one f x f system by one warp, matrix in shared memory with pitch F + 1.
+// Cholesky factor + solve of one F x F system by one warp, matrix in REGISTERS.
+//
+// The 32 lanes form a 4 x 8 grid; lane (lr, lc) holds the elements with row = 4a + lr and col = 8b + lc (cyclic in
+// both directions), so at step k every lane still has live elements and the finished part of the matrix drops out as
+// whole register rows / columns.  Column k and row k of the symmetric trailing matrix are fetched with one shuffle
+// per register (row k sits in the lanes with lr == k % 4, column k in the lanes with lc == k % 8), the rank-one update
+// runs on registers, and the right-hand side rides along as an extra row, which makes the forward substitution part of
+// the factorisation.  Steps are grouped in phases of eight columns: inside a phase the register column is static and
+// the two candidate register rows are picked with a select, so each phase is a rolled loop of eight steps.
 // ------------------------------------------------------------------------------------------------------------
 namespace chol {
 
-// In place: lower triangle of A becomes L (A = L L').  Returns false if a pivot is not positive.
-template <int F>
-__device__ __forceinline__ bool factor(float* __restrict__ A, const int f, const int lane) {
-  constexpr int P = F + 1;
-  bool ok = true;
-  for (int k = 0; k < f; ++k) {
-    const float akk = A[k * P + k];
-    if (!(akk > 0.f)) ok = false;
-    const float inv = rsqrtf(fmaxf(akk, 1e-30f));
-    __syncwarp();
-    for (int i = k + lane; i < f; i += 32) A[i * P + k] = i == k ? akk * inv : A[i * P + k] * inv;
-    __syncwarp();
-    // column k now holds L[k][k] = sqrt(akk) (akk * inv) and L[i][k] = A[i][k] * inv
-    for (int i = k + 1 + lane; i < f; i += 32) {
-      const float lik = A[i * P + k];
-      for (int j = k + 1; j <= i; ++j) A[i * P + j] = fmaf(-lik, A[j * P + k], A[i * P + j]);
+template <int F, int BQ>
+__device__ __forceinline__ void factor_phase(float (&acc)[F / 4][F / 8], float (&bx)[F / 8], const int lr, const int lc,
+                                             bool& ok) {
+  constexpr int TR = F / 4, TC = F / 8, A0 = 2 * BQ;
+#pragma unroll 1
+  for (int kk = 0; kk < 8; ++kk) {
+    const int k = 8 * BQ + kk;
+    const bool hi = kk >= 4;                       // row k sits in register row A0 + hi of the lanes lr == k % 4
+    const int own = (k & 3) << 3;
+    const float d = __shfl_sync(0xffffffffu, hi ? acc[A0 + 1][BQ] : acc[A0][BQ], own + kk);
+    if (!(d > 0.f)) ok = false;
+    const float dc = fmaxf(d, 1e-30f);
+    float inv = rsqrtf(dc);
+    inv = inv * fmaf(-0.5f * dc, inv * inv, 1.5f);   // one Newton step: full fp32 accuracy
+    float lj[TC];
+#pragma unroll
+    for (int b = BQ; b < TC; ++b) lj[b] = __shfl_sync(0xffffffffu, hi ? acc[A0 + 1][b] : acc[A0][b], own + lc) * inv;
+    if (lc <= kk) lj[BQ] = 0.f;                    // columns <= k are finished
+    float li[TR];
+#pragma unroll
+    for (int a = A0; a < TR; ++a) li[a] = __shfl_sync(0xffffffffu, acc[a][BQ], (lr << 3) + kk) * inv;
+    const float zk = __shfl_sync(0xffffffffu, bx[BQ], (lr << 3) + kk) * inv;
+    if (lc == kk) {                                // the owner lanes keep the finished column of L
+#pragma unroll
+      for (int a = A0; a < TR; ++a) {
+        const int row = 4 * a + lr;
+        if (row >= k) acc[a][BQ] = row == k ? d * inv : li[a];
+      }
+      bx[BQ] = zk;
     }
-    __syncwarp();
+    if (4 * A0 + lr <= k) li[A0] = 0.f;            // rows <= k are finished (only these two register rows can be)
+    if (4 * (A0 + 1) + lr <= k) li[A0 + 1] = 0.f;
+#pragma unroll
+    for (int a = A0; a < TR; ++a)
+#pragma unroll
+      for (int b = BQ; b < TC; ++b) acc[a][b] = fmaf(-li[a], lj[b], acc[a][b]);
+#pragma unroll
+    for (int b = BQ; b < TC; ++b) bx[b] = fmaf(-zk, lj[b], bx[b]);
   }
-  return ok;
 }
 
-// Solves L L' x = b in place (b in shared memory).
+template <int F, int BQ>
+__device__ __forceinline__ void back_phase(const float (&acc)[F / 4][F / 8], float (&bx)[F / 8], const int lc) {
+  constexpr int A0 = 2 * BQ;
+#pragma unroll 1
+  for (int kk = 7; kk >= 0; --kk) {
+    const int k = 8 * BQ + kk;
+    const bool hi = kk >= 4;
+    const int own = (k & 3) << 3;
+    const float lkk = __shfl_sync(0xffffffffu, hi ? acc[A0 + 1][BQ] : acc[A0][BQ], own + kk);
+    const float zk = __shfl_sync(0xffffffffu, bx[BQ], kk);
+    const float xk = zk / lkk;
+    if (lc == kk) bx[BQ] = xk;
+#pragma unroll
+    for (int b = 0; b <= BQ; ++b) {
+      float v = __shfl_sync(0xffffffffu, hi ? acc[A0 + 1][b] : acc[A0][b], own + lc);
+      if (b == BQ && lc >= kk) v = 0.f;            // only columns < k
+      bx[b] = fmaf(-v, xk, bx[b]);
+    }
+  }
+}
+
+template <int F, int BQ>
+struct Phases {
+  static __device__ __forceinline__ void factor(float (&acc)[F / 4][F / 8], float (&bx)[F / 8], int lr, int lc, bool& ok) {
+    factor_phase<F, BQ>(acc, bx, lr, lc, ok);
+    Phases<F, BQ + 1>::factor(acc, bx, lr, lc, ok);
+  }
+  static __device__ __forceinline__ void back(const float (&acc)[F / 4][F / 8], float (&bx)[F / 8], int lc) {
+    Phases<F, BQ + 1>::back(acc, bx, lc);
+    back_phase<F, BQ>(acc, bx, lc);
+  }
+};
 template <int F>
-__device__ __forceinline__ void solve(const float* __restrict__ A, float* __restrict__ b, const int f, const int lane) {
-  constexpr int P = F + 1;
-  for (int k = 0; k < f; ++k) {                  // forward: L z = b
-    const float zk = b[k] / A[k * P + k];
-    __syncwarp();
-    if (lane == 0) b[k] = zk;
-    for (int i = k + 1 + lane; i < f; i += 32) b[i] = fmaf(-A[i * P + k], zk, b[i]);
-    __syncwarp();
-  }
-  for (int k = f - 1; k >= 0; --k) {             // backward: L' x = z
-    const float xk = b[k] / A[k * P + k];
-    __syncwarp();
-    if (lane == 0) b[k] = xk;
-    for (int i = lane; i < k; i += 32) b[i] = fmaf(-A[k * P + i], xk, b[i]);
-    __syncwarp();
-  }
+struct Phases<F, F / 8> {
+  static __device__ __forceinline__ void factor(float (&)[F / 4][F / 8], float (&)[F / 8], int, int, bool&) {}
+  static __device__ __forceinline__ void back(const float (&)[F / 4][F / 8], float (&)[F / 8], int) {}
+};
+
+// acc: the symmetric matrix (both triangles), bx: the right-hand side replicated over lr.  On return the lower
+// triangle of acc is L, bx is the solution (x[8b + lc] in bx[b] of every lane with that lc).
+template <int F>
+__device__ __forceinline__ bool factor_solve(float (&acc)[F / 4][F / 8], float (&bx)[F / 8], const int lr, const int lc,
+                                             const bool want_solution) {
+  bool ok = true;
+  Phases<F, 0>::factor(acc, bx, lr, lc, ok);
+  if (want_solution) Phases<F, 0>::back(acc, bx, lc);
+  return ok;
 }
 
 constexpr int WARPS = 4;
 
-// A: [batch][f][f] symmetric positive definite (only the lower triangle is read), B: [batch][f].
+// A: [batch][f][f] symmetric positive definite, B: [batch][f] or NULL.
 // X: [batch][f] solutions; L_out (optional): [batch][f][f] lower factors; info[0] counts failed factorisations.
 template <int F>
 __global__ void __launch_bounds__(WARPS * 32)
 potrs_batched_kernel(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ X,
                      float* __restrict__ L_out, const int f, const long long batch, int* __restrict__ info) {
-  extern __shared__ __align__(16) float sm[];
+  constexpr int TR = F / 4, TC = F / 8;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* As = sm + (size_t)warp * (F * (F + 1) + F);
-  float* bs = As + F * (F + 1);
+  const int lr = lane >> 3, lc = lane & 7;
   for (long long m = (long long)blockIdx.x * WARPS + warp; m < batch; m += (long long)gridDim.x * WARPS) {
-    const float* a = A + (size_t)m * f * f;
-    for (int i = lane; i < f * f; i += 32) {
-      const int r = i / f, c = i - r * f;
-      As[r * (F + 1) + c] = a[i];
-    }
-    for (int i = lane; i < f; i += 32) bs[i] = B ? B[(size_t)m * f + i] : 0.f;
-    __syncwarp();
-    const bool ok = factor<F>(As, f, lane);
+    const float* a_ = A + (size_t)m * f * f;
+    float acc[TR][TC], bx[TC];
+#pragma unroll
+    for (int a = 0; a < TR; ++a)
+#pragma unroll
+      for (int b = 0; b < TC; ++b) {
+        const int r = 4 * a + lr, c = 8 * b + lc;
+        acc[a][b] = (r < f && c < f) ? a_[(size_t)r * f + c] : (r == c ? 1.f : 0.f);
+      }
+#pragma unroll
+    for (int b = 0; b < TC; ++b) bx[b] = (B && 8 * b + lc < f) ? B[(size_t)m * f + 8 * b + lc] : 0.f;
+    const bool ok = factor_solve<F>(acc, bx, lr, lc, X != nullptr);
     if (!ok && lane == 0) atomicAdd(info, 1);
     if (L_out) {
       float* l = L_out + (size_t)m * f * f;
-      for (int i = lane; i < f * f; i += 32) {
-        const int r = i / f, c = i - r * f;
-        l[i] = c <= r ? As[r * (F + 1) + c] : 0.f;
-      }
+#pragma unroll
+      for (int a = 0; a < TR; ++a)
+#pragma unroll
+        for (int b = 0; b < TC; ++b) {
+          const int r = 4 * a + lr, c = 8 * b + lc;
+          if (r < f && c < f) l[(size_t)r * f + c] = c <= r ? acc[a][b] : 0.f;
+        }
     }
-    if (X) {
-      solve<F>(As, bs, f, lane);
-      for (int i = lane; i < f; i += 32) X[(size_t)m * f + i] = bs[i];
+    if (X && lr == 0) {
+#pragma unroll
+      for (int b = 0; b < TC; ++b)
+        if (8 * b + lc < f) X[(size_t)m * f + 8 * b + lc] = bx[b];
     }
-    __syncwarp();
   }
 }
 
@@ -350,10 +386,10 @@ potrs_batched_kernel(const float* __restrict__ A, const float* __restrict__ B, f
 
 // ------------------------------------------------------------------------------------------------------------
 // Implicit ALS, step 4: x_u = (Y'Y + Y_u'(C_u - I)Y_u + lambda I)^-1 Y_u' C_u p_u,  c_ui = 1 + alpha r_ui.
-// One warp per row u.  The 32 lanes form a 4 x 8 grid; lane (lr, lc) keeps the (F/4) x (F/8) block of the normal
-// matrix in registers and adds one weighted outer product per rating.  Ratings are taken four at a time: the four
-// factor rows are fetched with coalesced loads, parked in shared memory, and every lane picks the F/4 + F/8 entries
-// it needs.  Rows are claimed dynamically (row lengths are heavy-tailed).
+// One warp per row u, normal matrix in the register layout of chol:: above: one weighted outer product per rating is
+// added to every lane's (F/4) x (F/8) elements.  Ratings are taken four at a time: the four factor rows are fetched
+// with coalesced loads and parked in shared memory twice, permuted so that each lane reads the entries of its rows
+// and of its columns with 128-bit loads.  Rows are claimed dynamically (row lengths are heavy-tailed).
 // ------------------------------------------------------------------------------------------------------------
 namespace als {
 
@@ -361,7 +397,7 @@ constexpr int WARPS = 8;
 constexpr int BATCH = 4;
 
 template <int F>
-constexpr size_t warp_smem_floats() { return (size_t)F * (F + 1) + F + BATCH * F; }
+constexpr size_t warp_smem_floats() { return (size_t)2 * BATCH * F; }
 
 template <int F>
 __global__ void __launch_bounds__(WARPS * 32)
@@ -369,41 +405,47 @@ solve_kernel(const long long* __restrict__ ptr, const int* __restrict__ idx, con
              const float* __restrict__ Y, const float* __restrict__ YtY, const float lam, const float alpha,
              const int* __restrict__ rows, const int n_rows, const int f, float* __restrict__ Xout,
              int* __restrict__ counter, int* __restrict__ info) {
-  constexpr int TR = F / 4, TC = F / 8, Q = (F + 31) / 32, P = F + 1;
+  constexpr int TR = F / 4, TC = F / 8, Q = (F + 31) / 32;
   extern __shared__ __align__(16) float sm[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* As = sm + (size_t)warp * warp_smem_floats<F>();
-  float* bs = As + F * P;
-  float* ys = bs + F;
+  float* ysr = sm + (size_t)warp * warp_smem_floats<F>();   // [BATCH][4][TR]: y[4a + lr] at lr*TR + a
+  float* ysc = ysr + BATCH * F;                              // [BATCH][8][TC]: y[8b + lc] at lc*TC + b
   const int lr = lane >> 3, lc = lane & 7;
-  const int r0 = lr * TR, c0 = lc * TC;
   for (;;) {
     int claim = 0;
     if (lane == 0) claim = atomicAdd(counter, 1);
     claim = __shfl_sync(0xffffffffu, claim, 0);
     if (claim >= n_rows) break;
     const int u = rows ? rows[claim] : claim;
-    const long long a = ptr[u], e = ptr[u + 1];
-    float acc[TR][TC];
+    const long long a0 = ptr[u], e = ptr[u + 1];
+    if (a0 == e) {                                  // no ratings: the factor row is zero (as the reference leaves it)
 #pragma unroll
-    for (int i = 0; i < TR; ++i)
+      for (int q = 0; q < Q; ++q) {
+        const int c = lane + 32 * q;
+        if (c < F) Xout[(size_t)u * F + c] = 0.f;
+      }
+      continue;
+    }
+    float acc[TR][TC], bx[TC];
 #pragma unroll
-      for (int j = 0; j < TC; ++j) {
-        const int r = r0 + i, c = c0 + j;
+    for (int a = 0; a < TR; ++a)
+#pragma unroll
+      for (int b = 0; b < TC; ++b) {
+        const int r = 4 * a + lr, c = 8 * b + lc;
         float v = YtY[r * F + c];
         if (r == c) v += r < f ? lam : 1.f;        // padded coordinates get an identity block
-        acc[i][j] = v;
+        acc[a][b] = v;
       }
-    float bv[Q];
 #pragma unroll
-    for (int q = 0; q < Q; ++q) bv[q] = 0.f;
-    for (long long t = a; t < e; t += BATCH) {
-      float yl[BATCH][Q], w[BATCH];
+    for (int b = 0; b < TC; ++b) bx[b] = 0.f;
+    for (long long t = a0; t < e; t += BATCH) {
+      float yl[BATCH][Q], w[BATCH], cw[BATCH];
 #pragma unroll
       for (int s = 0; s < BATCH; ++s) {
         const bool on = t + s < e;
         const int it = on ? idx[t + s] : 0;
         w[s] = on ? alpha * val[t + s] : 0.f;
+        cw[s] = on ? 1.f + w[s] : 0.f;
 #pragma unroll
         for (int q = 0; q < Q; ++q) {
           const int c = lane + 32 * q;
@@ -416,50 +458,35 @@ solve_kernel(const long long* __restrict__ ptr, const int* __restrict__ idx, con
 #pragma unroll
         for (int q = 0; q < Q; ++q) {
           const int c = lane + 32 * q;
-          if (c < F) ys[s * F + c] = yl[s][q];
-          bv[q] = fmaf(t + s < e ? 1.f + w[s] : 0.f, yl[s][q], bv[q]);
+          if (c < F) {
+            ysr[s * F + (c & 3) * TR + (c >> 2)] = yl[s][q];
+            ysc[s * F + (c & 7) * TC + (c >> 3)] = yl[s][q];
+          }
         }
       __syncwarp();
 #pragma unroll
       for (int s = 0; s < BATCH; ++s) {
         float yr[TR], yc[TC];
 #pragma unroll
-        for (int i = 0; i < TR; ++i) yr[i] = ys[s * F + r0 + i] * w[s];
+        for (int a = 0; a < TR; ++a) yr[a] = ysr[s * F + lr * TR + a] * w[s];
 #pragma unroll
-        for (int j = 0; j < TC; ++j) yc[j] = ys[s * F + c0 + j];
+        for (int b = 0; b < TC; ++b) yc[b] = ysc[s * F + lc * TC + b];
 #pragma unroll
-        for (int i = 0; i < TR; ++i)
+        for (int a = 0; a < TR; ++a)
 #pragma unroll
-          for (int j = 0; j < TC; ++j) acc[i][j] = fmaf(yr[i], yc[j], acc[i][j]);
+          for (int b = 0; b < TC; ++b) acc[a][b] = fmaf(yr[a], yc[b], acc[a][b]);
+#pragma unroll
+        for (int b = 0; b < TC; ++b) bx[b] = fmaf(cw[s], yc[b], bx[b]);
       }
     }
-    __syncwarp();
+    if (!chol::factor_solve<F>(acc, bx, lr, lc, true) && lane == 0) atomicAdd(info, 1);
+    if (lr == 0) {
 #pragma unroll
-    for (int i = 0; i < TR; ++i)
-#pragma unroll
-      for (int j = 0; j < TC; ++j) As[(r0 + i) * P + c0 + j] = acc[i][j];
-#pragma unroll
-    for (int q = 0; q < Q; ++q) {
-      const int c = lane + 32 * q;
-      if (c < F) bs[c] = bv[q];
-    }
-    __syncwarp();
-    if (a == e) {                                   // no ratings: the factor row is zero (as the reference leaves it)
-#pragma unroll
-      for (int q = 0; q < Q; ++q) {
-        const int c = lane + 32 * q;
-        if (c < F) Xout[(size_t)u * F + c] = 0.f;
+      for (int b = 0; b < TC; ++b) {
+        const int c = 8 * b + lc;
+        Xout[(size_t)u * F + c] = c < f ? bx[b] : 0.f;
       }
-      continue;
     }
-    if (!chol::factor<F>(As, f, lane) && lane == 0) atomicAdd(info, 1);
-    chol::solve<F>(As, bs, f, lane);
-#pragma unroll
-    for (int q = 0; q < Q; ++q) {
-      const int c = lane + 32 * q;
-      if (c < F) Xout[(size_t)u * F + c] = c < f ? bs[c] : 0.f;
-    }
-    __syncwarp();
   }
 }
 
@@ -512,13 +539,7 @@ int hb_potrs_batched(const float* A, const float* B, float* X, float* L, int f, 
   long long blocks = (batch + chol::WARPS - 1) / chol::WARPS;
   const long long cap = (long long)sm_count() * 8;
   const int grid = (int)(blocks < cap ? blocks : cap);
-#define HB_POTRS(FF)                                                                                             \
-  {                                                                                                              \
-    const size_t smem = (size_t)chol::WARPS * (FF * (FF + 1) + FF) * sizeof(float);                              \
-    HB_CUDA_OK(cudaFuncSetAttribute(chol::potrs_batched_kernel<FF>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                    (int)smem));                                                                 \
-    chol::potrs_batched_kernel<FF><<<grid, chol::WARPS * 32, smem, stream>>>(A, B, X, L, f, batch, info);        \
-  }
+#define HB_POTRS(FF) chol::potrs_batched_kernel<FF><<<grid, chol::WARPS * 32, 0, stream>>>(A, B, X, L, f, batch, info);
   switch (F) {
     case 16: HB_POTRS(16) break;
     case 32: HB_POTRS(32) break;
@@ -562,3 +583,4 @@ int hb_als_solve(const long long* ptr, const int* idx, const float* val, const f
 }
 
 }  // extern "C"
+

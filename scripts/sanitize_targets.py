@@ -97,7 +97,7 @@ def sec_lda():
     for kw in (dict(sampler="dense", fused=False), dict(sampler="dense", fused=True, cluster=1),
                dict(sampler="dense", fused=True, cluster=4, loopback=True),
                dict(sampler="tokenlist", cluster=1), dict(sampler="tokenlist", cluster=4, loopback=True)):
-        for K in (16, 100):
+        for K in (16, 128):
             eng = LDAEngine(d, w, 300, 200, K, 0.1, 0.01, seed=1, **kw)
             l0 = eng.log_likelihood()
             for _ in range(2):

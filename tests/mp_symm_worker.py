@@ -154,7 +154,7 @@ def main():
                 else:
                     break
                 torch.cuda.synchronize()
-                assert _native.launches() > l0, op
+                assert world == 1 or _native.launches() > l0, op
                 same(t, g_) if dt == torch.float64 else None
                 if rep_ > 0:
                     # steady state: the dense route did no metadata exchange at all (the generic twin does its own)
@@ -187,7 +187,7 @@ def main():
         for rmap in (None, perm, None):
             l0 = _native.launches()
             assert C.rotate(comm_s, t, rmap); C.rotate(comm_g, g_, rmap); torch.cuda.synchronize()
-            assert _native.launches() > l0
+            assert world == 1 or _native.launches() > l0
             same(t, g_)
         # push / pull (K18): local = all P rows on every rank, global = the rows this rank owns
         nown = (P + world - 1) // world
@@ -199,7 +199,7 @@ def main():
             lt2, gt2 = twin(lt), twin(gt)
             l0 = _native.launches()
             assert C.push(comm_s, lt, gt, Partitioner(world)); C.push(comm_g, lt2, gt2, Partitioner(world)); torch.cuda.synchronize()
-            assert _native.launches() > l0
+            assert world == 1 or _native.launches() > l0
             if dt == torch.float64:
                 same(gt, gt2)
             lslab.zero_()
