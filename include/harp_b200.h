@@ -253,6 +253,81 @@ int hb_ipc_close(void* ptr);
 int hb_slab_alloc(size_t bytes, void** out_ptr);
 int hb_slab_free(void* ptr);
 
+/* ---- split-precision K-means (fp32-faithful tensor-core mode) ----
+ * prec 0: TF32; 1: fp16 hi/lo halves of x * scale (scale a power of two); 2: bf16 hi/lo halves.
+ * Three kind::f16 MMAs per product (hi*hi + lo*hi + hi*lo), exact two-pass arg-max.
+ * (MJ/kmeans/regroupallgather/CenCalcTask.java:67-100) */
+size_t hb_kmeans_split_row_bytes(int d);
+int hb_kmeans_split_rows(const float* X, long long n, int d, float scale, int prec, void* Xs, void* stream);
+int hb_kmeans_fused_prep2(void* state, int k, int d, int parity, int prec, float scale, void* stream);
+int hb_kmeans_fused_step2(const float* X, const void* Xs, long long n, int d, int k, void* const* peer_state, int rank,
+                          int world, unsigned epoch, int keep_empty, int* assign, int prec, float scale, void* stream);
+
+/* ---- whole-epoch rotation kernels (csrc/rotate_ring.cuh) ----
+ * One cooperative launch trains `steps` panels; the model slices rotate inside the kernel: a communication warp per
+ * CTA pulls the next slice from the symmetric slab of src_rank[step] while the other warps train
+ * (MJ/dymoro/Rotator.java:53-67, RotateTask.java:107-124,158-210).  peer_state, off_ctl, off_buf4, bytes2, src_rank, cnt_base,
+ * par_base2 and timeout_ns come from harp_b200.parallel.ring.RingState.ring_args(); world 0 = no ring, 1 = loop-back.
+ * Bounded waits record a code in the ring control block (words 10, 11) and drain instead of trapping. */
+int hb_ring_ctl_bytes(void);
+int hb_sgd_epoch_max_workers(int rank, int cs);
+int hb_sgd_epoch_trace(unsigned long long* buf);
+int hb_sgd_epoch(float* W, const void* panels_host, int npanels, const int* panel_of_step_host, int steps, int S,
+                 int workers, int cs_and_flags, int rank, float eps, float lambda, unsigned ticket_epoch,
+                 unsigned long long deadline_ns, unsigned long long* trained, void* const* peer_state, int my_rank,
+                 int world, unsigned long long off_ctl, const unsigned long long* off_buf4,
+                 const unsigned long long* bytes2, const int* src_rank_host, unsigned cnt_base,
+                 const unsigned* par_base2, unsigned long long timeout_ns, void* stream);
+int hb_lda_epoch_supported(int K, int dk16);
+int hb_lda_epoch_max_workers(int K, int dk16, int cs);
+int hb_lda_epoch(void* n_dk, int dk16, const float* commons, const void* panels_host, int npanels,
+                 const int* panel_of_step_host, int steps, int S, int workers, int cs, int K, float alpha, float beta,
+                 unsigned long long seed, unsigned ticket_epoch, unsigned long long deadline_ns,
+                 unsigned long long* trained, void* const* peer_state, int my_rank, int world,
+                 unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
+                 const int* src_rank_host, unsigned cnt_base, const unsigned* par_base2,
+                 unsigned long long timeout_ns, void* stream);
+/* Token-list (SparseLDA-style) sampler, K up to 16384: the doc side is the document's own topic list
+ * (MJ/lda/LDAMPTask.java:85-132,209-254). */
+int hb_lda_tl_supported(int K);
+int hb_lda_tl_max_workers(int K, int cs);
+int hb_lda_tl_epoch(int* doc_z, const int* d_ptr, const float* commons, const void* panels_host, int npanels,
+                    const int* panel_of_step_host, int steps, int S, int workers, int cs, int K, float alpha,
+                    float beta, unsigned long long seed, unsigned ticket_epoch, unsigned long long deadline_ns,
+                    unsigned long long* trained, void* const* peer_state, int my_rank, int world,
+                    unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
+                    const int* src_rank_host, unsigned cnt_base, const unsigned* par_base2,
+                    unsigned long long timeout_ns, void* stream);
+/* sum over nonzero counts of lgamma(count + add), fp64, plus the number of nonzeros
+ * (MJ/lda/CalcLikelihoodTask.java:57-77). */
+int hb_lgamma_sum(const int* counts, long long n, double add, double* out, unsigned long long* nnz, void* stream);
+
+/* ---- dense linear algebra (csrc/linalg.cu) ---- */
+int hb_tsqr_pad(int d);
+size_t hb_tsqr_workspace_bytes(int d);
+int hb_tsqr(const float* X, long long n, int d, long long ld, float* work, float* R_out, void* stream);
+int hb_chol_pad(int f);
+int hb_potrs_batched(const float* A, const float* B, float* X, float* L, int f, long long batch, int* info,
+                     void* stream);
+int hb_als_solve(const long long* ptr, const int* idx, const float* val, const float* Y, const float* YtY, float lam,
+                 float alpha, const int* rows, int n_rows, int f, float* Xout, int* counter, int* info, void* stream);
+
+/* ---- NVLink SHARP (multimem) and the VMM slab behind it (csrc/nvls.cu) ----
+ * hb_coll_nvls: mode 0 allreduce (multimem.ld_reduce + multimem.st, f32 sum), 1 broadcast from `root`, 2 allgather.
+ * The slab is a cuMemCreate allocation exported as a POSIX fd, mapped by every rank, and bound to a multicast object. */
+int hb_coll_nvls(const void* const* peer_ptrs, void* mc_ptr, int rank, int world, size_t offset_bytes, size_t bytes,
+                 int mode, int root, size_t flags_offset, uint32_t ticket, void* stream);
+int hb_nvls_probe(int world, size_t bytes, char* msg, int msg_len);
+int hb_vmm_granularity(int world, size_t* out);
+int hb_vmm_create(size_t bytes, unsigned long long* handle_out, int* fd_out);
+int hb_vmm_import(int fd, unsigned long long* handle_out);
+int hb_vmm_map(unsigned long long handle, size_t bytes, size_t align, void** ptr_out);
+int hb_vmm_unmap(void* ptr, size_t bytes);
+int hb_vmm_release(unsigned long long handle);
+int hb_mc_create(int world, size_t bytes, unsigned long long* handle_out, int* fd_out);
+int hb_mc_add_device(unsigned long long mc_handle);
+int hb_mc_bind(unsigned long long mc_handle, unsigned long long mem_handle, size_t bytes);
+
 #ifdef __cplusplus
 }
 #endif

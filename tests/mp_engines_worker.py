@@ -24,7 +24,9 @@ def main():
     Ht = torch.randn(nc, 8, device=dev, generator=torch.Generator(device=dev).manual_seed(77)) / math.sqrt(8)
     r = torch.randint(0, nr, (nnz,), device=dev, generator=g); c = torch.randint(0, nc, (nnz,), device=dev, generator=g)
     v = (Wt[r] * Ht[c]).sum(1) * 2 + 3
-    eng = MFSGDEngine(r, c, v, nr, nc, rk, 0.01, 0.02, symm=ws, seed=5)
+    # a world of one (the driver's single-GPU box) runs the same rotation protocol as a ring of one rank
+    one = dict(fused=True, loopback=True) if world == 1 else {}
+    eng = MFSGDEngine(r, c, v, nr, nc, rk, 0.01, 0.02, symm=ws, seed=5, **one)
     assert eng.fused and eng.S == 2, "the default path must be the whole-epoch kernel with two slices in flight"
     e0 = eng.rmse(r, c, v)
     from harp_b200 import _native
@@ -43,7 +45,7 @@ def main():
     D, V, K, L = 3000, 2000, 64, 50
     docs = torch.arange(D, device=dev).repeat_interleave(L)
     words = (torch.rand(D * L, device=dev, generator=g) ** 2 * V).long() % V
-    lda = LDAEngine(docs, words, D, V, K, 0.1, 0.01, symm=ws, seed=2)
+    lda = LDAEngine(docs, words, D, V, K, 0.1, 0.01, symm=ws, seed=2, **one)
     assert int(lda.topic_sums.sum()) == D * L * world
     ll0 = lda.log_likelihood()
     for it in range(8):
