@@ -11,7 +11,7 @@ timeout 600 python scripts/sanitize_targets.py $sections > gpurun_out/sanitize_p
 rc=$?
 tail -3 gpurun_out/sanitize_plain.log
 if [ $rc -ne 0 ]; then echo "plain run failed rc=$rc"; exit $rc; fi
-timeout 2400 compute-sanitizer --tool $tool --error-exitcode 99 --launch-timeout 300 \
+timeout ${SAN_TIMEOUT:-1500} compute-sanitizer --tool $tool --error-exitcode 99 --launch-timeout 300 \
   python scripts/sanitize_targets.py $sections > gpurun_out/sanitize_$tool.log 2>&1
 rc=$?
 echo "sanitize $tool rc=$rc"
