@@ -38,13 +38,15 @@ constexpr int STAGE_BYTES = 2 * OPER_BYTES;      // A + B
 constexpr int LBO_BYTES = KC * SLAB * 4;         // 2048: next 32-feature slab
 constexpr int SBO_BYTES = 4 * SLAB * 4;          // 512: next group of 4 rows (the 32B-base swizzle atom)
 constexpr int KSTEP_BYTES = UK * SLAB * 4;       // 1024: 8 rows = one tcgen05.mma K step
-constexpr int NTHREADS = 192;
+constexpr int NTHREADS = 320;            // TMA warp, MMA warp, 4 epilogue warps, 4 column-statistics warps
+constexpr int STAT_WARP0 = 6;
 constexpr int TMEM_COLS = 512;
 
 struct Smem {
   static constexpr int stages = 0;
   static constexpr int bars = NSTAGE * STAGE_BYTES;   // 196608
   static constexpr int tmem_slot = bars + 32 * 8;
+  static constexpr int prog = tmem_slot + 8;         // number of pipeline stages the TMA warp has issued
   static constexpr int total = tmem_slot + 16;
 };
 enum : int { B_FULL = 0, B_EMPTY = NSTAGE, T_FULL = 2 * NSTAGE, T_EMPTY = 2 * NSTAGE + 1 };
@@ -106,6 +108,16 @@ struct GramFused {
   int rank, world;
   uint32_t epoch;
   int pad;
+};
+
+// Column statistics produced by the same launch (all four arrays of d entries, initialised by the host wrapper):
+// the statistics warps of a CTA re-read, through L2, the rows its TMA warp is streaming for a DIAGONAL macro-tile
+// (each 256-column block of X is on exactly one diagonal tile per row slab), so X still leaves HBM once.
+struct GramStats {
+  double* sum;
+  double* sumsq;
+  float* mn;
+  float* mx;
 };
 
 __device__ __forceinline__ void gram_spin(const uint32_t* p, uint32_t target, bool sys, const char* what) {
@@ -196,13 +208,15 @@ __device__ __noinline__ void gram_fused_tail(const GramFused& fa, int d) {
 template <int FUSED>
 __global__ void __launch_bounds__(NTHREADS, 1)
 gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int nmt, int ntri,
-               long long rows_per_slab, long long nslabs, float* __restrict__ G, const GramFused fa) {
+               long long rows_per_slab, long long nslabs, float* __restrict__ G, const GramFused fa,
+               const float* __restrict__ X, const GramStats stats) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = smem_u32(smem_raw);
   if ((base & 1023u) != 0) { if (threadIdx.x == 0) printf("harp_b200: smem base not 1024-aligned\n"); __trap(); }
   const uint32_t bars = base + Smem::bars;
   auto bar = [&](int i) -> uint32_t { return bars + 8u * i; };
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem_raw + Smem::tmem_slot);
+  volatile uint32_t* prog = reinterpret_cast<volatile uint32_t*>(smem_raw + Smem::prog);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long nunits = (long long)ntri * nslabs;
 
@@ -210,6 +224,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int
     for (int s = 0; s < NSTAGE; ++s) { mbar_init(bar(B_FULL + s), 1); mbar_init(bar(B_EMPTY + s), 1); }
     mbar_init(bar(T_FULL), 1);
     mbar_init(bar(T_EMPTY), 4);
+    *prog = 0u;
     fence_barrier_init();
   }
   if (warp == 1) { tmem_alloc_1sm(smem_u32(const_cast<uint32_t*>(tmem_slot)), TMEM_COLS); tmem_relinquish_1sm(); }
@@ -237,6 +252,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int
           const uint32_t dst = base + Smem::stages + st * STAGE_BYTES;
           tma_load_3d(dst, &tmap, bar(B_FULL + st), 0, (int32_t)r, ti * (MT / SLAB), pol);
           if (!diag) tma_load_3d(dst + OPER_BYTES, &tmap, bar(B_FULL + st), 0, (int32_t)r, tj * (MT / SLAB), pol);
+          *prog = it + 1u;
         }
       }
     }
@@ -281,6 +297,63 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int
           }
           __syncwarp();
           first = 0;
+        }
+      }
+    }
+  } else if (warp >= STAT_WARP0) {
+    // ===================== Column statistics of the diagonal tiles' rows =====================
+    if (stats.sum != nullptr) {
+      const int sw = warp - STAT_WARP0;
+      uint32_t it = 0;
+      for (long long u = blockIdx.x; u < nunits; u += gridDim.x) {
+        int ti, tj; long long s;
+        decode_unit(u, ntri, nmt, ti, tj, s);
+        const long long r0 = s * rows_per_slab;
+        long long r1 = r0 + rows_per_slab; if (r1 > n) r1 = n;
+        const uint32_t nst = (uint32_t)((r1 - r0 + KC - 1) / KC);
+        const int col = ti * MT + lane * 8;
+        if (ti != tj || col >= d) { it += nst; continue; }
+        double ds[8], dss[8];
+        float fs[8], fss[8], lo[8], hi[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) { ds[q] = 0.0; dss[q] = 0.0; fs[q] = 0.f; fss[q] = 0.f; lo[q] = CUDART_INF_F; hi[q] = -CUDART_INF_F; }
+        uint32_t k = 0;
+        for (long long r = r0; r < r1; r += KC, ++it, ++k) {
+          while (*prog <= it) __nanosleep(64);                 // stay right behind the TMA warp: its rows are in L2
+          const long long rr = r + sw * (KC / 4);
+          float4 v[KC / 4][2];
+#pragma unroll
+          for (int j = 0; j < KC / 4; ++j) {
+            const bool on = rr + j < r1;
+            const float* src = X + (size_t)(on ? rr + j : r0) * d + col;
+            v[j][0] = ld_nc_v4(src);
+            v[j][1] = ld_nc_v4(src + 4);
+            if (!on) { v[j][0] = make_float4(0.f, 0.f, 0.f, 0.f); v[j][1] = v[j][0]; }
+          }
+#pragma unroll
+          for (int j = 0; j < KC / 4; ++j) {
+            if (rr + j < r1) {
+              const float e[8] = {v[j][0].x, v[j][0].y, v[j][0].z, v[j][0].w, v[j][1].x, v[j][1].y, v[j][1].z, v[j][1].w};
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                fs[q] += e[q]; fss[q] = fmaf(e[q], e[q], fss[q]);
+                lo[q] = fminf(lo[q], e[q]); hi[q] = fmaxf(hi[q], e[q]);
+              }
+            }
+          }
+          if ((k & 15u) == 15u) {                               // fp32 partials of 64 rows fold into fp64
+#pragma unroll
+            for (int q = 0; q < 8; ++q) { ds[q] += (double)fs[q]; dss[q] += (double)fss[q]; fs[q] = 0.f; fss[q] = 0.f; }
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          atomicAdd(stats.sum + col + q, ds[q] + (double)fs[q]);
+          atomicAdd(stats.sumsq + col + q, dss[q] + (double)fss[q]);
+          int* imn = reinterpret_cast<int*>(stats.mn + col + q);
+          int* imx = reinterpret_cast<int*>(stats.mx + col + q);
+          if (lo[q] >= 0.f) atomicMin(imn, __float_as_int(lo[q])); else atomicMax(reinterpret_cast<unsigned int*>(imn), __float_as_uint(lo[q]));
+          if (hi[q] >= 0.f) atomicMax(imx, __float_as_int(hi[q])); else atomicMin(reinterpret_cast<unsigned int*>(imx), __float_as_uint(hi[q]));
         }
       }
     }
@@ -597,7 +670,9 @@ int hb_gram(const float* X, long long n, int d, float* G, int flags, void* strea
     HB_CUDA_OK(cudaFuncSetAttribute(gram_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::total));
     GramFused nofuse;
     memset(&nofuse, 0, sizeof(nofuse));
-    gram_tc_kernel<0><<<P.grid, NTHREADS, Smem::total, stream>>>(P.tm, n, d, P.nmt, P.ntri, P.rows_per_slab, P.nslabs, G, nofuse);
+    GramStats nostats;
+    memset(&nostats, 0, sizeof(nostats));
+    gram_tc_kernel<0><<<P.grid, NTHREADS, Smem::total, stream>>>(P.tm, n, d, P.nmt, P.ntri, P.rows_per_slab, P.nslabs, G, nofuse, X, nostats);
     HB_CUDA_OK(cudaGetLastError());
     mirror_kernel<<<sms * 2, 256, 0, stream>>>(G, d);
     HB_CUDA_OK(cudaGetLastError());
@@ -622,9 +697,25 @@ size_t hb_gram_fused_state_bytes(int d) { return 256 + (size_t)d * d * sizeof(fl
 // XᵀX of this rank's rows + allreduce over the ranks in ONE launch; the result is left in every rank's state
 // block at byte offset 256 (row-major d x d).  `epoch` = 0, 1, 2, ... per state block, identical on all ranks;
 // the block must be zero-filled once before epoch 0 (and all ranks synchronised) so the flags start at 0.
+int hb_gram_allreduce_fused_stats(const float* X, long long n, int d, void* const* peer_state, int rank, int world,
+                                  unsigned epoch, double* sum, double* sumsq, float* mn, float* mx, void* stream_);
 int hb_gram_allreduce_fused(const float* X, long long n, int d, void* const* peer_state, int rank, int world,
                             unsigned epoch, void* stream_) {
+  return hb_gram_allreduce_fused_stats(X, n, d, peer_state, rank, world, epoch, nullptr, nullptr, nullptr, nullptr, stream_);
+}
+
+// Same launch, and the column statistics of THIS rank's rows (sum, sum of squares in fp64, min, max; d entries each,
+// (re)initialised here) come out of it too: X is streamed from HBM once for Gram + moments.  sum == NULL skips them.
+int hb_gram_allreduce_fused_stats(const float* X, long long n, int d, void* const* peer_state, int rank, int world,
+                                  unsigned epoch, double* sum, double* sumsq, float* mn, float* mx, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
+  HB_REQUIRE(sum == nullptr || (sumsq != nullptr && mn != nullptr && mx != nullptr), "hb_gram_allreduce_fused_stats: all four statistics arrays or none");
+  if (sum != nullptr) {
+    moments_init_kernel<<<(d + 255) / 256, 256, 0, stream>>>(d, sum, sumsq, mn, mx);
+    HB_CUDA_OK(cudaGetLastError());
+  }
+  GramStats stats;
+  stats.sum = sum; stats.sumsq = sumsq; stats.mn = mn; stats.mx = mx;
   HB_REQUIRE(world >= 1 && world <= HB_MAX_RANKS && rank >= 0 && rank < world, "hb_gram_allreduce_fused: bad rank %d / world %d", rank, world);
   HB_REQUIRE(n >= 0 && n < (1LL << 31) && hb_gram_tc_supported(d), "hb_gram_allreduce_fused: shape (n=%lld, d=%d) not supported", n, d);
   GramFused fa;
@@ -655,7 +746,7 @@ int hb_gram_allreduce_fused(const float* X, long long n, int d, void* const* pee
   attr[0].val.cooperative = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  HB_CUDA_OK(cudaLaunchKernelEx(&cfg, gram_tc_kernel<1>, P.tm, n, d, P.nmt, P.ntri, P.rows_per_slab, P.nslabs, G, fa));
+  HB_CUDA_OK(cudaLaunchKernelEx(&cfg, gram_tc_kernel<1>, P.tm, n, d, P.nmt, P.ntri, P.rows_per_slab, P.nslabs, G, fa, X, stats));
   return 0;
 }
 

@@ -842,9 +842,10 @@ static const void* lda_epoch_fn(int K, bool dk16, size_t* smem, int* threads) {
 int hb_lda_epoch_supported(int K, int dk16) { return (K >= 2 && K <= 1024 && (dk16 ? K % 8 == 0 : K % 4 == 0)) ? 1 : 0; }
 
 int hb_lda_epoch_max_workers(int K, int dk16, int cs) {
-  if (cs < 1 || cs > 8 || (cs & (cs - 1)) != 0 || !hb_lda_epoch_supported(K, dk16)) return 0;
+  if (cs < 1 || cs > 16 || (cs & (cs - 1)) != 0 || !hb_lda_epoch_supported(K, dk16)) return 0;
   size_t smem = 0; int threads = 0;
   const void* fn = lda_epoch_fn(K, dk16 != 0, &smem, &threads);
+  if (cs > 8 && cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return 0; }
   if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) { cudaGetLastError(); return 0; }
   if (cs == 1) return sm_count();
   cudaLaunchConfig_t cfg = {};

@@ -455,7 +455,8 @@ extern "C" {
 int hb_lda_tl_supported(int K) { return (K >= 2 && K <= MAX_K) ? 1 : 0; }
 
 int hb_lda_tl_max_workers(int K, int cs) {
-  if (cs < 1 || cs > 8 || (cs & (cs - 1)) != 0 || !hb_lda_tl_supported(K)) return 0;
+  if (cs < 1 || cs > 16 || (cs & (cs - 1)) != 0 || !hb_lda_tl_supported(K)) return 0;
+  if (cs > 8 && cudaFuncSetAttribute(epoch_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return 0; }
   const size_t smem = tl_smem_bytes(K);
   if (cudaFuncSetAttribute(epoch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) { cudaGetLastError(); return 0; }
   if (cs == 1) return sm_count();

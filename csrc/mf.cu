@@ -782,7 +782,11 @@ static int sgd_epoch_threads(int rank) { return epoch_threads(sgd_use_quad(rank)
 
 // How many workers (clusters of `cs` CTAs, one CTA per SM) one cooperative launch keeps resident.
 int hb_sgd_epoch_max_workers(int rank, int cs) {
-  if (cs < 1 || cs > 8 || (cs & (cs - 1)) != 0) return 0;
+  if (cs < 1 || cs > 16 || (cs & (cs - 1)) != 0) return 0;
+  if (cs > 8 && cudaFuncSetAttribute(sgd_epoch_fn(rank), cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(sm_count() / cs * cs));
   cfg.blockDim = dim3((unsigned)sgd_epoch_threads(rank));

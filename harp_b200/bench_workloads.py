@@ -150,10 +150,10 @@ def measure_workload(workload, steps, warmup, rank, world, dev, symm, sampler_cl
 
         def step():
             if fused is not None:
-                fused(X)
+                _, m = fused(X, want_moments=True)     # Gram + allreduce + column moments: one pass over X
             else:
                 gram(X, out=G)
-            m = moments(X)
+                m = moments(X)
             if world > 1:
                 if symm is not None:
                     s.copy_(m.sum); symm.allreduce_sum_(s)

@@ -39,15 +39,31 @@ def _f64(t: torch.Tensor) -> torch.Tensor:
     return t.double()
 
 
+def _fused_for(X: torch.Tensor, comm):
+    return fused_gram_for(comm, X.shape[1], X.device) if X.dtype == torch.float32 and X.shape[0] < (1 << 31) else None
+
+
 def _gram_allreduced(X: torch.Tensor, comm) -> torch.Tensor:
     """Global ``XᵀX`` in float64.  On CUDA with a tensor-core-sized ``d`` the partial Gram and its allreduce
     are ONE kernel launch (``ops.gram.FusedGram``); otherwise Gram + ``_allreduce_``."""
-    fg = fused_gram_for(comm, X.shape[1], X.device) if X.dtype == torch.float32 and X.shape[0] < (1 << 31) else None
+    fg = _fused_for(X, comm)
     if fg is not None:
         return _f64(fg(X))
     G = _f64(gram(X))
     _allreduce_(G, comm)
     return G
+
+
+def _gram_and_moments(X: torch.Tensor, comm):
+    """(global XᵀX in float64, this rank's column ``Moments``): ONE pass over X when the fused kernel applies (its
+    statistics warps produce Σx, Σx², min, max alongside the Gram), two kernels otherwise."""
+    fg = _fused_for(X, comm)
+    if fg is not None:
+        G, m = fg(X, want_moments=True)
+        return _f64(G), m
+    G = _f64(gram(X))
+    _allreduce_(G, comm)
+    return G, moments(X)
 
 
 # ---------------------------------------------------------------------------------------
@@ -100,8 +116,8 @@ def _cross_product_partials(X: torch.Tensor, comm) -> Tuple[torch.Tensor, torch.
     """(XᵀX, Σx, n) allreduced — DAAL covariance partial results (nObservations, sum, crossProduct)."""
     if X.layout != torch.strided:
         X = X.to_dense()
-    G = _gram_allreduced(X, comm)
-    s = moments(X).sum.clone()
+    G, m = _gram_and_moments(X, comm)
+    s = m.sum.clone()
     n = torch.tensor([float(X.shape[0])], dtype=torch.float64, device=X.device)
     _allreduce_(s, comm); _allreduce_(n, comm)
     return G, s, float(n.item())
@@ -118,8 +134,12 @@ def covariance(X: torch.Tensor, comm=None, center: Optional[bool] = None) -> Cov
     if X.layout != torch.strided:
         X = X.to_dense()
     if center is not False and X.is_floating_point():
-        from ..ops.gram import centered_gram, xty
-        mom = moments(X)
+        from ..ops.gram import centered_gram
+        G1 = None
+        if center is None:
+            G1, mom = _gram_and_moments(X, comm)      # one pass: usually the answer, always the decision
+        else:
+            mom = moments(X)
         st = torch.stack([mom.sum.double(), mom.sumsq.double(),
                           torch.full_like(mom.sum.double(), float(X.shape[0]))])
         _allreduce_(st, comm)
@@ -134,6 +154,10 @@ def covariance(X: torch.Tensor, comm=None, center: Optional[bool] = None) -> Cov
             _allreduce_(Gc, comm)
             delta = mean - m32.double()                      # the shift was the float32-rounded mean
             cov = (Gc - N * torch.outer(delta, delta)) / max(N - 1.0, 1.0)
+            sd = cov.diag().clamp(min=1e-300).sqrt()
+            return CovResult(cov, mean, int(N), cov / torch.outer(sd, sd))
+        if G1 is not None:
+            cov = (G1 - N * torch.outer(mean, mean)) / max(N - 1.0, 1.0)
             sd = cov.diag().clamp(min=1e-300).sqrt()
             return CovResult(cov, mean, int(N), cov / torch.outer(sd, sd))
     G, s, N = _cross_product_partials(X, comm)

@@ -78,7 +78,7 @@ class LDAEngine:
         self.fused = bool(fused)
         self.cs = 1
         if cuda and self.fused:
-            self.cs = int(cluster) if cluster else _mf.pick_cluster(per_panel * 8)    # a token costs ~8x a rating
+            self.cs = int(cluster) if cluster else _mf.pick_cluster(per_panel, "lda")
             maxw = (lambda c: L.tl_max_workers(self.K, c)) if self.tl else (lambda c: L.epoch_max_workers(self.K, self.dk16, c))
             mx = maxw(self.cs)
             while mx < 1 and self.cs > 1:

@@ -146,21 +146,39 @@ class FusedGram:
         self._peers = (ctypes.c_void_p * self.world)(*[ctypes.c_void_p(int(p)) for p in peer_ptrs])
         self.G = state[256:256 + d * d * 4].view(torch.float32).view(d, d)
         self.epoch = 0
+        self._stats = None
+        lib.hb_gram_allreduce_fused_stats.argtypes = [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_void_p,
+                                                      ctypes.c_int, ctypes.c_int, ctypes.c_uint, ctypes.c_void_p,
+                                                      ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         state[:256].zero_()          # flags start at 0; the caller barriers across ranks before the first call
 
     @staticmethod
     def state_bytes(d: int) -> int:
         return 256 + d * d * 4
 
-    def __call__(self, X: torch.Tensor) -> torch.Tensor:
-        """Returns the global Gram matrix (a view of the state, overwritten by the next call)."""
+    def __call__(self, X: torch.Tensor, want_moments: bool = False):
+        """Returns the global Gram matrix (a view of the state, overwritten by the next call).  With ``want_moments``
+        also the column ``Moments`` of THIS rank's rows, produced by the same launch (the statistics warps of the
+        Gram kernel re-read through L2 what its TMA warp streams, so X leaves HBM once for both)."""
         assert X.dtype == torch.float32 and X.dim() == 2 and X.shape[1] == self.d
         X = X.contiguous()
-        rc = self.lib.hb_gram_allreduce_fused(_native.ptr(X), X.shape[0], self.d, ctypes.cast(self._peers, ctypes.c_void_p),
-                                              self.rank, self.world, self.epoch, _native.stream_ptr())
-        _native.check(rc, "hb_gram_allreduce_fused")
-        _native.count_launch(1)
+        P = ctypes.c_void_p
+        if want_moments:
+            if self._stats is None:
+                dev = X.device
+                self._stats = (torch.empty(self.d, dtype=torch.float64, device=dev), torch.empty(self.d, dtype=torch.float64, device=dev),
+                               torch.empty(self.d, dtype=torch.float32, device=dev), torch.empty(self.d, dtype=torch.float32, device=dev))
+            sp = [_native.ptr(t) for t in self._stats]
+        else:
+            sp = [P(0)] * 4
+        rc = self.lib.hb_gram_allreduce_fused_stats(_native.ptr(X), X.shape[0], self.d, ctypes.cast(self._peers, P),
+                                                    self.rank, self.world, self.epoch, *sp, _native.stream_ptr())
+        _native.check(rc, "hb_gram_allreduce_fused_stats")
+        _native.count_launch(2 if want_moments else 1)
         self.epoch += 1
+        if want_moments:
+            s, ss, mn, mx = self._stats
+            return self.G, Moments(s, ss, mn, mx, X.shape[0])
         return self.G
 
 

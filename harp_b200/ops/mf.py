@@ -67,15 +67,20 @@ def epoch_max_workers(rank: int, cs: int) -> int:
     return int(lib.hb_sgd_epoch_max_workers(rank, cs))
 
 
-def pick_cluster(nnz_per_panel: float) -> int:
+def pick_cluster(nnz_per_panel: float, kind: str = "sgd") -> int:
     """CTAs per worker for the whole-epoch kernels.  A pass costs B hand-overs (each ends with a gpu-scope fence that
     has to drain the cell's stores: ~5 us measured) plus nnz / (B x warps per worker) updates, so few, fat workers
     win at every size tried: clusters of 8 (15 workers on a B200: two 8-SM clusters fit per GPC) beat 4, 2 and 1 at
-    781 K, 3 M and 12 M ratings per panel (``scripts/tune_sgd_virtual.py``).  ``HB_EPOCH_CS`` overrides."""
+    781 K, 3 M and 12 M ratings per panel.  For small panels even clusters of 16 (non-portable size; only 7 fit, 112
+    of 148 SMs) win, because 7 hand-overs per pass instead of 15 outweigh the idle SMs: SGD at 781 K ratings per panel
+    (8 ranks) 3.33 -> 2.97 ms per epoch, LDA at 781 K / 3.1 M tokens per panel 13.3 -> 12.5 / 21.6 -> 20.6 ms; at
+    3.1 M ratings (SGD) and 12.5 M (both) clusters of 8 are ahead again (``scripts/tune_*_virtual.py``,
+    ``profiles/EXPERIMENTS.md``).  ``HB_EPOCH_CS`` overrides."""
     import os
     if os.environ.get("HB_EPOCH_CS"):
         return int(os.environ["HB_EPOCH_CS"])
-    return 8
+    small = 1.5e6 if kind == "sgd" else 5e6
+    return 16 if nnz_per_panel < small else 8
 
 
 def epoch_run_slots(rank: int) -> int:

@@ -302,6 +302,10 @@ int hb_lda_tl_epoch(int* doc_z, const int* d_ptr, const float* commons, const vo
  * (MJ/lda/CalcLikelihoodTask.java:57-77). */
 int hb_lgamma_sum(const int* counts, long long n, double add, double* out, unsigned long long* nnz, void* stream);
 
+/* Gram + allreduce + column statistics of this rank's rows in one launch (sum == NULL: no statistics). */
+int hb_gram_allreduce_fused_stats(const float* X, long long n, int d, void* const* peer_state, int rank, int world,
+                                  unsigned epoch, double* sum, double* sumsq, float* mn, float* mx, void* stream);
+
 /* ---- dense linear algebra (csrc/linalg.cu) ---- */
 int hb_tsqr_pad(int d);
 size_t hb_tsqr_workspace_bytes(int d);

@@ -98,3 +98,41 @@ def test_xty_and_linear_regression_without_copy(native_built):
     torch.testing.assert_close(model.beta, beta, rtol=5e-2, atol=5e-2)
     pred = model.predict(X)
     assert float((pred - Y.double()).pow(2).mean().sqrt()) < 0.05
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,d", [(100_003, 256), (50_001, 1024), (7_777, 288), (15, 64), (300_000, 512), (0, 64)])
+def test_gram_fused_with_column_moments(native_built, n, d):
+    """The statistics warps of the Gram kernel: sum / sum of squares / min / max of every column from the SAME launch
+    that produces the Gram matrix, against fp64 torch; repeated so that re-initialisation of the arrays is covered."""
+    from harp_b200.ops.gram import FusedGram
+    st = torch.empty(FusedGram.state_bytes(d), dtype=torch.uint8, device="cuda")
+    fg = FusedGram(st, [st.data_ptr()], 0, d)
+    g = torch.Generator(device="cuda").manual_seed(n + d)
+    for rep in range(2):
+        X = torch.randn(n, d, device="cuda", generator=g) * 3 + torch.linspace(-50, 50, d, device="cuda")
+        G, m = fg(X, want_moments=True)
+        torch.cuda.synchronize()
+        assert m.n == n
+        if n == 0:
+            assert float(m.sum.abs().max()) == 0.0 and bool(torch.isinf(m.min).all())
+            continue
+        Xd = X.double()
+        torch.testing.assert_close(m.sum, Xd.sum(0), rtol=1e-6, atol=1e-6 * n)
+        torch.testing.assert_close(m.sumsq, (Xd * Xd).sum(0), rtol=1e-6, atol=1e-6 * n)
+        assert torch.equal(m.min, X.min(0).values) and torch.equal(m.max, X.max(0).values)
+        ref = Xd.t() @ Xd
+        assert float((G.double() - ref).abs().max() / ref.abs().max()) < 2e-3
+
+
+@pytest.mark.gpu
+def test_covariance_takes_one_pass_when_the_mean_is_small(native_built):
+    from harp_b200 import _native
+    from harp_b200.daal import linalg as L
+    X = torch.randn(200_000, 256, device="cuda") * 2 + 0.3
+    _native.reset_launches()
+    res = L.covariance(X)
+    assert _native.launches() == 2                     # init of the statistics + the fused Gram launch, nothing else
+    ref = torch.cov(X.double().t())
+    assert float((res.covariance - ref).abs().max()) < 2e-2
+    torch.testing.assert_close(res.mean, X.double().mean(0), rtol=1e-6, atol=1e-6)
