@@ -19,6 +19,7 @@
 //   * split-K partial tiles are folded into G with 16-byte L2 reductions; a mirror pass fills
 //     the lower triangle.
 // Column moments (sum, sum of squares, min, max) come from a separate streaming kernel.
+#include <stdlib.h>
 #include "common.cuh"
 #include "../include/harp_b200.h"
 
@@ -38,7 +39,8 @@ constexpr int STAGE_BYTES = 2 * OPER_BYTES;      // A + B
 constexpr int LBO_BYTES = KC * SLAB * 4;         // 2048: next 32-feature slab
 constexpr int SBO_BYTES = 4 * SLAB * 4;          // 512: next group of 4 rows (the 32B-base swizzle atom)
 constexpr int KSTEP_BYTES = UK * SLAB * 4;       // 1024: 8 rows = one tcgen05.mma K step
-constexpr int NTHREADS = 320;            // TMA warp, MMA warp, 4 epilogue warps, 4 column-statistics warps
+constexpr int NSTAT = 8;                 // column-statistics warps
+constexpr int NTHREADS = (6 + NSTAT) * 32;   // TMA warp, MMA warp, 4 epilogue warps, the statistics warps
 constexpr int STAT_WARP0 = 6;
 constexpr int TMEM_COLS = 512;
 
@@ -62,6 +64,13 @@ __device__ __forceinline__ uint64_t desc_mnmajor_sw128(uint32_t smem_addr) {
   d |= static_cast<uint64_t>(1) << 46;
   d |= static_cast<uint64_t>(1) << 61;   // SWIZZLE_128B_BASE32B
   return d;
+}
+
+__device__ __forceinline__ float4 ld_nc_v4_hint(const float* p, uint64_t policy) {
+  float4 v;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p), "l"(policy));
+  return v;
 }
 
 __device__ __forceinline__ void tma_load_3d(uint32_t dst_smem, const CUtensorMap* m, uint32_t bar,
@@ -118,6 +127,7 @@ struct GramStats {
   double* sumsq;
   float* mn;
   float* mx;
+  int dbg;          // HB_GRAM_STATS_DBG triage switches: 1 no loads, 2 no arithmetic, 8 pace on the MMA pipeline
 };
 
 __device__ __forceinline__ void gram_spin(const uint32_t* p, uint32_t target, bool sys, const char* what) {
@@ -252,7 +262,6 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int
           const uint32_t dst = base + Smem::stages + st * STAGE_BYTES;
           tma_load_3d(dst, &tmap, bar(B_FULL + st), 0, (int32_t)r, ti * (MT / SLAB), pol);
           if (!diag) tma_load_3d(dst + OPER_BYTES, &tmap, bar(B_FULL + st), 0, (int32_t)r, tj * (MT / SLAB), pol);
-          *prog = it + 1u;
         }
       }
     }
@@ -274,6 +283,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int
         for (long long r = r0; r < r1; r += KC, ++it) {
           const uint32_t st = it % NSTAGE, ph = (it / NSTAGE) & 1;
           mbar_wait(bar(B_FULL + st), ph);
+          if (lane == 0) *prog = it + 1u;                 // the stage has landed in L2 and smem: statistics warps may read its rows
           tc_fence_after();
           const uint32_t a_addr = base + Smem::stages + st * STAGE_BYTES;
           const uint32_t b_addr = diag ? a_addr : a_addr + OPER_BYTES;
@@ -302,8 +312,15 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int
     }
   } else if (warp >= STAT_WARP0) {
     // ===================== Column statistics of the diagonal tiles' rows =====================
+    // Warp sw covers 128 of the tile's 256 columns (sw & 1) and 4 of a stage's 16 rows (sw >> 1), one float4 per lane
+    // and row.  The tile's rows pass through L2 about one latency (~700 cycles) after the TMA warp asked for them and
+    // a stage lasts ~520 cycles; to hit L2 the warps must keep the TMA warp's pace, so three stages of loads stay in
+    // flight per lane (four register buffers) and the per-stage arithmetic is fp32 (four rows), folded into the fp64
+    // accumulators once per stage.
     if (stats.sum != nullptr) {
       const int sw = warp - STAT_WARP0;
+      const int chalf = sw & 1, rpart = sw >> 1;
+      constexpr int RPS = KC / (NSTAT / 2);
       uint32_t it = 0;
       for (long long u = blockIdx.x; u < nunits; u += gridDim.x) {
         int ti, tj; long long s;
@@ -311,45 +328,67 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmap, long long n, int d, int
         const long long r0 = s * rows_per_slab;
         long long r1 = r0 + rows_per_slab; if (r1 > n) r1 = n;
         const uint32_t nst = (uint32_t)((r1 - r0 + KC - 1) / KC);
-        const int col = ti * MT + lane * 8;
+        const int col = ti * MT + chalf * (MT / 2) + lane * 4;
         if (ti != tj || col >= d) { it += nst; continue; }
-        double ds[8], dss[8];
-        float fs[8], fss[8], lo[8], hi[8];
+        double ds[4], dss[4];
+        float lo[4], hi[4];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) { ds[q] = 0.0; dss[q] = 0.0; fs[q] = 0.f; fss[q] = 0.f; lo[q] = CUDART_INF_F; hi[q] = -CUDART_INF_F; }
-        uint32_t k = 0;
-        for (long long r = r0; r < r1; r += KC, ++it, ++k) {
-          while (*prog <= it) __nanosleep(64);                 // stay right behind the TMA warp: its rows are in L2
-          const long long rr = r + sw * (KC / 4);
-          float4 v[KC / 4][2];
+        for (int q = 0; q < 4; ++q) { ds[q] = 0.0; dss[q] = 0.0; lo[q] = CUDART_INF_F; hi[q] = -CUDART_INF_F; }
+        const float* base = X + (size_t)col;
+        const uint64_t pol = policy_evict_last();            // same L2 priority as the TMA loads of the same lines
+        float4 buf[4][RPS];
+        auto fetch = [&](float4 (&b)[RPS], uint32_t k) {       // rows of stage k that this warp owns
+          if (stats.dbg & 8) while (*prog <= it + k) __nanosleep(32);   // optional: only rows whose stage has landed (slower, see EXPERIMENTS.md)
+          const long long rb = r0 + (long long)k * KC + rpart * RPS;
 #pragma unroll
-          for (int j = 0; j < KC / 4; ++j) {
-            const bool on = rr + j < r1;
-            const float* src = X + (size_t)(on ? rr + j : r0) * d + col;
-            v[j][0] = ld_nc_v4(src);
-            v[j][1] = ld_nc_v4(src + 4);
-            if (!on) { v[j][0] = make_float4(0.f, 0.f, 0.f, 0.f); v[j][1] = v[j][0]; }
+          for (int j = 0; j < RPS; ++j) {
+            const long long row = rb + j < r1 ? rb + j : r1 - 1;
+            if (stats.dbg & 1) b[j] = make_float4(1.f, 2.f, 3.f, (float)k); else
+            b[j] = ld_nc_v4_hint(base + (size_t)row * d, pol);
           }
+        };
+        auto consume = [&](const float4 (&b)[RPS], uint32_t k) {
+          const long long rb = r0 + (long long)k * KC + rpart * RPS;
+          float fs[4] = {0.f, 0.f, 0.f, 0.f}, fss[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int j = 0; j < KC / 4; ++j) {
-            if (rr + j < r1) {
-              const float e[8] = {v[j][0].x, v[j][0].y, v[j][0].z, v[j][0].w, v[j][1].x, v[j][1].y, v[j][1].z, v[j][1].w};
+          for (int j = 0; j < RPS; ++j) {
+            if (stats.dbg & 2) { lo[0] = fminf(lo[0], b[j].x + b[j].y + b[j].z + b[j].w); continue; }
+            if (rb + j < r1) {
+              const float e[4] = {b[j].x, b[j].y, b[j].z, b[j].w};
 #pragma unroll
-              for (int q = 0; q < 8; ++q) {
+              for (int q = 0; q < 4; ++q) {
                 fs[q] += e[q]; fss[q] = fmaf(e[q], e[q], fss[q]);
                 lo[q] = fminf(lo[q], e[q]); hi[q] = fmaxf(hi[q], e[q]);
               }
             }
           }
-          if ((k & 15u) == 15u) {                               // fp32 partials of 64 rows fold into fp64
 #pragma unroll
-            for (int q = 0; q < 8; ++q) { ds[q] += (double)fs[q]; dss[q] += (double)fss[q]; fs[q] = 0.f; fss[q] = 0.f; }
+          for (int q = 0; q < 4; ++q) { ds[q] += (double)fs[q]; dss[q] += (double)fss[q]; }
+        };
+        fetch(buf[0], 0);
+        if (nst > 1) fetch(buf[1], 1);
+        if (nst > 2) fetch(buf[2], 2);
+        for (uint32_t k = 0; k < nst; k += 4) {
+          if (k + 3 < nst) fetch(buf[3], k + 3);
+          consume(buf[0], k);
+          if (k + 1 < nst) {
+            if (k + 4 < nst) fetch(buf[0], k + 4);
+            consume(buf[1], k + 1);
+          }
+          if (k + 2 < nst) {
+            if (k + 5 < nst) fetch(buf[1], k + 5);
+            consume(buf[2], k + 2);
+          }
+          if (k + 3 < nst) {
+            if (k + 6 < nst) fetch(buf[2], k + 6);
+            consume(buf[3], k + 3);
           }
         }
+        it += nst;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          atomicAdd(stats.sum + col + q, ds[q] + (double)fs[q]);
-          atomicAdd(stats.sumsq + col + q, dss[q] + (double)fss[q]);
+        for (int q = 0; q < 4; ++q) {
+          atomicAdd(stats.sum + col + q, ds[q]);
+          atomicAdd(stats.sumsq + col + q, dss[q]);
           int* imn = reinterpret_cast<int*>(stats.mn + col + q);
           int* imx = reinterpret_cast<int*>(stats.mx + col + q);
           if (lo[q] >= 0.f) atomicMin(imn, __float_as_int(lo[q])); else atomicMax(reinterpret_cast<unsigned int*>(imn), __float_as_uint(lo[q]));
@@ -716,6 +755,7 @@ int hb_gram_allreduce_fused_stats(const float* X, long long n, int d, void* cons
   }
   GramStats stats;
   stats.sum = sum; stats.sumsq = sumsq; stats.mn = mn; stats.mx = mx;
+  stats.dbg = getenv("HB_GRAM_STATS_DBG") ? atoi(getenv("HB_GRAM_STATS_DBG")) : 0;
   HB_REQUIRE(world >= 1 && world <= HB_MAX_RANKS && rank >= 0 && rank < world, "hb_gram_allreduce_fused: bad rank %d / world %d", rank, world);
   HB_REQUIRE(n >= 0 && n < (1LL << 31) && hb_gram_tc_supported(d), "hb_gram_allreduce_fused: shape (n=%lld, d=%d) not supported", n, d);
   GramFused fa;

@@ -10,6 +10,8 @@ import json
 import math
 import time
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -147,10 +149,14 @@ def measure_workload(workload, steps, warmup, rank, world, dev, symm, sampler_cl
                 fused = FusedGram(st, [st.data_ptr()], 0, d)
             barrier()
         G = torch.empty(d, d, device=dev) if fused is None else None
+        fuse_stats = os.environ.get("HB_GRAM_FUSED_STATS", "0") == "1"   # 1: moments inside the Gram launch (A/B; not faster under the power cap)
 
         def step():
-            if fused is not None:
+            if fused is not None and fuse_stats:
                 _, m = fused(X, want_moments=True)     # Gram + allreduce + column moments: one pass over X
+            elif fused is not None:
+                fused(X)
+                m = moments(X)
             else:
                 gram(X, out=G)
                 m = moments(X)

@@ -14,6 +14,8 @@ from __future__ import annotations
 import math
 from typing import Dict, NamedTuple, Optional, Tuple
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -55,12 +57,16 @@ def _gram_allreduced(X: torch.Tensor, comm) -> torch.Tensor:
 
 
 def _gram_and_moments(X: torch.Tensor, comm):
-    """(global XᵀX in float64, this rank's column ``Moments``): ONE pass over X when the fused kernel applies (its
-    statistics warps produce Σx, Σx², min, max alongside the Gram), two kernels otherwise."""
+    """(global XᵀX in float64, this rank's column ``Moments``): the fused Gram launch plus the moments kernel, or ONE
+    launch for both with ``HB_GRAM_FUSED_STATS=1`` (statistics warps inside the Gram kernel)."""
     fg = _fused_for(X, comm)
     if fg is not None:
-        G, m = fg(X, want_moments=True)
-        return _f64(G), m
+        # statistics inside the Gram launch save the second HBM pass but not time: the kernel is power-capped and the
+        # extra work lowers its clocks by as much as the separate pass costs (profiles/EXPERIMENTS.md), so opt-in
+        if os.environ.get("HB_GRAM_FUSED_STATS", "0") == "1":
+            G, m = fg(X, want_moments=True)
+            return _f64(G), m
+        return _f64(fg(X)), moments(X)
     G = _f64(gram(X))
     _allreduce_(G, comm)
     return G, moments(X)
