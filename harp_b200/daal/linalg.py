@@ -142,8 +142,15 @@ def covariance(X: torch.Tensor, comm=None, center: Optional[bool] = None) -> Cov
     if center is not False and X.is_floating_point():
         from ..ops.gram import centered_gram
         G1 = None
+        guess = center
         if center is None:
-            G1, mom = _gram_and_moments(X, comm)      # one pass: usually the answer, always the decision
+            ms = moments(X[:1 << 16])                  # a 64 K-row prefix predicts the route; the full moments confirm it
+            mu = ms.sum / max(ms.n, 1)
+            flag = (mu.abs() > 4.0 * (ms.sumsq / max(ms.n, 1) - mu * mu).clamp(min=0).sqrt()).any().double().reshape(1)
+            _allreduce_(flag, comm, "max")            # every rank must take the same route (the routes differ in collectives)
+            guess = bool(flag.item() > 0)
+        if center is None and not guess:
+            G1, mom = _gram_and_moments(X, comm)      # usually the answer, always the decision
         else:
             mom = moments(X)
         st = torch.stack([mom.sum.double(), mom.sumsq.double(),
