@@ -24,6 +24,7 @@ import numpy as np
 import torch
 
 from ..io import formats as F
+from .. import _native
 from ..mapper import CollectiveMapper, Context, KeyValReader, LOG
 from ..ops.kmeans import kmeans_step
 from ..partition import DoubleArrPlus, Partition, Partitioner, Table
@@ -155,7 +156,9 @@ class KMeansRegroupAllgatherMapper(CollectiveMapper):
 
 class ContribKMeansMapper(CollectiveMapper):
     """conf keys (``KMeansConstants``): ``num_centroids``, ``vector_size``, ``num_iterations``,
-    ``centroid_file``, ``work_dir``, ``comm`` (one of the four variants)."""
+    ``centroid_file``, ``work_dir``, ``comm`` (one of the four variants), ``tables`` (``dense`` on GPUs with a symmetric
+    workspace: the centroid table is one slab and the collectives run on the NVLink kernels; ``sparse``: partition
+    objects, generic path)."""
 
     VARIANTS = ("allreduce", "regroup-allgather", "broadcast-reduce", "push-pull")
 
@@ -167,6 +170,7 @@ class ContribKMeansMapper(CollectiveMapper):
         self.cen_file = c["centroid_file"]
         self.work_dir = c.get("work_dir")
         self.variant = c.get("comm", "allreduce")
+        self.tables = c.get("tables", "dense")         # "sparse": one partition per live centroid (generic object path)
         assert self.variant in self.VARIANTS, self.variant
 
     def map_collective(self, reader: KeyValReader, context: Context) -> None:
@@ -210,9 +214,102 @@ class ContribKMeansMapper(CollectiveMapper):
                 row[:d] /= row[d]
                 row[d] = 0
 
+    def _run_dense(self, files: List[str], context: Context) -> None:
+        """The same four variants with the centroid table as ONE dense slab in the symmetric workspace, so that every
+        collective of the iteration runs on the NVLink kernels (allreduce; regroup rows + allgather rows; reduce +
+        broadcast; push with ``red.add`` + pull with owner broadcast).  A centroid nobody was assigned to drops out of
+        later iterations exactly as its partition does in the sparse form: the count column is kept (the reference
+        zeroes it) and the rows with count 0 are masked in the next assignment pass."""
+        N, d, K = self.get_num_workers(), self.dimension, self.num_centroids
+        dt = _work_dtype(self.device)
+        symm = self.comm.symm
+        slabs = [symm.alloc(K * (d + 1), dt).view(K, d + 1) for _ in range(2)]
+        owned = [p for p in range(K) if p % N == self.get_self_id()]
+        gslab = symm.alloc(max(len(owned), 1) * (d + 1), dt).view(max(len(owned), 1), d + 1) if self.variant == "push-pull" else None
+        cur = slabs[0]
+        cur.zero_()
+        if self.is_master():
+            init = F.read_centroids_text(self.cen_file, d)
+            cur[:, :d] = torch.from_numpy(np.asarray(init)[:K, :d]).to(self.device, dt)
+            cur[:, d] = 1.0
+        tables = [Table.dense(0, DoubleArrPlus(), s_) for s_ in slabs]        # layout check cached per table
+        gtable = Table.dense(1, DoubleArrPlus(), gslab[:len(owned)], owned) if gslab is not None else None
+        if not self.broadcast("main", "broadcast-centroids", tables[0], self.get_master_id(), False):
+            raise IOError("Fail to bcast")
+        points = self._load_data(files)
+        self.num_points = points.shape[0]
+        live = torch.ones(K, dtype=torch.bool, device=self.device)
+        mse = 0.0
+        self.collective_launches = 0
+
+        def divide(rows: torch.Tensor) -> None:
+            cnt = rows[:, d:d + 1]
+            rows[:, :d] = torch.where(cnt > 0, rows[:, :d] / cnt.clamp(min=1), rows[:, :d])
+
+        for it in range(self.iteration):
+            prev, cur = slabs[it % 2], slabs[(it + 1) % 2]
+            table = tables[(it + 1) % 2]
+            if table.get_num_partitions() != K:                            # a regroup of an earlier iteration left only owned rows
+                table = tables[(it + 1) % 2] = Table.dense(0, DoubleArrPlus(), cur)
+            cur.zero_()
+            idx = torch.nonzero(live).flatten()
+            mse = 0.0
+            if points.shape[0] and idx.numel():
+                C = prev[idx, :d].contiguous()
+                res = kmeans_step(points, C.float() if C.dtype != torch.float32 and self.device.type == "cuda" else C, want_assign=True)
+                mse = float((points - C[res.assign.long()]).pow(2).sum(1).sqrt().sum().item())
+                cur[idx, :d] = res.sums.to(dt)
+                cur[idx, d] = res.counts.to(dt)
+            l0 = _native.launches()
+            if self.variant == "allreduce":
+                self.allreduce("main", f"allreduce_{it}", table)
+                divide(cur)
+            elif self.variant == "regroup-allgather":
+                self.regroup("main", f"regroup_{it}", table, Partitioner(N))
+                if owned:
+                    rows = cur[owned]
+                    divide(rows)
+                    cur[owned] = rows
+                self.allgather("main", f"allgather_{it}", table)
+            elif self.variant == "broadcast-reduce":
+                self.reduce("main", f"reduce_{it}", table, self.get_master_id())
+                if self.is_master():
+                    divide(cur)
+                self.broadcast("main", f"bcast_{it}", table, self.get_master_id(), False)
+            else:  # push-pull
+                gslab.zero_()
+                self.push("main", f"push_{it}", table, gtable, Partitioner(N))
+                if owned:
+                    divide(gslab[:len(owned)])
+                cur.zero_()
+                self.pull("main", f"pull_{it}", table, gtable, True)
+            self.collective_launches += _native.launches() - l0      # NVLink kernels of this iteration's collectives
+            live = cur[:, d] > 0
+            context.progress()
+        mse_table = Table(0, DoubleArrPlus())
+        mse_table.add_partition(Partition(0, torch.tensor([float(self.num_points), mse], dtype=torch.float64,
+                                                          device=self.device)))
+        self.allreduce("main", "allreduce-mse", mse_table)
+        arr = mse_table.get_partition(0).get()
+        self.final_mse = float(arr[1]) / max(float(arr[0]), 1.0)
+        final = Table(0, DoubleArrPlus())
+        for j in torch.nonzero(live).flatten().tolist():
+            row = cur[j].clone(); row[d] = 0
+            final.add_partition(Partition(j, row))
+        self.cen_table = final
+        if self.is_master():
+            if self.work_dir:
+                F.write_evaluation(os.path.join(self.work_dir, "evaluation"), "MSE", self.final_mse)
+            for pid in sorted(final.get_partition_ids()):
+                row = final.get_partition(pid).get()[:d].double().cpu().tolist()
+                context.write(None, "\t".join(repr(x) for x in row) + "\t")
+
     def run_kmeans(self, files: List[str], context: Context) -> None:
         N, d = self.get_num_workers(), self.dimension
         dt = _work_dtype(self.device)
+        if (self.device.type == "cuda" and N > 1 and getattr(self.comm, "symm", None) is not None
+                and self.tables != "sparse"):
+            return self._run_dense(files, context)
         cen_table = Table(0, DoubleArrPlus())
         if self.is_master():
             init = F.read_centroids_text(self.cen_file, d)

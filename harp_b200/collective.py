@@ -296,7 +296,10 @@ def reduce(comm: Comm, table: Table, root: int) -> bool:
     if slab is not None:
         comm.symm.reduce_(slab.view(-1), root, "sum")       # the root sums every rank's rows over NVLink
         if comm.rank != root:
-            table.release()                                  # ReduceCollective.java:234-238
+            # ReduceCollective.java:234-238 releases the non-root's partitions.  A slab table stays dense instead and its
+            # rows become zero (the SUM identity): an "empty" table that a following broadcast / allreduce of the same
+            # table can still take to the kernels on EVERY rank (mixed routes would deadlock)
+            slab.zero_()
         return True
     send = {}
     if comm.rank != root:

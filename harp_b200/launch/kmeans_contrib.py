@@ -48,6 +48,8 @@ def main(argv=None) -> int:
     run_mapper(mapper, data_dir, conf, out_dir, retries=3)
     if rank == 0:
         print(f"K-means ({op}) finished: MSE : {mapper.final_mse}")
+        if getattr(mapper, "collective_launches", None) is not None:
+            print(f"collective kernel launches: {mapper.collective_launches}")
     return 0
 
 

@@ -161,8 +161,16 @@ def main():
                     pass
             if op == "reduce":
                 assert C.reduce(comm_s, t, 1 % world); C.reduce(comm_g, g_, 1 % world); torch.cuda.synchronize()
-                if dt == torch.float64:
-                    same(t, g_)
+                if rank == 1 % world:
+                    if dt == torch.float64:
+                        same(t, g_)
+                elif world > 1:
+                    # the generic table is released on non-roots; the slab table stays dense with zero rows, so that
+                    # a following broadcast takes the kernel route on every rank
+                    assert g_.get_num_partitions() == 0 and t.is_dense() and float(t.slab.abs().max()) == 0.0
+                    assert C.broadcast(comm_s, t, 1 % world) is True
+                if world > 1 and rank == 1 % world:
+                    assert C.broadcast(comm_s, t, 1 % world) is True
         # regroup -> (divide) -> allgather = aggregate, three rounds on the same table: K2 + allgather rows
         t, slab = make(dt, seed=2); g_ = twin(t)
         for rep_ in range(3):

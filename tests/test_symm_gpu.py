@@ -50,3 +50,29 @@ def test_workers_in_a_world_of_one(native_built, worker, token, port):
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=400)
     sys.stdout.write(res.stdout[-4000:]); sys.stderr.write(res.stderr[-4000:])
     assert res.returncode == 0 and token in res.stdout
+
+
+@pytest.mark.multigpu
+@pytest.mark.parametrize("op", ["allreduce", "regroup-allgather", "broadcast-reduce", "push-pull"])
+def test_contrib_kmeans_variants_run_on_the_nvlink_kernels(native_built, tmp_path, op):
+    """The four tutorial variants with the centroid table as a dense slab: every collective of every iteration is a
+    launch of the NVLink kernels (counted), and the result equals the sparse partition-object path."""
+    import re
+    from harp_b200.io import formats as F
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    out = {}
+    for tables in ("dense", "sparse"):
+        work = tmp_path / f"{op}-{tables}"
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+               "--master-port", "29537", "-m", "harp_b200.launch.kmeans_contrib", "4000", "12", "16", "2", "8", str(work),
+               str(tmp_path / "local"), op, f"--tables={tables}"]
+        res = subprocess.run(cmd, capture_output=True, text=True, timeout=150, cwd=str(ROOT),
+                             env=dict(os.environ, HB_WAIT_TIMEOUT_S="20"))
+        sys.stdout.write(res.stdout[-1500:]); sys.stderr.write(res.stderr[-3000:])
+        assert res.returncode == 0
+        m = re.search(r"collective kernel launches: (\d+)", res.stdout)
+        out[tables] = (F.read_evaluation(str(work / "evaluation"))[1], int(m.group(1)) if m else None)
+    assert out["dense"][1] is not None and out["dense"][1] >= 8, out
+    assert out["sparse"][1] is None
+    assert abs(out["dense"][0] - out["sparse"][0]) <= 1e-3 * abs(out["sparse"][0]), out
