@@ -308,6 +308,7 @@ struct SgdEpochArgs {
   unsigned long long deadline_ns;  // per step, 0 = none
   unsigned int ticket_epoch;       // launches of this kernel so far (every panel is visited once per launch)
   int cs;                          // CTAs per worker (cluster size)
+  int C;                           // column-blocks per panel (>= workers; the surplus hides the hand-over latency)
   unsigned long long* trace;       // optional [steps][B][workers][3] %globaltimer stamps: wait start, go, done (tuning aid)
   int rank;
   float eps, lambda;
@@ -535,7 +536,7 @@ __global__ void __launch_bounds__(epoch_threads(QUAD), 1) sgd_epoch_kernel(const
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cs = (uint32_t)a.cs;
   const uint32_t crank = cs > 1 ? cluster_ctarank() : 0u;
-  const int worker = blockIdx.x / cs, B = gridDim.x / cs;
+  const int worker = blockIdx.x / cs, B = gridDim.x / cs, C = a.C;
   const uint32_t bar_go = smem_u32(&s_bar[0]), bar_done = smem_u32(&s_bar[1]);
   const int nl4 = a.rank >> 2;
   const bool ring_on = a.ring.world > 0;
@@ -567,19 +568,22 @@ __global__ void __launch_bounds__(epoch_threads(QUAD), 1) sgd_epoch_kernel(const
       core.seg_col = pdp->seg_col; core.seg_ptr = pdp->seg_ptr; core.r_row = pdp->r_row; core.r_val = pdp->r_val;
       core.rank = a.rank; core.eps = a.eps; core.lambda = a.lambda;
       const unsigned long long t_end = a.deadline_ns ? globaltimer_ns() + a.deadline_ns : 0ULL;
-      for (int t = 0; t < B; ++t) {
-        const int c = (worker + t) % B;
+      for (int t = 0; t < C; ++t) {
+        const int c = (worker + t) % C;
         if (leader) {
           unsigned int* tick = pdp->col_ticket + c;
-          const int* bsp = pdp->blk_seg_ptr + (size_t)worker * B + c;
+          const int* bsp = pdp->blk_seg_ptr + (size_t)worker * C + c;
           const int s0 = bsp[0], s1 = bsp[1];                 // independent of the ticket: issued before the spin
           unsigned int fl = 0u;
-          unsigned long long* tr = a.trace ? a.trace + (((size_t)g * B + t) * B + worker) * 27 : nullptr;
+          unsigned long long* tr = a.trace ? a.trace + (((size_t)g * C + t) * B + worker) * 27 : nullptr;
           if (tr) tr[0] = rot::now_ns();
           if (t == 0 && ring_on && !rot::wait_slice(a.ring, g)) fl = 2u;
           if (fl == 0u) {
             // column-block c is ours once its previous holder has released it
-            const unsigned int want = tbase + (unsigned)t;
+            // block c is visited at step t' by worker (c - t') mod C when that is < B: our turn comes after the
+            // workers worker+1 .. worker+t (mod C) that exist
+            const int before = min(t, B - 1 - worker) + max(0, worker + t - C + 1);
+            const unsigned int want = tbase + (unsigned)before;
             if (ld_acquire_gpu(tick) != want) {
               const unsigned long long t0 = rot::now_ns();
               unsigned spins = 0;
@@ -617,7 +621,7 @@ __global__ void __launch_bounds__(epoch_threads(QUAD), 1) sgd_epoch_kernel(const
         if (threadIdx.x == 0) { if (cs > 1) mbar_wait_acq_cluster(bar_go, ph_go); else { while (!mbar_try_wait(bar_go, ph_go)) {} } }
         ph_go ^= 1u;
         asm volatile("bar.sync 2, %0;" ::"r"(ntrain) : "memory");
-        unsigned long long* trc = (a.trace && threadIdx.x == 0) ? a.trace + (((size_t)g * B + t) * B + worker) * 27 + 3 + crank * 3 : nullptr;
+        unsigned long long* trc = (a.trace && threadIdx.x == 0) ? a.trace + (((size_t)g * C + t) * B + worker) * 27 + 3 + crank * 3 : nullptr;
         if (trc) trc[0] = rot::now_ns();
         const unsigned int fl = *reinterpret_cast<volatile unsigned int*>(&s_flags);
         if (!(fl & 3u)) {
@@ -638,8 +642,11 @@ __global__ void __launch_bounds__(epoch_threads(QUAD), 1) sgd_epoch_kernel(const
         if (leader) {
           ph_done ^= 1u;
           // tickets keep moving even when the step was cut short (deadline / abort) so nobody waits for ever
-          if (a.trace) a.trace[(((size_t)g * B + t) * B + worker) * 27 + 2] = rot::now_ns();
-          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(pdp->col_ticket + c), "r"(tbase + (unsigned)t + 1u) : "memory");
+          if (a.trace) a.trace[(((size_t)g * C + t) * B + worker) * 27 + 2] = rot::now_ns();
+          {
+            const int before = min(t, B - 1 - worker) + max(0, worker + t - C + 1);
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(pdp->col_ticket + c), "r"(tbase + (unsigned)before + 1u) : "memory");
+          }
         }
         if (fl & 2u) { dead = true; break; }
       }
@@ -819,7 +826,9 @@ int hb_sgd_epoch(float* W, const void* panels_host, int npanels, const int* pane
                  unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
                  const int* src_rank_host, unsigned cnt_base, const unsigned* par_base2,
                  unsigned long long timeout_ns, void* stream) {
-  const int cs = cs_and_flags;
+  const int cs = cs_and_flags & 0xff;
+  const int C = ((cs_and_flags >> 8) & 0xff) ? ((cs_and_flags >> 8) & 0xff) : workers;     // column-blocks per panel
+  HB_REQUIRE(C >= workers && C <= 255, "hb_sgd_epoch: %d column-blocks for %d workers", C, workers);
   HB_REQUIRE(rank >= 4 && rank % 4 == 0 && rank <= 512, "hb_sgd_epoch: need rank %% 4 == 0 and rank <= 512 (got %d)", rank);
   HB_REQUIRE(workers >= 1 && workers <= hb_sgd_epoch_max_workers(rank, cs),
              "hb_sgd_epoch: %d workers of %d CTAs cannot be co-resident (max %d)", workers, cs, hb_sgd_epoch_max_workers(rank, cs));
@@ -835,7 +844,7 @@ int hb_sgd_epoch(float* W, const void* panels_host, int npanels, const int* pane
     a.panel_of_step[g] = panel_of_step_host[g];
   }
   a.W = W;
-  a.trained = trained; a.deadline_ns = deadline_ns; a.ticket_epoch = ticket_epoch; a.cs = cs; a.trace = g_epoch_trace; a.rank = rank;
+  a.trained = trained; a.deadline_ns = deadline_ns; a.ticket_epoch = ticket_epoch; a.cs = cs; a.C = C; a.trace = g_epoch_trace; a.rank = rank;
   a.eps = eps; a.lambda = lambda;
   return rot::launch_epoch(sgd_epoch_fn(rank), sgd_epoch_threads(rank), 0, workers, cs, a, stream);
 }

@@ -33,7 +33,7 @@ class MFSGDEngine:
                  num_cols: int, rank: int, eps: float, lam: float, *, symm=None, blocks: Optional[int] = None,
                  seed: int = 0, group=None, num_slices: Optional[int] = None, fused: Optional[bool] = None,
                  cluster: Optional[int] = None, orders: Optional[Sequence[int]] = None, loopback: bool = False,
-                 max_run: Optional[int] = None, virtual_world: int = 0):
+                 max_run: Optional[int] = None, virtual_world: int = 0, col_blocks: Optional[int] = None):
         self.dev = rows.device
         self.rank_k = int(rank)
         self.eps, self.lam = float(eps), float(lam)
@@ -70,6 +70,7 @@ class MFSGDEngine:
             nnz_max = float(t.item())
         per_panel = nnz_max / (float(S) * N)
         self.cs = 1
+        self.C = None
         if cuda and self.fused:
             # worker = cluster of cs CTAs; B = as many workers as one cooperative launch keeps resident
             self.cs = int(cluster) if cluster else mf.pick_cluster(per_panel)
@@ -79,8 +80,12 @@ class MFSGDEngine:
                 mx = mf.epoch_max_workers(self.rank_k, self.cs)
             self.B = int(blocks) if blocks else mx
             self.B = max(1, min(self.B, mx))
+            # column-blocks per panel: a few more than workers, so that a block released by one worker has a whole
+            # cell of slack before the next one asks for it and the cross-worker hand-over latency leaves the
+            # critical path (B workers passing B tokens round a ring pay it at every step)
+            self.C = mf.pick_col_blocks(self.B, self.B - col_blocks if (col_blocks is not None and col_blocks < 0) else col_blocks)
             if max_run is None:
-                max_run = mf.pick_max_run(per_panel, self.B, self.cs, mf.epoch_run_slots(self.rank_k))
+                max_run = mf.pick_max_run(per_panel * self.B / self.C, self.B, self.cs, mf.epoch_run_slots(self.rank_k))
         elif cuda:
             mx = mf.max_blocks(self.rank_k)
             sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
@@ -119,7 +124,7 @@ class MFSGDEngine:
             per = []
             for k in range(S):
                 m = (shard == s) & (slc == k)
-                per.append(mf.build_panel(rows[m], local[m], vals[m], self.B, max_run=self.max_run))
+                per.append(mf.build_panel(rows[m], local[m], vals[m], self.B, max_run=self.max_run, C=self.C))
             self.panels.append(per)
         self.trained = torch.zeros(1, dtype=torch.int64, device=self.dev)
         self.epochs_fused = 0
@@ -190,7 +195,7 @@ class MFSGDEngine:
                     src_of_step.append(self.sched[k].rotate()[self.me])
         for k in range(S):
             self._wait_slice(k)
-        mf.sgd_epoch(self.W, self.desc, panel_of_step, S, self.B, self.cs, self.eps, self.lam, self.epochs_fused,
+        mf.sgd_epoch(self.W, self.desc, panel_of_step, S, self.B, self.cs | ((self.C or self.B) << 8), self.eps, self.lam, self.epochs_fused,
                      deadline_ms, self.trained, self.ring, src_of_step)
         self.epochs_fused += 1
         self.ring.advance(N)

@@ -83,6 +83,18 @@ def pick_cluster(nnz_per_panel: float, kind: str = "sgd") -> int:
     return 16 if nnz_per_panel < small else 8
 
 
+def pick_col_blocks(workers: int, col_blocks: Optional[int] = None) -> int:
+    """Column-blocks per panel for the whole-epoch kernels (>= workers).  ``HB_EPOCH_C`` overrides: an absolute count,
+    or ``+k`` for workers + k."""
+    import os
+    env = os.environ.get("HB_EPOCH_C")
+    if col_blocks is None and env:
+        col_blocks = workers + int(env[1:]) if env.startswith("+") else int(env)
+    if col_blocks is None:
+        col_blocks = workers
+    return max(workers, min(int(col_blocks), 255))
+
+
 def epoch_run_slots(rank: int) -> int:
     """Column runs one CTA of the whole-epoch kernel trains at the same time: 16 warps x 4 runs with the quad-run
     cell (rank <= 128), 31 warps x 1 run otherwise (``csrc/mf.cu``; ``HB_SGD_QUAD=0`` switches the quad cell off)."""

@@ -15,8 +15,11 @@ r = (torch.rand(nnz, device=dev, generator=g) ** 2 * rows).long() % rows
 c = (torch.rand(nnz, device=dev, generator=g) ** 2 * cols).long() % cols
 v = torch.rand(nnz, device=dev, generator=g) * 4 + 1
 for cs in css:
-    for mr in (None, 4, 6):
-        eng = MFSGDEngine(r, c, v, rows, cols, rk, 0.001, 0.01, seed=3, virtual_world=N, cluster=cs, max_run=mr)
+    import os
+    for extra in [int(x) for x in os.environ.get("TUNE_EXTRA_C", "0").split(",")]:
+        mr = None
+        eng = MFSGDEngine(r, c, v, rows, cols, rk, 0.001, 0.01, seed=3, virtual_world=N, cluster=cs, max_run=mr,
+                          col_blocks=(None if extra == 0 else -extra))
         for _ in range(3):
             eng.epoch()
         torch.cuda.synchronize()
@@ -29,5 +32,5 @@ for cs in css:
         words = eng.ring.state[:64].view(torch.int32).cpu().tolist()
         if int(t.item()) != nnz:
             print('TRAINED', int(t.item()), 'of', nnz, 'ctl', words[:12], flush=True)
-        print(f"N={N} cs={cs} B={eng.B} max_run={eng.max_run} ms/epoch {ms:.3f} -> {nnz / ms / 1e6:.2f} G updates/s per GPU, {N * nnz / ms / 1e6:.1f} G aggregate", flush=True)
+        print(f"N={N} cs={cs} B={eng.B} C={eng.C} max_run={eng.max_run} ms/epoch {ms:.3f} -> {nnz / ms / 1e6:.2f} G updates/s per GPU, {N * nnz / ms / 1e6:.1f} G aggregate", flush=True)
         del eng
