@@ -39,7 +39,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="harp_b200", choices=["harp_b200", "reference", "nccl_cublas"])
-    ap.add_argument("--workload", default="kmeans", choices=["kmeans", "sgd", "lda", "lda10k", "gram"])
+    ap.add_argument("--workload", default="kmeans", choices=["kmeans", "sgd", "lda", "lda10k", "gram", "ccd"])
     ap.add_argument("--comm", default="auto", choices=["auto", "nccl", "p2p", "fused"])
     ap.add_argument("--points-per-gpu", type=int, default=POINTS_PER_GPU)
     ap.add_argument("--dim", type=int, default=DIM)

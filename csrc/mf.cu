@@ -700,13 +700,74 @@ __global__ void ccd_update_kernel(const int* __restrict__ ptr, const int* __rest
       down = fmaf(hj, hj, down);
     }
     up = warp_sum(up); down = warp_sum(down);
-    const float wnew = up / (lambda + down);
+    const float wnew = up / (lambda * (float)(k1 - k0) + down);      // CCDMPTask.java:80: down = lambda * numV + sum h^2
     const float delta = wi - wnew;
     for (int k = k0 + lane; k < k1; k += 32) {
       const int rk = resid_perm ? resid_perm[k] : k;
       resid[rk] += delta * Hf[idx[k]];
     }
     if (lane == 0) Wf[i] = wnew;
+  }
+}
+
+
+// One CCD++ coordinate sweep of ONE feature over the rows (or columns) a rank owns, in a single pass over their
+// ratings (CCDMPTask.java:67-125: up = sum (m1 + w h) h, down = lambda numV + sum h^2, z* = up / down,
+// m1 -= (z* - w) h).  The two orders of the residual (by row for the W sweeps, by column for the H sweeps) are kept
+// in step without extra passes: a sweep leaves the OTHER order stale by one rank-one term, and the next sweep over
+// that order applies it on the fly:
+//     true residual = res[k] - pd_other[idx[k]] * pd_self[i]
+// (pd_other = change of the other side's vector in the pending sweep, all ids; pd_self = this side's value of the
+// pending feature for the owned id i).  G threads work on one id: a warp for short lists, a whole CTA for long ones.
+template <int G>
+__global__ void __launch_bounds__(256) ccd_sweep_kernel(const int* __restrict__ ptr, const int* __restrict__ idx,
+                                                        float* __restrict__ res, const float* __restrict__ pd_other,
+                                                        const float* __restrict__ pd_self, const float* __restrict__ other,
+                                                        float* __restrict__ self, float* __restrict__ dself, int n,
+                                                        float lambda) {
+  __shared__ float sh[2][8];
+  const int lg = threadIdx.x % G;
+  const int gi = (int)((blockIdx.x * (size_t)blockDim.x + threadIdx.x) / G);
+  const int ng = (int)(((size_t)gridDim.x * blockDim.x) / G);
+  for (int i = gi; i < n; i += ng) {
+    const int k0 = ptr[i], k1 = ptr[i + 1];
+    if (k0 == k1) {
+      if (lg == 0 && dself) dself[i] = 0.f;
+      continue;
+    }
+    const float s_old = self[i];
+    const float pds = pd_other ? pd_self[i] : 0.f;
+    float up = 0.f, down = 0.f;
+    for (int k = k0 + lg; k < k1; k += G) {
+      const int j = idx[k];
+      const float o = other[j];
+      float r = res[k];
+      if (pd_other) r = fmaf(-pd_other[j], pds, r);
+      up = fmaf(fmaf(s_old, o, r), o, up);
+      down = fmaf(o, o, down);
+    }
+    up = warp_sum(up); down = warp_sum(down);
+    if (G > 32) {
+      const int w = threadIdx.x >> 5;
+      __syncthreads();
+      if ((threadIdx.x & 31) == 0) { sh[0][w] = up; sh[1][w] = down; }
+      __syncthreads();
+      up = 0.f; down = 0.f;
+#pragma unroll
+      for (int q = 0; q < G / 32; ++q) { up += sh[0][q]; down += sh[1][q]; }
+    }
+    const float s_new = up / (lambda * (float)(k1 - k0) + down);
+    const float delta = s_new - s_old;
+    for (int k = k0 + lg; k < k1; k += G) {
+      const int j = idx[k];
+      float r = res[k];
+      if (pd_other) r = fmaf(-pd_other[j], pds, r);
+      res[k] = fmaf(-delta, other[j], r);
+    }
+    if (lg == 0) {
+      self[i] = s_new;
+      if (dself) dself[i] = delta;
+    }
   }
 }
 
@@ -875,6 +936,22 @@ int hb_ccd_update(const int* ptr, const int* idx, float* resid, const int* resid
   const long long cap = (long long)sm_count() * 16;
   if (blocks > cap) blocks = cap;
   ccd_update_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(ptr, idx, resid, resid_perm, Wf, Hf, nrows, lambda);
+  HB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// One CCD++ sweep of one feature over n owned ids (see ccd_sweep_kernel).  pd_other / pd_self may both be NULL (the
+// residual order is up to date); dself (the change of every owned entry) may be NULL.  wide != 0: one CTA per id.
+int hb_ccd_sweep(const int* ptr, const int* idx, float* res, const float* pd_other, const float* pd_self,
+                 const float* other, float* self, float* dself, int n, float lambda, int wide, void* stream) {
+  HB_REQUIRE((pd_other == nullptr) == (pd_self == nullptr), "hb_ccd_sweep: pending correction needs both vectors");
+  if (n <= 0) return 0;
+  const int per_cta = wide ? 1 : 8;
+  long long blocks = ((long long)n + per_cta - 1) / per_cta;
+  const long long cap = (long long)sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  if (wide) ccd_sweep_kernel<256><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(ptr, idx, res, pd_other, pd_self, other, self, dself, n, lambda);
+  else ccd_sweep_kernel<32><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(ptr, idx, res, pd_other, pd_self, other, self, dself, n, lambda);
   HB_CUDA_OK(cudaGetLastError());
   return 0;
 }

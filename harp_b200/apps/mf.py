@@ -184,93 +184,21 @@ class CCDCollectiveMapper(CollectiveMapper):
         nrows, ncols = (int(x) + 1 for x in t.get_partition(0).get().tolist())
         by_row = _regroup_by_owner(self, "ccd", "regroup-rows", raw, raw[:, 0].long() % N)      # rows i % N == me
         by_col = _regroup_by_owner(self, "ccd", "regroup-cols", raw, raw[:, 1].long() % N)      # cols j % N == me
-        wdt = torch.float32 if dev.type == "cuda" else torch.float64
-
-        def csr(trip, key_col, other_col, n_keys):
-            key = trip[:, key_col].long() // N                  # local index of the owned id
-            order = torch.argsort(key, stable=True)
-            trip = trip[order]
-            cnt = torch.bincount(trip[:, key_col].long() // N, minlength=n_keys)
-            ptr = torch.zeros(n_keys + 1, dtype=torch.int32, device=dev)
-            ptr[1:] = torch.cumsum(cnt, 0).to(torch.int32)
-            return trip, ptr, trip[:, other_col].to(torch.int32).contiguous()
-        nloc_r = (nrows - me + N - 1) // N if nrows > me else 0
-        nloc_c = (ncols - me + N - 1) // N if ncols > me else 0
-        R, ptr_r, idx_r = csr(by_row, 0, 1, nloc_r)
-        Cc, ptr_c, idx_c = csr(by_col, 1, 0, nloc_c)
-        g = torch.Generator(device=dev).manual_seed(self.seed + 11)
-        scale = 1.0 / math.sqrt(self.r)
         # W and H are SHARDED: rank r keeps the rank-one rows of its own ids (i % N == r) only, like the reference's
         # rotating W / H tables (CCDMPCollectiveMapper.java:546-547, :635-636); the full vectors u, v of the feature
-        # being updated exist only transiently, gathered over NVLink when the mapper has a symmetric workspace.
-        W_full0 = torch.rand(self.r, nrows, device=dev, generator=g, dtype=wdt) * scale      # same stream on every rank
-        own_r = torch.arange(me, nrows, N, device=dev)
-        own_c = torch.arange(me, ncols, N, device=dev)
-        W_loc = W_full0[:, own_r].contiguous()                                               # feature-major (rank-1 rows)
-        H_loc = torch.zeros(self.r, own_c.numel(), device=dev, dtype=wdt)                    # CCD++ starts from H = 0
-        del W_full0
-        symm = self.symm if (dev.type == "cuda" and N > 1 and wdt == torch.float32) else None
-        if symm is not None:
-            u_buf = symm.alloc(nrows, torch.float32)
-            v_buf = symm.alloc(ncols, torch.float32)
-        else:
-            u_buf = torch.zeros(nrows, device=dev, dtype=wdt)
-            v_buf = torch.zeros(ncols, device=dev, dtype=wdt)
-        res_r = R[:, 2].to(wdt).clone()                                                  # residual = v (since H = 0)
-        res_c = Cc[:, 2].to(wdt).clone()
-        rows_r, cols_r = R[:, 0].long(), R[:, 1].long()
-        rows_c, cols_c = Cc[:, 0].long(), Cc[:, 1].long()
-
-        def gather_vec(vec_full, own_idx, new_local, op):
-            if symm is not None:
-                # owners store their entries into every peer's copy (row p is owned by rank p % N): one NVLink kernel,
-                # no metadata — the W / H shard exchange of the reference's two rotators
-                vec_full[own_idx] = new_local.to(vec_full.dtype)
-                symm.allgather_rows_(vec_full.view(-1, 1))
-                return
-            tab = Table(0, FnCombiner(lambda a, b: a))            # disjoint ids: nothing ever combines
-            tab.add_partition(Partition(me, torch.stack([own_idx.to(new_local.dtype), new_local])))
-            self.allgather("ccd", op, tab)
-            for p in tab.get_partitions():
-                ids, vals = p.get()[0].long(), p.get()[1]
-                vec_full[ids] = vals.to(vec_full.dtype)
+        # being updated exist only transiently, gathered over NVLink when the mapper has a symmetric workspace.  One
+        # kernel pass per side and feature, residuals local (models/mfccd.py).
+        from ..models.mfccd import MFCCDEngine
+        symm = self.symm if (dev.type == "cuda" and N > 1) else None
+        eng = MFCCDEngine(by_row[:, 0].long(), by_row[:, 1].long(), by_row[:, 2], by_col[:, 0].long(), by_col[:, 1].long(),
+                          by_col[:, 2], nrows, ncols, self.r, self.lam, symm=symm, seed=self.seed, inner=self.inner)
+        wdt = eng.dt
         self.objective_history = []
-        step = 0
         for it in range(self.num_iterations):
-            for f in range(self.r):
-                u, v = u_buf, v_buf
-                gather_vec(u, own_r, W_loc[f], f"allgather-w0-{it}-{f}")
-                gather_vec(v, own_c, H_loc[f], f"allgather-h0-{it}-{f}")
-                # put feature f back into the residuals
-                res_r += u[rows_r] * v[cols_r]
-                res_c += u[rows_c] * v[cols_c]
-                for _ in range(self.inner):
-                    # --- H side: v_j for owned columns ---
-                    v_loc = v[own_c].contiguous()
-                    r_tmp = res_c - u[rows_c] * v[cols_c]        # kernel expects r = v_ij - u_i v_j form
-                    mf.ccd_update(ptr_c, idx_c, r_tmp, None, v_loc, u.contiguous(), self.lam)
-                    gather_vec(v, own_c, v_loc, f"allgather-h-{step}"); step += 1
-                    # --- W side: u_i for owned rows ---
-                    u_loc = u[own_r].contiguous()
-                    r_tmp = res_r - u[rows_r] * v[cols_r]
-                    mf.ccd_update(ptr_r, idx_r, r_tmp, None, u_loc, v.contiguous(), self.lam)
-                    gather_vec(u, own_r, u_loc, f"allgather-w-{step}"); step += 1
-                W_loc[f], H_loc[f] = u[own_r], v[own_c]
-                res_r -= u[rows_r] * v[cols_r]
-                res_c -= u[rows_c] * v[cols_c]
-            obj = Table(0, DoubleArrPlus())
-            obj.add_partition(Partition(0, torch.stack([(res_r.double() ** 2).sum(), torch.tensor(float(res_r.numel()), dtype=torch.float64, device=dev)])))
-            self.allreduce("ccd", f"allreduce-obj-{it}", obj)
-            se, cnt = obj.get_partition(0).get().tolist()
-            self.objective_history.append(math.sqrt(se / max(cnt, 1.0)))
+            self.objective_history.append(eng.iterate())
             context.progress()
-        # whole factors for the model files / test RMSE: gathered once, at the end
-        W = torch.zeros(self.r, nrows, device=dev, dtype=wdt)
-        H = torch.zeros(self.r, ncols, device=dev, dtype=wdt)
-        for f in range(self.r):
-            gather_vec(u_buf, own_r, W_loc[f], f"allgather-wend-{f}")
-            gather_vec(v_buf, own_c, H_loc[f], f"allgather-hend-{f}")
-            W[f], H[f] = u_buf, v_buf
+        W, H = eng.full_factors()
+        W_loc, H_loc = eng.W_loc, eng.H_loc
         self.W, self.H, self.W_loc, self.H_loc = W, H, W_loc, H_loc
         # test RMSE
         test_files = [f for i, f in enumerate(sorted(self.test_files)) if i % N == me]

@@ -131,6 +131,40 @@ def measure_workload(workload, steps, warmup, rank, world, dev, symm, sampler_cl
                                    "topics": K, "tokens": D * L, "parallelism": f"docs dp{world} + word-topic rotation",
                                    "l2": "doc-topic table (4 GB) exceeds L2"}})
             result = out
+    elif args.workload == "ccd":
+        # MF-CCD++ on the MF-SGD matrix (BASELINE config 3 shape), r = 120 as in the reference's clueweb run
+        # (website/content/docs/applications/mf.md:63): one step = one outer iteration = 120 features x (H sweep + W sweep)
+        from .models.mfccd import MFCCDEngine
+        nr, nc, nnz, r = 480_000, 17_700, 100_000_000, 120
+        g = torch.Generator(device=dev).manual_seed(17)          # the SAME rating set on every rank, then split by owner
+        rows = (torch.rand(nnz, device=dev, generator=g) ** 2 * nr).long() % nr
+        cols = (torch.rand(nnz, device=dev, generator=g) ** 2 * nc).long() % nc
+        vals = torch.rand(nnz, device=dev, generator=g) * 4 + 1
+        mr, mc = rows % world == rank, cols % world == rank
+        eng = MFCCDEngine(rows[mr], cols[mr], vals[mr], rows[mc], cols[mc], vals[mc], nr, nc, r, 0.1, symm=symm, seed=1)
+        del rows, cols, vals, mr, mc
+        torch.cuda.empty_cache()
+        e_first = None
+        for _ in range(args.warmup):
+            e = eng.iterate()
+            e_first = e if e_first is None else e_first
+        barrier()
+        _native.reset_launches()
+        smp = start_sampler()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier(); e0.record()
+        for _ in range(args.steps):
+            e_last = eng.iterate()
+        e1.record(); barrier()
+        ms, out = _finish(args, rank, world, dev, e0.elapsed_time(e1), {}, smp)
+        if rank == 0:
+            out.update({"metric": "mfccd_rating_visits_per_s", "value": 2.0 * r * nnz / (ms / 1e3), "unit": "rating visits/s",
+                        "higher_is_better": True, "scaling": "strong", "dtype": "fp32",
+                        "s_per_iteration": ms / 1e3, "train_rmse_first_last": [e_first, e_last],
+                        "config": {"model": "MF-CCD++ (W sharded by rows, H by columns, rank-one vectors all-gathered over NVLink)",
+                                   "rows": nr, "cols": nc, "ratings": nnz, "r": r, "parallelism": f"rows/cols dp{world}",
+                                   "l2": "two residual orders + index lists (1.6 GB per rank-share) exceed L2"}})
+            result = out
     else:  # gram
         from .ops.gram import gram, moments
         n, d = 50_000_000 // world, 1024

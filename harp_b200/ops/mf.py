@@ -25,6 +25,7 @@ def _declare(lib) -> None:
     lib.hb_sgd_pass_dynamic.argtypes = [P, P, P, P, P, P, P, I, I, I, F, F, P, ctypes.c_ulonglong, P, P]
     lib.hb_mf_sq_err.argtypes = [P, P, P, P, P, LL, I, P, P]
     lib.hb_ccd_update.argtypes = [P, P, P, P, P, P, I, F, P]
+    lib.hb_ccd_sweep.argtypes = [P, P, P, P, P, P, P, P, I, F, I, P]
     lib.hb_sgd_epoch_max_workers.argtypes = [I, I]
     lib.hb_sgd_epoch.argtypes = [P, P, I, P, I, I, I, I, I, F, F, U, ULL, P,
                                  P, I, I, ULL, P, P, P, U, P, ULL, P]
@@ -385,7 +386,7 @@ def ccd_update(ptr: torch.Tensor, idx: torch.Tensor, resid: torch.Tensor, perm: 
             rk = perm[k0:k1].long() if perm is not None else torch.arange(k0, k1)
             hj = Hf[j]
             wi = Wf[i]
-            wnew = ((resid[rk] + wi * hj) * hj).sum() / (lam + (hj * hj).sum())
+            wnew = ((resid[rk] + wi * hj) * hj).sum() / (lam * (k1 - k0) + (hj * hj).sum())     # CCDMPTask.java:80
             resid[rk] += (wi - wnew) * hj
             Wf[i] = wnew
         return
@@ -394,4 +395,40 @@ def ccd_update(ptr: torch.Tensor, idx: torch.Tensor, resid: torch.Tensor, perm: 
     rc = lib.hb_ccd_update(_native.ptr(ptr), _native.ptr(idx), _native.ptr(resid), _native.ptr(perm), _native.ptr(Wf),
                            _native.ptr(Hf), nrows, float(lam), _native.stream_ptr())
     _native.check(rc, "hb_ccd_update")
+    _native.count_launch()
+
+
+def ccd_sweep(ptr: torch.Tensor, idx: torch.Tensor, res: torch.Tensor, other: torch.Tensor, self_: torch.Tensor,
+              lam: float, pd_other: Optional[torch.Tensor] = None, pd_self: Optional[torch.Tensor] = None,
+              dself: Optional[torch.Tensor] = None, wide: bool = False) -> None:
+    """One CCD++ sweep of ONE feature over the owned ids of one side, in a single pass over their ratings
+    (``hb_ccd_sweep``; ``CCDMPTask.java:67-125``).  ``res`` is this side's residual order, stale by the rank-one term
+    ``pd_other[idx] * pd_self[i]`` when the previous sweep ran on the other order; it is brought up to date and then
+    updated for the new value, ``self_`` is overwritten with the new values and ``dself`` receives their change."""
+    n = self_.numel()
+    if self_.device.type != "cuda":
+        for i in range(n):
+            k0, k1 = int(ptr[i]), int(ptr[i + 1])
+            if k0 == k1:
+                if dself is not None:
+                    dself[i] = 0
+                continue
+            j = idx[k0:k1].long()
+            o = other[j]
+            r = res[k0:k1]
+            if pd_other is not None:
+                r = r - pd_other[j] * pd_self[i]
+            s_old = self_[i].clone()
+            s_new = ((r + s_old * o) * o).sum() / (lam * (k1 - k0) + (o * o).sum())
+            res[k0:k1] = r - (s_new - s_old) * o
+            self_[i] = s_new
+            if dself is not None:
+                dself[i] = s_new - s_old
+        return
+    lib = _native.lib()
+    _declare(lib)
+    rc = lib.hb_ccd_sweep(_native.ptr(ptr), _native.ptr(idx), _native.ptr(res), _native.ptr(pd_other), _native.ptr(pd_self),
+                          _native.ptr(other), _native.ptr(self_), _native.ptr(dself), n, float(lam), 1 if wide else 0,
+                          _native.stream_ptr())
+    _native.check(rc, "hb_ccd_sweep")
     _native.count_launch()

@@ -302,6 +302,11 @@ int hb_lda_tl_epoch(int* doc_z, const int* d_ptr, const float* commons, const vo
  * (MJ/lda/CalcLikelihoodTask.java:57-77). */
 int hb_lgamma_sum(const int* counts, long long n, double add, double* out, unsigned long long* nnz, void* stream);
 
+/* One CCD++ sweep of one feature over n owned ids in a single pass (residual update included; the other residual
+ * order is brought up to date on the fly through pd_other / pd_self).  (MJ/ccd/CCDMPTask.java:67-125) */
+int hb_ccd_sweep(const int* ptr, const int* idx, float* res, const float* pd_other, const float* pd_self,
+                 const float* other, float* self, float* dself, int n, float lambda, int wide, void* stream);
+
 /* Gram + allreduce + column statistics of this rank's rows in one launch (sum == NULL: no statistics). */
 int hb_gram_allreduce_fused_stats(const float* X, long long n, int d, void* const* peer_state, int rank, int world,
                                   unsigned epoch, double* sum, double* sumsq, float* mn, float* mx, void* stream);

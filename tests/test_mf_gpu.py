@@ -174,3 +174,25 @@ def test_sgd_epoch_deadline_and_collision_bound(native_built):
     frac = mf.row_collision_bound(eng.panels[0][0])
     print(f"row exposure bound of panel (0,0): {frac:.4f}")
     assert 0.0 <= frac <= 1.0, frac
+
+
+@pytest.mark.parametrize("nr,nc,nnz", [(3000, 400, 60000), (200, 50, 150000)])
+def test_ccd_engine_device_matches_cpu(native_built, nr, nc, nnz):
+    """csrc/mf.cu::ccd_sweep_kernel (warp per id, and CTA per id for the long lists of the second shape) against the
+    fp64 CPU engine: same RMSE trajectory and factors after three outer iterations."""
+    from harp_b200 import _native
+    from harp_b200.models.mfccd import MFCCDEngine
+    g = torch.Generator().manual_seed(1)
+    key = torch.unique(torch.randint(0, nr * nc, (nnz,), generator=g))
+    rows, cols = key // nc, key % nc
+    vals = (torch.rand(key.numel(), generator=g) * 4 + 1).double()
+    cpu = MFCCDEngine(rows, cols, vals, rows, cols, vals, nr, nc, 6, 0.05, seed=2)
+    gpu = MFCCDEngine(rows.cuda(), cols.cuda(), vals.cuda(), rows.cuda(), cols.cuda(), vals.cuda(), nr, nc, 6, 0.05, seed=2)
+    assert gpu.wide_c == (nnz > 100000)
+    l0 = _native.launches()
+    for it in range(3):
+        a, b = cpu.iterate(), gpu.iterate()
+        assert abs(a - b) < 2e-4 * a, (it, a, b)
+    assert _native.launches() - l0 == 3 * 6 * 2            # one kernel pass per side and feature, nothing else
+    torch.testing.assert_close(gpu.W_loc.cpu().double(), cpu.W_loc, rtol=5e-3, atol=5e-4)
+    torch.testing.assert_close(gpu.H_loc.cpu().double(), cpu.H_loc, rtol=5e-3, atol=5e-4)

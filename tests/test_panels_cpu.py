@@ -162,3 +162,37 @@ def test_host_cpp_lda_pass_keeps_the_tables_consistent(dk):
     nd = torch.zeros(D, K, dtype=torch.int32); nw = torch.zeros(V, K, dtype=torch.int32)
     L.count_into(panel.tok_doc, panel.tok_z, K, nd); L.count_into(panel.tok_word, panel.tok_z, K, nw)
     assert torch.equal(nd, n_dk.int()) and torch.equal(nw, n_wk) and int(n_dk.min()) >= 0
+
+
+def test_ccd_engine_equals_the_reference_loops():
+    """MFCCDEngine (two residual orders, pending rank-one term applied on the fly, one pass per side and feature)
+    against a direct restatement of CCDMPTask.doColCCD / doRowCCD on ONE residual array, inner = 2."""
+    import math
+    import torch
+    from harp_b200.models.mfccd import MFCCDEngine
+    g = torch.Generator().manual_seed(0)
+    nr, nc, r, lam = 60, 40, 4, 0.1
+    key = torch.unique(torch.randint(0, nr * nc, (900,), generator=g))
+    rows, cols = key // nc, key % nc
+    vals = torch.rand(key.numel(), generator=g, dtype=torch.float64) * 4 + 1
+    eng = MFCCDEngine(rows, cols, vals, rows, cols, vals, nr, nc, r, lam, seed=3, inner=2)
+    W, H, res = eng.W_loc.clone(), eng.H_loc.clone(), vals.clone()
+    for it in range(3):
+        for f in range(r):
+            for _ in range(2):
+                for j in range(nc):
+                    m = cols == j
+                    if m.any():
+                        wt, ht = W[f, rows[m]], H[f, j].clone()
+                        s = ((res[m] + ht * wt) * wt).sum() / (lam * float(m.sum()) + (wt * wt).sum())
+                        res[m] -= (s - ht) * wt
+                        H[f, j] = s
+                for i in range(nr):
+                    m = rows == i
+                    if m.any():
+                        ht, wt = H[f, cols[m]], W[f, i].clone()
+                        z = ((res[m] + wt * ht) * ht).sum() / (lam * float(m.sum()) + (ht * ht).sum())
+                        res[m] -= (z - wt) * ht
+                        W[f, i] = z
+        assert abs(eng.iterate() - math.sqrt(float((res ** 2).mean()))) < 1e-12
+    assert torch.allclose(eng.W_loc, W, atol=1e-12) and torch.allclose(eng.H_loc, H, atol=1e-12)
