@@ -188,6 +188,7 @@ def test_ccd_engine_device_matches_cpu(native_built, nr, nc, nnz):
     vals = (torch.rand(key.numel(), generator=g) * 4 + 1).double()
     cpu = MFCCDEngine(rows, cols, vals, rows, cols, vals, nr, nc, 6, 0.05, seed=2)
     gpu = MFCCDEngine(rows.cuda(), cols.cuda(), vals.cuda(), rows.cuda(), cols.cuda(), vals.cuda(), nr, nc, 6, 0.05, seed=2)
+    gpu.W_loc.copy_(cpu.W_loc)                  # the device generator draws a different initial W
     assert gpu.wide_c == (nnz > 100000)
     l0 = _native.launches()
     for it in range(3):
