@@ -719,7 +719,7 @@ __global__ void ccd_update_kernel(const int* __restrict__ ptr, const int* __rest
 //     true residual = res[k] - pd_other[idx[k]] * pd_self[i]
 // (pd_other = change of the other side's vector in the pending sweep, all ids; pd_self = this side's value of the
 // pending feature for the owned id i).  G threads work on one id: a warp for short lists, a whole CTA for long ones.
-template <int G>
+template <int G, int U>
 __global__ void __launch_bounds__(256) ccd_sweep_kernel(const int* __restrict__ ptr, const int* __restrict__ idx,
                                                         float* __restrict__ res, const float* __restrict__ pd_other,
                                                         const float* __restrict__ pd_self, const float* __restrict__ other,
@@ -738,7 +738,27 @@ __global__ void __launch_bounds__(256) ccd_sweep_kernel(const int* __restrict__ 
     const float s_old = self[i];
     const float pds = pd_other ? pd_self[i] : 0.f;
     float up = 0.f, down = 0.f;
-    for (int k = k0 + lg; k < k1; k += G) {
+    // the first U*G ratings of the list stay in registers between the two passes (U independent index -> gather
+    // chains in flight per thread); longer lists re-read their tail
+    float rc[U], oc[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int k = k0 + lg + u * G;
+      rc[u] = 0.f; oc[u] = 0.f;
+      if (k < k1) {
+        const int j = idx[k];
+        const float o = other[j];
+        float r = res[k];
+        if (pd_other) r = fmaf(-pd_other[j], pds, r);
+        rc[u] = r; oc[u] = o;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      up = fmaf(fmaf(s_old, oc[u], rc[u]), oc[u], up);
+      down = fmaf(oc[u], oc[u], down);
+    }
+    for (int k = k0 + lg + U * G; k < k1; k += G) {
       const int j = idx[k];
       const float o = other[j];
       float r = res[k];
@@ -758,7 +778,12 @@ __global__ void __launch_bounds__(256) ccd_sweep_kernel(const int* __restrict__ 
     }
     const float s_new = up / (lambda * (float)(k1 - k0) + down);
     const float delta = s_new - s_old;
-    for (int k = k0 + lg; k < k1; k += G) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int k = k0 + lg + u * G;
+      if (k < k1) res[k] = fmaf(-delta, oc[u], rc[u]);
+    }
+    for (int k = k0 + lg + U * G; k < k1; k += G) {
       const int j = idx[k];
       float r = res[k];
       if (pd_other) r = fmaf(-pd_other[j], pds, r);
@@ -950,8 +975,8 @@ int hb_ccd_sweep(const int* ptr, const int* idx, float* res, const float* pd_oth
   long long blocks = ((long long)n + per_cta - 1) / per_cta;
   const long long cap = (long long)sm_count() * 8;
   if (blocks > cap) blocks = cap;
-  if (wide) ccd_sweep_kernel<256><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(ptr, idx, res, pd_other, pd_self, other, self, dself, n, lambda);
-  else ccd_sweep_kernel<32><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(ptr, idx, res, pd_other, pd_self, other, self, dself, n, lambda);
+  if (wide) ccd_sweep_kernel<256, 24><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(ptr, idx, res, pd_other, pd_self, other, self, dself, n, lambda);
+  else ccd_sweep_kernel<32, 8><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(ptr, idx, res, pd_other, pd_self, other, self, dself, n, lambda);
   HB_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -83,6 +83,21 @@ def main():
             assert int(lda2.iterate().item()) == D * L
         lda2.synchronize()
         assert lda2.log_likelihood() > m0 and int(lda2.topic_sums.sum()) == D * L * world, kw
+    # ---- MF-CCD++: sharded factors, rank-one vectors all-gathered over NVLink; equals the single-process engine ----
+    from harp_b200.models.mfccd import MFCCDEngine
+    gc = torch.Generator(device="cpu").manual_seed(9)
+    cr, cc_, cnnz = 3000, 500, 80000
+    key = torch.unique(torch.randint(0, cr * cc_, (cnnz,), generator=gc))
+    crow, ccol = (key // cc_).to(dev), (key % cc_).to(dev)
+    cval = (torch.rand(key.numel(), generator=gc) * 4 + 1).to(dev)
+    mr_, mc_ = crow % world == rank, ccol % world == rank
+    ccd = MFCCDEngine(crow[mr_], ccol[mr_], cval[mr_], crow[mc_], ccol[mc_], cval[mc_], cr, cc_, 5, 0.05, symm=ws, seed=4)
+    hist = [ccd.iterate() for _ in range(3)]
+    assert hist[2] < hist[0], hist
+    Wc, Hc = ccd.full_factors()
+    pred = (Wc[:, crow] * Hc[:, ccol]).sum(0)
+    rm = float(((cval - pred) ** 2).mean().sqrt())
+    assert abs(rm - hist[2]) < 1e-3 * hist[2], (rm, hist)          # the local residuals ARE the model's residuals
     dist.barrier()
     if rank == 0:
         print(f"ENGINES_OK world={world} sgd_rmse {e0:.4f}->{e1:.4f} lda_ll {ll0:.4e}->{ll1:.4e}", flush=True)
