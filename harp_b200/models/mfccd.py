@@ -64,8 +64,8 @@ class MFCCDEngine:
                 (lambda n: torch.zeros(n, device=dev, dtype=self.dt))
         self.u = alloc(n_rows)             # the feature's full vectors, gathered from the owners
         self.v = alloc(n_cols)
-        self.du = torch.zeros(n_rows, device=dev, dtype=self.dt)
-        self.dv = torch.zeros(n_cols, device=dev, dtype=self.dt)
+        self.du = alloc(n_rows)            # ... and their change in the sweep just done
+        self.dv = alloc(n_cols)
         self.du_loc = torch.zeros(self.own_r.numel(), device=dev, dtype=self.dt)
         self.dv_loc = torch.zeros(self.own_c.numel(), device=dev, dtype=self.dt)
         self.pend_c: Optional[torch.Tensor] = None     # owned-column values of the feature whose W sweep res_c has not seen
@@ -80,20 +80,12 @@ class MFCCDEngine:
             full.copy_(local)
             return
         if self.symm is not None:
-            full[own] = local.to(full.dtype)
+            full[self.me::self.N] = local              # owners' entries, then every owner stores its rows into every peer
             self.symm.allgather_rows_(full.view(-1, 1))
             return
         full.zero_()
-        full[own] = local
+        full[self.me::self.N] = local
         dist.all_reduce(full, group=self.group)
-
-    def _full_delta(self, out: torch.Tensor, own: torch.Tensor, local: torch.Tensor) -> None:
-        if self.N == 1:
-            out.copy_(local)
-            return
-        out.zero_()
-        out[own] = local
-        dist.all_reduce(out, group=self.group)
 
     def iterate(self) -> float:
         """One outer iteration (all r features); returns the training RMSE from the residuals."""
@@ -107,14 +99,14 @@ class MFCCDEngine:
                              dself=self.dv_loc, wide=self.wide_c)
                 self.pend_c = None
                 self._gather(self.v, self.own_c, v_loc)
-                self._full_delta(self.dv, self.own_c, self.dv_loc)
+                self._gather(self.dv, self.own_c, self.dv_loc)
                 # W sweep over the owned rows; res_r lacks the H sweep just done: dv[j] * u_old[i]
                 u_loc = self.W_loc[f]
                 u_old = u_loc.clone()
                 mf.ccd_sweep(self.ptr_r, self.idx_r, self.res_r, self.v, u_loc, self.lam,
                              pd_other=self.dv, pd_self=u_old, dself=self.du_loc, wide=self.wide_r)
                 self._gather(self.u, self.own_r, u_loc)
-                self._full_delta(self.du, self.own_r, self.du_loc)
+                self._gather(self.du, self.own_r, self.du_loc)
                 self.pend_c = v_loc.clone()            # res_c lacks du[i] * v_new[j]
         self.iteration += 1
         return self.rmse()
