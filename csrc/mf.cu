@@ -621,7 +621,7 @@ __global__ void __launch_bounds__(epoch_threads(QUAD), 1) sgd_epoch_kernel(const
         if (threadIdx.x == 0) { if (cs > 1) mbar_wait_acq_cluster(bar_go, ph_go); else { while (!mbar_try_wait(bar_go, ph_go)) {} } }
         ph_go ^= 1u;
         asm volatile("bar.sync 2, %0;" ::"r"(ntrain) : "memory");
-        unsigned long long* trc = (a.trace && threadIdx.x == 0) ? a.trace + (((size_t)g * C + t) * B + worker) * 27 + 3 + crank * 3 : nullptr;
+        unsigned long long* trc = (a.trace && threadIdx.x == 0 && crank < 8u) ? a.trace   /* the slot holds 8 CTAs */ + (((size_t)g * C + t) * B + worker) * 27 + 3 + crank * 3 : nullptr;
         if (trc) trc[0] = rot::now_ns();
         const unsigned int fl = *reinterpret_cast<volatile unsigned int*>(&s_flags);
         if (!(fl & 3u)) {

@@ -39,7 +39,8 @@ for gi in range(min(steps, 3)):
     print(f" step {gi}: start {float(t[gi, 0, :, 0].min()):.1f} end {float(t[gi, -1, :, 2].max()):.1f} cell max per hand-over:",
           [round(float(cell[gi, ti].max()), 1) for ti in range(min(B, 8))], "min:", [round(float(cell[gi, ti].min()), 1) for ti in range(min(B, 8))])
 
-c = (full[..., 3:3 + 3 * eng.cs].reshape(steps, B, B, eng.cs, 3) - t0) / 1e3      # per CTA: work start, work end, fenced
+ncs = min(eng.cs, 8)                   # the trace slot records the first eight CTAs of a worker
+c = (full[..., 3:3 + 3 * ncs].reshape(steps, B, B, ncs, 3) - t0) / 1e3      # per CTA: work start, work end, fenced
 go = t[..., 1].unsqueeze(-1)
 print(f"per CTA: go->work start {float((c[..., 0] - go).mean()):.2f} us, work {float((c[..., 1] - c[..., 0]).mean()):.2f} us "
       f"(max over CTAs of a worker {float((c[..., 1] - c[..., 0]).max(-1).values.mean()):.2f}), fence {float((c[..., 2] - c[..., 1]).mean()):.2f} us, "
