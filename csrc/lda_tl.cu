@@ -70,6 +70,7 @@ struct PanelDesc {
 
 struct Core {
   int* n_wk;
+  int* n_wb;                   // [words][nb] exact per-32-topic block counts of n_wk (NULL: not kept)
   const int* seg_word; const int* seg_ptr; const int* tok_doc; int* tok_z; const int* tok_pos;
   int* doc_z; const int* d_ptr;
   unsigned long long seed;
@@ -103,16 +104,39 @@ __device__ __forceinline__ unsigned long long run_segment(const Core& a, int seg
   const int word = a.seg_word[seg] & 0x7FFFFFFF;
   const int k0 = a.seg_ptr[seg], k1 = a.seg_ptr[seg + 1];
   int* wrow = a.n_wk + (size_t)word * K;
-  // block sums of the word bucket, one coalesced 128-byte row segment per block
+  // block sums of the word bucket, one coalesced 128-byte row segment per block.  With the block counts only the
+  // blocks that hold any of the word's tokens are read (a word with 100 tokens touches at most 100 of the 313 blocks
+  // of a 10 000-topic row; most words far fewer), instead of the whole 40 KB row per run.
+  int* wbrow = a.n_wb ? a.n_wb + (size_t)word * nb : nullptr;
   float wsum = 0.f;
   __syncwarp();
-  for (int b = 0; b < nb; ++b) {
-    const int k = b * 32 + lane;
-    float v = (k < K) ? (float)ldcg_i32(wrow + k) * s_cm[k] : 0.f;
+  if (wbrow != nullptr) {
+    for (int b0 = 0; b0 < nb; b0 += 32) {
+      const int b = b0 + lane;
+      const int cnt = b < nb ? ldcg_i32(wbrow + b) : 0;
+      if (b < nb) bs[b] = 0.f;
+      unsigned m = __ballot_sync(0xffffffffu, cnt > 0);
+      __syncwarp();
+      while (m) {
+        const int bb = b0 + __ffs(m) - 1;
+        m &= m - 1;
+        const int k = bb * 32 + lane;
+        float v = (k < K) ? (float)ldcg_i32(wrow + k) * s_cm[k] : 0.f;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) bs[b] = v;
-    wsum += v;
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) bs[bb] = v;
+        wsum += v;
+      }
+    }
+  } else {
+    for (int b = 0; b < nb; ++b) {
+      const int k = b * 32 + lane;
+      float v = (k < K) ? (float)ldcg_i32(wrow + k) * s_cm[k] : 0.f;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) bs[b] = v;
+      wsum += v;
+    }
   }
   __syncwarp();
   for (int tk = k0; tk < k1; ++tk) {
@@ -221,6 +245,10 @@ __device__ __forceinline__ unsigned long long run_segment(const Core& a, int seg
       if (znew != zold) {
         atomicAdd(wrow + znew, 1);
         atomicSub(wrow + zold, 1);
+        if (wbrow != nullptr && (znew >> 5) != (zold >> 5)) {
+          atomicAdd(wbrow + (znew >> 5), 1);
+          atomicSub(wbrow + (zold >> 5), 1);
+        }
         a.doc_z[pos] = znew;
         a.tok_z[tk] = znew;
       }
@@ -244,6 +272,7 @@ struct EpochArgs {
   unsigned int ticket_epoch;
   int cs, K;
   float alpha, beta;
+  unsigned long long wb_off;             // element offset of the block counts inside a slice (0: none)
   rot::RingArgs ring;
 };
 
@@ -343,6 +372,7 @@ __global__ void __launch_bounds__(THREADS, 1) epoch_kernel(const __grid_constant
       Core core;
       core.n_wk = ring_on ? reinterpret_cast<int*>(rot::slice_ptr(a.ring, g))
                           : reinterpret_cast<int*>(a.ring.peer[0] + a.ring.off_buf[g % a.ring.S][0]);
+      core.n_wb = a.wb_off ? core.n_wk + a.wb_off : nullptr;
       core.seg_word = pdp->seg_word; core.seg_ptr = pdp->seg_ptr; core.tok_doc = pdp->tok_doc; core.tok_z = pdp->tok_z;
       core.tok_pos = pdp->tok_pos; core.doc_z = a.doc_z; core.d_ptr = a.d_ptr;
       core.seed = a.seed + (unsigned long long)g * 0x9E3779B97F4A7C15ULL; core.alpha = a.alpha; core.beta = a.beta;
@@ -477,6 +507,15 @@ int hb_lda_tl_max_workers(int K, int cs) {
 // no document-topic table — doc_z[ntok_local] holds this rank's tokens in document order (current topics),
 // d_ptr[docs + 1] the documents' extents, and every panel descriptor has a 7th pointer tok_pos (token -> index
 // into doc_z).  K <= 16384.
+// Same, with per-32-topic block counts kept next to the word-topic rows: every slice is
+// [words x K counts | words x ceil(K/32) block counts], wb_off = words x K (in elements; 0 = no block counts).
+int hb_lda_tl_epoch2(int* doc_z, const int* d_ptr, const float* commons, const void* panels_host, int npanels,
+                     const int* panel_of_step_host, int steps, int S, int workers, int cs, int K, float alpha, float beta,
+                     unsigned long long seed, unsigned ticket_epoch, unsigned long long deadline_ns,
+                     unsigned long long* trained, void* const* peer_state, int my_rank, int world,
+                     unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
+                     const int* src_rank_host, unsigned cnt_base, const unsigned* par_base2,
+                     unsigned long long timeout_ns, unsigned long long wb_off, void* stream);
 int hb_lda_tl_epoch(int* doc_z, const int* d_ptr, const float* commons, const void* panels_host, int npanels,
                     const int* panel_of_step_host, int steps, int S, int workers, int cs, int K, float alpha, float beta,
                     unsigned long long seed, unsigned ticket_epoch, unsigned long long deadline_ns,
@@ -484,6 +523,18 @@ int hb_lda_tl_epoch(int* doc_z, const int* d_ptr, const float* commons, const vo
                     unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
                     const int* src_rank_host, unsigned cnt_base, const unsigned* par_base2,
                     unsigned long long timeout_ns, void* stream) {
+  return hb_lda_tl_epoch2(doc_z, d_ptr, commons, panels_host, npanels, panel_of_step_host, steps, S, workers, cs, K, alpha,
+                          beta, seed, ticket_epoch, deadline_ns, trained, peer_state, my_rank, world, off_ctl, off_buf4,
+                          bytes2, src_rank_host, cnt_base, par_base2, timeout_ns, 0ULL, stream);
+}
+
+int hb_lda_tl_epoch2(int* doc_z, const int* d_ptr, const float* commons, const void* panels_host, int npanels,
+                     const int* panel_of_step_host, int steps, int S, int workers, int cs, int K, float alpha, float beta,
+                     unsigned long long seed, unsigned ticket_epoch, unsigned long long deadline_ns,
+                     unsigned long long* trained, void* const* peer_state, int my_rank, int world,
+                     unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
+                     const int* src_rank_host, unsigned cnt_base, const unsigned* par_base2,
+                     unsigned long long timeout_ns, unsigned long long wb_off, void* stream) {
   HB_REQUIRE(hb_lda_tl_supported(K), "hb_lda_tl_epoch: need 2 <= K <= %d topics (got %d)", MAX_K, K);
   HB_REQUIRE(workers >= 1 && workers <= hb_lda_tl_max_workers(K, cs),
              "hb_lda_tl_epoch: %d workers of %d CTAs cannot be co-resident (max %d)", workers, cs, hb_lda_tl_max_workers(K, cs));
@@ -499,7 +550,7 @@ int hb_lda_tl_epoch(int* doc_z, const int* d_ptr, const float* commons, const vo
     a.panel_of_step[g] = panel_of_step_host[g];
   }
   a.commons = commons; a.doc_z = doc_z; a.d_ptr = d_ptr; a.trained = trained; a.deadline_ns = deadline_ns; a.seed = seed;
-  a.ticket_epoch = ticket_epoch; a.cs = cs; a.K = K; a.alpha = alpha; a.beta = beta;
+  a.ticket_epoch = ticket_epoch; a.cs = cs; a.K = K; a.alpha = alpha; a.beta = beta; a.wb_off = wb_off;
   const size_t smem = tl_smem_bytes(K);
   HB_CUDA_OK(cudaFuncSetAttribute(epoch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   return rot::launch_epoch((const void*)epoch_kernel, THREADS, smem, workers, cs, a, stream);

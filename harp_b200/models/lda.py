@@ -10,6 +10,7 @@ ones, where one fatter panel per rotation step keeps the block schedule efficien
 from __future__ import annotations
 
 import math
+import os
 from typing import List, Optional
 
 import torch
@@ -134,9 +135,13 @@ class LDAEngine:
         self._cur = [0] * S
         self.sched = [RingSchedule(self.N, None) for _ in range(S)]     # plain ring (LDAMPCollectiveMapper.java:255-259)
         if cuda:
-            self.ring = RingState(self.dev, self.cap * self.K, cdt, S, symm=self.symm, rank=self.me, world=self.N,
-                                  loopback=loopback)
-            self.Wbuf = [[b_.view(self.cap, self.K) for b_ in pair] for pair in self.ring.buf]
+            # token-list sampler: every slice carries, behind its word rows, the exact per-32-topic block counts of
+            # those rows (they rotate together); a run then reads only the non-empty blocks of its word's row
+            self.nb = (self.K + 31) // 32 if (self.tl and os.environ.get("HB_LDA_TL_BLOCKS", "1") != "0") else 0
+            self.ring = RingState(self.dev, self.cap * (self.K + self.nb), cdt, S, symm=self.symm, rank=self.me,
+                                  world=self.N, loopback=loopback)
+            self.Wbuf = [[b_[:self.cap * self.K].view(self.cap, self.K) for b_ in pair] for pair in self.ring.buf]
+            self.Bbuf = [[b_[self.cap * self.K:].view(self.cap, self.nb) for b_ in pair] for pair in self.ring.buf] if self.nb else None
         else:
             self.Wbuf = [[torch.zeros(self.cap, self.K, dtype=cdt, device=self.dev) for _ in range(2 if N > 1 else 1)]
                          for _ in range(S)]
@@ -154,6 +159,10 @@ class LDAEngine:
                 L.count_into(p.tok_word, p.tok_z, self.K, self.Wbuf[k][self.cur[k]])
                 if not self.Nv:
                     self._rotate(k)
+        if cuda and self.nb:
+            for k in range(self.S):
+                self._wait_slice(k)
+                self._rebuild_block_counts(k)
         self.topic_sums = torch.zeros(self.K, dtype=torch.int64, device=self.dev)
         self.commons = torch.zeros(self.K, dtype=torch.float32, device=self.dev)
         self.trained = torch.zeros(1, dtype=torch.int64, device=self.dev)
@@ -207,6 +216,17 @@ class LDAEngine:
                 r.wait()
         self.cur[k] ^= 1
 
+    def _rebuild_block_counts(self, k: int) -> None:
+        """Block counts of slice k's current buffer from its word rows (the kernel keeps them exact afterwards)."""
+        W, Bc = self.Wbuf[k][self.cur[k]], self.Bbuf[k][self.cur[k]]
+        step = max(1, (1 << 28) // max(self.K, 1))              # bounded scratch: 1 GB of rows at a time
+        for r0 in range(0, self.cap, step):
+            w = W[r0:r0 + step]
+            full = (self.K // 32) * 32
+            Bc[r0:r0 + step, :self.K // 32] = w[:, :full].view(w.shape[0], -1, 32).sum(-1, dtype=torch.int32)
+            if full < self.K:
+                Bc[r0:r0 + step, self.K // 32] = w[:, full:].sum(-1, dtype=torch.int32)
+
     def _refresh_topic_sums(self) -> None:
         self.topic_sums.zero_()
         for k in range(self.S):
@@ -237,7 +257,8 @@ class LDAEngine:
             seed_it = self.seed * 1000003 + self.iteration * 7919 + 104729 * self.me
             if self.tl:
                 L.lda_tl_epoch(self.doc_z, self.d_ptr, self.commons, self.K, self.desc, pos_l, S, self.B, self.cs, self.alpha,
-                               self.beta, seed_it, self.epochs_fused, deadline_ms, self.trained, self.ring, src_l)
+                               self.beta, seed_it, self.epochs_fused, deadline_ms, self.trained, self.ring, src_l,
+                               wb_off=self.cap * self.K if self.nb else 0)
             else:
                 L.lda_epoch(self._n_dk, self.commons, self.desc, pos_l, S, self.B, self.cs, self.alpha, self.beta,
                             seed_it, self.epochs_fused, deadline_ms, self.trained, self.ring, src_l)

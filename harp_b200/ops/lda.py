@@ -31,6 +31,8 @@ def _declare(lib) -> None:
     lib.hb_lda_tl_max_workers.argtypes = [I, I]
     lib.hb_lda_tl_epoch.argtypes = [P, P, P, P, I, P, I, I, I, I, I, F, F, ULL, U, ULL, P,
                                     P, I, I, ULL, P, P, P, U, P, ULL, P]
+    lib.hb_lda_tl_epoch2.argtypes = [P, P, P, P, I, P, I, I, I, I, I, F, F, ULL, U, ULL, P,
+                                     P, I, I, ULL, P, P, P, U, P, ULL, ULL, P]
     lib.hb_lgamma_sum.argtypes = [P, LL, ctypes.c_double, P, P, P]
     lib._hb_lda_declared = True
 
@@ -110,18 +112,19 @@ def tl_panel_descriptors(panels):
 
 def lda_tl_epoch(doc_z: torch.Tensor, d_ptr: torch.Tensor, commons: torch.Tensor, K: int, desc, panel_of_step, S: int,
                  workers: int, cs: int, alpha: float, beta: float, seed: int, ticket_epoch: int,
-                 deadline_ms: Optional[float], trained: torch.Tensor, ring, src_of_step) -> None:
-    """One iteration with the SparseLDA-style token-list sampler (``hb_lda_tl_epoch``), any K <= 16384."""
+                 deadline_ms: Optional[float], trained: torch.Tensor, ring, src_of_step, wb_off: int = 0) -> None:
+    """One iteration with the SparseLDA-style token-list sampler (``hb_lda_tl_epoch2``), any K <= 16384.  ``wb_off``:
+    element offset of the per-32-topic block counts inside every slice (0: slices hold the word rows only)."""
     lib = _native.lib()
     _declare(lib)
     deadline = int(deadline_ms * 1e6) if deadline_ms is not None else 0
     steps = len(panel_of_step)
     pos = (ctypes.c_int * steps)(*panel_of_step)
-    rc = lib.hb_lda_tl_epoch(_native.ptr(doc_z), _native.ptr(d_ptr), _native.ptr(commons), desc, len(desc) // 7, pos, steps,
-                             S, workers, cs, int(K), float(alpha), float(beta), int(seed) & 0xFFFFFFFFFFFFFFFF,
-                             ticket_epoch & 0xFFFFFFFF, deadline, _native.ptr(trained), *ring.ring_args(src_of_step),
-                             _native.stream_ptr())
-    _native.check(rc, "hb_lda_tl_epoch")
+    rc = lib.hb_lda_tl_epoch2(_native.ptr(doc_z), _native.ptr(d_ptr), _native.ptr(commons), desc, len(desc) // 7, pos, steps,
+                              S, workers, cs, int(K), float(alpha), float(beta), int(seed) & 0xFFFFFFFFFFFFFFFF,
+                              ticket_epoch & 0xFFFFFFFF, deadline, _native.ptr(trained), *ring.ring_args(src_of_step),
+                              int(wb_off), _native.stream_ptr())
+    _native.check(rc, "hb_lda_tl_epoch2")
     _native.count_launch()
 
 

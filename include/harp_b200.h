@@ -298,6 +298,15 @@ int hb_lda_tl_epoch(int* doc_z, const int* d_ptr, const float* commons, const vo
                     unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
                     const int* src_rank_host, unsigned cnt_base, const unsigned* par_base2,
                     unsigned long long timeout_ns, void* stream);
+/* hb_lda_tl_epoch2: the same with exact per-32-topic block counts kept behind the word-topic rows of every slice
+ * ([words x K | words x ceil(K/32)], wb_off = words x K elements): a run reads only the non-empty blocks of its row. */
+int hb_lda_tl_epoch2(int* doc_z, const int* d_ptr, const float* commons, const void* panels_host, int npanels,
+                     const int* panel_of_step_host, int steps, int S, int workers, int cs, int K, float alpha,
+                     float beta, unsigned long long seed, unsigned ticket_epoch, unsigned long long deadline_ns,
+                     unsigned long long* trained, void* const* peer_state, int my_rank, int world,
+                     unsigned long long off_ctl, const unsigned long long* off_buf4, const unsigned long long* bytes2,
+                     const int* src_rank_host, unsigned cnt_base, const unsigned* par_base2,
+                     unsigned long long timeout_ns, unsigned long long wb_off, void* stream);
 /* sum over nonzero counts of lgamma(count + add), fp64, plus the number of nonzeros
  * (MJ/lda/CalcLikelihoodTask.java:57-77). */
 int hb_lgamma_sum(const int* counts, long long n, double add, double* out, unsigned long long* nnz, void* stream);

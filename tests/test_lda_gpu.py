@@ -101,6 +101,13 @@ def _check_tl_consistency(eng, D, K, ntok):
             if len(eng.panels) == 1:
                 assert torch.equal(tab, eng.Wbuf[k][eng.cur[k]])
     assert int(eng.n_dk.sum()) == ntok and int(eng.Wbuf[0][eng.cur[0]].min()) >= 0
+    if getattr(eng, "nb", 0):
+        # the per-32-topic block counts the kernel maintains next to the word rows are exact
+        for k in range(eng.S):
+            W = eng.Wbuf[k][eng.cur[k]]
+            pad = torch.zeros(eng.cap, eng.nb * 32, dtype=torch.int32, device="cuda")
+            pad[:, :K] = W
+            assert torch.equal(pad.view(eng.cap, eng.nb, 32).sum(-1, dtype=torch.int32), eng.Bbuf[k][eng.cur[k]])
 
 
 @pytest.mark.parametrize("K,cluster,loopback", [(8, 1, False), (64, 4, True), (1000, 8, True), (10000, 8, True), (777, 2, False)])
