@@ -162,7 +162,7 @@ __device__ __forceinline__ unsigned long long run_segment(const Core& a, int seg
       if (p0 + r * 32 < p1) {
         if (j < p1 && j != pos) {
           zr[r] = a.doc_z[j];
-          const int nw = ldcg_i32(wrow + zr[r]) - (zr[r] == zold ? 1 : 0);
+          const int nw = bs[zr[r] >> 5] > 1e-12f ? ldcg_i32(wrow + zr[r]) - (zr[r] == zold ? 1 : 0) : 0;   // empty block: no gather
           vr[r] = ((float)max(nw, 0) + a.beta) * s_cm[zr[r]];
         }
         float t = vr[r];
@@ -177,7 +177,7 @@ __device__ __forceinline__ unsigned long long run_segment(const Core& a, int seg
       float v = 0.f;
       if (j < p1 && j != pos) {
         const int z = a.doc_z[j];
-        const int nw = ldcg_i32(wrow + z) - (z == zold ? 1 : 0);
+        const int nw = bs[z >> 5] > 1e-12f ? ldcg_i32(wrow + z) - (z == zold ? 1 : 0) : 0;
         v = ((float)max(nw, 0) + a.beta) * s_cm[z];
       }
 #pragma unroll
@@ -212,7 +212,7 @@ __device__ __forceinline__ unsigned long long run_segment(const Core& a, int seg
         int z = zold;
         if (j < p1 && j != pos) {
           z = a.doc_z[j];
-          const int nw = ldcg_i32(wrow + z) - (z == zold ? 1 : 0);
+          const int nw = bs[z >> 5] > 1e-12f ? ldcg_i32(wrow + z) - (z == zold ? 1 : 0) : 0;
           v = ((float)max(nw, 0) + a.beta) * s_cm[z];
         }
         const float inc = warp_incl_scan(v, lane);
