@@ -55,7 +55,8 @@ __device__ __forceinline__ bool cta_barrier_all(const Peers& P, int rank, int wo
   int bad = 0;
   if (threadIdx.x < world) {
     const int p = threadIdx.x;
-    fence_sys();  // make this CTA's prior (peer) writes visible before the flag
+    // the release store is cumulative over what the barrier above ordered before it: the CTA's prior (peer) writes are
+    // visible to whoever acquires the flag; a separate fence.sys in front of it only added a second MEMBAR.SYS
     st_release_sys(flag_ptr(P.base[p], flags_off, blockIdx.x, rank), ticket);
     const uint32_t* mine = flag_ptr(P.base[rank], flags_off, blockIdx.x, p);
     if ((int32_t)(ld_acquire_sys(mine) - ticket) < 0) {
@@ -342,7 +343,7 @@ nvls_kernel(Peers P, uint8_t* mc, int rank, int world, size_t off, size_t bytes,
       multimem_st_v4(mc + b, *reinterpret_cast<const float4*>(P.base[rank] + b));
     }
   }
-  __threadfence_system();      // multimem stores are ordered before the flags of the closing barrier
+  // the multimem stores are ordered before the flags of the closing barrier by its bar.sync + release stores
   (void)cta_barrier_all(P, rank, world, flags_off, ticket + 1);
 }
 
