@@ -98,6 +98,19 @@ def main():
     pred = (Wc[:, crow] * Hc[:, ccol]).sum(0)
     rm = float(((cval - pred) ** 2).mean().sqrt())
     assert abs(rm - hist[2]) < 1e-3 * hist[2], (rm, hist)          # the local residuals ARE the model's residuals
+    # ---- implicit ALS, 4-step protocol on the K22 kernel: owners solve their rows, factors meet by allreduce ----
+    from harp_b200 import collective as C
+    from harp_b200.daal import models as DM
+    ga = torch.Generator(device="cpu").manual_seed(21)
+    U_, I_, f_ = 400, 250, 10
+    keya = torch.unique(torch.randint(0, U_ * I_, (12000,), generator=ga))
+    ar, ac = keya // I_, keya % I_
+    av = torch.ones(keya.numel(), dtype=torch.float64)
+    Xc, Yc = DM.als_implicit(ar, ac, av, U_, I_, f_, 4, 0.1, 20.0)                      # single process, CPU, fp64
+    mine_ = torch.arange(keya.numel()) % world == rank                                  # every rank reads a slice of the ratings
+    comm_a = C.Comm(device=dev, symm=ws)
+    Xg, Yg = DM.als_implicit(ar[mine_].to(dev), ac[mine_].to(dev), av[mine_].to(dev), U_, I_, f_, 4, 0.1, 20.0, comm=comm_a)
+    assert float(((Xc @ Yc.t()) - (Xg @ Yg.t()).cpu()).abs().max()) < 5e-3
     dist.barrier()
     if rank == 0:
         print(f"ENGINES_OK world={world} sgd_rmse {e0:.4f}->{e1:.4f} lda_ll {ll0:.4e}->{ll1:.4e}", flush=True)
