@@ -29,7 +29,11 @@ def _check(n, d, k, force_simt, seed=0, scale=1.0, variant="auto"):
     tol = (1e-5 if force_simt else 4e-3) * d * scale * scale
     assert float((chosen - bestd).max()) <= tol, float((chosen - bestd).max())
     mismatch = float((a != best).double().mean())
-    assert mismatch <= (1e-4 if force_simt else 0.05), mismatch
+    print(f"KMEANS_DISAGREEMENT n={n} d={d} k={k} simt={force_simt} variant={variant} scale={scale}: {mismatch:.3e}")
+    # measured over the shapes of this file on B200: TF32 at most 3.1e-3 (n = 50 000, k = 3000, d = 128: many
+    # near-ties between uniform random centroids), 0 for the small shapes; exact-fp32 SIMT 0.  Bounds = measured
+    # maximum x 2 (the split-precision modes have their own, 100x tighter, test below).
+    assert mismatch <= (1e-4 if force_simt else 6.5e-3), mismatch
     # sums / counts must be exactly consistent with the kernel's own assignment
     sums_a = torch.zeros(k, d, dtype=torch.float64, device="cuda").index_add_(0, a, X.double())
     counts_a = torch.zeros(k, dtype=torch.float64, device="cuda").index_add_(0, a, torch.ones(n, dtype=torch.float64, device="cuda"))
