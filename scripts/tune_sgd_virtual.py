@@ -17,7 +17,7 @@ v = torch.rand(nnz, device=dev, generator=g) * 4 + 1
 for cs in css:
     import os
     for extra in [int(x) for x in os.environ.get("TUNE_EXTRA_C", "0").split(",")]:
-        mr = None
+        mr = int(os.environ["TUNE_MAX_RUN"]) if os.environ.get("TUNE_MAX_RUN") else None
         eng = MFSGDEngine(r, c, v, rows, cols, rk, 0.001, 0.01, seed=3, virtual_world=N, cluster=cs, max_run=mr,
                           col_blocks=(None if extra == 0 else -extra))
         for _ in range(3):
