@@ -64,49 +64,46 @@ class SubTemplate:
         return frozenset(seen)
 
 
-def _popcount_masks(k: int, size: int) -> List[int]:
-    return [m for m in range(1 << k) if bin(m).count("1") == size]
-
-
-def colour_coding_pass(adj: torch.Tensor, colours: torch.Tensor, template: SubTemplate, k: int,
-                       neighbour_sum=None) -> torch.Tensor:
-    """One colouring.  ``adj``: sparse [n_local, n_total] adjacency of the locally owned vertices; ``colours``:
-    colour of every locally owned vertex.  ``neighbour_sum(table_local) -> [n_local, 2^k]`` supplies
-    ``Σ_{u ∈ N(v)} table[u]`` including remote neighbours (default: purely local SpMM)."""
+def colour_coding_pass(nbr_ptr: torch.Tensor, nbr_idx: torch.Tensor, colours: torch.Tensor, template: SubTemplate, k: int,
+                       fetch_rows=None, presummed=None) -> torch.Tensor:
+    """One colouring.  ``nbr_ptr / nbr_idx``: CSR of the locally owned vertices; ``nbr_idx`` names the ROW of every
+    neighbour in the table that ``fetch_rows(local table)`` returns (local rows first, then the remote rows this rank
+    needs; default: the local table itself).  ``presummed(local table) -> [n_local, cols]``, when given, supplies the
+    neighbour sums instead (rotation mode: the shards visit one after the other).  Tables are compressed: a
+    sub-template of size s has one column per colour set of size s (``ops/subgraph.py``); returns the ``[n, 1]``
+    table of the whole template (the only colour set of size k is all colours)."""
+    from ..ops import subgraph as SG
     n = colours.numel()
     dev = colours.device
-    nmask = 1 << k
-    if neighbour_sum is None:
-        neighbour_sum = lambda tab: torch.sparse.mm(adj, tab)
+    dt = torch.float32 if dev.type == "cuda" else torch.float64
+    self_ptr = torch.arange(n + 1, dtype=torch.int64, device=dev)
+    self_idx = torch.arange(n, dtype=torch.int32, device=dev)
 
     def solve(t: SubTemplate) -> torch.Tensor:
         if t.size == 1:
-            tab = torch.zeros(n, nmask, dtype=torch.float64, device=dev)
-            tab[torch.arange(n, device=dev), (1 << colours.long())] = 1.0
+            tab = torch.zeros(n, k, dtype=dt, device=dev)            # colour sets of size 1 in mask order = colours 0..k-1
+            tab[torch.arange(n, device=dev), colours.long()] = 1.0
             return tab
         act = solve(t.active)
-        pas = neighbour_sum(solve(t.passive))
-        out = torch.zeros(n, nmask, dtype=torch.float64, device=dev)
-        sa = t.active.size
-        for C in _popcount_masks(k, t.size):
-            subs = [m for m in _popcount_masks(k, sa) if m & C == m]
-            if subs:
-                ia = torch.tensor(subs, device=dev)
-                ip = torch.tensor([C ^ m for m in subs], device=dev)
-                out[:, C] = (act[:, ia] * pas[:, ip]).sum(1)
-        return out
+        pas = solve(t.passive)
+        sa, sp = SG.split_tables(k, t.size, t.active.size, dev)
+        if presummed is not None:
+            return SG.combine(self_ptr, self_idx, act, presummed(pas), sa, sp)
+        return SG.combine(nbr_ptr, nbr_idx, act, pas if fetch_rows is None else fetch_rows(pas), sa, sp)
     return solve(template)
 
 
 class SubgraphMapper(CollectiveMapper):
-    """conf: ``template_file``, ``num_iterations`` (colourings), ``comm`` (``allgather`` | ``rotation``), ``seed``;
-    input = adjacency files ``v\\tn1,n2,...,``; vertices are owned by ``v % N``."""
+    """conf: ``template_file``, ``num_iterations`` (colourings), ``comm`` (``exchange`` = default, also selected by the
+    old name ``allgather``: every rank receives exactly the passive-table rows of its remote neighbours, compressed;
+    ``rotation``: the passive shards visit every worker in turn), ``seed``; input = adjacency files
+    ``v\\tn1,n2,...,``; vertices are owned by ``v % N``."""
 
     def setup(self, context: Context) -> None:
         c = context.get_configuration()
         self.nv, self.edges = F.read_template(c["template_file"])
         self.iters = int(c.get("num_iterations", 10))
-        self.mode = c.get("comm", "allgather")
+        self.mode = c.get("comm", "exchange")
         self.seed = int(c.get("seed", 0))
 
     def map_collective(self, reader: KeyValReader, context: Context) -> None:
@@ -137,30 +134,56 @@ class SubgraphMapper(CollectiveMapper):
         aut = automorphisms(k, self.edges)
         p_colourful = math.factorial(k) / float(k ** k)
         ri, ci = torch.tensor(rows, dtype=torch.long), torch.tensor(cols, dtype=torch.long)
-        vals = torch.ones(ri.numel(), dtype=torch.float64)
-        A_full = torch.sparse_coo_tensor(torch.stack([ri, ci]), vals, (n_loc, n_total)).coalesce().to(dev)
+        order = torch.argsort(ri, stable=True)
+        ri, ci = ri[order], ci[order]
+        nbr_ptr = torch.zeros(n_loc + 1, dtype=torch.int64)
+        nbr_ptr[1:] = torch.cumsum(torch.bincount(ri, minlength=n_loc), 0)
+        # remote neighbours: the sorted distinct ids per owner; their rows follow the local rows in the fetched table
+        need: Dict[int, torch.Tensor] = {}
+        row_of = torch.empty(ci.numel(), dtype=torch.long)
+        local = (ci % N) == me
+        row_of[local] = ci[local] // N
+        base = n_loc
+        for r in range(N):
+            if r == me:
+                continue
+            m = (ci % N) == r
+            ids = torch.unique(ci[m])
+            need[r] = ids
+            if ids.numel():
+                row_of[m] = base + torch.searchsorted(ids, ci[m])
+            base += ids.numel()
+        # owners learn once which of their rows each peer wants (the adjacency never changes)
+        serve: Dict[int, torch.Tensor] = {}
+        if N > 1:
+            got = self.comm.exchange({r: [(0, need[r].to(dev))] for r in need if need[r].numel()})
+            for src, _pid, ids in got:
+                serve[src] = (ids.to(dev).long() // N)
+        nbr_ptr_d, nbr_idx_d = nbr_ptr.to(dev), row_of.to(torch.int32).to(dev)
         # per-shard adjacency blocks for the rotation mode: columns owned by worker s, re-indexed locally
         A_shard = []
         if self.mode == "rotation":
-            for s in range(N):
-                m = (ci % N) == s
-                ns = (n_total - s + N - 1) // N if n_total > s else 0
+            vals = torch.ones(ri.numel(), dtype=torch.float32 if dev.type == "cuda" else torch.float64)
+            for s_ in range(N):
+                m = (ci % N) == s_
+                ns = (n_total - s_ + N - 1) // N if n_total > s_ else 0
                 A_shard.append(torch.sparse_coo_tensor(torch.stack([ri[m], ci[m] // N]), vals[m], (n_loc, max(ns, 1))).coalesce().to(dev))
         self.estimates: List[float] = []
         self.comm_time = 0.0
+        self.exchanged_bytes = 0
         step = [0]
 
-        def nsum_allgather(tab: torch.Tensor) -> torch.Tensor:
+        def fetch_rows(tab: torch.Tensor) -> torch.Tensor:
+            if N == 1:
+                return tab
             t0 = time.perf_counter()
-            tbl = Table(1, FnCombiner(lambda a, b: a))
-            tbl.add_partition(Partition(me, tab))
-            self.allgather("sc", f"allgather-{step[0]}", tbl); step[0] += 1
-            full = torch.zeros(n_total, tab.shape[1], dtype=tab.dtype, device=dev)
-            for p in tbl.get_partitions():
-                idx = torch.arange(p.id(), n_total, N, device=dev)
-                full[idx] = p.get().to(dev)
+            got = self.comm.exchange({r: [(0, tab[idx])] for r, idx in serve.items()})
+            step[0] += 1
+            by_src = {src: payload.to(dev) for src, _pid, payload in got}
+            parts = [tab] + [by_src[r] for r in range(N) if r != me and need[r].numel()]
+            self.exchanged_bytes += sum(int(p_.numel()) * p_.element_size() for p_ in parts[1:])
             self.comm_time += time.perf_counter() - t0
-            return torch.sparse.mm(A_full, full)
+            return torch.cat(parts, 0)
 
         def nsum_rotation(tab: torch.Tensor) -> torch.Tensor:
             acc = torch.zeros(n_loc, tab.shape[1], dtype=tab.dtype, device=dev)
@@ -168,21 +191,22 @@ class SubgraphMapper(CollectiveMapper):
             tbl.add_partition(Partition(me, tab.clone()))
             for j in range(N):
                 (p,) = tbl.get_partitions()
-                s = p.id()
+                s_ = p.id()
                 pt = p.get().to(dev)
                 if pt.shape[0]:
-                    acc += torch.sparse.mm(A_shard[s][:, :pt.shape[0]] if A_shard[s].shape[1] != pt.shape[0] else A_shard[s], pt)
+                    acc += torch.sparse.mm(A_shard[s_][:, :pt.shape[0]] if A_shard[s_].shape[1] != pt.shape[0] else A_shard[s_], pt)
                 t0 = time.perf_counter()
                 self.rotate("sc", f"rotate-{step[0]}", tbl, None); step[0] += 1
                 self.comm_time += time.perf_counter() - t0
             return acc
-        nsum = nsum_rotation if self.mode == "rotation" else nsum_allgather
         for it in range(self.iters):
             gcol = torch.Generator().manual_seed(self.seed * 7919 + it)           # same colouring on all workers
             colours_all = torch.randint(0, k, (n_total,), generator=gcol)
-            tab = colour_coding_pass(A_full, colours_all[own].to(dev), tmpl, k, nsum if N > 1 else None)
+            tab = colour_coding_pass(nbr_ptr_d, nbr_idx_d, colours_all[own].to(dev), tmpl, k,
+                                     fetch_rows=fetch_rows if self.mode != "rotation" else None,
+                                     presummed=nsum_rotation if (self.mode == "rotation" and N > 1) else None)
             tot = Table(2, DoubleArrPlus())
-            tot.add_partition(Partition(0, tab[:, (1 << k) - 1].sum().view(1)))
+            tot.add_partition(Partition(0, tab[:, 0].double().sum().view(1)))
             self.allreduce("sc", f"allreduce-count-{it}", tot)
             self.estimates.append(float(tot.get_partition(0).get().item()) / (p_colourful * aut))
             context.progress()

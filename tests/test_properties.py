@@ -101,3 +101,39 @@ def test_cvb_alpha_newton_recovers_the_dirichlet_mle():
     # a fixed point: the gradient D (psi(sum a) - psi(a)) + s vanishes there
     grad = D * (torch.digamma(est.sum()) - torch.digamma(est)) + suff
     assert float(grad.abs().max()) / D < 1e-4
+
+
+def _random_graph_csr(n, m, seed):
+    import numpy as np
+    import torch
+    rs = np.random.default_rng(seed)
+    und = {(min(a, b), max(a, b)) for a, b in rs.integers(0, n, (m, 2)) if a != b}
+    adj = {v: sorted({b for a, b in und if a == v} | {a for a, b in und if b == v}) for v in range(n)}
+    ptr = torch.zeros(n + 1, dtype=torch.int64)
+    ptr[1:] = torch.cumsum(torch.tensor([len(adj[v]) for v in range(n)]), 0)
+    idx = torch.tensor([u for v in range(n) for u in adj[v]], dtype=torch.int32)
+    return adj, ptr, idx
+
+
+def test_colour_coding_dp_counts_colourful_embeddings_exactly():
+    """The compressed colour-coding DP (ops/subgraph.py + apps/graph.py::colour_coding_pass) against brute force: for
+    a FIXED colouring the DP total is exactly the number of injective, edge-preserving maps of the template whose
+    images carry pairwise different colours (colorcount_HJ.java:861-925)."""
+    import itertools
+    import torch
+    from harp_b200.apps.graph import SubTemplate, colour_coding_pass
+    n = 11
+    adj, ptr, idx = _random_graph_csr(n, 26, 4)
+    for k, edges in ((3, [(0, 1), (1, 2)]), (4, [(0, 1), (0, 2), (0, 3)]), (5, [(0, 1), (1, 2), (1, 3), (3, 4)]),
+                     (6, [(0, 1), (0, 2), (2, 3), (2, 4), (4, 5)])):
+        adj_t = {i: [] for i in range(k)}
+        for a, b in edges:
+            adj_t[a].append(b); adj_t[b].append(a)
+        tmpl = SubTemplate(0, frozenset(range(k)), adj_t)
+        colours = torch.randint(0, k, (n,), generator=torch.Generator().manual_seed(k))
+        got = float(colour_coding_pass(ptr, idx, colours, tmpl, k)[:, 0].sum())
+        want = 0
+        for phi in itertools.permutations(range(n), k):
+            if len({int(colours[v]) for v in phi}) == k and all(phi[b] in adj[phi[a]] for a, b in edges):
+                want += 1
+        assert got == want, (k, got, want)
