@@ -320,6 +320,13 @@ int hb_ccd_sweep(const int* ptr, const int* idx, float* res, const float* pd_oth
 int hb_gram_allreduce_fused_stats(const float* X, long long n, int d, void* const* peer_state, int rank, int world,
                                   unsigned epoch, double* sum, double* sumsq, float* mn, float* mx, void* stream);
 
+/* Colour-coding DP step of subgraph counting: out[v, c] = sum_j act[v, split_a[c, j]] * (sum over neighbours u of v of
+ * pas[u, split_p[c, j]]); compressed tables (one column per colour set of the sub-template's size).
+ * (MJ/subgraph/colorcount_HJ.java:861-925) */
+int hb_subgraph_combine(const long long* nbr_ptr, const int* nbr_idx, const float* act, const float* pas,
+                        const short* split_a, const short* split_p, int na, int np, int nC, int nsplit, float* out,
+                        int n, void* stream);
+
 /* ---- dense linear algebra (csrc/linalg.cu) ---- */
 int hb_tsqr_pad(int d);
 size_t hb_tsqr_workspace_bytes(int d);
