@@ -133,6 +133,28 @@ def sec_linalg():
         assert int(side.info.item()) == 0 and bool(torch.isfinite(out).all())
 
 
+def sec_subgraph():
+    from harp_b200.apps.graph import SubTemplate, colour_coding_pass
+    g = torch.Generator().manual_seed(2)
+    n, deg, k = 3000, 5, 6
+    src = torch.arange(n).repeat_interleave(deg)
+    dst = torch.randint(0, n, (n * deg,), generator=g)
+    key = torch.unique(torch.cat([src, dst]) * n + torch.cat([dst, src]))
+    a, b = key // n, key % n
+    a, b = a[a != b], b[a != b]
+    ptr = torch.zeros(n + 1, dtype=torch.int64); ptr[1:] = torch.cumsum(torch.bincount(a, minlength=n), 0)
+    idx = b.to(torch.int32)
+    edges = [(0, 1), (0, 2), (2, 3), (2, 4), (4, 5)]
+    adj_t = {i: [] for i in range(k)}
+    for x, y in edges:
+        adj_t[x].append(y); adj_t[y].append(x)
+    tmpl = SubTemplate(0, frozenset(range(k)), adj_t)
+    colours = torch.randint(0, k, (n,), generator=g)
+    want = colour_coding_pass(ptr, idx, colours, tmpl, k)[:, 0]
+    got = colour_coding_pass(ptr.cuda(), idx.cuda(), colours.cuda(), tmpl, k)[:, 0]
+    assert float((got.double().cpu() - want).abs().max()) <= 1e-4 * float(want.abs().max()) + 1e-3
+
+
 def sec_coll():
     """World of one: the flag protocols and row kernels against the rank's own slab."""
     import os
@@ -155,7 +177,7 @@ def sec_coll():
     dist.destroy_process_group()
 
 
-SECTIONS = {"kmeans": sec_kmeans, "gram": sec_gram, "mf": sec_mf, "lda": sec_lda, "linalg": sec_linalg, "coll": sec_coll}
+SECTIONS = {"kmeans": sec_kmeans, "gram": sec_gram, "mf": sec_mf, "lda": sec_lda, "linalg": sec_linalg, "subgraph": sec_subgraph, "coll": sec_coll}
 
 if __name__ == "__main__":
     names = sys.argv[1:] or list(SECTIONS)

@@ -32,7 +32,7 @@ def test_the_guard_itself_catches_a_stray_write():
         assert [nb for _, nb in g.check()] == [84]
 
 
-@pytest.mark.parametrize("section", ["kmeans", "gram", "mf", "lda", "linalg"])
+@pytest.mark.parametrize("section", ["kmeans", "gram", "mf", "lda", "linalg", "subgraph"])
 def test_no_kernel_writes_outside_its_buffers(native_built, section):
     if not torch.cuda.is_available():
         pytest.skip("needs a GPU")
