@@ -276,15 +276,14 @@ class WDAMDSMapper(CollectiveMapper):
         def v_times(Y_full: torch.Tensor) -> torch.Tensor:                     # rows of V·Y owned here
             return vdiag_local[:, None] * Y_full[ids] - W @ Y_full
         it_total = 0
+        from ..ops import mds as KM
+        D32 = D.float() if dev.type == "cuda" else D                            # the n_local x n matrix is read in fp32 there
         while True:
-            Dt = (D - T * math.sqrt(2.0 * d)).clamp(min=0.0) if T > 0 else D
+            shift = T * math.sqrt(2.0 * d) if T > 0 else 0.0
             prev = float("inf")
             for _ in range(self.max_iter):
-                diff = X[ids][:, None, :] - X[None, :, :]
-                dist = diff.pow(2).sum(2).sqrt()
-                ratio = torch.where(dist > 1e-12, W * Dt / dist.clamp(min=1e-12), torch.zeros_like(dist))
-                # B(X) X on local rows: b_ii = Σ_j ratio_ij, b_ij = -ratio_ij
-                BX = ratio.sum(1)[:, None] * X[ids] - ratio @ X
+                # B(X) X on local rows (b_ii = Σ_j ratio_ij, b_ij = -ratio_ij): one fused pass over the distance rows
+                BX = KM.bc_stress(D32, ids, X, shift)[0].double()
                 # solve V X_new = BX by CG (V is singular along constants: work in the centred subspace)
                 Xn = X.clone()
                 R_loc = BX - v_times(Xn)
@@ -304,9 +303,7 @@ class WDAMDSMapper(CollectiveMapper):
                 X = Xn - Xn.mean(0)
                 if float(X.abs().max()) < 1e-12:                     # collapsed: restart from a small random layout
                     X = (torch.rand(n, d, generator=g, dtype=torch.float64).to(dev) - 0.5) * 1e-2
-                diff = X[ids][:, None, :] - X[None, :, :]
-                dist = diff.pow(2).sum(2).sqrt()
-                st = self._allsum(torch.stack([(W * (dist - Dt) ** 2).sum(), (W * Dt ** 2).sum()]), f"stress-{step}"); step += 1
+                st = self._allsum(KM.bc_stress(D32, ids, X, shift)[1], f"stress-{step}"); step += 1
                 stress = float(st[0] / st[1].clamp(min=1e-300))
                 it_total += 1
                 if abs(prev - stress) < self.threshold:

@@ -327,6 +327,11 @@ int hb_subgraph_combine(const long long* nbr_ptr, const int* nbr_idx, const floa
                         const short* split_a, const short* split_p, int na, int np, int nC, int nsplit, float* out,
                         int n, void* stream);
 
+/* WDA-MDS: rows of B(X) X and the stress numerator / denominator in one pass over the local distance rows
+ * (MJ/wdamds/BCCalcTask.java, StressCalcTask.java:44-101); dt = max(D - shift, 0), dim <= 8. */
+int hb_mds_bc_stress(const float* D, const long long* ids, const float* X, int m, int n, int dim, float shift, float* BX,
+                     double* stress, void* stream);
+
 /* ---- dense linear algebra (csrc/linalg.cu) ---- */
 int hb_tsqr_pad(int d);
 size_t hb_tsqr_workspace_bytes(int d);
