@@ -42,18 +42,52 @@ def _files(reader: KeyValReader) -> List[str]:
 
 # ---------------------------------------------------------------------------------------
 class PageRankMapper(CollectiveMapper):
-    """conf: ``num_urls``, ``num_iterations``; input lines ``src dst dst ...`` (no targets = dangling)."""
+    """conf: ``num_urls``, ``num_iterations``, ``tables`` (``kv`` | ``dense`` | ``auto`` = dense on GPUs); input lines
+    ``src dst dst ...`` (no targets = dangling)."""
 
     def setup(self, context: Context) -> None:
         c = context.get_configuration()
         self.num_urls = int(c["num_urls"])
         self.num_iterations = int(c["num_iterations"])
+        self.tables = c.get("tables", "auto")          # "kv": the reference's key-value tables; "dense": rank vector + push kernel
+
+    def _run_dense(self, graph: Dict[int, np.ndarray], context: Context) -> None:
+        """Device formulation: dense rank vector, CSR of the local pages, one push kernel + one allreduce per iteration
+        (``csrc/graph.cu::pagerank_push_kernel``); same arithmetic as the key-value tables of the reference."""
+        from ..ops import graphops as GO
+        dev, n = self.device, self.num_urls
+        srcs = sorted(graph)
+        deg = [graph[s_].size for s_ in srcs]
+        ptr = torch.zeros(len(srcs) + 1, dtype=torch.int64)
+        ptr[1:] = torch.cumsum(torch.tensor(deg, dtype=torch.int64), 0) if srcs else ptr[1:]
+        idx = torch.from_numpy(np.concatenate([graph[s_] for s_ in srcs]).astype(np.int32)) if srcs and sum(deg) else torch.zeros(0, dtype=torch.int32)
+        ptr, idx, src_ids = ptr.to(dev), idx.to(dev), torch.tensor(srcs, dtype=torch.int64, device=dev)
+        # initial table: 1/n on every page that appears as a source somewhere (allgather_initPRTable)
+        pr = torch.zeros(n, dtype=torch.float64, device=dev)
+        pr[src_ids] = 1.0 / n
+        t0 = Table(0, DoubleArrPlus()); t0.add_partition(Partition(0, pr))
+        self.allreduce("harp-pagerank", "allgather_initPRTable", t0)
+        pr = t0.get_partition(0).get()
+        for it in range(self.num_iterations):
+            buf = torch.zeros(n + 1, dtype=torch.float64, device=dev)          # [ranks | dangling mass]
+            GO.pagerank_push(ptr, idx, src_ids, pr, buf[:n], buf[n:])
+            tt = Table(1, DoubleArrPlus()); tt.add_partition(Partition(0, buf))
+            self.allreduce("harp-pagerank", f"allgather_{it}", tt)
+            buf = tt.get_partition(0).get()
+            pr = 0.85 * (buf[:n] + buf[n] / n) + 0.15 / n
+            context.progress()
+        self.ranks = pr.cpu()
+        if self.is_master():
+            for i in range(n):
+                context.write(i, repr(float(self.ranks[i])))
 
     def map_collective(self, reader: KeyValReader, context: Context) -> None:
         graph: Dict[int, np.ndarray] = {}
         for f in _files(reader):
             graph.update(F.read_pagerank_graph(f))
         n = self.num_urls
+        if self.tables == "dense" or (self.tables == "auto" and self.device.type == "cuda"):
+            return self._run_dense(graph, context)
         local = Long2DoubleKVTable(1, TypeCombiner("sum"))
         if graph:
             local.add_batch(torch.tensor(sorted(graph)), torch.full((len(graph),), 1.0 / n, dtype=torch.float64))

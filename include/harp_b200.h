@@ -332,6 +332,11 @@ int hb_subgraph_combine(const long long* nbr_ptr, const int* nbr_idx, const floa
 int hb_mds_bc_stress(const float* D, const long long* ids, const float* X, int m, int n, int dim, float shift, float* BX,
                      double* stress, void* stream);
 
+/* One PageRank propagation over m local source pages (contrib PageRankMapper.java): out[t] += pr[s] / outdeg(s),
+ * *dangling += pr of pages without out-links. */
+int hb_pagerank_push(const long long* ptr, const int* idx, const long long* src_ids, const double* pr, double* out,
+                     double* dangling, int m, void* stream);
+
 /* ---- dense linear algebra (csrc/linalg.cu) ---- */
 int hb_tsqr_pad(int d);
 size_t hb_tsqr_workspace_bytes(int d);

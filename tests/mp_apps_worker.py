@@ -47,6 +47,8 @@ def main():
     r = np.full(n, 1 / n)
     for _ in range(30): r = 0.85 * P @ r + 0.15 / n
     np.testing.assert_allclose(m.ranks.numpy(), r, rtol=1e-9)
+    m = AC.PageRankMapper(); run(m, [f"{base}/pr/part{k}" for k in range(3)], {"num_urls": n, "num_iterations": 30, "tables": "dense"})
+    np.testing.assert_allclose(m.ranks.numpy(), r, rtol=1e-9)            # dense rank vector + push op == key-value tables
 
     # ---------------- iterative SVM ----------------
     rng = np.random.default_rng(0)

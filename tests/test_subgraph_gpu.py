@@ -36,3 +36,23 @@ def test_colour_coding_pass_device_matches_cpu(native_built, k, edges):
     assert _native.launches() - l0 == k - 1                              # one fused launch per DP step (template edge)
     torch.testing.assert_close(got.double().cpu(), want, rtol=2e-5, atol=1e-3)
     assert float(want.sum()) > 0
+
+
+def test_pagerank_push_device_matches_cpu(native_built):
+    from harp_b200.ops import graphops as GO
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    g = torch.Generator().manual_seed(3)
+    n, m = 50_000, 20_000
+    deg = torch.randint(0, 12, (m,), generator=g)
+    deg[::7] = 0                                              # dangling pages
+    ptr = torch.zeros(m + 1, dtype=torch.int64); ptr[1:] = torch.cumsum(deg, 0)
+    idx = torch.randint(0, n, (int(ptr[-1]),), generator=g).to(torch.int32)
+    src = torch.randperm(n, generator=g)[:m]
+    pr = torch.rand(n, generator=g, dtype=torch.float64)
+    oc, dc = torch.zeros(n, dtype=torch.float64), torch.zeros(1, dtype=torch.float64)
+    GO.pagerank_push(ptr, idx, src, pr, oc, dc)
+    og, dg = torch.zeros(n, dtype=torch.float64, device="cuda"), torch.zeros(1, dtype=torch.float64, device="cuda")
+    GO.pagerank_push(ptr.cuda(), idx.cuda(), src.cuda(), pr.cuda(), og, dg)
+    torch.testing.assert_close(og.cpu(), oc, rtol=1e-12, atol=1e-12)
+    torch.testing.assert_close(dg.cpu(), dc, rtol=1e-12, atol=1e-12)
