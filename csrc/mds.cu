@@ -18,43 +18,58 @@ namespace mds {
 constexpr int THREADS = 256;
 constexpr int MAX_DIM = 8;
 
+template <int DIMT>          // compile-time bound of the layout dimension (2, 3, 4 or 8): the per-pair loops unroll to it
 __global__ void __launch_bounds__(THREADS)
 bc_stress_kernel(const float* __restrict__ D, const long long* __restrict__ ids, const float* __restrict__ X,
                  const int m, const int n, const int dim, const float shift, float* __restrict__ BX,
                  double* __restrict__ stress) {
   __shared__ float red[THREADS / 32][MAX_DIM + 3];
+  constexpr int MD = DIMT;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int i = blockIdx.x; i < m; i += gridDim.x) {
     const long long gi = ids[i];
-    float xi[MAX_DIM];
+    float xi[MD];
 #pragma unroll
-    for (int c = 0; c < MAX_DIM; ++c) xi[c] = c < dim ? X[gi * dim + c] : 0.f;
-    float b = 0.f, snum = 0.f, sden = 0.f, bx[MAX_DIM];
+    for (int c = 0; c < MD; ++c) xi[c] = c < dim ? X[gi * dim + c] : 0.f;
+    float b = 0.f, snum = 0.f, sden = 0.f, bx[MD];
 #pragma unroll
-    for (int c = 0; c < MAX_DIM; ++c) bx[c] = 0.f;
+    for (int c = 0; c < MD; ++c) bx[c] = 0.f;
     const float* drow = D + (size_t)i * n;
-    for (int j = threadIdx.x; j < n; j += THREADS) {
-      float xj[MAX_DIM], d2 = 0.f;
+    // four columns per thread and trip: four independent (distance, layout row) loads in flight hide the stream's latency
+    for (int j0 = threadIdx.x; j0 < n; j0 += THREADS * 4) {
+      float dv[4];
 #pragma unroll
-      for (int c = 0; c < MAX_DIM; ++c) {
-        xj[c] = c < dim ? X[(size_t)j * dim + c] : 0.f;
-        const float t = xi[c] - xj[c];
-        d2 = fmaf(t, t, d2);
+      for (int q = 0; q < 4; ++q) {
+        const int j = j0 + q * THREADS;
+        dv[q] = j < n ? drow[j] : 0.f;
       }
-      const float dist = sqrtf(d2);
-      const float w = (j == gi) ? 0.f : 1.f;
-      const float dt = fmaxf(drow[j] - shift, 0.f);
-      const float r = dist > 1e-12f ? w * dt / dist : 0.f;
-      b += r;
 #pragma unroll
-      for (int c = 0; c < MAX_DIM; ++c) bx[c] = fmaf(r, xj[c], bx[c]);
-      const float e = dist - dt;
-      snum = fmaf(w * e, e, snum);
-      sden = fmaf(w * dt, dt, sden);
+      for (int q = 0; q < 4; ++q) {
+        const int j = j0 + q * THREADS;
+        if (j < n) {
+          float xj[MD], d2 = 0.f;
+#pragma unroll
+          for (int c = 0; c < MD; ++c) {
+            xj[c] = c < dim ? X[(size_t)j * dim + c] : 0.f;
+            const float t = xi[c] - xj[c];
+            d2 = fmaf(t, t, d2);
+          }
+          const float dist = sqrtf(d2);
+          const float w = (j == gi) ? 0.f : 1.f;
+          const float dt = fmaxf(dv[q] - shift, 0.f);
+          const float r = dist > 1e-12f ? w * dt / dist : 0.f;
+          b += r;
+#pragma unroll
+          for (int c = 0; c < MD; ++c) bx[c] = fmaf(r, xj[c], bx[c]);
+          const float e = dist - dt;
+          snum = fmaf(w * e, e, snum);
+          sden = fmaf(w * dt, dt, sden);
+        }
+      }
     }
     float vals[MAX_DIM + 3];
 #pragma unroll
-    for (int c = 0; c < MAX_DIM; ++c) vals[c] = bx[c];
+    for (int c = 0; c < MAX_DIM; ++c) vals[c] = c < MD ? bx[c < MD ? c : 0] : 0.f;
     vals[MAX_DIM] = b; vals[MAX_DIM + 1] = snum; vals[MAX_DIM + 2] = sden;
 #pragma unroll
     for (int q = 0; q < MAX_DIM + 3; ++q) {
@@ -74,7 +89,7 @@ bc_stress_kernel(const float* __restrict__ D, const long long* __restrict__ ids,
       red[0][threadIdx.x] = s;
     }
     __syncthreads();
-    if (threadIdx.x < dim) BX[(size_t)i * dim + threadIdx.x] = red[0][MAX_DIM] * xi[threadIdx.x] - red[0][threadIdx.x];
+    if (threadIdx.x < dim) BX[(size_t)i * dim + threadIdx.x] = red[0][MAX_DIM] * X[gi * dim + threadIdx.x] - red[0][threadIdx.x];
     if (threadIdx.x == 0 && stress != nullptr) {
       atomicAdd(stress, (double)red[0][MAX_DIM + 1]);
       atomicAdd(stress + 1, (double)red[0][MAX_DIM + 2]);
@@ -96,7 +111,10 @@ int hb_mds_bc_stress(const float* D, const long long* ids, const float* X, int m
   HB_REQUIRE(dim >= 1 && dim <= mds::MAX_DIM, "hb_mds_bc_stress: dim = %d outside 1..%d", dim, mds::MAX_DIM);
   if (m <= 0 || n <= 0) return 0;
   int grid = m < sm_count() * 8 ? m : sm_count() * 8;
-  mds::bc_stress_kernel<<<grid, mds::THREADS, 0, (cudaStream_t)stream>>>(D, ids, X, m, n, dim, shift, BX, stress);
+  if (dim <= 2) mds::bc_stress_kernel<2><<<grid, mds::THREADS, 0, (cudaStream_t)stream>>>(D, ids, X, m, n, dim, shift, BX, stress);
+  else if (dim == 3) mds::bc_stress_kernel<3><<<grid, mds::THREADS, 0, (cudaStream_t)stream>>>(D, ids, X, m, n, dim, shift, BX, stress);
+  else if (dim == 4) mds::bc_stress_kernel<4><<<grid, mds::THREADS, 0, (cudaStream_t)stream>>>(D, ids, X, m, n, dim, shift, BX, stress);
+  else mds::bc_stress_kernel<8><<<grid, mds::THREADS, 0, (cudaStream_t)stream>>>(D, ids, X, m, n, dim, shift, BX, stress);
   HB_CUDA_OK(cudaGetLastError());
   return 0;
 }
