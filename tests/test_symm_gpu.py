@@ -76,3 +76,15 @@ def test_contrib_kmeans_variants_run_on_the_nvlink_kernels(native_built, tmp_pat
     assert out["dense"][1] is not None and out["dense"][1] >= 8, out
     assert out["sparse"][1] is None
     assert abs(out["dense"][0] - out["sparse"][0]) <= 1e-3 * abs(out["sparse"][0]), out
+
+
+@pytest.mark.multigpu
+def test_round2_app_kernels_multi_gpu(native_built, tmp_path):
+    """PageRank (dense push), subgraph counting (exchange / rotation), WDA-MDS and MF-CCD mappers on 2 GPUs."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29538", str(ROOT / "tests" / "mp_apps_gpu_worker.py"), str(tmp_path)]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, HB_WAIT_TIMEOUT_S="30"))
+    sys.stdout.write(res.stdout[-2000:]); sys.stderr.write(res.stderr[-3000:])
+    assert res.returncode == 0 and "APPS_GPU_OK" in res.stdout
