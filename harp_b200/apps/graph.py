@@ -284,6 +284,9 @@ class WDAMDSMapper(CollectiveMapper):
             for _ in range(self.max_iter):
                 # B(X) X on local rows (b_ii = Σ_j ratio_ij, b_ij = -ratio_ij): one fused pass over the distance rows
                 BX = KM.bc_stress(D32, ids, X, shift)[0].double()
+                # 1'B(X)X = 0 exactly; the fp32 pass leaves ~1e-7 of it, which lies in the null space of V and would
+                # blow the conjugate gradient up: remove the global column mean before solving
+                BX = BX - self._allsum(BX.sum(0), f"bx-mean-{step}") / float(n); step += 1
                 # solve V X_new = BX by CG (V is singular along constants: work in the centred subspace)
                 Xn = X.clone()
                 R_loc = BX - v_times(Xn)
