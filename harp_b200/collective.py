@@ -101,7 +101,7 @@ class Comm:
                     nb = flat.numel()
                     pad = (-nb) % 16
                     m.append(("t", pid, str(t.dtype), tuple(t.shape), nb,
-                              type(payload).__name__ if isinstance(payload, Array) else None))
+                              type(payload).__name__ if isinstance(payload, Array) else None, t.device.type))
                     ch.append(flat.to(self.device))
                     if pad:
                         ch.append(torch.zeros(pad, dtype=torch.uint8, device=self.device))
@@ -136,10 +136,12 @@ class Comm:
                 continue
             for e in all_meta[src].get(me, []):
                 if e[0] == "t":
-                    _, pid, dt, shape, nb, arr_cls = e
+                    _, pid, dt, shape, nb, arr_cls, src_dev = e
                     dtype = getattr(torch, dt.replace("torch.", ""))
                     t = outbuf[off:off + nb].view(dtype).view(shape)
                     off += nb + ((-nb) % 16)
+                    if src_dev == "cpu" and t.device.type != "cpu":
+                        t = t.cpu()              # a host payload stays a host payload (it only travelled through the GPU)
                     if arr_cls is not None:
                         from . import resource as _r
                         t = getattr(_r, arr_cls).wrap(t.view(-1))
