@@ -6,7 +6,9 @@ import sys
 from pathlib import Path
 
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
-os.environ["HARP_FORCE_CPU"] = "1"
+GPU = os.environ.get("HARP_MP_TESTS_GPU", "0") == "1"
+if not GPU:
+    os.environ["HARP_FORCE_CPU"] = "1"
 import torch
 import torch.distributed as dist
 
@@ -184,7 +186,7 @@ class Verify(CollectiveMapper):
 
 
 def main():
-    rank, world, dev = init_distributed("gloo")
+    rank, world, dev = init_distributed("nccl" if GPU else "gloo")
     Verify().run([])
     if world > 1:
         dist.barrier()

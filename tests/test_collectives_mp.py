@@ -13,7 +13,11 @@ _PORT = [29700]
 
 def _torchrun(nproc, args, timeout=600):
     _PORT[0] += 1
-    env = dict(os.environ, HARP_FORCE_CPU="1", OMP_NUM_THREADS="2")
+    # HARP_MP_TESTS_GPU=1 runs the same launchers one rank per GPU over NCCL (a multi-GPU box; tolerances that assume the
+    # fp64 CPU paths then apply to fp32 / TF32 device kernels, so this is a smoke run of the device routes, not the gate)
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    if os.environ.get("HARP_MP_TESTS_GPU", "0") != "1":
+        env["HARP_FORCE_CPU"] = "1"
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(_PORT[0])] + args
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env, cwd=str(ROOT))
