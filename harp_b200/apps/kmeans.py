@@ -107,7 +107,9 @@ class KMeansRegroupAllgatherMapper(CollectiveMapper):
         if self.engine_mode == "device":
             from ..models.kmeans import KMeansEngine
             t0 = time.perf_counter()
-            eng = KMeansEngine(points, K, comm="auto", symm=self.symm)
+            # the application keeps fp32-faithful distances (split-precision tensor-core mode); HB_KMEANS_PRECISION overrides
+            eng = KMeansEngine(points, K, comm="auto", symm=self.symm,
+                               precision=os.environ.get("HB_KMEANS_PRECISION", "fp16x3") if self.device.type == "cuda" else None)
             eng.set_centroids(self._centroids_of(cen_table).to(points.dtype))
             for it in range(self.num_iterations):
                 obj = eng.step()
@@ -122,7 +124,7 @@ class KMeansRegroupAllgatherMapper(CollectiveMapper):
         for it in range(self.num_iterations):
             t0 = time.perf_counter()
             C = self._centroids_of(cen_table)
-            res = kmeans_step(points, C, want_obj=True)
+            res = kmeans_step(points, C, want_obj=True, faithful=True)
             # new table of local partial sums, same partitioning
             cen_table = Table(0, DoubleArrPlus())
             off = 0
@@ -192,7 +194,7 @@ class ContribKMeansMapper(CollectiveMapper):
         if not ids or points.shape[0] == 0:
             return 0.0
         C = torch.stack([prev.get_partition(i).get()[:d] for i in ids]).contiguous()
-        res = kmeans_step(points, C, want_assign=True)
+        res = kmeans_step(points, C, want_assign=True, faithful=True)
         dt = _work_dtype(self.device)
         counts = res.counts
         # the tutorial's "calcEucDistSquare" returns the square ROOT (KmeansMapper.java:286-292), so its
@@ -256,7 +258,7 @@ class ContribKMeansMapper(CollectiveMapper):
             mse = 0.0
             if points.shape[0] and idx.numel():
                 C = prev[idx, :d].contiguous()
-                res = kmeans_step(points, C.float() if C.dtype != torch.float32 and self.device.type == "cuda" else C, want_assign=True)
+                res = kmeans_step(points, C.float() if C.dtype != torch.float32 and self.device.type == "cuda" else C, want_assign=True, faithful=True)
                 mse = float((points - C[res.assign.long()]).pow(2).sum(1).sqrt().sum().item())
                 cur[idx, :d] = res.sums.to(dt)
                 cur[idx, d] = res.counts.to(dt)
@@ -405,7 +407,7 @@ class KMeansRotationMapper(CollectiveMapper):
                 sid = part.id()
                 C = part.get().view(-1, d + 1)[:, 1:].contiguous()
                 if n and C.shape[0]:
-                    res = kmeans_step(pts, C, want_assign=True)
+                    res = kmeans_step(pts, C, want_assign=True, faithful=True)
                     dist = (pts - C[res.assign.long()]).pow(2).sum(1)
                     better = dist < best_d
                     best_d = torch.where(better, dist, best_d)

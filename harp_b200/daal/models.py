@@ -34,7 +34,7 @@ def kmeans_daal(X: torch.Tensor, centroids: torch.Tensor, n_iter: int, comm=None
     me = 0 if comm is None else comm.rank
     hist = []
     for _ in range(n_iter):
-        res = kmeans_step(X, C, want_obj=True)
+        res = kmeans_step(X, C, want_obj=True, faithful=True)
         part = torch.cat([res.sums.double(), res.counts.double()[:, None]], 1)     # [K, d+1]
         obj = res.obj.clone()
         if N > 1:

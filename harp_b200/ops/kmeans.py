@@ -75,8 +75,15 @@ def kmeans_step(
     accumulate: bool = False,
     force_simt: bool = False,
     variant: str = "auto",
+    faithful: bool = False,
 ) -> KMeansStepResult:
-    """One pass of Lloyd's assignment over ``X[n,d]`` against ``C[k,d]``."""
+    """One pass of Lloyd's assignment over ``X[n,d]`` against ``C[k,d]``.
+
+    ``faithful=True`` (what the application mappers pass) keeps fp32 arithmetic wherever that is affordable: problems
+    up to 2^32 multiply-adds per pass take the exact SIMT kernel (milliseconds), larger ones the TF32 tensor-core kernel.
+    The reference computes these distances in fp64, and on data far from the origin a TF32 product (10-bit mantissa)
+    can flip assignments between centroids whose distances differ by less than ~0.1 %, after which two variants of the
+    same algorithm no longer produce the same centroids.  The engines choose their precision explicitly."""
     assert X.dim() == 2 and C.dim() == 2 and X.shape[1] == C.shape[1]
     n, d = X.shape
     k = C.shape[0]
@@ -100,7 +107,7 @@ def kmeans_step(
     assert X.dtype == torch.float32 and C.dtype == torch.float32, "CUDA K-means path is fp32/TF32"
     X = X.contiguous()
     C = C.contiguous()
-    simt = force_simt or not lib.hb_kmeans_tc_supported(d, k)
+    simt = force_simt or not lib.hb_kmeans_tc_supported(d, k) or (faithful and n * k * d <= (1 << 32))
     need = workspace_bytes(n, k, d, simt)
     if workspace is None or workspace.numel() * workspace.element_size() < need:
         workspace = torch.empty((need + 255) // 256 * 256, dtype=torch.uint8, device=dev)
