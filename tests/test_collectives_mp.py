@@ -8,6 +8,8 @@ import numpy as np
 import pytest
 
 ROOT = Path(__file__).resolve().parent.parent
+# fp64 CPU paths agree to rounding; one rank per GPU (HARP_MP_TESTS_GPU=1) runs fp32 kernels with atomically ordered sums
+TOL = 1e-5 if os.environ.get("HARP_MP_TESTS_GPU", "0") == "1" else 1e-9
 _PORT = [29700]
 
 
@@ -67,7 +69,7 @@ def test_kmeans_rotation_matches_regroup_allgather(tmp_path):
     _torchrun(2, ["-m", "harp_b200.launch.kmeans_rotation", "600", "8", "12", "2", "2", "1", "5", str(b), str(tmp_path / "l")])
     ca = F.read_centroids_text(str(a / "centroids" / "out" / "output"), 12)
     cb = F.read_centroids_text(str(b / "centroids" / "out" / "output"), 12)
-    np.testing.assert_allclose(ca, cb, rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose(ca, cb, rtol=TOL, atol=TOL)
 
 
 def test_kmeans_launcher_device_engine_matches_the_table_path(tmp_path):
@@ -80,7 +82,7 @@ def test_kmeans_launcher_device_engine_matches_the_table_path(tmp_path):
     _torchrun(2, ["-m", "harp_b200.launch.kmeans"] + args + [str(b), str(tmp_path / "l"), "--engine=device"])
     ca = F.read_centroids_text(str(a / "centroids" / "out" / "output"), 12)
     cb = F.read_centroids_text(str(b / "centroids" / "out" / "output"), 12)
-    np.testing.assert_allclose(ca, cb, rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose(ca, cb, rtol=TOL, atol=TOL)
 
 
 def test_kmeans_resume_continues_from_a_centroid_dump(tmp_path):
@@ -94,7 +96,7 @@ def test_kmeans_resume_continues_from_a_centroid_dump(tmp_path):
                   f"--resume={b / 'centroids' / 'out' / 'output'}"])
     ca = F.read_centroids_text(str(a / "centroids" / "out" / "output"), 12)
     cb = F.read_centroids_text(str(b / "centroids" / "out" / "output"), 12)
-    np.testing.assert_allclose(ca, cb, rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose(ca, cb, rtol=TOL, atol=TOL)
 
 
 def test_numpy_session_api():
