@@ -73,15 +73,12 @@ class MFSGDEngine:
         self.C = None
         if cuda and self.fused:
             # worker = cluster of cs CTAs; B = as many workers as one cooperative launch keeps resident
-            tiny = per_panel < 65536 and not cluster and not blocks
-            # toy panels: a whole GPU's run slots on a few thousand ratings only multiplies concurrent updates of the
-            # same rows (quality), so the grid shrinks to what the panel can feed: one CTA per ~2048 ratings
-            self.cs = int(cluster) if cluster else (1 if tiny else mf.pick_cluster(per_panel))
+            self.cs = int(cluster) if cluster else mf.pick_cluster(per_panel)
             mx = mf.epoch_max_workers(self.rank_k, self.cs)
             while mx < 1 and self.cs > 1:
                 self.cs //= 2
                 mx = mf.epoch_max_workers(self.rank_k, self.cs)
-            self.B = int(blocks) if blocks else (max(1, int(per_panel) // 2048) if tiny else mx)
+            self.B = int(blocks) if blocks else mx
             self.B = max(1, min(self.B, mx))
             # column-blocks per panel: a few more than workers, so that a block released by one worker has a whole
             # cell of slack before the next one asks for it and the cross-worker hand-over latency leaves the
