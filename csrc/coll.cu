@@ -95,6 +95,7 @@ template <typename T> __device__ __forceinline__ void st16(void* p, const Vec16<
 
 template <int OP, typename T> __device__ __forceinline__ T apply(T a, T b) {
   if (OP == HB_OP_SUM) return a + b;
+  if (OP == HB_OP_MINUS) return a - b;            // folded in ascending rank order: v0 - v1 - ... (Operation.MINUS)
   if (OP == HB_OP_MAX) return a > b ? a : b;
   if (OP == HB_OP_MIN) return a < b ? a : b;
   if (OP == HB_OP_PROD) return a * b;
@@ -387,6 +388,7 @@ static int dispatch_op(int op, const Peers& P, int rank, int world, size_t off, 
                        cudaStream_t s) {
   switch (op) {
     case HB_OP_SUM: return launch_reduce<HB_OP_SUM, T>(P, rank, world, off, count, flags_off, ticket, mode, root, grid, s);
+    case HB_OP_MINUS: return launch_reduce<HB_OP_MINUS, T>(P, rank, world, off, count, flags_off, ticket, mode, root, grid, s);
     case HB_OP_MAX: return launch_reduce<HB_OP_MAX, T>(P, rank, world, off, count, flags_off, ticket, mode, root, grid, s);
     case HB_OP_MIN: return launch_reduce<HB_OP_MIN, T>(P, rank, world, off, count, flags_off, ticket, mode, root, grid, s);
     case HB_OP_PROD: return launch_reduce<HB_OP_PROD, T>(P, rank, world, off, count, flags_off, ticket, mode, root, grid, s);
@@ -449,7 +451,7 @@ int hb_coll_reduce(const void* const* peer_ptrs, int rank, int world, size_t off
   HB_REQUIRE((offset_bytes & 15) == 0, "hb_coll_reduce: offset must be 16-byte aligned");
   HB_REQUIRE(mode >= 0 && mode <= 2, "hb_coll_reduce: bad mode %d", mode);
   cudaStream_t s = (cudaStream_t)stream;
-  const size_t esz = (dtype == HB_F64 || dtype == HB_I64) ? 8 : 4;
+  const size_t esz = (dtype == HB_F64 || dtype == HB_I64) ? 8 : (dtype == HB_I16 ? 2 : (dtype == HB_I8 ? 1 : 4));
   const size_t per_rank = mode == 2 ? count : (count + world - 1) / world;
   const int grid = pick_grid(per_rank * esz / 16 + 1, 512);
   switch (dtype) {
@@ -457,6 +459,8 @@ int hb_coll_reduce(const void* const* peer_ptrs, int rank, int world, size_t off
     case HB_F64: return dispatch_op<double>(op, P, rank, world, offset_bytes, count, flags_offset, ticket, mode, root, grid, s);
     case HB_I32: return dispatch_op<int>(op, P, rank, world, offset_bytes, count, flags_offset, ticket, mode, root, grid, s);
     case HB_I64: return dispatch_op<long long>(op, P, rank, world, offset_bytes, count, flags_offset, ticket, mode, root, grid, s);
+    case HB_I16: return dispatch_op<short>(op, P, rank, world, offset_bytes, count, flags_offset, ticket, mode, root, grid, s);
+    case HB_I8: return dispatch_op<signed char>(op, P, rank, world, offset_bytes, count, flags_offset, ticket, mode, root, grid, s);
   }
   hb::set_error("hb_coll_reduce: unsupported dtype %d", dtype);
   return -2;

@@ -42,7 +42,8 @@ from .resource import Array, decode_payload, encode_payload
 
 _REDUCE_OPS = {Operation.SUM: dist.ReduceOp.SUM, Operation.MAX: dist.ReduceOp.MAX,
                Operation.MIN: dist.ReduceOp.MIN, Operation.MULTIPLY: dist.ReduceOp.PRODUCT}
-_SYMM_OPS = {Operation.SUM: "sum", Operation.MAX: "max", Operation.MIN: "min", Operation.MULTIPLY: "prod"}
+_SYMM_OPS = {Operation.SUM: "sum", Operation.MAX: "max", Operation.MIN: "min", Operation.MULTIPLY: "prod",
+             Operation.MINUS: "minus"}     # MINUS folds in ascending rank order (v0 - v1 - ...), like the generic path
 
 
 class Comm:
@@ -327,7 +328,7 @@ def allreduce(comm: Comm, table: Table, assume_uniform: Optional[bool] = None) -
             and table.get_num_partitions() > 0:
         buf, is_view = _dense_buffer(comm, table)
         if comm.symm is not None and is_view and comm.symm.contains(buf) and buf.dtype in (
-                torch.float32, torch.float64, torch.int32, torch.int64):
+                torch.float32, torch.float64, torch.int32, torch.int64, torch.int16, torch.int8):
             comm.symm.allreduce_(buf, _SYMM_OPS[comb.op])       # in-kernel NVLink allreduce
             return True
         work = buf if buf.device == comm.device else buf.to(comm.device)

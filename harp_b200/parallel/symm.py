@@ -35,7 +35,7 @@ import torch.distributed as dist
 
 from .. import _native
 
-_DT = {torch.float32: 0, torch.float64: 1, torch.int32: 2, torch.int64: 3}
+_DT = {torch.float32: 0, torch.float64: 1, torch.int32: 2, torch.int64: 3, torch.int16: 4, torch.int8: 5}
 _OPS = {"sum": 0, "minus": 1, "prod": 2, "max": 3, "min": 4}
 
 

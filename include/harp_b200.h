@@ -202,7 +202,7 @@ int hb_smo_binary(const double* K, const double* y, int n, double C, double tol,
  * order; waits for a peer are bounded by hb_coll_set_timeout_ns. */
 #define HB_MAX_RANKS 16
 #define HB_COLL_MAX_CTAS 256
-enum { HB_F32 = 0, HB_F64 = 1, HB_I32 = 2, HB_I64 = 3 };
+enum { HB_F32 = 0, HB_F64 = 1, HB_I32 = 2, HB_I64 = 3, HB_I16 = 4, HB_I8 = 5 };   /* the six array types of HC/resource */
 enum { HB_OP_SUM = 0, HB_OP_MINUS = 1, HB_OP_PROD = 2, HB_OP_MAX = 3, HB_OP_MIN = 4 };
 
 size_t hb_coll_flags_bytes(void);

@@ -24,13 +24,22 @@ def main():
 
     # allreduce, several sizes / dtypes / ops, repeated to exercise ticket reuse
     for n in (1, 7, 1000, 1 << 20, 1290000 + 3):
-        for dt in (torch.float32, torch.float64, torch.int32, torch.int64):
+        for dt in (torch.float32, torch.float64, torch.int32, torch.int64, torch.int16, torch.int8):
             ws.reset()
             t = ws.alloc(n, dt)
-            for op, red in (("sum", dist.ReduceOp.SUM), ("max", dist.ReduceOp.MAX), ("min", dist.ReduceOp.MIN)):
+            for op, red in (("sum", dist.ReduceOp.SUM), ("max", dist.ReduceOp.MAX), ("min", dist.ReduceOp.MIN), ("minus", None)):
                 for rep in range(2):
-                    src = (torch.rand(n, device=dev, generator=g) * 100).to(dt)
-                    ref = src.clone(); dist.all_reduce(ref, op=red)
+                    src = (torch.rand(n, device=dev, generator=g) * (100 if dt.is_floating_point or dt in (torch.int32, torch.int64) else 12)).to(dt)
+                    wide = torch.float64 if dt.is_floating_point else torch.int64        # NCCL has no int16; reduce wide, narrow after
+                    if red is None:                                                    # Operation.MINUS: v0 - v1 - ... in rank order
+                        parts = [torch.empty(n, dtype=wide, device=dev) for _ in range(world)]
+                        dist.all_gather(parts, src.to(wide))
+                        ref = parts[0].clone()
+                        for p_ in parts[1:]:
+                            ref -= p_
+                        ref = ref.to(dt)
+                    else:
+                        ref = src.to(wide); dist.all_reduce(ref, op=red); ref = ref.to(dt)
                     t.copy_(src)
                     ws.allreduce_(t, op)
                     torch.cuda.synchronize()
