@@ -39,12 +39,12 @@ def main():
                             ref -= p_
                         ref = ref.to(dt)
                     else:
-                        ref = src.to(wide); dist.all_reduce(ref, op=red); ref = ref.to(dt)
+                        ref = src.to(wide, copy=True); dist.all_reduce(ref, op=red); ref = ref.to(dt)
                     t.copy_(src)
                     ws.allreduce_(t, op)
                     torch.cuda.synchronize()
                     if dt.is_floating_point:
-                        torch.testing.assert_close(t, ref, rtol=1e-5, atol=1e-4)
+                        torch.testing.assert_close(t, ref, rtol=1e-5, atol=1e-4, msg=lambda m: f"{m} [n={n} {dt} {op} rep={rep} t={t[:4].tolist()} ref={ref[:4].tolist()} src={src[:4].tolist()}]")
                     else:
                         assert torch.equal(t, ref), (n, dt, op)
     # reduce-scatter / reduce / allgather / broadcast / rotate / barrier
