@@ -305,6 +305,12 @@ class ContribKMeansMapper(CollectiveMapper):
             for pid in sorted(final.get_partition_ids()):
                 row = final.get_partition(pid).get()[:d].double().cpu().tolist()
                 context.write(None, "\t".join(repr(x) for x in row) + "\t")
+        # the slabs go back to the workspace's free list (same order on every rank): a long-lived mapper can run again
+        torch.cuda.synchronize(self.device)
+        if gslab is not None:
+            symm.free(gslab)
+        for s_ in reversed(slabs):
+            symm.free(s_)
 
     def run_kmeans(self, files: List[str], context: Context) -> None:
         N, d = self.get_num_workers(), self.dimension

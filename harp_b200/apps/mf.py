@@ -199,6 +199,7 @@ class CCDCollectiveMapper(CollectiveMapper):
             context.progress()
         W, H = eng.full_factors()
         W_loc, H_loc = eng.W_loc, eng.H_loc
+        eng.close()
         self.W, self.H, self.W_loc, self.H_loc = W, H, W_loc, H_loc
         # test RMSE
         test_files = [f for i, f in enumerate(sorted(self.test_files)) if i % N == me]

@@ -58,11 +58,14 @@ class KMeansEngine:
         if self.comm != "fused":
             self.precision = "tf32" if self.dev.type == "cuda" else "exact"
         self.Xs = None
+        self._symm_allocs = []          # what close() hands back to the workspace
+        self._symm_ws = symm
         if self.comm == "fused":
             nbytes = kops.FusedKMeans.state_bytes(k, d)
             if self.world > 1:
                 assert symm is not None, "comm='fused' on several ranks needs a SymmetricWorkspace"
                 st = symm.alloc(nbytes, torch.uint8)
+                self._symm_allocs.append(st)
                 off = symm.offset_of(st)
                 peers = [p + off for p in symm.peer_ptrs]
             else:
@@ -97,6 +100,7 @@ class KMeansEngine:
         if self.comm == "p2p" and self.world > 1:
             assert symm is not None, "comm='p2p' needs a SymmetricWorkspace"
             self.acc = symm.alloc(k * d + k, torch.float32)
+            self._symm_allocs.append(self.acc)
         else:
             self.acc = torch.zeros(k * d + k, dtype=wdt, device=self.dev)
         self._sums = self.acc[: k * d].view(k, d)
@@ -106,6 +110,7 @@ class KMeansEngine:
             self.obj.zero_()
             self._C = symm.alloc(k * d, torch.float32).view(k, d)
             self._C.zero_()
+            self._symm_allocs += [self.obj, self._C]
         else:
             self.obj = torch.zeros(1, dtype=torch.float64, device=self.dev)
             self._C = torch.zeros(k, d, dtype=wdt, device=self.dev)
@@ -141,6 +146,14 @@ class KMeansEngine:
             self.fused.set_centroids(C, non_blocking=non_blocking)
         else:
             self._C.copy_(C.view(self.k, self.d), non_blocking=non_blocking)
+
+    def close(self) -> None:
+        """Gives the engine's blocks of the symmetric workspace back (every rank, same order); unusable afterwards."""
+        if self._symm_allocs:
+            torch.cuda.synchronize(self.dev)
+            for t in reversed(self._symm_allocs):
+                self._symm_ws.free(t)
+            self._symm_allocs = []
 
     def step(self, want_obj: bool = True) -> Optional[torch.Tensor]:
         """One Lloyd iteration; returns the (device) Σ min-distance² of the *input* centroids."""

@@ -308,6 +308,12 @@ class LDAEngine:
         acc += -(torch.lgamma(self.topic_sums.double() + V * b)).sum() + K * math.lgamma(V * b)
         return float(acc.item())
 
+    def close(self) -> None:
+        """Gives the engine's block of the symmetric workspace back (every rank, same order); unusable afterwards."""
+        self.synchronize()
+        if self.ring is not None:
+            self.ring.release()
+
     def synchronize(self) -> None:
         if self.dev.type == "cuda":
             for k in range(self.S):

@@ -111,6 +111,14 @@ class MFCCDEngine:
         self.iteration += 1
         return self.rmse()
 
+    def close(self) -> None:
+        """Gives the gathered-vector buffers back to the symmetric workspace (every rank, same order)."""
+        if self.symm is not None:
+            torch.cuda.synchronize(self.dev)
+            for t in (self.dv, self.du, self.v, self.u):
+                self.symm.free(t)
+            self.symm = None
+
     def rmse(self) -> float:
         st = torch.stack([(self.res_r.double() ** 2).sum(), torch.tensor(float(self.res_r.numel()), dtype=torch.float64, device=self.dev)])
         if self.N > 1:

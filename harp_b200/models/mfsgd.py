@@ -238,6 +238,13 @@ class MFSGDEngine:
             dist.all_reduce(cnt, group=self.group)
         return float(acc.item()), int(cnt.item())
 
+    def close(self) -> None:
+        """Gives the engine's block of the symmetric workspace back (call on every rank, in the same order as other
+        allocations / frees); the engine is unusable afterwards."""
+        self.synchronize()
+        if self.ring is not None:
+            self.ring.release()
+
     def rmse(self, rows, cols, vals) -> float:
         se, n = self.sq_err(rows, cols, vals)
         return math.sqrt(se / max(n, 1))

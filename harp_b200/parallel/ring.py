@@ -81,6 +81,7 @@ class RingState:
         nbuf = 2 if self.ring_world > 0 else 1
         self.nbuf = nbuf
         total = 256 + self.S * nbuf * self.slice_bytes
+        self._symm = symm if (symm is not None and self.world > 1) else None
         if symm is not None and self.world > 1:
             self.state = symm.alloc(total, torch.uint8)
             base = symm.offset_of(self.state)
@@ -105,6 +106,12 @@ class RingState:
                                                   [ctypes.c_void_p(0)] * (16 - len(self.peer_ptrs))))
         self._off_arr = (ctypes.c_ulonglong * 4)(*(self.off_buf + [0] * (4 - len(self.off_buf))))
         self._bytes_arr = (ctypes.c_ulonglong * 2)(*([self.slice_bytes] * self.S + [0] * (2 - self.S)))
+
+    def release(self) -> None:
+        """Returns the ring's slab allocation to the workspace (every rank, same order; nothing may be in flight)."""
+        if self._symm is not None and self.state is not None:
+            self._symm.free(self.state)
+        self.state = None
 
     def current(self, k: int) -> torch.Tensor:
         return self.buf[k][self.cur[k]]

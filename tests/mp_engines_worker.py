@@ -17,6 +17,7 @@ def main():
     from harp_b200.models.mfsgd import MFSGDEngine
     from harp_b200.models.lda import LDAEngine
     ws = SymmetricWorkspace(dev, 512 << 20)
+    in_use0 = ws.bytes_in_use()
     # ---- MF-SGD ----
     g = torch.Generator(device=dev).manual_seed(1 + rank)
     nr, nc, nnz, rk = 20000, 3000, 600000, 64
@@ -111,6 +112,18 @@ def main():
     comm_a = C.Comm(device=dev, symm=ws)
     Xg, Yg = DM.als_implicit(ar[mine_].to(dev), ac[mine_].to(dev), av[mine_].to(dev), U_, I_, f_, 4, 0.1, 20.0, comm=comm_a)
     assert float(((Xc @ Yc.t()) - (Xg @ Yg.t()).cpu()).abs().max()) < 5e-3
+    # engines hand their slab blocks back: a long-lived process can build engines again and again
+    if world > 1:
+        from harp_b200.models.kmeans import KMeansEngine
+        before = ws.bytes_in_use()
+        for rep_ in range(3):
+            e_s = MFSGDEngine(r, c, v, nr, nc, rk, 0.01, 0.02, symm=ws, seed=5)
+            e_l = LDAEngine(docs, words, D, V, K, 0.1, 0.01, symm=ws, seed=2)
+            e_k = KMeansEngine(torch.rand(20000, 64, device=dev), 300, comm="fused", symm=ws)
+            e_s.epoch(); e_l.iterate(); e_k.step()
+            e_k.close(); e_l.close(); e_s.close()
+            assert ws.bytes_in_use() == before, (rep_, ws.bytes_in_use(), before)
+        ccd.close()
     dist.barrier()
     if rank == 0:
         print(f"ENGINES_OK world={world} sgd_rmse {e0:.4f}->{e1:.4f} lda_ll {ll0:.4e}->{ll1:.4e}", flush=True)
