@@ -18,25 +18,120 @@ from .linalg import _allreduce_
 # ---------------------------------------------------------------------------------------
 # K-means (daal_kmeans/regroupallgather with 4 selectable comm patterns, daal_kmeans/allreducecsr)
 # ---------------------------------------------------------------------------------------
+def kmeans_init(X: torch.Tensor, k: int, method: str = "random", seed: int = 0, comm=None) -> torch.Tensor:
+    """DAAL ``kmeans.init`` for dense and CSR input (``daal_kmeans/allreducecsr/KMeansDaalCollectiveMapper.java``:
+    ``init.Method.randomCSR`` / ``deterministicCSR``; dense twins ``randomDense`` / ``deterministicDense`` /
+    ``plusPlusDense``): ``deterministic`` = the first k rows of the global data set, ``random`` = k distinct rows drawn
+    with a seed shared by all ranks, ``plusPlus`` = D^2 seeding.  Row-distributed: every rank contributes the rows it
+    holds (global row order = rank order) and all ranks return the same [k, d] dense float64 centroids."""
+    N = 1 if comm is None else comm.world
+    me = 0 if comm is None else comm.rank
+    n_loc = X.shape[0]
+    counts = [n_loc] if N == 1 else comm.all_gather_object(n_loc)
+    start = sum(counts[:me])
+    total = sum(counts)
+    assert total >= k, "fewer rows than centroids"
+
+    def rows(global_ids: torch.Tensor) -> torch.Tensor:
+        loc = global_ids - start
+        mine = (loc >= 0) & (loc < n_loc)
+        out = torch.zeros(global_ids.numel(), X.shape[1], dtype=torch.float64)
+        if bool(mine.any()):
+            sel = loc[mine]
+            blk = X.index_select(0, sel.to(X.device)) if X.layout == torch.strided else \
+                torch.stack([X[int(i)].to_dense() for i in sel])          # CSR: only the chosen rows are densified
+            out[mine] = blk.double().cpu()
+        if N > 1:
+            _allreduce_(out, comm)
+        return out
+    g = torch.Generator().manual_seed(seed)
+    if method == "deterministic":
+        return rows(torch.arange(k))
+    if method == "random":
+        return rows(torch.randperm(total, generator=g)[:k].sort().values)
+    if method == "plusPlus":
+        C = rows(torch.randint(0, total, (1,), generator=g))
+        for _ in range(1, k):
+            d2 = _sq_dist_to_nearest(X, C)                          # local rows
+            tot = d2.sum().double().reshape(1).cpu()
+            if N > 1:
+                _allreduce_(tot, comm)
+            u = float(torch.rand(1, generator=g)) * float(tot)
+            # the rank whose cumulative share contains u picks the row
+            shares = [float(d2.sum())] if N == 1 else comm.all_gather_object(float(d2.sum()))
+            acc, pick = 0.0, torch.full((1,), -1, dtype=torch.long)
+            for r_, sh in enumerate(shares):
+                if u < acc + sh or r_ == N - 1:
+                    if r_ == me:
+                        idx = int(torch.searchsorted(torch.cumsum(d2.double().cpu(), 0), torch.tensor(u - acc)).clamp(max=n_loc - 1))
+                        pick[0] = start + idx
+                    break
+                acc += sh
+            if N > 1:
+                pk = pick.double()
+                _allreduce_(pk, comm, "max")
+                pick = pk.long()
+            C = torch.cat([C, rows(pick)], 0)
+        return C
+    raise ValueError(method)
+
+
+def _sq_dist_to_nearest(X: torch.Tensor, C: torch.Tensor) -> torch.Tensor:
+    """min_j ||x - c_j||^2 for dense or CSR rows (CSR: x.c through a sparse product, nothing densified)."""
+    Cd = C.to(X.device, torch.float64)
+    if X.layout == torch.strided:
+        return torch.cdist(X.double(), Cd).pow(2).min(1).values
+    Xd = X.to(torch.float64)
+    xn = torch.sparse.sum(Xd * Xd, 1).to_dense() if Xd.layout != torch.sparse_csr else \
+        torch.zeros(X.shape[0], dtype=torch.float64, device=X.device).index_add_(
+            0, torch.repeat_interleave(torch.arange(X.shape[0], device=X.device), Xd.crow_indices()[1:] - Xd.crow_indices()[:-1]),
+            Xd.values() ** 2)
+    cross = torch.sparse.mm(Xd, Cd.t())
+    return (xn[:, None] - 2 * cross + (Cd * Cd).sum(1)[None, :]).clamp(min=0).min(1).values
+
+
+def kmeans_csr_step(X: torch.Tensor, C: torch.Tensor):
+    """One Lloyd pass over CSR rows without densifying them (``daal_kmeans/allreducecsr``): returns
+    ``(sums [k, d], counts [k], objective)`` in float64; x.c and the per-cluster sums are sparse products."""
+    Xd = X.to(torch.float64)
+    Cd = C.to(X.device, torch.float64)
+    n, k = X.shape[0], C.shape[0]
+    crow = Xd.crow_indices()
+    row_of = torch.repeat_interleave(torch.arange(n, device=X.device), crow[1:] - crow[:-1])
+    xn = torch.zeros(n, dtype=torch.float64, device=X.device).index_add_(0, row_of, Xd.values() ** 2)
+    d2 = (xn[:, None] - 2 * torch.sparse.mm(Xd, Cd.t()) + (Cd * Cd).sum(1)[None, :]).clamp(min=0)
+    best_d, best = d2.min(1)
+    onehot = torch.sparse_coo_tensor(torch.stack([best, torch.arange(n, device=X.device)]), torch.ones(n, dtype=torch.float64, device=X.device), (k, n))
+    sums = torch.sparse.mm(onehot, Xd.to_sparse_coo()).to_dense()
+    counts = torch.bincount(best, minlength=k).double()
+    return sums, counts, best_d.sum()
+
+
 def kmeans_daal(X: torch.Tensor, centroids: torch.Tensor, n_iter: int, comm=None, comm_mode: str = "allreduce"):
     """DAAL ``kmeans.DistributedStep1Local`` partial results (partialSums, nObservations) per iteration, combined
     with one of the reference's four patterns (``KMeansDaalCollectiveMapper.java:435-532``).  With tensors all four
     move the same fixed-shape ``[K, d+1]`` block; they differ in who divides:
     ``allreduce`` (everyone), ``regroup_allgather`` (owners of row ranges), ``broadcastreduce`` (rank 0),
     ``push_pull`` (owners, then pulled)."""
-    if X.layout != torch.strided:
+    sparse = X.layout == torch.sparse_csr
+    if X.layout != torch.strided and not sparse:
         X = X.to_dense()
-    C = centroids.clone().to(X.device, X.dtype if X.device.type == "cuda" else torch.float64)
-    if X.device.type != "cuda":
+    C = centroids.clone().to(X.device, torch.float64 if (sparse or X.device.type != "cuda") else X.dtype)
+    if X.device.type != "cuda" and not sparse:
         X = X.double()
     K, d = C.shape
     N = 1 if comm is None else comm.world
     me = 0 if comm is None else comm.rank
     hist = []
     for _ in range(n_iter):
-        res = kmeans_step(X, C, want_obj=True, faithful=True)
-        part = torch.cat([res.sums.double(), res.counts.double()[:, None]], 1)     # [K, d+1]
-        obj = res.obj.clone()
+        if sparse:                         # allreducecsr: the CSR rows are never densified
+            sums_, counts_, obj_ = kmeans_csr_step(X, C)
+            part = torch.cat([sums_, counts_[:, None]], 1)
+            obj = obj_.reshape(1).clone()
+        else:
+            res = kmeans_step(X, C, want_obj=True, faithful=True)
+            part = torch.cat([res.sums.double(), res.counts.double()[:, None]], 1)     # [K, d+1]
+            obj = res.obj.clone()
         if N > 1:
             if comm_mode in ("allreduce",):
                 _allreduce_(part, comm)

@@ -189,3 +189,22 @@ def test_initialize_create_job_runs_a_mapper(tmp_path):
     job = init.createJob("count", None, CountRows)
     assert init.getSysArgNum() == 6 and init.app_args() == ["extra"] and job.getConfiguration()["num_iterations"] == 3
     assert job.waitForCompletion(True) and job.isSuccessful() and job.mapper.rows == 40
+
+
+def test_kmeans_init_methods_and_csr_kmeans_without_densifying():
+    """daal_kmeans/allreducecsr: kmeans.init (deterministic / random / plusPlus, dense and CSR give the same centroids)
+    and Lloyd passes over CSR rows through sparse products equal the dense run."""
+    g = torch.Generator().manual_seed(0)
+    Xd = torch.rand(300, 20, generator=g, dtype=torch.float64)
+    Xd[Xd < 0.7] = 0
+    Xs = Xd.to_sparse_csr()
+    for method in ("deterministic", "random", "plusPlus"):
+        Cd, Cs = M.kmeans_init(Xd, 6, method, seed=3), M.kmeans_init(Xs, 6, method, seed=3)
+        assert Cd.shape == (6, 20) and torch.allclose(Cd, Cs), method
+    assert torch.equal(M.kmeans_init(Xd, 4, "deterministic"), Xd[:4])
+    C0 = M.kmeans_init(Xs, 6, "plusPlus", seed=1)
+    Ca, ha = M.kmeans_daal(Xd, C0, 8)
+    Cb, hb = M.kmeans_daal(Xs, C0, 8)
+    np.testing.assert_allclose(ha, hb, rtol=1e-9)
+    assert torch.allclose(Ca.double(), Cb, atol=1e-9)
+    assert all(a >= b - 1e-9 for a, b in zip(hb, hb[1:]))
